@@ -1,0 +1,141 @@
+"""Thin object wrapper over the C-ABI (one engine per process per GPU).
+
+PyTorch is used only to hold device memory: every tensor handed to the library is
+passed as ``tensor.data_ptr()`` and kept referenced here so it outlives the shard.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional, Sequence
+
+import numpy as np
+
+from . import _lib
+from ._lib import FcbConfig, FcbFilter, FcbShard, check
+
+
+def make_filter(row_begin: int, row_end: int, date_lo: Optional[int] = None,
+                date_hi: Optional[int] = None, category_mask: Optional[int] = None) -> FcbFilter:
+    return FcbFilter(int(row_begin), int(row_end),
+                     _lib.FCB_DATE_MIN if date_lo is None else max(int(date_lo), _lib.FCB_DATE_MIN),
+                     _lib.FCB_DATE_MAX if date_hi is None else min(int(date_hi), _lib.FCB_DATE_MAX),
+                     _lib.FCB_ALL_CATEGORIES if category_mask is None else int(category_mask))
+
+
+class Engine:
+    def __init__(self, device: int = 0, max_batch: int = 1, max_k: int = 16):
+        self._lib = _lib.load()
+        self._h = C.c_void_p()
+        cfg = FcbConfig(device, max_batch, max_k, 0)
+        check(self._lib.fcb_open(C.byref(cfg), C.byref(self._h)))
+        self.device, self.max_batch, self.max_k = device, max_batch, max_k
+        self._keep = None
+        self.dim = 0
+        self.n_rows = 0
+        self.row_base = 0
+
+    def close(self) -> None:
+        if getattr(self, "_h", None) is not None and self._h:
+            self._lib.fcb_close(self._h)
+            self._h = C.c_void_p()
+            self._keep = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- shard
+    def load_shard(self, vectors, *, ids=None, id_rank=None, dates=None, categories=None, cents=None,
+                   seg_offsets=None, row_base: int = 0) -> None:
+        """``vectors``: CUDA tensor [n, dim], float32 or bfloat16, contiguous. Optional CUDA
+        column tensors: ids uint64/int64 [n], id_rank int32/uint32 [n], dates int32 [n],
+        categories uint8 [n], cents int32 [n], seg_offsets int64 [n_segs+1]."""
+        import torch
+        if not vectors.is_cuda or not vectors.is_contiguous() or vectors.dim() != 2:
+            raise ValueError("vectors must be a contiguous 2-D CUDA tensor")
+        if vectors.dtype == torch.float32:
+            dt = _lib.FCB_DTYPE_F32
+        elif vectors.dtype == torch.bfloat16:
+            dt = _lib.FCB_DTYPE_BF16
+        else:
+            raise ValueError("vectors must be float32 or bfloat16")
+        n, dim = vectors.shape
+
+        def col(t, dtypes, name, length=n):
+            if t is None:
+                return None
+            if not t.is_cuda or not t.is_contiguous() or t.dtype not in dtypes or t.numel() != length:
+                raise ValueError(f"{name}: need contiguous CUDA tensor of {dtypes} with {length} elements")
+            return t.data_ptr()
+        n_segs = 0 if seg_offsets is None else seg_offsets.numel() - 1
+        sh = FcbShard(vectors.data_ptr(),
+                      col(ids, (torch.int64, torch.uint64), "ids"),
+                      col(id_rank, (torch.int32, torch.uint32), "id_rank"),
+                      col(dates, (torch.int32,), "dates"),
+                      col(categories, (torch.uint8,), "categories"),
+                      col(cents, (torch.int32,), "cents"),
+                      col(seg_offsets, (torch.int64,), "seg_offsets", n_segs + 1) if seg_offsets is not None else None,
+                      n, n_segs, row_base, dim, dt)
+        check(self._lib.fcb_load_shard(self._h, C.byref(sh)), self._h)
+        self._keep = (vectors, ids, id_rank, dates, categories, cents, seg_offsets)
+        self.dim, self.n_rows, self.row_base = dim, n, row_base
+
+    # ---- search
+    def search_host(self, queries: np.ndarray, filters: Sequence[FcbFilter], k: int):
+        """queries float64 [B, dim] (host). Returns (ids uint64 [B,k], scores float64 [B,k],
+        counts int32 [B]) as numpy arrays. Synchronous (fcb_search_host)."""
+        q = np.ascontiguousarray(queries, dtype=np.float64).reshape(-1, self.dim)
+        B = q.shape[0]
+        if len(filters) != B:
+            raise ValueError("one filter per query")
+        farr = (FcbFilter * B)(*filters)
+        ids = np.empty((B, k), dtype=np.uint64)
+        scores = np.empty((B, k), dtype=np.float64)
+        counts = np.empty(B, dtype=np.int32)
+        check(self._lib.fcb_search_host(self._h, q.ctypes.data, farr, B, k, ids.ctypes.data,
+                                        scores.ctypes.data, counts.ctypes.data), self._h)
+        return ids, scores, counts
+
+    def search_device(self, d_queries, filters: Sequence[FcbFilter], k: int, out_ids, out_scores,
+                      out_counts, stream: Optional[int] = None) -> None:
+        """Asynchronous fcb_search: CUDA tensors in (float64 [B,dim]) and out (int64/uint64 [B,k],
+        float64 [B,k], int32 [B]); ``stream`` is a raw cudaStream_t (default: torch's current)."""
+        import torch
+        B = d_queries.shape[0]
+        farr = (FcbFilter * B)(*filters)
+        if stream is None:
+            stream = torch.cuda.current_stream(self.device).cuda_stream
+        check(self._lib.fcb_search(self._h, d_queries.data_ptr(), farr, B, k, out_ids.data_ptr(),
+                                   out_scores.data_ptr(), out_counts.data_ptr(), C.c_void_p(stream)), self._h)
+
+    @property
+    def last_search_ms(self) -> float:
+        return float(self._lib.fcb_last_search_ms(self._h))
+
+    @property
+    def last_search_launches(self) -> int:
+        return int(self._lib.fcb_last_search_launches(self._h))
+
+
+def synth_vectors(out, row_lo: int, seed: int, n_clusters: int) -> None:
+    """Fill CUDA tensor ``out`` [n, dim] (float32/bfloat16) with rows row_lo.. of the synthetic corpus."""
+    import torch
+    lib = _lib.load()
+    dt = _lib.FCB_DTYPE_F32 if out.dtype == torch.float32 else _lib.FCB_DTYPE_BF16
+    n, dim = out.shape
+    st = torch.cuda.current_stream(out.device).cuda_stream
+    check(lib.fcb_synth_vectors(out.device.index, out.data_ptr(), dt, row_lo, n, dim, seed, n_clusters,
+                                C.c_void_p(st)))
+
+
+def synth_columns(row_lo: int, n_rows: int, seed: int, n_categories: int, date_span_seconds: int,
+                  dates=None, categories=None, cents=None) -> None:
+    import torch
+    lib = _lib.load()
+    t = next(x for x in (dates, categories, cents) if x is not None)
+    st = torch.cuda.current_stream(t.device).cuda_stream
+    p = lambda x: None if x is None else x.data_ptr()
+    check(lib.fcb_synth_columns(t.device.index, p(dates), p(categories), p(cents), row_lo, n_rows, seed,
+                                n_categories, date_span_seconds, C.c_void_p(st)))

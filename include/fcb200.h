@@ -1,0 +1,146 @@
+/* fcb200.h — C ABI of the B200-native transaction retrieval / aggregation library.
+ *
+ * This is the drop-in boundary for the ONE hot path of kyshu11027/financial-chatbot-llm:
+ * the payload-filtered top-k lookup of tools/qdrant_tool.py and the group-by sum of
+ * tools/plot_tool.py. Every entry point names the reference interface it replaces
+ * (file:line in the reference tree). The reference binds that path through the
+ * third-party `qdrant-client` Python package; the binding a maintainer adds is the ctypes
+ * stub in INTEGRATION.md (financial-chatbot-llm_b200/_lib.py is that stub, shipped).
+ *
+ * Conventions
+ *   - plain C types only; every function returns FCB_OK (0) or a negative FCB_ERR_* code and
+ *     never throws across the ABI; fcb_last_error() returns the message for the last failure
+ *     on that engine (or, with a NULL engine, for the last failed fcb_open on this thread).
+ *   - the CALLER owns every corpus/query/result buffer. "device" pointers are CUDA device
+ *     pointers on the engine's device (e.g. torch.Tensor.data_ptr()); they must stay alive
+ *     while the shard is loaded. The library allocates only its own scratch, in fcb_open and
+ *     fcb_load_shard, and frees it in fcb_close.
+ *   - one call in flight per engine (not re-entrant); distinct engines may run concurrently.
+ *   - `stream` is a cudaStream_t passed as void* (NULL = the legacy default stream). The
+ *     *_host variants take host buffers, run on the engine's own stream and return after
+ *     the results are in the caller's memory.
+ *   - there is no CPU fallback: without a CUDA device every call fails with FCB_ERR_CUDA.
+ */
+#ifndef FCB200_H
+#define FCB200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FCB_ABI_VERSION 1
+
+#define FCB_OK 0
+#define FCB_ERR_INVALID (-1)     /* bad argument                                   */
+#define FCB_ERR_CUDA (-2)        /* a CUDA runtime call or kernel failed            */
+#define FCB_ERR_NOMEM (-3)       /* scratch allocation failed                        */
+#define FCB_ERR_STATE (-4)       /* no shard loaded / wrong order of calls           */
+#define FCB_ERR_UNSUPPORTED (-5) /* valid request outside what this build implements */
+
+#define FCB_DTYPE_F32 0
+#define FCB_DTYPE_BF16 1
+
+#define FCB_MAX_K 10000          /* = the tool's default and maximum limit, tools/qdrant_tool.py:46-51,145 */
+#define FCB_DATE_MIN INT64_MIN
+#define FCB_DATE_MAX INT64_MAX
+#define FCB_ALL_CATEGORIES UINT64_MAX
+
+typedef struct fcb_engine fcb_engine; /* opaque */
+
+typedef struct fcb_config {
+    int32_t device;     /* CUDA device ordinal                                              */
+    int32_t max_batch;  /* largest `batch` fcb_search will be given (>=1)                   */
+    int32_t max_k;      /* largest `k` fcb_search will be given (1..FCB_MAX_K)              */
+    int32_t reserved;   /* must be 0                                                        */
+} fcb_config;
+
+/* One contiguous point range of the collection, resident on the engine's device.
+ * Rows are sorted by user; a user's rows are the CSR segment [seg_offsets[u], seg_offsets[u+1])
+ * in GLOBAL row numbers; this shard holds global rows [row_base, row_base + n_rows).
+ * Replaces: the collection a Qdrant server holds for QDRANT_COLLECTION_NAME
+ * (reference config.py:47), with the payload fields the tool filters on stored as columns:
+ * metadata.user_id -> segment, metadata.date -> dates (tools/qdrant_tool.py:107,120). */
+typedef struct fcb_shard {
+    const void *vectors;        /* device [n_rows, dim] row-major, float32 or bfloat16; 16-byte aligned */
+    const uint64_t *ids;        /* device [n_rows] point ids, or NULL: id = row_base + row              */
+    const uint32_t *id_rank;    /* device [n_rows] rank of ids[row] among the shard's ids, or NULL when
+                                   ids ascend with the row number (always true when ids == NULL)       */
+    const int32_t *dates;       /* device [n_rows] metadata.date, unix seconds; NULL: date filters reject */
+    const uint8_t *categories;  /* device [n_rows] category code 0..63; NULL: category filters reject    */
+    const int32_t *cents;       /* device [n_rows] signed integer cents (aggregation only), or NULL       */
+    const int64_t *seg_offsets; /* device [n_segs + 1] global CSR offsets (aggregation only), or NULL     */
+    int64_t n_rows;
+    int64_t n_segs;
+    int64_t row_base;
+    int32_t dim;                /* multiple of 8 (bf16) / 4 (f32), <= 8192                               */
+    int32_t dtype;              /* FCB_DTYPE_*                                                           */
+} fcb_shard;
+
+/* The filter the tool builds at tools/qdrant_tool.py:105-131, already resolved by the host:
+ *   FieldCondition(key="metadata.user_id", match=MatchValue(user_id))  -> [row_begin, row_end)
+ *   FieldCondition(key="metadata.date", range=Range(gte/gt/lte/lt))    -> [date_lo, date_hi] inclusive
+ *   FieldCondition(key="metadata.category", match=MatchValue/MatchAny) -> category_mask (north_star
+ *   extension; the reference has no category filter). */
+typedef struct fcb_filter {
+    int64_t row_begin, row_end; /* global rows; empty when row_begin >= row_end (unknown user) */
+    int64_t date_lo, date_hi;   /* FCB_DATE_MIN / FCB_DATE_MAX = unbounded                      */
+    uint64_t category_mask;     /* bit c set = category c passes; FCB_ALL_CATEGORIES = no filter */
+} fcb_filter;
+
+int32_t fcb_abi_version(void);
+
+/* Replaces QdrantHttpClient(url=..., api_key=...) at tools/qdrant_tool.py:24-27 (one backend
+ * object per process). Allocates the engine's scratch on cfg->device. */
+int32_t fcb_open(const fcb_config *cfg, fcb_engine **out);
+int32_t fcb_close(fcb_engine *e);
+const char *fcb_last_error(const fcb_engine *e);
+
+/* Attach a resident shard (see fcb_shard) and compute the library-owned float32 inverse row
+ * norms (4 bytes/row). Replaces the server-side collection load; nothing in the reference
+ * writes points. Synchronous. */
+int32_t fcb_load_shard(fcb_engine *e, const fcb_shard *shard);
+
+/* Replaces client.query_points(collection_name, query, limit, search_params,
+ * query_filter).points at tools/qdrant_tool.py:147-153, for `batch` independent queries.
+ *   queries      device [batch, dim] float64 (the list[float] embed_query returns, :137)
+ *   filters      HOST  [batch]
+ *   k            limit, 1..cfg.max_k
+ *   out_ids      device [batch, k]   point ids, best first
+ *   out_scores   device [batch, k]   float64 cosine scores (canonical order of operations,
+ *                                    see DESIGN.md "canonical score")
+ *   out_counts   device [batch]      number of valid results (<= k)
+ * Exact (every filtered-in row is scored); search_params (hnsw_ef / exact, :98-101) have no
+ * counterpart because nothing is approximate. Order: score descending, ties by ascending id.
+ * Asynchronous on `stream`. */
+int32_t fcb_search(fcb_engine *e, const double *queries, const fcb_filter *filters, int32_t batch,
+                   int32_t k, uint64_t *out_ids, double *out_scores, int32_t *out_counts,
+                   void *stream);
+
+/* Same call with HOST buffers for queries and results (the shape the Python tool has in hand:
+ * a list of floats in, scored points out). Copies in, searches, copies out, synchronises. */
+int32_t fcb_search_host(fcb_engine *e, const double *queries, const fcb_filter *filters,
+                        int32_t batch, int32_t k, uint64_t *out_ids, double *out_scores,
+                        int32_t *out_counts);
+
+/* Duration in milliseconds of the device work of the last fcb_search_host call (CUDA events on
+ * the engine's stream around the kernels, excluding the copies); < 0 if none. Measurement aid. */
+float fcb_last_search_ms(const fcb_engine *e);
+
+/* Number of kernels the last fcb_search / fcb_search_host call launched. Measurement aid. */
+int32_t fcb_last_search_launches(const fcb_engine *e);
+
+/* Synthetic corpus (no counterpart in the reference, which has no ingestion code or data —
+ * SURVEY.md §2 row 13, §8d): counter-based integer generator, bit-identical to
+ * financial-chatbot-llm_b200/synth.py, writing straight into caller-owned device buffers. */
+int32_t fcb_synth_vectors(int32_t device, void *out, int32_t dtype, int64_t row_lo, int64_t n_rows,
+                          int32_t dim, uint64_t seed, int32_t n_clusters, void *stream);
+int32_t fcb_synth_columns(int32_t device, int32_t *dates, uint8_t *categories, int32_t *cents,
+                          int64_t row_lo, int64_t n_rows, uint64_t seed, int32_t n_categories,
+                          int64_t date_span_seconds, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FCB200_H */

@@ -1,0 +1,97 @@
+"""Host-side mirror of the reference interface: filter resolution, query_points plumbing,
+retrieve_transactions behaviour (reference tools/qdrant_tool.py:75-177). No GPU: the engine is
+replaced by a recording fake so only the host logic is exercised."""
+import datetime as dt
+
+import numpy as np
+import pytest
+
+from financial_chatbot_llm_b200 import _lib, client, tools
+from financial_chatbot_llm_b200 import qdrant_models as m
+
+
+def test_range_bounds_are_inclusive_integers():
+    pf = client.parse_filter(m.Filter(must=[
+        m.FieldCondition(key="metadata.user_id", match=m.MatchValue(value="u1")),
+        m.FieldCondition(key="metadata.date", range=m.Range(gte=10.5, lt=20)),
+        m.FieldCondition(key="metadata.date", range=m.Range(gt=11, lte=30.9))]))
+    assert pf.has_user and pf.user_id == "u1" and (pf.date_lo, pf.date_hi) == (12, 19)
+    assert client.parse_filter(None).has_user is False
+
+
+def test_unsupported_filters_raise():
+    with pytest.raises(NotImplementedError):
+        client.parse_filter(m.Filter(should=[m.FieldCondition(key="metadata.user_id", match=m.MatchValue(value="a"))]))
+    with pytest.raises(NotImplementedError):
+        client.parse_filter(m.Filter(must=[m.FieldCondition(key="metadata.amount", range=m.Range(gte=1))]))
+
+
+class FakeEngine:
+    dim, row_base = 4, 0
+
+    def __init__(self):
+        self.calls = []
+
+    def search_host(self, q, filters, k):
+        self.calls.append((q.copy(), filters[0], k))
+        f = filters[0]
+        rows = np.arange(f.row_begin, f.row_end, dtype=np.uint64)[:k]
+        ids = np.full((1, k), np.iinfo(np.uint64).max, dtype=np.uint64)
+        sc = np.full((1, k), -np.inf)
+        ids[0, :rows.size] = rows
+        sc[0, :rows.size] = 1.0 - 0.01 * np.arange(rows.size)
+        return ids, sc, np.array([rows.size], dtype=np.int32)
+
+
+def make_client(wrong_user_rows=()):
+    eng = FakeEngine()
+    users = ["alice", "bob"]
+    offsets = np.array([0, 3, 8])
+
+    def payload(row):
+        u = "mallory" if row in wrong_user_rows else users[0 if row < 3 else 1]
+        return {"page_content": f"txn {row}", "metadata": {"user_id": u, "date": 100 + row}}
+    col = client.Collection("transactions", eng, users, offsets, payload, category_codes={"Rent": 2})
+    c = client.B200QdrantClient(url="http://ignored", api_key="ignored")
+    c.attach_collection(col)
+    return c, eng
+
+
+def test_query_points_shape_and_filter_resolution():
+    c, eng = make_client()
+    flt = m.Filter(must=[m.FieldCondition(key="metadata.user_id", match=m.MatchValue(value="bob")),
+                         m.FieldCondition(key="metadata.category", match=m.MatchValue(value="Rent"))])
+    res = c.query_points(collection_name="transactions", query=[1, 0, 0, 0], limit=3,
+                         search_params=m.SearchParams(hnsw_ef=128, exact=False), query_filter=flt)
+    assert [p.id for p in res.points] == [3, 4, 5] and res.points[0].version == 0
+    assert res.points[0].payload["page_content"] == "txn 3" and res.points[0].vector is None
+    f = eng.calls[0][1]
+    assert (f.row_begin, f.row_end, f.category_mask) == (3, 8, 1 << 2)
+    assert f.date_lo == _lib.FCB_DATE_MIN and f.date_hi == _lib.FCB_DATE_MAX
+    # unknown user -> empty segment; offset and score_threshold are applied host-side
+    assert c.query_points("transactions", query=[1, 0, 0, 0], limit=5, query_filter=m.Filter(must=[
+        m.FieldCondition(key="metadata.user_id", match=m.MatchValue(value="nobody"))])).points == []
+    pts = c.query_points("transactions", query=[1, 0, 0, 0], limit=2, offset=1, score_threshold=0.985,
+                         query_filter=flt).points
+    assert [p.id for p in pts] == [4]
+    with pytest.raises(ValueError):
+        c.query_points("missing", query=[1, 0, 0, 0])
+
+
+def test_retrieve_transactions_behaviour():
+    c, eng = make_client(wrong_user_rows={4})
+    now = dt.datetime(2024, 6, 1, 12, 0, 0)
+    tools.configure(c, lambda text: [0.0, 1.0, 0.0, 0.0], now=lambda: now)
+    assert tools.retrieve_transactions(user_id="") == []                       # :89-91, no search
+    assert eng.calls == []
+    out = tools.retrieve_transactions(user_id="bob", num_transactions=4, time_period_days=30)
+    assert out == ["txn 3", "txn 5", "txn 6"]                                  # row 4 fails the post-check
+    _, f, k = eng.calls[-1]
+    assert k == 4 and f.date_lo == int((now - dt.timedelta(days=30)).timestamp())
+    tools.retrieve_transactions(user_id="bob", time_period_days=0)             # 0 => no date filter (:116)
+    _, f, k = eng.calls[-1]
+    assert k == 10000 and f.date_lo == _lib.FCB_DATE_MIN                       # default limit (:145)
+    tools.configure(c, lambda text: 1 / 0)                                     # any exception -> [] (:175-177)
+    assert tools.retrieve_transactions(user_id="bob") == []
+    with pytest.raises(Exception):
+        tools.RetrievalIntent(num_transactions=10001)
