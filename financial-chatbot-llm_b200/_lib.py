@@ -59,6 +59,9 @@ SIGNATURES = {
                                C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "fcb_search_host": (C.c_int32, [C.c_void_p, C.c_void_p, C.POINTER(FcbFilter), C.c_int32,
                                     C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "fcb_search_noalloc": (C.c_int32, [C.c_int32, C.POINTER(FcbShard), C.c_void_p, C.POINTER(FcbFilter),
+                                       C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                       C.c_char_p, C.c_int32]),
     "fcb_last_search_ms": (C.c_float, [C.c_void_p]),
     "fcb_last_search_launches": (C.c_int32, [C.c_void_p]),
     "fcb_synth_vectors": (C.c_int32, [C.c_int32, C.c_void_p, C.c_int32, C.c_int64, C.c_int64,

@@ -139,3 +139,21 @@ def synth_columns(row_lo: int, n_rows: int, seed: int, n_categories: int, date_s
     p = lambda x: None if x is None else x.data_ptr()
     check(lib.fcb_synth_columns(t.device.index, p(dates), p(categories), p(cents), row_lo, n_rows, seed,
                                 n_categories, date_span_seconds, C.c_void_p(st)))
+
+
+def search_noalloc(device: int, shard: FcbShard, d_query, filt: FcbFilter, k: int, out_ids, out_scores,
+                   out_count, stream: Optional[int] = None) -> None:
+    """fcb_search_noalloc: one query, no engine and no allocation inside the library (for callers
+    that cannot allocate GPU memory — see include/fcb200.h). ``shard`` is a host FcbShard whose
+    pointers are CUDA tensors' data_ptr(); query/outputs are CUDA tensors the caller owns.
+    Asynchronous on ``stream`` (default: torch's current stream). Calls sharing a GPU must not overlap."""
+    import torch
+    lib = _lib.load()
+    if stream is None:
+        stream = torch.cuda.current_stream(device).cuda_stream
+    err = C.create_string_buffer(256)
+    rc = lib.fcb_search_noalloc(device, C.byref(shard), d_query.data_ptr(), C.byref(filt), k,
+                                out_ids.data_ptr(), out_scores.data_ptr(), out_count.data_ptr(),
+                                C.c_void_p(stream), err, 256)
+    if rc != _lib.FCB_OK:
+        raise _lib.FcbError(rc, err.value.decode() or "fcb_search_noalloc failed")

@@ -124,6 +124,24 @@ int32_t fcb_search_host(fcb_engine *e, const double *queries, const fcb_filter *
                         int32_t batch, int32_t k, uint64_t *out_ids, double *out_scores,
                         int32_t *out_counts);
 
+/* No counterpart in the reference (nothing there allocates GPU memory at all). The same
+ * filtered top-k as fcb_search, for ONE query, for callers that may not allocate: a worker
+ * sharing a GPU whose memory a resident corpus owner has already filled, or a request thread that
+ * must not meet the device-wide synchronisation of cudaMalloc/cudaFree. Needs no engine: the
+ * caller passes the shard description (HOST struct, device pointers inside), the query
+ * (device, float64 [dim]), the filter (HOST) and the three output buffers (device: k ids,
+ * k float64 scores, 1 count). Makes no allocation on host or device; its scratch is a
+ * 262,400-byte array inside the library image that every GPU loading the library keeps until
+ * the process exits. Limits: k <= 16, dim <= 8192, one query per call — larger requests are
+ * refused with FCB_ERR_UNSUPPORTED. All calls on a GPU share the scratch: calls that can
+ * overlap on the device race (serialise them on one stream). The first call on each device
+ * resolves the scratch address and should happen before any stream capture begins. Errors are
+ * described in the caller's `err` buffer (may be NULL). Asynchronous on `stream`. */
+int32_t fcb_search_noalloc(int32_t device, const fcb_shard *shard, const double *query,
+                           const fcb_filter *filter, int32_t k, uint64_t *out_ids,
+                           double *out_scores, int32_t *out_count, void *stream, char *err,
+                           int32_t err_len);
+
 /* Duration in milliseconds of the device work of the last fcb_search_host call (CUDA events on
  * the engine's stream around the kernels, excluding the copies); < 0 if none. Measurement aid. */
 float fcb_last_search_ms(const fcb_engine *e);
