@@ -64,6 +64,8 @@ SIGNATURES = {
                                        C.c_char_p, C.c_int32]),
     "fcb_last_search_ms": (C.c_float, [C.c_void_p]),
     "fcb_last_search_launches": (C.c_int32, [C.c_void_p]),
+    "fcb_aggregate": (C.c_int32, [C.c_void_p, C.c_int64, C.c_int64, C.c_int32, C.c_int32, C.c_int32,
+                                  C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "fcb_synth_vectors": (C.c_int32, [C.c_int32, C.c_void_p, C.c_int32, C.c_int64, C.c_int64,
                                       C.c_int32, C.c_uint64, C.c_int32, C.c_void_p]),
     "fcb_synth_columns": (C.c_int32, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,

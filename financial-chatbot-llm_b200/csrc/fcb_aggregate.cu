@@ -1,0 +1,196 @@
+// Segmented integer-cents group-by: the replacement for
+//     transactions.groupby(plot_config.group_by)[plot_config.y_axis].sum()
+// (reference tools/plot_tool.py:45 and :52) over device-resident columns, for the key
+// (user, category, UTC calendar month) of BASELINE.json config 5. Exact int64 sums.
+//
+// HBM-bound target: 9 bytes per row (cents 4 + date 4 + category 1; the user is implicit in the
+// CSR segment) + 9 bytes per output cell.
+//
+// Work = fixed tiles of AGG_TILE consecutive rows, grid-strided over a persistent grid. A tile is
+// cut into pieces at user boundaries (binary search in seg_offsets). A piece accumulates into
+// per-CTA shared-memory cells with native 32-bit atomics: each value is split as
+// v = hi * 65536 + lo with lo in [-32768, 32767], so AGG_TILE <= 32768 rows can never overflow an
+// int32 cell whatever the int32 input; `hi` is zero for |v| < 32768 and then costs nothing.
+// Presence of a group (pandas lists observed groups only, even when their sum is 0) is a bitmap
+// tested before it is set. Cells are flushed to the dense int64 output with one 64-bit global
+// reduction per non-empty cell; very short pieces skip shared memory and reduce straight to global.
+// The month of a row is a table lookup: day -> month index, built once per CTA in shared memory
+// with the same civil-from-days arithmetic as the oracle.
+#include "fcb_internal.cuh"
+
+#define AGG_THREADS 256
+#define AGG_TILE 4096
+#define AGG_SMALL_PIECE 96
+#define AGG_MAX_MONTHS 240
+#define AGG_MAX_CELLS 4096
+
+struct AggParams {
+    const int64_t *seg_offsets;
+    const int32_t *dates;
+    const uint8_t *cats;
+    const int32_t *cents;
+    int64_t seg_begin, seg_end;
+    int64_t row_base, n_rows;
+    int32_t month_lo, n_months, n_categories;
+    int32_t day0, n_days;                  // table covers days [day0, day0 + n_days)
+    int64_t *sums;                         // [segs, n_categories, n_months]
+    uint8_t *present;                      // same shape
+    unsigned long long *dropped;           // rows outside the category / month window
+};
+
+// months since 1970-01 of a day number (days since 1970-01-01), proleptic Gregorian
+__host__ __device__ inline int32_t month_of_day(int32_t days) {
+    const int32_t z = days + 719468;
+    const int32_t era = (z >= 0 ? z : z - 146096) / 146097;
+    const int32_t doe = z - era * 146097;
+    const int32_t yoe = (doe - doe / 1460 + doe / 36524 - doe / 146096) / 365;
+    int32_t y = yoe + era * 400;
+    const int32_t doy = doe - (365 * yoe + yoe / 4 - yoe / 100);
+    const int32_t mp = (5 * doy + 2) / 153;
+    const int32_t m = mp < 10 ? mp + 3 : mp - 9;
+    if (m <= 2) ++y;
+    return (y - 1970) * 12 + (m - 1);
+}
+
+// first day (days since epoch) of month index mi
+static int32_t first_day_of_month(int32_t mi) {
+    int32_t y = 1970 + (mi >= 0 ? mi / 12 : -((-mi + 11) / 12));
+    int32_t m = mi - (y - 1970) * 12 + 1;                  // 1..12
+    // days-from-civil
+    y -= m <= 2;
+    const int32_t era = (y >= 0 ? y : y - 399) / 400;
+    const int32_t yoe = y - era * 400;
+    const int32_t doy = (153 * (m > 2 ? m - 3 : m + 9) + 2) / 5;
+    const int32_t doe = yoe * 365 + yoe / 4 - yoe / 100 + doy;
+    return era * 146097 + doe - 719468;
+}
+
+__device__ __forceinline__ int32_t floor_day(int32_t ts) {
+    int32_t d = ts / 86400;
+    if (ts - d * 86400 < 0) --d;
+    return d;
+}
+
+__global__ void __launch_bounds__(AGG_THREADS, 4) aggregate_kernel(const __grid_constant__ AggParams p) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int C = p.n_categories * p.n_months;
+    int32_t *c_lo = reinterpret_cast<int32_t *>(smem_raw);             // [C]
+    int32_t *c_hi = c_lo + C;                                          // [C]
+    uint32_t *c_present = reinterpret_cast<uint32_t *>(c_hi + C);      // [(C + 31) / 32]
+    uint16_t *month_tab = reinterpret_cast<uint16_t *>(c_present + (C + 31) / 32);   // [n_days]
+    __shared__ int64_t s_piece[2];
+
+    const int tid = threadIdx.x;
+    for (int i = tid; i < p.n_days; i += AGG_THREADS) month_tab[i] = (uint16_t)(month_of_day(p.day0 + i) - p.month_lo);
+    for (int i = tid; i < C; i += AGG_THREADS) { c_lo[i] = 0; c_hi[i] = 0; }
+    for (int i = tid; i < (C + 31) / 32; i += AGG_THREADS) c_present[i] = 0;
+    __syncthreads();
+
+    int64_t R0 = p.seg_offsets[p.seg_begin], R1 = p.seg_offsets[p.seg_end];
+    if (R0 < p.row_base) R0 = p.row_base;
+    if (R1 > p.row_base + p.n_rows) R1 = p.row_base + p.n_rows;
+    const int64_t n_tiles = R1 > R0 ? (R1 - R0 + AGG_TILE - 1) / AGG_TILE : 0;
+    unsigned dropped = 0;
+
+    for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+        const int64_t a = R0 + t * AGG_TILE;
+        const int64_t b = a + AGG_TILE < R1 ? a + AGG_TILE : R1;
+        // first user whose segment ends after a
+        if (tid == 0) {
+            int64_t lo = p.seg_begin, hi = p.seg_end - 1;
+            while (lo < hi) {
+                const int64_t mid = (lo + hi) >> 1;
+                if (p.seg_offsets[mid + 1] > a) hi = mid; else lo = mid + 1;
+            }
+            s_piece[0] = lo;
+        }
+        __syncthreads();
+        int64_t u = s_piece[0];
+        __syncthreads();
+        int64_t pa = a;
+        while (pa < b) {
+            int64_t uend = p.seg_offsets[u + 1];
+            while (uend <= pa) { ++u; uend = p.seg_offsets[u + 1]; }   // skip empty users
+            const int64_t pb = uend < b ? uend : b;
+            int64_t *out_s = p.sums + (u - p.seg_begin) * (int64_t)C;
+            uint8_t *out_p = p.present + (u - p.seg_begin) * (int64_t)C;
+            const bool small = pb - pa < AGG_SMALL_PIECE;
+            for (int64_t r = pa + tid; r < pb; r += AGG_THREADS) {
+                const int64_t lr = r - p.row_base;
+                const int32_t v = p.cents[lr];
+                const unsigned cat = p.cats[lr];
+                const int32_t di = floor_day(p.dates[lr]) - p.day0;
+                const unsigned mo = (unsigned)di < (unsigned)p.n_days ? month_tab[di] : 0xffffu;
+                if (cat >= (unsigned)p.n_categories || mo >= (unsigned)p.n_months) { ++dropped; continue; }
+                const int cell = cat * p.n_months + mo;
+                if (small) {
+                    atomicAdd(reinterpret_cast<unsigned long long *>(out_s + cell), (unsigned long long)(long long)v);
+                    out_p[cell] = 1;
+                } else {
+                    const int32_t lo16 = (int32_t)(int16_t)(v & 0xffff);
+                    const int32_t hi16 = (int32_t)(((int64_t)v - lo16) >> 16);   // [-32768, 32768]
+                    atomicAdd(&c_lo[cell], lo16);
+                    if (hi16) atomicAdd(&c_hi[cell], hi16);
+                    const uint32_t bit = 1u << (cell & 31);
+                    if (!(c_present[cell >> 5] & bit)) atomicOr(&c_present[cell >> 5], bit);
+                }
+            }
+            if (!small) {
+                __syncthreads();
+                for (int c = tid; c < C; c += AGG_THREADS) {
+                    if (c_present[c >> 5] & (1u << (c & 31))) {
+                        const long long s = (long long)c_hi[c] * 65536 + c_lo[c];
+                        atomicAdd(reinterpret_cast<unsigned long long *>(out_s + c), (unsigned long long)s);
+                        out_p[c] = 1;
+                        c_lo[c] = 0; c_hi[c] = 0;
+                    }
+                }
+                __syncthreads();
+                for (int i = tid; i < (C + 31) / 32; i += AGG_THREADS) c_present[i] = 0;
+                __syncthreads();
+            }
+            pa = pb;
+        }
+    }
+    if (dropped) atomicAdd(p.dropped, (unsigned long long)dropped);
+}
+
+extern "C" int32_t fcb_aggregate(fcb_engine *e, int64_t seg_begin, int64_t seg_end, int32_t month_lo, int32_t n_months,
+                                 int32_t n_categories, int64_t *sums, uint8_t *present, uint64_t *dropped, void *stream) {
+    if (!e) return FCB_ERR_INVALID;
+    if (!e->loaded) return fcb_fail(e, FCB_ERR_STATE, "fcb_aggregate: no shard loaded");
+    const fcb_shard &s = e->shard;
+    if (!s.dates || !s.categories || !s.cents || !s.seg_offsets)
+        return fcb_fail(e, FCB_ERR_STATE, "fcb_aggregate: the shard needs dates, categories, cents and seg_offsets");
+    if (!sums || !present || !dropped) return fcb_fail(e, FCB_ERR_INVALID, "fcb_aggregate: NULL output");
+    if (seg_begin < 0 || seg_end > s.n_segs || seg_begin > seg_end)
+        return fcb_fail(e, FCB_ERR_INVALID, "fcb_aggregate: segment range [%lld, %lld) outside 0..%lld",
+                        (long long)seg_begin, (long long)seg_end, (long long)s.n_segs);
+    if (n_months < 1 || n_months > AGG_MAX_MONTHS || n_categories < 1 || n_categories > 64 ||
+        (int64_t)n_months * n_categories > AGG_MAX_CELLS)
+        return fcb_fail(e, FCB_ERR_UNSUPPORTED, "fcb_aggregate: need 1..%d months, 1..64 categories, <= %d cells per user",
+                        AGG_MAX_MONTHS, AGG_MAX_CELLS);
+    FcbDeviceGuard g(e->device);
+    if (!g.ok) return fcb_fail(e, FCB_ERR_CUDA, "fcb_aggregate: cannot select device %d", e->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    const int64_t segs = seg_end - seg_begin;
+    const int C = n_months * n_categories;
+    FCB_CUDA(e, cudaMemsetAsync(sums, 0, (size_t)segs * C * sizeof(int64_t), st));
+    FCB_CUDA(e, cudaMemsetAsync(present, 0, (size_t)segs * C, st));
+    FCB_CUDA(e, cudaMemsetAsync(dropped, 0, sizeof(uint64_t), st));
+    if (segs == 0) return FCB_OK;
+
+    AggParams p{};
+    p.seg_offsets = s.seg_offsets; p.dates = s.dates; p.cats = s.categories; p.cents = s.cents;
+    p.seg_begin = seg_begin; p.seg_end = seg_end; p.row_base = s.row_base; p.n_rows = s.n_rows;
+    p.month_lo = month_lo; p.n_months = n_months; p.n_categories = n_categories;
+    p.day0 = first_day_of_month(month_lo);
+    p.n_days = first_day_of_month(month_lo + n_months) - p.day0;
+    p.sums = sums; p.present = present; p.dropped = (unsigned long long *)dropped;
+    const size_t smem = (size_t)C * 8 + (size_t)((C + 31) / 32) * 4 + (size_t)p.n_days * 2;
+    if (smem > 48 * 1024)
+        FCB_CUDA(e, cudaFuncSetAttribute(aggregate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    aggregate_kernel<<<e->num_sms * 4, AGG_THREADS, smem, st>>>(p);
+    FCB_CUDA(e, cudaGetLastError());
+    return FCB_OK;
+}

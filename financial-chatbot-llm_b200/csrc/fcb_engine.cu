@@ -38,6 +38,7 @@ extern "C" int32_t fcb_close(fcb_engine *e) {
         cudaDeviceSynchronize();
         free_host_staging(e);
         cudaFree(e->inv_norm);
+        fcb_general_free(e);
         cudaFree(e->d_filters);
         cudaFree(e->d_cand);
         cudaFree(e->d_counters);
@@ -165,6 +166,7 @@ extern "C" int32_t fcb_load_shard(fcb_engine *e, const fcb_shard *s) {
 
     e->loaded = false;
     cudaFree(e->inv_norm); e->inv_norm = nullptr;
+    fcb_general_free(e);
     free_host_staging(e);
     if (cudaMalloc(&e->inv_norm, (size_t)s->n_rows * sizeof(float)) != cudaSuccess) {
         cudaGetLastError();
@@ -188,8 +190,12 @@ extern "C" int32_t fcb_load_shard(fcb_engine *e, const fcb_shard *s) {
     FCB_CUDA(e, cudaMalloc(&e->d_scores, B * K * sizeof(double)));
     FCB_CUDA(e, cudaMallocHost(&e->h_counts, B * sizeof(int32_t)));
     FCB_CUDA(e, cudaMalloc(&e->d_counts, B * sizeof(int32_t)));
-    FCB_CUDA(e, cudaStreamSynchronize(e->stream));
     e->shard = *s;
+    if (e->max_k > FCB_FUSED_MAX_K) {
+        const int32_t rc = fcb_general_alloc(e);
+        if (rc != FCB_OK) return rc;
+    }
+    FCB_CUDA(e, cudaStreamSynchronize(e->stream));
     e->loaded = true;
     return FCB_OK;
 }

@@ -54,10 +54,30 @@ struct fcb_engine {
     double *h_scores = nullptr, *d_scores = nullptr;
     int32_t *h_counts = nullptr, *d_counts = nullptr;
 
+    // general-k path (k > FCB_FUSED_MAX_K), allocated in fcb_load_shard when max_k needs it
+    uint64_t *d_keys = nullptr;            // [n_rows] sortable (score32, tie) keys of one query
+    struct FcbSelectState *d_sel = nullptr;
+    uint32_t *d_sel_rows = nullptr;        // [kprime_max] selected rows
+    double *d_sel_scores = nullptr;        // [kprime_max] canonical float64 scores
+    uint64_t *d_sel_ids = nullptr;         // [kprime_max]
+    int kprime_max = 0;
+
     float last_ms = -1.f;
     int last_launches = 0;
     std::string err;
 };
+
+// device-resident state of one general-k selection (fcb_select.cu)
+struct FcbSelectState {
+    unsigned hist[8][256];                 // digit histograms of the 8 radix passes (MSB first)
+    unsigned n_pass;                       // rows that passed the filter
+    unsigned n_selected;                   // compaction cursor
+};
+
+int32_t fcb_general_alloc(fcb_engine *e);  // called by fcb_load_shard
+void fcb_general_free(fcb_engine *e);
+int32_t fcb_search_general(fcb_engine *e, const double *d_query, const fcb_filter &f, int32_t k,
+                           uint64_t *d_out_ids, double *d_out_scores, int32_t *d_out_count, cudaStream_t st);
 
 // error plumbing (fcb_engine.cu)
 int32_t fcb_fail(fcb_engine *e, int32_t code, const char *fmt, ...);

@@ -282,9 +282,19 @@ static int32_t search_device(fcb_engine *e, const double *d_queries, const fcb_f
                              cudaStream_t st) {
     const fcb_shard &s = e->shard;
     e->last_launches = 0;
-    if (k > FCB_FUSED_MAX_K)
-        return fcb_fail(e, FCB_ERR_UNSUPPORTED, "fcb_search: k=%d > %d needs the general-k path (not in this build)",
-                        k, FCB_FUSED_MAX_K);
+    if (k > FCB_FUSED_MAX_K) {
+        // general-k path: one query at a time, stream-ordered (fcb_select.cu)
+        for (int b = 0; b < batch; ++b) {
+            fcb_filter f = h_filters[b];
+            const bool has_date = f.date_lo != FCB_DATE_MIN || f.date_hi != FCB_DATE_MAX;
+            const bool has_cat = f.category_mask != FCB_ALL_CATEGORIES;
+            if ((has_date && !s.dates) || (has_cat && !s.categories) || f.date_lo > f.date_hi) f.row_end = f.row_begin;
+            const int32_t rc = fcb_search_general(e, d_queries + (size_t)b * s.dim, f, k, d_out_ids + (size_t)b * k,
+                                                  d_out_scores + (size_t)b * k, d_out_counts + b, st);
+            if (rc != FCB_OK) return rc;
+        }
+        return FCB_OK;
+    }
     ScanParams p{};
     p.vectors = s.vectors; p.inv_norm = e->inv_norm; p.ids = s.ids; p.id_rank = s.id_rank;
     p.dates = s.dates; p.cats = s.categories; p.queries = d_queries;

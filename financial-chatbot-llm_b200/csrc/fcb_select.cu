@@ -1,0 +1,315 @@
+// General-k path of fcb_search (16 < k <= 10000; the tool's default limit is 10000,
+// reference tools/qdrant_tool.py:145). One query at a time, everything stream-ordered, no host
+// round trip:
+//   1. scan_keys_kernel      the same predicate + GEMV scan as the fused path, but every row of
+//                            the segment gets a sortable 64-bit key (float32 score, tie order);
+//                            rows failing the predicate get key 0 and are never fetched.
+//                            (+8 bytes written per row next to the 4*dim read: HBM-bound as before)
+//   2. radix_hist_kernel x8  MSB-first radix select of the K'-th largest key, K' = k + margin;
+//                            each pass re-derives (prefix, remaining) from the earlier
+//                            histograms, so no host sync and no extra "pick bucket" launches.
+//                            Keys are L2-resident for segments up to ~15M rows.
+//   3. compact_kernel        rows with key >= threshold -> candidate list (exactly K' rows)
+//   4. rescore_kernel        canonical float64 score per candidate (one warp each)
+//   5. rank_scatter_kernel   rank by (score desc, id asc) and write the first k
+#include "fcb_internal.cuh"
+
+#define SEL_THREADS 256
+
+static inline int kprime_for(int k) {
+    int margin = k / 16;
+    if (margin < 32) margin = 32;
+    return k + margin;
+}
+
+void fcb_general_free(fcb_engine *e) {
+    cudaFree(e->d_keys); cudaFree(e->d_sel); cudaFree(e->d_sel_rows);
+    cudaFree(e->d_sel_scores); cudaFree(e->d_sel_ids);
+    e->d_keys = nullptr; e->d_sel = nullptr; e->d_sel_rows = nullptr;
+    e->d_sel_scores = nullptr; e->d_sel_ids = nullptr; e->kprime_max = 0;
+}
+
+int32_t fcb_general_alloc(fcb_engine *e) {
+    e->kprime_max = kprime_for(e->max_k);
+    const size_t n = (size_t)e->shard.n_rows, kp = (size_t)e->kprime_max;
+    if (cudaMalloc(&e->d_keys, n * sizeof(uint64_t)) != cudaSuccess ||
+        cudaMalloc(&e->d_sel, sizeof(FcbSelectState)) != cudaSuccess ||
+        cudaMalloc(&e->d_sel_rows, kp * sizeof(uint32_t)) != cudaSuccess ||
+        cudaMalloc(&e->d_sel_scores, kp * sizeof(double)) != cudaSuccess ||
+        cudaMalloc(&e->d_sel_ids, kp * sizeof(uint64_t)) != cudaSuccess) {
+        cudaGetLastError();
+        fcb_general_free(e);
+        return fcb_fail(e, FCB_ERR_NOMEM, "fcb_load_shard: cannot allocate general-k scratch (%zu bytes of keys)",
+                        n * sizeof(uint64_t));
+    }
+    return FCB_OK;
+}
+
+struct KeyScanParams {
+    const void *vectors;
+    const float *inv_norm;
+    const uint32_t *id_rank;
+    const int32_t *dates;
+    const uint8_t *cats;
+    const double *query;
+    fcb_filter filter;
+    int64_t n_rows, row_base;
+    int dim;
+    uint64_t *keys;                        // [segment rows], index = row - lo
+    FcbSelectState *state;
+};
+
+__device__ __forceinline__ uint64_t make_key(float score, uint32_t tie) {
+    uint32_t u = __float_as_uint(score);
+    u ^= (u >> 31) ? 0xffffffffu : 0x80000000u;             // monotone float -> unsigned
+    return ((uint64_t)u << 32) | (uint64_t)(0xffffffffu - tie);   // larger key = better
+}
+
+template <typename T> struct KeyDot;
+template <> struct KeyDot<float> {
+    static constexpr int VEC = 4;
+    __device__ static __forceinline__ float dot(uint4 v, const float *q, float acc) {
+        acc = fmaf(__uint_as_float(v.x), q[0], acc); acc = fmaf(__uint_as_float(v.y), q[1], acc);
+        acc = fmaf(__uint_as_float(v.z), q[2], acc); acc = fmaf(__uint_as_float(v.w), q[3], acc);
+        return acc;
+    }
+};
+template <> struct KeyDot<__nv_bfloat16> {
+    static constexpr int VEC = 8;
+    __device__ static __forceinline__ float dot(uint4 v, const float *q, float acc) {
+        acc = fmaf(fcb_bf16lo(v.x), q[0], acc); acc = fmaf(fcb_bf16hi(v.x), q[1], acc);
+        acc = fmaf(fcb_bf16lo(v.y), q[2], acc); acc = fmaf(fcb_bf16hi(v.y), q[3], acc);
+        acc = fmaf(fcb_bf16lo(v.z), q[4], acc); acc = fmaf(fcb_bf16hi(v.z), q[5], acc);
+        acc = fmaf(fcb_bf16lo(v.w), q[6], acc); acc = fmaf(fcb_bf16hi(v.w), q[7], acc);
+        return acc;
+    }
+};
+
+template <typename T>
+__global__ void __launch_bounds__(FCB_SCAN_THREADS, 2) scan_keys_kernel(const __grid_constant__ KeyScanParams p) {
+    constexpr int R = 4;
+    constexpr int VEC = KeyDot<T>::VEC;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    float *q_s = reinterpret_cast<float *>(smem_raw);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const fcb_filter f = p.filter;
+    for (int i = tid; i < p.dim; i += FCB_SCAN_THREADS) q_s[i] = (float)p.query[i];
+    __syncthreads();
+
+    int64_t lo = f.row_begin - p.row_base, hi = f.row_end - p.row_base;
+    if (lo < 0) lo = 0;
+    if (hi > p.n_rows) hi = p.n_rows;
+    const int64_t nrows = hi > lo ? hi - lo : 0;
+    const int64_t ngroups = (nrows + R - 1) / R;
+    const bool has_date = f.date_lo != FCB_DATE_MIN || f.date_hi != FCB_DATE_MAX;
+    const bool has_cat = f.category_mask != FCB_ALL_CATEGORIES;
+    const int nv = p.dim / VEC;
+    const T *__restrict__ vec = reinterpret_cast<const T *>(p.vectors);
+    unsigned n_pass = 0;
+
+    const int64_t stride = (int64_t)gridDim.x * FCB_SCAN_WARPS;
+    for (int64_t g = (int64_t)blockIdx.x * FCB_SCAN_WARPS + warp; g < ngroups; g += stride) {
+        const int64_t r0 = lo + g * R;
+        bool pass = false, in_seg = false;
+        float inv = 0.f;
+        uint32_t tie = 0;
+        if (lane < R && r0 + lane < hi) {
+            const int64_t row = r0 + lane;
+            in_seg = pass = true;
+            if (has_date) { const int64_t d = p.dates[row]; pass = d >= f.date_lo && d <= f.date_hi; }
+            if (pass && has_cat) { const unsigned c = p.cats[row]; pass = c < 64 && ((f.category_mask >> c) & 1ull); }
+            if (pass) { inv = p.inv_norm[row]; tie = p.id_rank ? p.id_rank[row] : (uint32_t)row; }
+        }
+        const unsigned pm = __ballot_sync(FCB_FULL, pass);
+        float acc[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) acc[r] = 0.f;
+        if (pm) {
+            const uint4 *__restrict__ base = reinterpret_cast<const uint4 *>(vec + r0 * (int64_t)p.dim);
+#pragma unroll 4
+            for (int c = lane; c < nv; c += 32) {
+                float qv[VEC];
+#pragma unroll
+                for (int i = 0; i < VEC; i += 4)
+                    *reinterpret_cast<float4 *>(&qv[i]) = *reinterpret_cast<const float4 *>(&q_s[c * VEC + i]);
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    const uint4 v = fcb_ldg_stream(base + (int64_t)r * nv + c, (pm >> r) & 1u);
+                    acc[r] = KeyDot<T>::dot(v, qv, acc[r]);
+                }
+            }
+#pragma unroll
+            for (int r = 0; r < R; ++r) acc[r] = fcb_warp_sum(acc[r]);
+        }
+        // lane r (< R) owns row r0 + r: pick its sum without dynamic register indexing
+        float mine = acc[0];
+#pragma unroll
+        for (int r = 1; r < R; ++r) mine = (lane == r) ? acc[r] : mine;
+        if (in_seg) p.keys[r0 + lane - lo] = pass ? make_key(mine * inv, tie) : 0ull;
+        n_pass += __popc(pm);
+    }
+    if (lane == 0 && n_pass) atomicAdd(&p.state->n_pass, n_pass);
+}
+
+// (prefix, remaining) after `passes` completed radix passes; all threads of the CTA call this.
+// K' = min(kprime, n_pass). remaining == 0 means "nothing to select".
+__device__ void resolve_state(const FcbSelectState *st, int passes, unsigned kprime, uint64_t &prefix,
+                              unsigned &remaining, unsigned *s_scan /* [256] */, unsigned *s_out /* [2] */) {
+    const int tid = threadIdx.x;
+    unsigned rem = st->n_pass < kprime ? st->n_pass : kprime;
+    uint64_t pre = 0;
+    for (int q = 0; q < passes && rem > 0; ++q) {
+        // suffix-inclusive sums over digits 255..0 (Hillis-Steele on reversed index)
+        const unsigned h = tid < 256 ? st->hist[q][255 - tid] : 0;       // position tid <-> digit 255 - tid
+        if (tid < 256) s_scan[tid] = h;
+        __syncthreads();
+        for (int off = 1; off < 256; off <<= 1) {
+            unsigned add = 0;
+            if (tid < 256 && tid >= off) add = s_scan[tid - off];
+            __syncthreads();
+            if (tid < 256) s_scan[tid] += add;
+            __syncthreads();
+        }
+        if (tid < 256) {
+            const unsigned incl = s_scan[tid], excl = incl - h;           // keys with a larger digit: excl
+            if (excl < rem && rem <= incl) { s_out[0] = 255 - tid; s_out[1] = rem - excl; }
+        }
+        __syncthreads();
+        pre |= (uint64_t)s_out[0] << (56 - 8 * q);
+        rem = s_out[1];
+        __syncthreads();
+    }
+    prefix = pre;
+    remaining = rem;
+}
+
+__global__ void __launch_bounds__(SEL_THREADS) radix_hist_kernel(const uint64_t *__restrict__ keys, int64_t n,
+                                                                 FcbSelectState *st, int pass, unsigned kprime) {
+    __shared__ unsigned s_scan[256], s_out[2], s_hist[256];
+    uint64_t prefix;
+    unsigned remaining;
+    resolve_state(st, pass, kprime, prefix, remaining, s_scan, s_out);
+    if (remaining == 0) return;
+    const int tid = threadIdx.x;
+    s_hist[tid] = 0;
+    __syncthreads();
+    const int shift = 56 - 8 * pass;
+    const uint64_t himask = pass == 0 ? 0ull : ~0ull << (shift + 8);
+    for (int64_t i = (int64_t)blockIdx.x * SEL_THREADS + tid; i < n; i += (int64_t)gridDim.x * SEL_THREADS) {
+        const uint64_t key = keys[i];
+        if (key != 0ull && (key & himask) == prefix) atomicAdd(&s_hist[(unsigned)(key >> shift) & 255u], 1u);
+    }
+    __syncthreads();
+    if (s_hist[tid]) atomicAdd(&st->hist[pass][tid], s_hist[tid]);
+}
+
+__global__ void __launch_bounds__(SEL_THREADS) compact_kernel(const uint64_t *__restrict__ keys, int64_t n, int64_t lo,
+                                                              FcbSelectState *st, unsigned kprime,
+                                                              uint32_t *__restrict__ sel_rows) {
+    __shared__ unsigned s_scan[256], s_out[2];
+    uint64_t thr;
+    unsigned remaining;
+    resolve_state(st, 8, kprime, thr, remaining, s_scan, s_out);
+    if (remaining == 0) return;                                    // nothing passed the filter
+    for (int64_t i = (int64_t)blockIdx.x * SEL_THREADS + threadIdx.x; i < n; i += (int64_t)gridDim.x * SEL_THREADS) {
+        const uint64_t key = keys[i];
+        if (key != 0ull && key >= thr) {
+            const unsigned slot = atomicAdd(&st->n_selected, 1u);
+            if (slot < kprime) sel_rows[slot] = (uint32_t)(lo + i);
+        }
+    }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(SEL_THREADS) rescore_kernel(const T *__restrict__ vectors, const uint64_t *__restrict__ ids,
+                                                              int64_t row_base, int dim, const double *__restrict__ q,
+                                                              const FcbSelectState *st, unsigned kprime,
+                                                              const uint32_t *__restrict__ sel_rows,
+                                                              double *__restrict__ sel_scores, uint64_t *__restrict__ sel_ids) {
+    const unsigned n_sel = st->n_pass < kprime ? st->n_pass : kprime;
+    const int lane = threadIdx.x & 31;
+    const unsigned w = blockIdx.x * (SEL_THREADS / 32) + (threadIdx.x >> 5);
+    if (w >= n_sel) return;
+    const uint32_t row = sel_rows[w];
+    const double sc = fcb_canon_score_warp<T>(vectors + (int64_t)row * dim, q, dim, lane);
+    if (lane == 0) { sel_scores[w] = sc; sel_ids[w] = ids ? ids[row] : (uint64_t)(row_base + row); }
+}
+
+__global__ void __launch_bounds__(128) rank_scatter_kernel(const FcbSelectState *st, unsigned kprime, int k,
+                                                           const double *__restrict__ sel_scores,
+                                                           const uint64_t *__restrict__ sel_ids, uint64_t *__restrict__ out_ids,
+                                                           double *__restrict__ out_scores, int32_t *__restrict__ out_count) {
+    __shared__ double t_s[512];
+    __shared__ uint64_t t_i[512];
+    const unsigned n_sel = st->n_pass < kprime ? st->n_pass : kprime;
+    const unsigned count = n_sel < (unsigned)k ? n_sel : (unsigned)k;
+    const unsigned i = blockIdx.x * 128 + threadIdx.x;
+    if (i == 0) *out_count = (int32_t)count;
+    if (i >= count && i < (unsigned)k) { out_ids[i] = UINT64_MAX; out_scores[i] = -INFINITY; }   // pad the tail
+    if (blockIdx.x * 128 >= n_sel) return;
+    const bool mine = i < n_sel;
+    const double ms = mine ? sel_scores[i] : 0.0;
+    const uint64_t mi = mine ? sel_ids[i] : 0;
+    unsigned rank = 0;
+    for (unsigned base = 0; base < n_sel; base += 512) {
+        __syncthreads();
+        for (unsigned t = threadIdx.x; t < 512; t += 128) {
+            const unsigned j = base + t;
+            t_s[t] = j < n_sel ? sel_scores[j] : -INFINITY;
+            t_i[t] = j < n_sel ? sel_ids[j] : UINT64_MAX;
+        }
+        __syncthreads();
+        const unsigned lim = n_sel - base < 512 ? n_sel - base : 512;
+        for (unsigned t = 0; t < lim; ++t) rank += fcb_better64(t_s[t], t_i[t], ms, mi);
+    }
+    if (mine && rank < (unsigned)k) { out_ids[rank] = mi; out_scores[rank] = ms; }
+}
+
+template <typename T>
+static int32_t general_impl(fcb_engine *e, const double *d_query, const fcb_filter &f, int32_t k, uint64_t *d_out_ids,
+                            double *d_out_scores, int32_t *d_out_count, cudaStream_t st) {
+    const fcb_shard &s = e->shard;
+    const unsigned kprime = (unsigned)kprime_for(k);
+    int64_t lo = f.row_begin - s.row_base, hi = f.row_end - s.row_base;
+    if (lo < 0) lo = 0;
+    if (hi > s.n_rows) hi = s.n_rows;
+    const int64_t n = hi > lo ? hi - lo : 0;
+
+    FCB_CUDA(e, cudaMemsetAsync(e->d_sel, 0, sizeof(FcbSelectState), st));
+    if (n > 0) {
+        KeyScanParams p{};
+        p.vectors = s.vectors; p.inv_norm = e->inv_norm; p.id_rank = s.id_rank; p.dates = s.dates; p.cats = s.categories;
+        p.query = d_query; p.filter = f; p.n_rows = s.n_rows; p.row_base = s.row_base; p.dim = s.dim;
+        p.keys = e->d_keys; p.state = e->d_sel;
+        const int64_t groups = (n + 3) / 4;
+        int64_t ctas = (groups + 2 * FCB_SCAN_WARPS - 1) / (2 * FCB_SCAN_WARPS);
+        if (ctas > 2 * (int64_t)e->num_sms) ctas = 2 * (int64_t)e->num_sms;
+        if (ctas < 1) ctas = 1;
+        scan_keys_kernel<T><<<(unsigned)ctas, FCB_SCAN_THREADS, (size_t)s.dim * sizeof(float), st>>>(p);
+        FCB_CUDA(e, cudaGetLastError());
+        int64_t sel_ctas = (n + SEL_THREADS * 16 - 1) / (SEL_THREADS * 16);
+        if (sel_ctas > 4 * (int64_t)e->num_sms) sel_ctas = 4 * (int64_t)e->num_sms;
+        for (int pass = 0; pass < 8; ++pass)
+            radix_hist_kernel<<<(unsigned)sel_ctas, SEL_THREADS, 0, st>>>(e->d_keys, n, e->d_sel, pass, kprime);
+        compact_kernel<<<(unsigned)sel_ctas, SEL_THREADS, 0, st>>>(e->d_keys, n, lo, e->d_sel, kprime, e->d_sel_rows);
+        rescore_kernel<T><<<(kprime + SEL_THREADS / 32 - 1) / (SEL_THREADS / 32), SEL_THREADS, 0, st>>>(
+            (const T *)s.vectors, s.ids, s.row_base, s.dim, d_query, e->d_sel, kprime, e->d_sel_rows, e->d_sel_scores,
+            e->d_sel_ids);
+        FCB_CUDA(e, cudaGetLastError());
+        e->last_launches += 11;
+    }
+    const unsigned span = kprime > (unsigned)k ? kprime : (unsigned)k;
+    rank_scatter_kernel<<<(span + 127) / 128, 128, 0, st>>>(e->d_sel, kprime, k, e->d_sel_scores, e->d_sel_ids, d_out_ids,
+                                                          d_out_scores, d_out_count);
+    FCB_CUDA(e, cudaGetLastError());
+    e->last_launches += 1;
+    return FCB_OK;
+}
+
+int32_t fcb_search_general(fcb_engine *e, const double *d_query, const fcb_filter &f, int32_t k, uint64_t *d_out_ids,
+                           double *d_out_scores, int32_t *d_out_count, cudaStream_t st) {
+    if (!e->d_keys) return fcb_fail(e, FCB_ERR_STATE, "fcb_search: general-k scratch missing (max_k <= %d at fcb_open?)", FCB_FUSED_MAX_K);
+    if (e->shard.dtype == FCB_DTYPE_F32)
+        return general_impl<float>(e, d_query, f, k, d_out_ids, d_out_scores, d_out_count, st);
+    return general_impl<__nv_bfloat16>(e, d_query, f, k, d_out_ids, d_out_scores, d_out_count, st);
+}

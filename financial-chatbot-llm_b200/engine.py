@@ -110,6 +110,27 @@ class Engine:
         check(self._lib.fcb_search(self._h, d_queries.data_ptr(), farr, B, k, out_ids.data_ptr(),
                                    out_scores.data_ptr(), out_counts.data_ptr(), C.c_void_p(stream)), self._h)
 
+    # ---- aggregation
+    def aggregate(self, seg_begin: int, seg_end: int, month_lo: int, n_months: int, n_categories: int,
+                  sums=None, present=None, dropped=None, stream: Optional[int] = None):
+        """fcb_aggregate over the loaded shard. Returns CUDA tensors (sums int64 [S, C, M],
+        present uint8 [S, C, M], dropped int64 [1]); asynchronous on torch's current stream."""
+        import torch
+        dev = torch.device("cuda", self.device)
+        S = seg_end - seg_begin
+        if sums is None:
+            sums = torch.empty((S, n_categories, n_months), dtype=torch.int64, device=dev)
+        if present is None:
+            present = torch.empty((S, n_categories, n_months), dtype=torch.uint8, device=dev)
+        if dropped is None:
+            dropped = torch.empty(1, dtype=torch.int64, device=dev)
+        if stream is None:
+            stream = torch.cuda.current_stream(self.device).cuda_stream
+        check(self._lib.fcb_aggregate(self._h, seg_begin, seg_end, month_lo, n_months, n_categories,
+                                      sums.data_ptr(), present.data_ptr(), dropped.data_ptr(),
+                                      C.c_void_p(stream)), self._h)
+        return sums, present, dropped
+
     @property
     def last_search_ms(self) -> float:
         return float(self._lib.fcb_last_search_ms(self._h))

@@ -149,6 +149,22 @@ float fcb_last_search_ms(const fcb_engine *e);
 /* Number of kernels the last fcb_search / fcb_search_host call launched. Measurement aid. */
 int32_t fcb_last_search_launches(const fcb_engine *e);
 
+/* Replaces transactions.groupby(plot_config.group_by)[plot_config.y_axis].sum() at
+ * tools/plot_tool.py:45 (bar) and :52 (pie), over the shard's device columns, for the key
+ * (user, category, UTC calendar month) of BASELINE.json config 5. Exact int64 sums of int32 cents.
+ *   seg_begin/end   user (CSR segment) range; rows outside this shard's row range are skipped
+ *   month_lo        first month of the dense window, in months since 1970-01 (UTC)
+ *   n_months        1..240; n_categories 1..64; n_months * n_categories <= 4096
+ *   sums            device int64  [seg_end-seg_begin, n_categories, n_months]   (zeroed by the call)
+ *   present         device uint8  same shape: 1 where the group has at least one row — pandas
+ *                   lists observed groups only, in ascending key order = this dense order
+ *   dropped         device uint64 [1]: rows whose category/month fall outside the window (must
+ *                   read 0 for the result to be the complete group-by)
+ * Asynchronous on `stream`. */
+int32_t fcb_aggregate(fcb_engine *e, int64_t seg_begin, int64_t seg_end, int32_t month_lo,
+                      int32_t n_months, int32_t n_categories, int64_t *sums, uint8_t *present,
+                      uint64_t *dropped, void *stream);
+
 /* Synthetic corpus (no counterpart in the reference, which has no ingestion code or data —
  * SURVEY.md §2 row 13, §8d): counter-based integer generator, bit-identical to
  * financial-chatbot-llm_b200/synth.py, writing straight into caller-owned device buffers. */

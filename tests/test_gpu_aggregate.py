@@ -1,0 +1,144 @@
+"""Aggregation kernel (fcb_aggregate) against pandas (the reference's own library call,
+tools/plot_tool.py:45,52), the C restatement and the committed golden fixtures. Integer sums:
+bit-exact."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def make_engine(spec, cents=None, dates=None, cats=None, offsets=None):
+    import torch
+    from financial_chatbot_llm_b200 import synth
+    from financial_chatbot_llm_b200.engine import Engine
+    n = spec.n_rows
+    dev = torch.device("cuda", 0)
+    offsets = synth.segment_offsets(spec) if offsets is None else offsets
+    d = synth.dates(spec, 0, n) if dates is None else dates
+    c = synth.categories(spec, 0, n) if cats is None else cats
+    v = synth.cents(spec, 0, n) if cents is None else cents
+    eng = Engine(device=0, max_batch=1, max_k=1)
+    eng.load_shard(torch.zeros((n, 4), dtype=torch.float32, device=dev), dates=torch.from_numpy(d).to(dev),
+                   categories=torch.from_numpy(c).to(dev), cents=torch.from_numpy(v).to(dev),
+                   seg_offsets=torch.from_numpy(offsets).to(dev))
+    return eng, offsets, d, c, v
+
+
+def month_window(d):
+    from oracle import groupby
+    m = groupby.month_index(d)
+    return int(m.min()), int(m.max() - m.min() + 1)
+
+
+def test_user_category_month_equals_pandas_golden(built):
+    from financial_chatbot_llm_b200 import aggregate, synth
+    g = json.load(open(os.path.join(HERE, "golden", "groupby_golden.json")))["columns"]
+    spec = synth.SynthSpec(**g["spec"])
+    eng, off, d, c, v = make_engine(spec)
+    mlo, nm = month_window(d)
+    u, cat, mo, s = aggregate.groupby_user_category_month(eng, 0, spec.n_users, mlo, nm, 16)
+    assert u.tolist() == g["user"] and cat.tolist() == g["category"] and mo.tolist() == g["month"]
+    assert s.tolist() == g["sum"]
+    # a sub-range of users
+    u2, _, _, s2 = aggregate.groupby_user_category_month(eng, 5, 9, mlo, nm, 16)
+    sel = (np.array(g["user"]) >= 5) & (np.array(g["user"]) < 9)
+    assert u2.tolist() == np.array(g["user"])[sel].tolist() and s2.tolist() == np.array(g["sum"])[sel].tolist()
+    eng.close()
+
+
+def test_ragged_users_extreme_values_and_zero_sums(built):
+    """Tiny users (global-atomic path), a whale (shared-memory path, many tiles), full-range int32
+    values (lo/hi split), groups whose sum is exactly 0, dates before 1970."""
+    from financial_chatbot_llm_b200 import aggregate, synth
+    from oracle import canon, groupby
+    rng = np.random.default_rng(5)
+    sizes = np.array([1, 2, 3, 50000, 95, 96, 97, 4096, 4097, 1, 20000, 7], dtype=np.int64)
+    off = np.zeros(len(sizes) + 1, dtype=np.int64)
+    np.cumsum(sizes, out=off[1:])
+    n = int(off[-1])
+    spec = synth.SynthSpec(n_rows=n, dim=4, n_users=len(sizes))
+    v = rng.integers(-(2 ** 31), 2 ** 31, size=n, dtype=np.int64).astype(np.int32)
+    v[::7] = 2 ** 31 - 1
+    v[1::7] = -(2 ** 31)
+    v[int(off[4]):int(off[5])] = np.where(np.arange(95) % 2 == 0, 777, -777)[:95]
+    v[int(off[4])] = 0                                          # 47 x +777, 47 x -777, one 0 -> group sums can be 0
+    d = rng.integers(-86400 * 400, 86400 * 400, size=n).astype(np.int32)     # 1968-11 .. 1971-02
+    c = rng.integers(0, 5, size=n).astype(np.uint8)
+    c[int(off[4]):int(off[5])] = 2
+    d[int(off[4]):int(off[5])] = 86400 * 45
+    eng, *_ = make_engine(spec, cents=v, dates=d, cats=c, offsets=off)
+    mlo, nm = month_window(d)
+    u, cat, mo, s = aggregate.groupby_user_category_month(eng, 0, len(sizes), mlo, nm, 5)
+    ser = groupby.groupby_user_category_month(synth.row_users(off, np.arange(n)), c, d, v)
+    idx = ser.index.to_frame(index=False)
+    assert u.tolist() == idx["user"].tolist() and cat.tolist() == idx["category"].tolist()
+    assert mo.tolist() == idx["month"].tolist() and s.tolist() == ser.tolist()
+    cu, cc, cm, cs, _ = canon.groupby(off, d, c, v)
+    assert s.tolist() == cs.tolist() and mo.tolist() == cm.tolist()
+    assert 0 in s[u == 4].tolist()                              # the zero-sum group is present
+    # window too small -> rows are reported as dropped, never silently lost
+    with pytest.raises(ValueError, match="outside"):
+        aggregate.groupby_user_category_month(eng, 0, len(sizes), mlo + 1, nm - 1, 5)
+    with pytest.raises(ValueError, match="outside"):
+        aggregate.groupby_user_category_month(eng, 0, len(sizes), mlo, nm, 4)
+    eng.close()
+
+
+def test_size_independent_properties_at_scale(built):
+    """20M rows generated on the device: total of all cells == independent torch reduction of the
+    column; per-user totals == segment sums; a random sample of users == host pandas on regenerated rows."""
+    import torch
+    from financial_chatbot_llm_b200 import synth
+    from financial_chatbot_llm_b200.engine import Engine, synth_columns
+    from oracle import groupby
+    n, users = 20_000_000, 2000
+    spec = synth.SynthSpec(n_rows=n, dim=4, n_users=users, seed=4242)
+    dev = torch.device("cuda", 0)
+    d = torch.empty(n, dtype=torch.int32, device=dev)
+    c = torch.empty(n, dtype=torch.uint8, device=dev)
+    v = torch.empty(n, dtype=torch.int32, device=dev)
+    synth_columns(0, n, spec.seed, spec.n_categories, spec.date_span_seconds, dates=d, categories=c, cents=v)
+    off = synth.segment_offsets(spec)
+    eng = Engine(device=0, max_batch=1, max_k=1)
+    eng.load_shard(torch.zeros((n, 4), dtype=torch.float32, device=dev), dates=d, categories=c, cents=v,
+                   seg_offsets=torch.from_numpy(off).to(dev))
+    mlo = int(groupby.month_index(np.array([synth.DATE_BASE]))[0])
+    sums, present, dropped = eng.aggregate(0, users, mlo, 24, 16)
+    torch.cuda.synchronize()
+    assert int(dropped.item()) == 0
+    assert int(sums.sum().item()) == int(v.to(torch.int64).sum().item())
+    csum = torch.cat([torch.zeros(1, dtype=torch.int64, device=dev), v.to(torch.int64).cumsum(0)])
+    offs_d = torch.from_numpy(off).to(dev)
+    assert torch.equal(sums.sum(dim=(1, 2)), csum[offs_d[1:]] - csum[offs_d[:-1]])
+    for u in (0, 1, 17, 999, 1999):
+        lo, hi = int(off[u]), int(off[u + 1])
+        ser = groupby.groupby_user_category_month(np.zeros(hi - lo, dtype=np.int64), synth.categories(spec, lo, hi),
+                                                  synth.dates(spec, lo, hi), synth.cents(spec, lo, hi))
+        idx = ser.index.to_frame(index=False)
+        got = sums[u].cpu().numpy()
+        pres = present[u].cpu().numpy().astype(bool)
+        assert int(pres.sum()) == len(ser)
+        assert got[idx["category"].to_numpy(), idx["month"].to_numpy() - mlo].tolist() == ser.tolist()
+    eng.close()
+
+
+def test_tool_shaped_json_groupby_equals_pandas_golden(built):
+    from financial_chatbot_llm_b200 import aggregate
+    g = json.load(open(os.path.join(HERE, "golden", "groupby_golden.json")))
+    for key, want in g["json_groupby"].items():
+        gb, y = key.split("|")
+        s = aggregate.grouped_sum_json(g["transactions_json"], gb, y)
+        assert [x if isinstance(x, str) else int(x) for x in s.index.tolist()] == want["index"]
+        if want["dtype"] == "int64":
+            assert s.dtype == np.int64 and s.tolist() == want["values"]
+        else:
+            assert np.allclose(s.to_numpy(), want["values"], rtol=0, atol=1e-9)   # float cents: exact to 1e-9
+    out = aggregate.create_financial_plot(g["transactions_json"], aggregate.PlotConfig(
+        plot_type="bar", x_axis="category", y_axis="amount_cents", title="t", group_by="category"))
+    assert out.startswith("data:")
+    err = aggregate.create_financial_plot("not json", aggregate.PlotConfig(plot_type="bar", x_axis="a", y_axis="b", title="t", group_by="a"))
+    assert err.startswith("Error creating plot:")
