@@ -112,7 +112,7 @@ def host_sample(spec, rows: int, threads: int):
     return out, synth.dates(spec, 0, rows)
 
 
-def cpu_reference_qps(steps: int, warmup: int, sample_rows: int = 100_000):
+def cpu_reference_qps(steps: int, warmup: int, sample_rows: int = 100_000, n_gpus: int = 1):
     """The reference path's arithmetic (qdrant-client local mode, restated in oracle/local_mode.py:
     per-query float32 re-normalisation of the stored matrix, mixed f32 x f64 dot over ALL rows,
     payload mask, descending order) timed on the host cores with numpy's default BLAS threading.
@@ -136,7 +136,8 @@ def cpu_reference_qps(steps: int, warmup: int, sample_rows: int = 100_000):
         if i >= warmup:
             times.append(dt)
     qps_sample = len(times) / sum(times)
-    scale = sample_rows / ROWS_PER_GPU
+    # local mode scores EVERY stored row whatever the filter, so at N shards (N x 10M rows) a query costs N x more
+    scale = sample_rows / (ROWS_PER_GPU * n_gpus)
     try:
         from threadpoolctl import threadpool_info
         blas_threads = max([p.get("num_threads", 1) for p in threadpool_info()] or [1])
@@ -145,7 +146,7 @@ def cpu_reference_qps(steps: int, warmup: int, sample_rows: int = 100_000):
     return {
         "value": qps_sample * scale, "unit": UNIT, "cores": cores, "kind": "port",
         "blas_threads": blas_threads,
-        "sample": (f"{sample_rows} of 10M rows x {DIM} f32, {len(times)} single queries, whale tenant + date>=t0 "
+        "sample": (f"{sample_rows} of {n_gpus}x10M rows x {DIM} f32, {len(times)} single queries, whale tenant + date>=t0 "
                    f"(100% pass), vectorised payload mask; measured {qps_sample:.3f} q/s on the sample, scaled by "
                    f"{scale:g} (scan is O(N)); numpy {np.__version__}"),
         "ms_per_query_sample": 1e3 * statistics.median(times),
@@ -156,7 +157,7 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    cb = cpu_reference_qps(args.steps, args.warmup)
+    cb = cpu_reference_qps(args.steps, args.warmup, n_gpus=args.gpus)
     line = {
         "impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 / cb["value"], "higher_is_better": True,
@@ -221,17 +222,15 @@ def run_b200(args):
     n_q = 16
     q_host = [np.stack([synth.query_vector(spec, s * B + b) for b in range(B)]) for s in range(n_q)]
     q_dev = [torch.from_numpy(q).to(dev) for q in q_host]
-    out_ids = torch.empty((B, K), dtype=torch.int64, device=dev)
-    out_sc = torch.empty((B, K), dtype=torch.float64, device=dev)
-    out_cnt = torch.empty(B, dtype=torch.int32, device=dev)
-    if world > 1:
-        from financial_chatbot_llm_b200 import sharded
-        merger = sharded.ShardMerger(eng, world, B, K, dev)
+    from financial_chatbot_llm_b200 import sharded
+    searcher = sharded.ShardedSearcher(col, world, dev)
+    merger = searcher.merger(B, K)
+    out_ids, out_sc, out_cnt = merger.local_views          # fcb_search writes straight into the packed buffer
 
     def step(i):
         eng.search_device(q_dev[i % n_q], filters, K, out_ids, out_sc, out_cnt)
         if world > 1:
-            merger.merge(out_ids, out_sc, out_cnt)
+            merger.merge()                                  # one all_gather_into_tensor + fcb_merge_topk
 
     launches_per_step = 1 + (1 if world > 1 else 0)
 
@@ -267,28 +266,43 @@ def run_b200(args):
     final_ids = (merger.ids if world > 1 else out_ids).cpu().numpy().view(np.uint64)
     final_sc = (merger.scores if world > 1 else out_sc).cpu().numpy()
     assert np.all(np.diff(final_sc, axis=1) <= 0), "scores must be non-increasing"
+    for b in range(B):                                      # every hit belongs to the queried tenant's segment
+        assert np.all((final_ids[b] >= offsets[b]) & (final_ids[b] < offsets[b + 1]))
 
-    # ---- e2e: through the qdrant-shaped adapter, host list in, scored points out (rank-local tenant)
-    client = B200QdrantClient(url="unused")
-    client.attach_collection(col)
-    flt = models.Filter(must=[
-        models.FieldCondition(key="metadata.user_id", match=models.MatchValue(value=col.users[rank])),
-        models.FieldCondition(key="metadata.date", range=models.Range(gte=t_lo))])
-    q_lists = [q_host[s][rank].tolist() for s in range(n_q)]
+    # ---- e2e: through the public API with HOST buffers in and out.
+    #   N=1: B200QdrantClient.query_points (list[float] in, ScoredPoint + payload out).
+    #   N>1: ShardedSearcher.search (numpy batch in, numpy results out; collective on every rank).
+    t_lo_filter = t_lo
     e2e_steps = args.steps
-    for i in range(min(3, args.warmup)):
-        client.query_points("transactions", query=q_lists[i % n_q], limit=K, query_filter=flt)
-    if world > 1:
+    if world == 1:
+        client = B200QdrantClient(url="unused")
+        client.attach_collection(col)
+        flt = models.Filter(must=[
+            models.FieldCondition(key="metadata.user_id", match=models.MatchValue(value=col.users[0])),
+            models.FieldCondition(key="metadata.date", range=models.Range(gte=t_lo_filter))])
+        q_lists = [q_host[s][0].tolist() for s in range(n_q)]
+        for i in range(3):
+            client.query_points("transactions", query=q_lists[i % n_q], limit=K, query_filter=flt)
+        te = time.perf_counter()
+        for i in range(e2e_steps):
+            pts = client.query_points("transactions", query=q_lists[i % n_q], limit=K, query_filter=flt).points
+        te = time.perf_counter() - te
+        assert len(pts) == K
+        e2e_api = "B200QdrantClient.query_points (list[float] in, ScoredPoint+payload out)"
+    else:
+        for i in range(3):
+            searcher.search(q_host[i % n_q], filters, K)
         dist.barrier()
-    te = time.perf_counter()
-    for i in range(e2e_steps):
-        pts = client.query_points("transactions", query=q_lists[i % n_q], limit=K, query_filter=flt).points
-    te = time.perf_counter() - te
+        te = time.perf_counter()
+        for i in range(e2e_steps):
+            r_ids, r_sc, r_cnt = searcher.search(q_host[i % n_q], filters, K)
+        te = time.perf_counter() - te
+        assert int(r_cnt.min()) == K
+        e2e_api = "ShardedSearcher.search (numpy [B,dim] in, numpy ids/scores/counts out, collective)"
     tt = torch.tensor([te], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
     te = float(tt.item())
-    assert len(pts) == K
     kernel_ms_e2e = eng.last_search_ms
 
     if rank != 0:
@@ -301,7 +315,7 @@ def run_b200(args):
     peak, peak_src = measured_peaks()
     seg_rows = rows
     alg_bytes = seg_rows * DIM * 4 + seg_rows * 4              # vectors of passing rows + date predicate column
-    kern_ms = ms_per_step if world == 1 else kernel_ms_e2e     # N>1: the scan alone, from the engine's own events
+    kern_ms = ms_per_step                                      # N>1: scan + all-gather + merge (upper bound on the scan)
     achieved = alg_bytes / (kern_ms / 1e3) / 1e9
     line = {
         "metric": METRIC, "value": qps, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -311,8 +325,8 @@ def run_b200(args):
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": None, "kernel": "scan_topk_kernel<float,4>", "algorithmic_bytes_per_launch": alg_bytes,
                      "kernel_ms": kern_ms, "peak_source": peak_src, "frac_of_nominal_8TBs": achieved / 8000.0},
-        "e2e": {"value": B * e2e_steps / te, "unit": UNIT, "h2d_bytes_per_step": DIM * 8,
-                "d2h_bytes_per_step": K * 16 + 4, "api": "B200QdrantClient.query_points (list[float] in, ScoredPoint+payload out)",
+        "e2e": {"value": B * e2e_steps / te, "unit": UNIT, "h2d_bytes_per_step": B * DIM * 8,
+                "d2h_bytes_per_step": B * (K * 16 + 4), "api": e2e_api,
                 "ms_per_query": 1e3 * te / e2e_steps, "kernel_ms": kernel_ms_e2e},
         "gpu_launches": launches_per_step * args.steps,
         "clocks": clocks,
@@ -328,7 +342,7 @@ def run_b200(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", choices=["b200", "reference"], default="b200")
     ap.add_argument("--rows", type=int, default=ROWS_PER_GPU, help="rows per GPU (default: the BASELINE config)")

@@ -165,6 +165,19 @@ int32_t fcb_aggregate(fcb_engine *e, int64_t seg_begin, int64_t seg_end, int32_t
                       int32_t n_months, int32_t n_categories, int64_t *sums, uint8_t *present,
                       uint64_t *dropped, void *stream);
 
+/* The exchange step of the sharded search (north_star: "each shard computes a local top-k and the
+ * k x shards candidates are merged after a small NCCL allgather"). No counterpart in the
+ * reference, whose Qdrant server merges its own segments internally. Inputs are the
+ * all-gathered per-shard results of fcb_search for the same batch: shard g's ids / scores /
+ * counts start `shard_stride_bytes` * g bytes after shard 0's (device pointers). Each list is
+ * sorted (score desc, id asc) with `counts[b]` valid entries; ids are unique across shards.
+ * Writes the global top-k in the same order and format as fcb_search. Needs no engine and no
+ * scratch. Asynchronous on `stream`. */
+int32_t fcb_merge_topk(int32_t device, const uint64_t *cand_ids, const double *cand_scores,
+                       const int32_t *cand_counts, int64_t shard_stride_bytes, int32_t n_shards,
+                       int32_t batch, int32_t k, uint64_t *out_ids, double *out_scores,
+                       int32_t *out_counts, void *stream);
+
 /* Synthetic corpus (no counterpart in the reference, which has no ingestion code or data —
  * SURVEY.md §2 row 13, §8d): counter-based integer generator, bit-identical to
  * financial-chatbot-llm_b200/synth.py, writing straight into caller-owned device buffers. */

@@ -1,0 +1,111 @@
+"""Host-side logic of the sharded path on CPU: world_size-2 gloo process group, fake per-shard
+engines (numpy scoring through the ORACLE, test only) and a numpy merge injected in place of the
+CUDA merge kernel. Checks the packed buffer layout, the all-gather, shard clipping and that every
+rank ends with the single-shard answer."""
+import os
+import sys
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def numpy_merge(gathered, world, batch, k, merged):
+    from financial_chatbot_llm_b200.sharded import ShardMerger
+    outs = ShardMerger._views(merged, batch, k)
+    for b in range(batch):
+        cand = []
+        for g in range(world):
+            ids, sc, cnt = ShardMerger._views(gathered[g], batch, k)
+            for j in range(int(cnt[b])):
+                cand.append((-float(sc[b, j]), int(ids[b, j]) & (2 ** 64 - 1)))
+        cand.sort()
+        n = min(k, len(cand))
+        outs[2][b] = n
+        for j in range(k):
+            outs[0][b, j] = int(np.array(cand[j][1] if j < n else 2 ** 64 - 1, dtype=np.uint64).view(np.int64))
+            outs[1][b, j] = -cand[j][0] if j < n else -np.inf
+
+
+class FakeEngine:
+    """Per-shard exact search through the C oracle (rows [row_lo,row_hi) of the host corpus)."""
+    def __init__(self, hc, row_lo, row_hi):
+        self.hc, self.row_base, self.n = hc, row_lo, row_hi - row_lo
+        self.dim = hc.spec.dim
+
+    def search_device(self, dq, filters, k, ids, scores, counts, stream=None):
+        from oracle import canon
+        lo, hi = self.row_base, self.row_base + self.n
+        for b, f in enumerate(filters):
+            rb, re_ = max(f.row_begin, lo), min(f.row_end, hi)
+            oi, os_ = (np.zeros(0, np.uint64), np.zeros(0)) if re_ <= rb else canon.search(
+                self.hc.vectors, dq[b].numpy(), k, row_begin=rb, row_end=re_, ids=self.hc.ids,
+                dates=self.hc.dates, date_lo=None if f.date_lo < -2 ** 62 else f.date_lo)
+            counts[b] = len(oi)
+            ids[b, :len(oi)] = torch.from_numpy(oi.view(np.int64))
+            scores[b, :len(oi)] = torch.from_numpy(os_)
+
+
+def worker(rank, world, port, ret):
+    sys.path.insert(0, ROOT)
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from financial_chatbot_llm_b200 import qdrant_models as m
+        from financial_chatbot_llm_b200 import sharded, synth
+        from financial_chatbot_llm_b200.client import Collection
+        from financial_chatbot_llm_b200.engine import make_filter
+        from oracle import canon
+        spec = synth.SynthSpec(n_rows=3000, dim=64, n_users=7, seed=21)
+        hc = synth.make_host_corpus(spec)
+        ranges = sharded.shard_ranges(spec.n_rows, world)
+        lo, hi = ranges[rank]
+        eng = FakeEngine(hc, lo, hi)
+        col = Collection("transactions", eng, hc.users, hc.offsets, hc.payload, n_total_rows=spec.n_rows)
+        dev = torch.device("cpu")
+        s = sharded.ShardedSearcher(col, world, dev, merge_impl=numpy_merge)
+        t0 = int(np.median(hc.dates))
+        qs = np.stack([synth.query_vector(spec, i) for i in range(5)])
+        su = int(np.searchsorted(hc.offsets, ranges[0][1], side="right") - 1)   # the user straddling the cut
+        users = [0, su, 6, 2, 5]
+        fl = [make_filter(int(hc.offsets[u]), int(hc.offsets[u + 1]), t0 if i % 2 else None) for i, u in enumerate(users)]
+        ids, sc, cnt = s.search(qs, fl, 12)
+        ok = True
+        for i, u in enumerate(users):
+            oi, os_ = canon.search(hc.vectors, qs[i], 12, row_begin=int(hc.offsets[u]), row_end=int(hc.offsets[u + 1]),
+                                   ids=hc.ids, dates=hc.dates, date_lo=t0 if i % 2 else None)
+            ok &= ids[i, :cnt[i]].tolist() == oi.tolist() and sc[i, :cnt[i]].tolist() == os_.tolist()
+        straddles = any(hc.offsets[u] < ranges[0][1] < hc.offsets[u + 1] for u in users)
+        # the qdrant-shaped collective call
+        cl = sharded.ShardedB200Client(world, dev, merge_impl=numpy_merge)
+        cl.attach_collection(col)
+        pts = cl.query_points("transactions", query=qs[1].tolist(), limit=5, query_filter=m.Filter(must=[
+            m.FieldCondition(key="metadata.user_id", match=m.MatchValue(value=hc.users[3]))])).points
+        oi, _ = canon.search(hc.vectors, qs[1], 5, row_begin=int(hc.offsets[3]), row_end=int(hc.offsets[4]))
+        ok &= [p.id for p in pts] == oi.tolist() and all(p.payload["metadata"]["user_id"] == hc.users[3] for p in pts)
+        ret[rank] = (bool(ok), bool(straddles))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_world_size_2_gloo_sharded_search(built):
+    world = 2
+    port = 29500 + (os.getpid() % 2000)
+    with mp.Manager() as mgr:
+        ret = mgr.dict()
+        mp.spawn(worker, args=(world, port, ret), nprocs=world, join=True)
+        assert dict(ret) == {0: (True, True), 1: (True, True)}
+
+
+def test_shard_ranges_cover_and_align():
+    from financial_chatbot_llm_b200 import sharded, synth
+    assert sharded.shard_ranges(10, 4) == [(0, 2), (2, 5), (5, 8), (8, 10)]
+    off = synth.segment_offsets(synth.SynthSpec(n_rows=100000, n_users=1000))
+    r = sharded.shard_ranges(100000, 8, off)
+    assert r[0][0] == 0 and r[-1][1] == 100000 and all(a[1] == b[0] for a, b in zip(r, r[1:]))
+    assert all(c in set(off.tolist()) for _, c in r)
+    assert sharded.packed_len(64, 10) == 1312
