@@ -1,0 +1,499 @@
+// Batched dense path of fcb_search (BASELINE config 3): many concurrent queries against ONE shared
+// row range of a bfloat16 shard become a real contraction
+//     S[row, query] = sum_d X[row, d] * Q[query, d]
+// and run on the 5th-generation tensor cores: TMA (cp.async.bulk.tensor, 128-byte swizzle) stages
+// corpus and query tiles in shared memory, one elected thread issues tcgen05.mma (kind::f16,
+// bf16 x bf16 -> fp32) with the accumulators in TMEM, and the epilogue warps read them back with
+// tcgen05.ld and run a fused per-tile top-k filter. The corpus is streamed from HBM exactly once.
+//
+// One CTA per SM (persistent, 384 threads):
+//   warp 0      TMA producer: per k-stage (64 columns) loads two 128-row corpus tiles (A0, A1) and
+//               the 256-query tile (B) into a 3-deep ring (64 KB per stage), mbarrier expect_tx
+//   warp 1      MMA issuer: per stage 4 x UMMA(128x256x16) into accumulator 0 (TMEM cols 0..255)
+//               and 4 into accumulator 1 (cols 256..511), so every B tile read from L2 is used
+//               for 256 corpus rows; tcgen05.commit frees the stage / signals the epilogue
+//   warp 2      TMEM allocation (512 columns) and release
+//   warps 4-11  epilogue: warps 4-7 own accumulator 0, warps 8-11 accumulator 1 (TMEM lane = row).
+//               A thread scales its row's 256 scores by the row's inverse norm and compares each
+//               with that query's current threshold (shared memory); the rare survivors are pushed
+//               to a per-query pending list. After the super-tile, each warp folds the pending
+//               entries of its 32 queries into sorted top-32 lists and raises the thresholds.
+// After the grid finishes, dense_finalize_kernel merges the per-CTA lists per query, re-scores
+// the 32 survivors in float64 against the float64 query (canonical routine), ranks them and
+// writes the result — plus a certificate: the first pass used a bf16-rounded query, so a query is
+// certified only if the worst kept first-pass score lies a safe margin below the k-th exact score
+// (or fewer than 32 rows qualified). Uncertified queries are re-run by the exact fp32-query scan
+// kernel in the same stream (device-side flag, no host round trip).
+#include <cuda.h>
+
+#include "fcb_internal.cuh"
+
+#define DN_THREADS 384
+#define DN_BLOCK_M 128
+#define DN_SUPER_M 256                      // rows per super-tile (two accumulators)
+#define DN_N 256                            // queries per pass (padded with zero rows)
+#define DN_BLOCK_K 64                       // 64 bf16 = 128 bytes = one swizzle atom
+#define DN_STAGES 3
+#define DN_A_BYTES (DN_BLOCK_M * DN_BLOCK_K * 2)      // 16 KB
+#define DN_B_BYTES (DN_N * DN_BLOCK_K * 2)            // 32 KB
+#define DN_STAGE_BYTES (2 * DN_A_BYTES + DN_B_BYTES)  // 64 KB
+#define DN_TMEM_COLS 512
+#define DN_PEND_CAP 256                     // a query can receive at most 256 pushes per super-tile
+#define DN_SPIN_LIMIT (1u << 28)
+#define DN_CERT_MARGIN 1.0e-3               // ~30 sigma of the bf16-query first-pass error at dim 1536
+
+struct DenseParams {
+    const float *inv_norm;
+    const uint32_t *id_rank;
+    const int32_t *dates;
+    const uint8_t *cats;
+    fcb_filter filter;                      // shared by the whole batch
+    int64_t n_rows, row_base;
+    int dim;
+    FcbCand *cta_top;                       // [grid][DN_N][32] sorted per-CTA lists
+    FcbCand *pend;                          // [grid][DN_N][DN_PEND_CAP]
+    int *error_flag;
+};
+
+// ---- PTX wrappers -----------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t *bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile("{\n\t.reg .pred p;\n\t"
+                 "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+                 "selp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+    return ok != 0;
+}
+// bounded wait: a protocol bug must fault the launch, never hang the GPU
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity, int *error_flag, int code) {
+    uint32_t spins = 0;
+    while (!mbar_try_wait(bar, parity)) {
+        if (++spins > DN_SPIN_LIMIT) {
+            atomicExch(error_flag, code);
+            __threadfence_system();
+            asm volatile("trap;");
+        }
+    }
+}
+__device__ __forceinline__ void tma_load_2d(void *dst, const CUtensorMap *map, int c0, int c1, uint64_t *bar, uint64_t hint) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint "
+                 "[%0], [%1, {%3, %4}], [%2], %5;"
+                 ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "l"(hint) : "memory");
+}
+__device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+                 ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t *bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t *v) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+                 "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+                 "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                   "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+                   "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+                   "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+                 : "r"(taddr) : "memory");
+}
+
+// shared-memory matrix descriptor, K-major, 128-byte swizzle (cute::UMMA::SmemDescriptor layout):
+// start>>4 [0,14) | LBO>>4 [16,30) = 1 (unused) | SBO>>4 [32,46) = 1024 B between 8-row groups |
+// version [46,48) = 1 | layout_type [61,64) = 2 (SWIZZLE_128B)
+__device__ __forceinline__ uint64_t make_sw128_desc(uint32_t smem_addr) {
+    return (uint64_t)((smem_addr & 0x3FFFF) >> 4) | ((uint64_t)1 << 16) | ((uint64_t)(1024 >> 4) << 32) |
+           ((uint64_t)1 << 46) | ((uint64_t)2 << 61);
+}
+// instruction descriptor (cute::UMMA::InstrDescriptor): c_format F32 (1) [4,6), a/b format BF16 (1)
+// [7,10) / [10,13), both K-major, N>>3 [17,23), M>>4 [24,29)
+__device__ __forceinline__ constexpr uint32_t make_idesc_bf16(int M, int N) {
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+__device__ __forceinline__ uint32_t dn_tie_key(uint32_t row, const uint32_t *__restrict__ id_rank) {
+    return (row == FCB_NO_ROW || id_rank == nullptr) ? row : id_rank[row];
+}
+__device__ __forceinline__ void dn_insert(float &my_s, uint32_t &my_r, float s, uint32_t r,
+                                          const uint32_t *__restrict__ id_rank, int lane) {
+    bool mine_better = my_s > s;
+    if (my_s == s) mine_better = dn_tie_key(my_r, id_rank) < dn_tie_key(r, id_rank);
+    const int pos = __popc(__ballot_sync(FCB_FULL, mine_better));
+    const float up_s = __shfl_up_sync(FCB_FULL, my_s, 1);
+    const uint32_t up_r = __shfl_up_sync(FCB_FULL, my_r, 1);
+    if (lane == pos) { my_s = s; my_r = r; }
+    else if (lane > pos) { my_s = up_s; my_r = up_r; }
+}
+
+__global__ void __launch_bounds__(DN_THREADS, 1)
+dense_topk_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_q,
+                  const __grid_constant__ DenseParams p) {
+    extern __shared__ __align__(1024) unsigned char smem[];
+    // [stage][A0 | A1 | B] then barriers / bookkeeping
+    uint64_t *full_bar = reinterpret_cast<uint64_t *>(smem + DN_STAGES * DN_STAGE_BYTES);
+    uint64_t *empty_bar = full_bar + DN_STAGES;
+    uint64_t *tmem_full = empty_bar + DN_STAGES;
+    uint64_t *tmem_empty = tmem_full + 1;
+    uint32_t *tmem_ptr = reinterpret_cast<uint32_t *>(tmem_empty + 1);
+    float *thr_s = reinterpret_cast<float *>(tmem_ptr + 2);          // [DN_N]
+    int *cnt_s = reinterpret_cast<int *>(thr_s + DN_N);              // [DN_N]
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const fcb_filter f = p.filter;
+    int64_t lo = f.row_begin - p.row_base, hi = f.row_end - p.row_base;
+    if (lo < 0) lo = 0;
+    if (hi > p.n_rows) hi = p.n_rows;
+    const int64_t nrows = hi > lo ? hi - lo : 0;
+    const int n_super = (int)((nrows + DN_SUPER_M - 1) / DN_SUPER_M);
+    const int k_stages = p.dim / DN_BLOCK_K;
+
+    FcbCand *my_top = p.cta_top + (size_t)blockIdx.x * DN_N * FCB_FUSED_CAND;
+    FcbCand *my_pend = p.pend + (size_t)blockIdx.x * DN_N * DN_PEND_CAP;
+
+    if (warp == 0 && lane == 0) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_x) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_q) : "memory");
+    }
+    if (warp == 1 && lane == 0) {
+        for (int s = 0; s < DN_STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+        mbar_init(tmem_full, 1);
+        mbar_init(tmem_empty, 256);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 2) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_ptr)), "r"(DN_TMEM_COLS) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    for (int i = tid; i < DN_N; i += DN_THREADS) { thr_s[i] = -INFINITY; cnt_s[i] = 0; }
+    for (int i = tid; i < DN_N * FCB_FUSED_CAND; i += DN_THREADS) my_top[i] = FcbCand{-INFINITY, FCB_NO_ROW};
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_base = *tmem_ptr;
+
+    if (warp == 0) {
+        // ================= TMA producer =================
+        if (lane == 0) {
+            const uint64_t hint_stream = 0x12F0000000000000ull;      // evict-first: corpus is read once
+            const uint64_t hint_keep = 0x14F0000000000000ull;        // evict-last: queries are re-read by every tile
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int st = blockIdx.x; st < n_super; st += gridDim.x) {
+                const int row0 = (int)(lo + (int64_t)st * DN_SUPER_M);
+                for (int ks = 0; ks < k_stages; ++ks) {
+                    mbar_wait(&empty_bar[stage], phase ^ 1, p.error_flag, 1);
+                    unsigned char *sp = smem + stage * DN_STAGE_BYTES;
+                    mbar_expect_tx(&full_bar[stage], DN_STAGE_BYTES);
+                    tma_load_2d(sp, &map_x, ks * DN_BLOCK_K, row0, &full_bar[stage], hint_stream);
+                    tma_load_2d(sp + DN_A_BYTES, &map_x, ks * DN_BLOCK_K, row0 + DN_BLOCK_M, &full_bar[stage], hint_stream);
+                    tma_load_2d(sp + 2 * DN_A_BYTES, &map_q, ks * DN_BLOCK_K, 0, &full_bar[stage], hint_keep);
+                    if (++stage == DN_STAGES) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ================= MMA issuer =================
+        if (lane == 0) {
+            const uint32_t idesc = make_idesc_bf16(DN_BLOCK_M, DN_N);
+            int stage = 0;
+            uint32_t phase = 0;
+            int it = 0;
+            for (int st = blockIdx.x; st < n_super; st += gridDim.x, ++it) {
+                mbar_wait(tmem_empty, (it & 1) ^ 1, p.error_flag, 2);             // epilogue drained the accumulators
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                for (int ks = 0; ks < k_stages; ++ks) {
+                    mbar_wait(&full_bar[stage], phase, p.error_flag, 3);
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                    const uint32_t sa = smem_u32(smem + stage * DN_STAGE_BYTES);
+                    const uint64_t a0 = make_sw128_desc(sa), a1 = make_sw128_desc(sa + DN_A_BYTES),
+                                   b = make_sw128_desc(sa + 2 * DN_A_BYTES);
+#pragma unroll
+                    for (int kk = 0; kk < DN_BLOCK_K / 16; ++kk) {                // +32 bytes per UMMA_K: +2 in the >>4 field
+                        umma_bf16(tmem_base, a0 + 2 * kk, b + 2 * kk, idesc, (ks | kk) != 0);
+                        umma_bf16(tmem_base + DN_N, a1 + 2 * kk, b + 2 * kk, idesc, (ks | kk) != 0);
+                    }
+                    umma_commit(&empty_bar[stage]);                              // stage reusable once these MMAs retire
+                    if (++stage == DN_STAGES) { stage = 0; phase ^= 1; }
+                }
+                umma_commit(tmem_full);                                          // accumulators complete
+            }
+        }
+    } else if (warp >= 4) {
+        // ================= epilogue =================
+        const int ew = warp - 4;                           // 0..7
+        const int acc = ew >> 2;                           // accumulator 0 / 1
+        const int lane_row = (warp & 3) * 32 + lane;       // TMEM lane this thread may read
+        const bool has_date = f.date_lo != FCB_DATE_MIN || f.date_hi != FCB_DATE_MAX;
+        const bool has_cat = f.category_mask != FCB_ALL_CATEGORIES;
+        int it = 0;
+        for (int st = blockIdx.x; st < n_super; st += gridDim.x, ++it) {
+            const int64_t row = lo + (int64_t)st * DN_SUPER_M + acc * DN_BLOCK_M + lane_row;
+            bool valid = row < hi;
+            if (valid && has_date) { const int64_t d = p.dates[row]; valid = d >= f.date_lo && d <= f.date_hi; }
+            if (valid && has_cat) { const unsigned c = p.cats[row]; valid = c < 64 && ((f.category_mask >> c) & 1ull); }
+            const float inv = valid ? p.inv_norm[row] : 0.f;
+
+            mbar_wait(tmem_full, it & 1, p.error_flag, 4);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const uint32_t taddr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + acc * DN_N;
+#pragma unroll 1
+            for (int c = 0; c < DN_N; c += 32) {
+                uint32_t v[32];
+                tmem_ld32(taddr + c, v);
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                if (valid) {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {
+                        const float s = __uint_as_float(v[j]) * inv;
+                        if (s >= thr_s[c + j]) {
+                            const int slot = atomicAdd(&cnt_s[c + j], 1);
+                            my_pend[(size_t)(c + j) * DN_PEND_CAP + slot] = FcbCand{s, (uint32_t)row};
+                        }
+                    }
+                }
+            }
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            mbar_arrive(tmem_empty);                                             // MMA may overwrite TMEM
+            __threadfence_block();
+            asm volatile("bar.sync 1, 256;" ::: "memory");
+            // fold pending entries into the sorted per-query lists; warp ew owns queries ew, ew+8, ...
+            for (int q = ew; q < DN_N; q += 8) {
+                const int n = cnt_s[q];
+                if (n == 0) continue;
+                FcbCand e = my_top[(size_t)q * FCB_FUSED_CAND + lane];
+                float thr = __shfl_sync(FCB_FULL, e.score, 31);
+                for (int base = 0; base < n; base += 32) {
+                    FcbCand pe{-INFINITY, FCB_NO_ROW};
+                    if (base + lane < n) pe = my_pend[(size_t)q * DN_PEND_CAP + base + lane];
+                    const int m = n - base < 32 ? n - base : 32;
+                    for (int j = 0; j < m; ++j) {
+                        const float s = __shfl_sync(FCB_FULL, pe.score, j);
+                        const uint32_t r = __shfl_sync(FCB_FULL, pe.row, j);
+                        if (s >= thr) {
+                            dn_insert(e.score, e.row, s, r, p.id_rank, lane);
+                            thr = __shfl_sync(FCB_FULL, e.score, 31);
+                        }
+                    }
+                }
+                my_top[(size_t)q * FCB_FUSED_CAND + lane] = e;
+                if (lane == 31) thr_s[q] = e.score;
+                if (lane == 0) cnt_s[q] = 0;
+            }
+            asm volatile("bar.sync 1, 256;" ::: "memory");
+        }
+    }
+    __syncthreads();
+    if (warp == 2) {
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(DN_TMEM_COLS) : "memory");
+    }
+}
+
+// float64 queries -> bf16 [DN_N, dim], rows >= batch zero
+__global__ void __launch_bounds__(256) dense_pack_queries_kernel(const double *__restrict__ q, int batch, int dim,
+                                                                 __nv_bfloat16 *__restrict__ out) {
+    const int64_t total = (int64_t)DN_N * dim;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int b = (int)(i / dim);
+        out[i] = __float2bfloat16_rn(b < batch ? (float)q[i] : 0.f);
+    }
+}
+
+struct DenseFinalParams {
+    const void *vectors;
+    const uint64_t *ids;
+    const uint32_t *id_rank;
+    const double *queries;
+    const FcbCand *cta_top;
+    int n_lists;
+    int64_t row_base;
+    int dim, k;
+    uint64_t *out_ids;
+    double *out_scores;
+    int32_t *out_counts;
+    int32_t *redo;                          // [batch]: 1 = not certified, re-run exactly
+};
+
+__global__ void __launch_bounds__(256) dense_finalize_kernel(const __grid_constant__ DenseFinalParams p) {
+    __shared__ FcbCand m_s[8][FCB_FUSED_CAND];
+    __shared__ double f_score[FCB_FUSED_CAND];
+    __shared__ uint64_t f_id[FCB_FUSED_CAND];
+    __shared__ double s_kth;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int b = blockIdx.x;
+    const __nv_bfloat16 *vec = reinterpret_cast<const __nv_bfloat16 *>(p.vectors);
+    const double *qd = p.queries + (size_t)b * p.dim;
+    float my_s = -INFINITY;
+    uint32_t my_r = FCB_NO_ROW;
+    for (int L = warp; L < p.n_lists; L += 8) {
+        const FcbCand e = p.cta_top[((size_t)L * DN_N + b) * FCB_FUSED_CAND + lane];
+        float thr = __shfl_sync(FCB_FULL, my_s, 31);
+        for (int i = 0; i < FCB_FUSED_CAND; ++i) {
+            const float s = __shfl_sync(FCB_FULL, e.score, i);
+            const uint32_t r = __shfl_sync(FCB_FULL, e.row, i);
+            if (r == FCB_NO_ROW || !(s >= thr)) break;
+            dn_insert(my_s, my_r, s, r, p.id_rank, lane);
+            thr = __shfl_sync(FCB_FULL, my_s, 31);
+        }
+    }
+    m_s[warp][lane] = FcbCand{my_s, my_r};
+    __syncthreads();
+    if (warp == 0) {
+        for (int w = 1; w < 8; ++w) {
+            const FcbCand e = m_s[w][lane];
+            float thr = __shfl_sync(FCB_FULL, my_s, 31);
+            for (int i = 0; i < FCB_FUSED_CAND; ++i) {
+                const float s = __shfl_sync(FCB_FULL, e.score, i);
+                const uint32_t r = __shfl_sync(FCB_FULL, e.row, i);
+                if (r == FCB_NO_ROW || !(s >= thr)) break;
+                dn_insert(my_s, my_r, s, r, p.id_rank, lane);
+                thr = __shfl_sync(FCB_FULL, my_s, 31);
+            }
+        }
+        m_s[0][lane] = FcbCand{my_s, my_r};
+    }
+    __syncthreads();
+    for (int c = warp; c < FCB_FUSED_CAND; c += 8) {
+        const uint32_t row = m_s[0][c].row;
+        double sc = -INFINITY;
+        uint64_t id = UINT64_MAX;
+        if (row != FCB_NO_ROW) {
+            sc = fcb_canon_score_warp<__nv_bfloat16>(vec + (int64_t)row * p.dim, qd, p.dim, lane);
+            id = p.ids ? p.ids[row] : (uint64_t)(p.row_base + row);
+        }
+        if (lane == 0) { f_score[c] = sc; f_id[c] = id; }
+    }
+    __syncthreads();
+    if (warp == 0) {
+        const bool valid = m_s[0][lane].row != FCB_NO_ROW;
+        const int nvalid = __popc(__ballot_sync(FCB_FULL, valid));
+        const double ms = f_score[lane];
+        const uint64_t mi = f_id[lane];
+        int rank = 0;
+        for (int j = 0; j < FCB_FUSED_CAND; ++j)
+            rank += (m_s[0][j].row != FCB_NO_ROW) && fcb_better64(f_score[j], f_id[j], ms, mi);
+        const int count = nvalid < p.k ? nvalid : p.k;
+        if (valid && rank < p.k) { p.out_ids[(size_t)b * p.k + rank] = mi; p.out_scores[(size_t)b * p.k + rank] = ms; }
+        if (lane >= count && lane < p.k) { p.out_ids[(size_t)b * p.k + lane] = UINT64_MAX; p.out_scores[(size_t)b * p.k + lane] = -INFINITY; }
+        // certificate: the exact k-th score must clear the worst kept first-pass score by the margin
+        if (lane == 0) s_kth = -INFINITY;
+        __syncwarp();
+        if (valid && rank == count - 1) s_kth = ms;
+        __syncwarp();
+        const float worst = __shfl_sync(FCB_FULL, my_s, 31);
+        if (lane == 0) {
+            p.out_counts[b] = count;
+            p.redo[b] = (nvalid == FCB_FUSED_CAND && !((double)worst + DN_CERT_MARGIN < s_kth)) ? 1 : 0;
+        }
+    }
+}
+
+// ---- host side ----------------------------------------------------------------------------------
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                    const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static int32_t encode_map(fcb_engine *e, CUtensorMap *map, const void *base, uint64_t rows, uint64_t dim, uint32_t box_rows) {
+    static PFN_encodeTiled fn = nullptr;
+    if (!fn) {
+        void *sym = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &qres) != cudaSuccess || !sym)
+            return fcb_fail(e, FCB_ERR_CUDA, "cuTensorMapEncodeTiled is not available from the driver");
+        fn = (PFN_encodeTiled)sym;
+    }
+    const cuuint64_t gdim[2] = {dim, rows};
+    const cuuint64_t gstride[1] = {dim * 2};
+    const cuuint32_t box[2] = {DN_BLOCK_K, box_rows};
+    const cuuint32_t estr[2] = {1, 1};
+    const CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void *>(base), gdim, gstride, box, estr,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fcb_fail(e, FCB_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d)", (int)r);
+    return FCB_OK;
+}
+
+struct FcbDense {
+    CUtensorMap map_x, map_q;
+    __nv_bfloat16 *q_bf16 = nullptr;        // [DN_N, dim]
+    FcbCand *cta_top = nullptr, *pend = nullptr;
+    int32_t *redo = nullptr;
+    int *error_flag = nullptr;
+    int grid = 0;
+};
+
+void fcb_dense_free(fcb_engine *e) {
+    FcbDense *d = reinterpret_cast<FcbDense *>(e->dense);
+    if (!d) return;
+    cudaFree(d->q_bf16); cudaFree(d->cta_top); cudaFree(d->pend); cudaFree(d->redo); cudaFree(d->error_flag);
+    delete d;
+    e->dense = nullptr;
+}
+
+bool fcb_dense_eligible(const fcb_engine *e) {
+    const fcb_shard &s = e->shard;
+    return s.dtype == FCB_DTYPE_BF16 && s.dim % DN_BLOCK_K == 0 && e->max_batch >= FCB_DENSE_MIN_BATCH &&
+           s.n_rows < (int64_t)0x7fffff00 && ((uintptr_t)s.vectors & 127) == 0;
+}
+
+int32_t fcb_dense_alloc(fcb_engine *e) {
+    const fcb_shard &s = e->shard;
+    FcbDense *d = new FcbDense();
+    e->dense = d;
+    d->grid = e->num_sms;
+    const size_t lists = (size_t)d->grid * DN_N;
+    if (cudaMalloc(&d->q_bf16, (size_t)DN_N * s.dim * 2) != cudaSuccess ||
+        cudaMalloc(&d->cta_top, lists * FCB_FUSED_CAND * sizeof(FcbCand)) != cudaSuccess ||
+        cudaMalloc(&d->pend, lists * DN_PEND_CAP * sizeof(FcbCand)) != cudaSuccess ||
+        cudaMalloc(&d->redo, (size_t)DN_N * sizeof(int32_t)) != cudaSuccess ||
+        cudaMalloc(&d->error_flag, sizeof(int)) != cudaSuccess) {
+        cudaGetLastError();
+        fcb_dense_free(e);
+        return fcb_fail(e, FCB_ERR_NOMEM, "fcb_load_shard: cannot allocate the batched-path scratch");
+    }
+    FCB_CUDA(e, cudaMemset(d->error_flag, 0, sizeof(int)));
+    int32_t rc = encode_map(e, &d->map_x, s.vectors, (uint64_t)s.n_rows, (uint64_t)s.dim, DN_BLOCK_M);
+    if (rc == FCB_OK) rc = encode_map(e, &d->map_q, d->q_bf16, DN_N, (uint64_t)s.dim, DN_N);
+    if (rc != FCB_OK) { fcb_dense_free(e); return rc; }
+    const size_t smem = (size_t)DN_STAGES * DN_STAGE_BYTES + 4096;
+    FCB_CUDA(e, cudaFuncSetAttribute(dense_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    return FCB_OK;
+}
+
+// Runs the tensor-core pass + finalize for `batch` (<= DN_N) queries sharing filter `f`.
+// `redo_out` receives the device pointer of the per-query "not certified" flags.
+int32_t fcb_search_dense(fcb_engine *e, const double *d_queries, const fcb_filter &f, int32_t batch, int32_t k,
+                         uint64_t *d_out_ids, double *d_out_scores, int32_t *d_out_counts, cudaStream_t st,
+                         const int32_t **redo_out) {
+    FcbDense *d = reinterpret_cast<FcbDense *>(e->dense);
+    const fcb_shard &s = e->shard;
+    if (!d) return fcb_fail(e, FCB_ERR_STATE, "fcb_search: batched path not initialised");
+    dense_pack_queries_kernel<<<e->num_sms, 256, 0, st>>>(d_queries, batch, s.dim, d->q_bf16);
+    DenseParams p{};
+    p.inv_norm = e->inv_norm; p.id_rank = s.id_rank; p.dates = s.dates; p.cats = s.categories; p.filter = f;
+    p.n_rows = s.n_rows; p.row_base = s.row_base; p.dim = s.dim;
+    p.cta_top = d->cta_top; p.pend = d->pend; p.error_flag = d->error_flag;
+    const size_t smem = (size_t)DN_STAGES * DN_STAGE_BYTES + 4096;
+    dense_topk_kernel<<<d->grid, DN_THREADS, smem, st>>>(d->map_x, d->map_q, p);
+    FCB_CUDA(e, cudaGetLastError());
+    DenseFinalParams fp{};
+    fp.vectors = s.vectors; fp.ids = s.ids; fp.id_rank = s.id_rank; fp.queries = d_queries; fp.cta_top = d->cta_top;
+    fp.n_lists = d->grid; fp.row_base = s.row_base; fp.dim = s.dim; fp.k = k;
+    fp.out_ids = d_out_ids; fp.out_scores = d_out_scores; fp.out_counts = d_out_counts; fp.redo = d->redo;
+    dense_finalize_kernel<<<batch, 256, 0, st>>>(fp);
+    FCB_CUDA(e, cudaGetLastError());
+    e->last_launches += 3;
+    *redo_out = d->redo;
+    return FCB_OK;
+}

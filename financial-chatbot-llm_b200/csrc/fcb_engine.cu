@@ -39,6 +39,7 @@ extern "C" int32_t fcb_close(fcb_engine *e) {
         free_host_staging(e);
         cudaFree(e->inv_norm);
         fcb_general_free(e);
+        fcb_dense_free(e);
         cudaFree(e->d_filters);
         cudaFree(e->d_cand);
         cudaFree(e->d_counters);
@@ -167,6 +168,7 @@ extern "C" int32_t fcb_load_shard(fcb_engine *e, const fcb_shard *s) {
     e->loaded = false;
     cudaFree(e->inv_norm); e->inv_norm = nullptr;
     fcb_general_free(e);
+    fcb_dense_free(e);
     free_host_staging(e);
     if (cudaMalloc(&e->inv_norm, (size_t)s->n_rows * sizeof(float)) != cudaSuccess) {
         cudaGetLastError();
@@ -193,6 +195,10 @@ extern "C" int32_t fcb_load_shard(fcb_engine *e, const fcb_shard *s) {
     e->shard = *s;
     if (e->max_k > FCB_FUSED_MAX_K) {
         const int32_t rc = fcb_general_alloc(e);
+        if (rc != FCB_OK) return rc;
+    }
+    if (fcb_dense_eligible(e)) {
+        const int32_t rc = fcb_dense_alloc(e);
         if (rc != FCB_OK) return rc;
     }
     FCB_CUDA(e, cudaStreamSynchronize(e->stream));

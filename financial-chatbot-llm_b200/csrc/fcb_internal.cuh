@@ -17,6 +17,7 @@
 #define FCB_FUSED_MAX_K 16                 // fused path: k + margin(>=16) <= 32
 #define FCB_INLINE_FILTERS 4               // filters passed by value in the kernel parameters
 #define FCB_FILTER_SLOTS 8                 // ring of pinned filter staging slots (batch > inline)
+#define FCB_DENSE_MIN_BATCH 32             // batches at least this large may take the tensor-core path
 #define FCB_NO_ROW 0xffffffffu
 #define FCB_COS_EPS 1.1920929e-7           // zero-norm guard (float32 eps), as in the oracle
 
@@ -62,6 +63,8 @@ struct fcb_engine {
     uint64_t *d_sel_ids = nullptr;         // [kprime_max]
     int kprime_max = 0;
 
+    void *dense = nullptr;                 // FcbDense* (fcb_dense.cu): batched tensor-core path scratch
+
     float last_ms = -1.f;
     int last_launches = 0;
     std::string err;
@@ -78,6 +81,14 @@ int32_t fcb_general_alloc(fcb_engine *e);  // called by fcb_load_shard
 void fcb_general_free(fcb_engine *e);
 int32_t fcb_search_general(fcb_engine *e, const double *d_query, const fcb_filter &f, int32_t k,
                            uint64_t *d_out_ids, double *d_out_scores, int32_t *d_out_count, cudaStream_t st);
+
+// batched tensor-core path (fcb_dense.cu)
+bool fcb_dense_eligible(const fcb_engine *e);
+int32_t fcb_dense_alloc(fcb_engine *e);
+void fcb_dense_free(fcb_engine *e);
+int32_t fcb_search_dense(fcb_engine *e, const double *d_queries, const fcb_filter &f, int32_t batch, int32_t k,
+                         uint64_t *d_out_ids, double *d_out_scores, int32_t *d_out_counts, cudaStream_t st,
+                         const int32_t **redo_out);
 
 // error plumbing (fcb_engine.cu)
 int32_t fcb_fail(fcb_engine *e, int32_t code, const char *fmt, ...);

@@ -26,6 +26,7 @@ struct ScanParams {
     const fcb_filter *filters;             // device copy, used when !use_inline
     fcb_filter inl[FCB_INLINE_FILTERS];
     int use_inline;
+    const int32_t *only_if;                // optional [batch]: run query b only where only_if[b] != 0
     int64_t n_rows, row_base;
     int dim, k;
     FcbCand *cand;
@@ -99,6 +100,7 @@ scan_topk_kernel(const __grid_constant__ ScanParams p) {
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int b = blockIdx.y;
+    if (p.only_if != nullptr && p.only_if[b] == 0) return;      // block-uniform: re-run of uncertified queries only
     const fcb_filter f = p.use_inline ? p.inl[b] : p.filters[b];
     const double *__restrict__ qd = p.queries + (size_t)b * p.dim;
     const uint32_t *__restrict__ id_rank = p.id_rank;
@@ -301,6 +303,26 @@ static int32_t search_device(fcb_engine *e, const double *d_queries, const fcb_f
     p.n_rows = s.n_rows; p.row_base = s.row_base; p.dim = s.dim; p.k = k;
     p.cand = e->d_cand; p.counters = e->d_counters;
     p.out_ids = d_out_ids; p.out_scores = d_out_scores; p.out_counts = d_out_counts;
+
+    // batched dense path: bf16 shard, a large batch whose filters are all the same, a segment big
+    // enough to amortise the tensor-core pipeline. Uncertified queries are re-run by the exact scan below.
+    if (e->dense && batch >= FCB_DENSE_MIN_BATCH && batch <= 256) {
+        bool same = true;
+        for (int b = 1; b < batch && same; ++b) same = memcmp(&h_filters[b], &h_filters[0], sizeof(fcb_filter)) == 0;
+        fcb_filter f0 = h_filters[0];
+        const bool has_date = f0.date_lo != FCB_DATE_MIN || f0.date_hi != FCB_DATE_MAX;
+        const bool has_cat = f0.category_mask != FCB_ALL_CATEGORIES;
+        if ((has_date && !s.dates) || (has_cat && !s.categories) || f0.date_lo > f0.date_hi) f0.row_end = f0.row_begin;
+        int64_t lo = f0.row_begin - s.row_base, hi = f0.row_end - s.row_base;
+        if (lo < 0) lo = 0;
+        if (hi > s.n_rows) hi = s.n_rows;
+        if (same && hi - lo >= 65536) {
+            const int32_t *redo = nullptr;
+            const int32_t rc = fcb_search_dense(e, d_queries, f0, batch, k, d_out_ids, d_out_scores, d_out_counts, st, &redo);
+            if (rc != FCB_OK) return rc;
+            p.only_if = redo;
+        }
+    }
 
     // resolve filters on the host: clip to the shard, reject predicates on absent columns
     fcb_filter *stage = nullptr;
