@@ -497,3 +497,17 @@ int32_t fcb_search_dense(fcb_engine *e, const double *d_queries, const fcb_filte
     *redo_out = d->redo;
     return FCB_OK;
 }
+
+// Measurement aid: how many queries of the last batched-path call were NOT certified by the
+// tensor-core pass and were therefore answered by the exact scan. Synchronises the device.
+extern "C" int32_t fcb_last_dense_redo(fcb_engine *e, int32_t batch) {
+    if (!e || !e->dense || batch < 1 || batch > DN_N) return -1;
+    FcbDeviceGuard g(e->device);
+    FcbDense *d = reinterpret_cast<FcbDense *>(e->dense);
+    int32_t h[DN_N];
+    if (cudaDeviceSynchronize() != cudaSuccess) return -1;
+    if (cudaMemcpy(h, d->redo, (size_t)batch * sizeof(int32_t), cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
+    int32_t n = 0;
+    for (int i = 0; i < batch; ++i) n += h[i] != 0;
+    return n;
+}

@@ -135,6 +135,10 @@ class Engine:
     def last_search_ms(self) -> float:
         return float(self._lib.fcb_last_search_ms(self._h))
 
+    def last_dense_redo(self, batch: int) -> int:
+        """Queries of the last batched tensor-core call answered by the exact re-run (-1: path inactive)."""
+        return int(self._lib.fcb_last_dense_redo(self._h, batch))
+
     @property
     def last_search_launches(self) -> int:
         return int(self._lib.fcb_last_search_launches(self._h))

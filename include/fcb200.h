@@ -146,6 +146,11 @@ int32_t fcb_search_noalloc(int32_t device, const fcb_shard *shard, const double 
  * the engine's stream around the kernels, excluding the copies); < 0 if none. Measurement aid. */
 float fcb_last_search_ms(const fcb_engine *e);
 
+/* Batched tensor-core path only (bf16 shard, batch >= 32, identical filters): number of queries of
+ * the last call that the bf16 first pass could not certify and the exact scan answered instead;
+ * -1 if the path is not active. Synchronises the device. Measurement aid. */
+int32_t fcb_last_dense_redo(fcb_engine *e, int32_t batch);
+
 /* Number of kernels the last fcb_search / fcb_search_host call launched. Measurement aid. */
 int32_t fcb_last_search_launches(const fcb_engine *e);
 

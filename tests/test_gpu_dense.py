@@ -7,7 +7,7 @@ import pytest
 pytestmark = [pytest.mark.gpu, pytest.mark.timeout(300)]
 
 
-def run_case(spec, whale_rows, batches, k=10, date_frac=None, mutate=None):
+def run_case(spec, whale_rows, batches, k=10, date_frac=None, mutate=None, expect_redo=False):
     import torch
     from financial_chatbot_llm_b200 import loader, synth
     from financial_chatbot_llm_b200.engine import Engine, make_filter
@@ -24,6 +24,8 @@ def run_case(spec, whale_rows, batches, k=10, date_frac=None, mutate=None):
         qs = np.stack([synth.query_vector(spec, 1000 + i) for i in range(B)])
         ids, sc, cnt = eng.search_host(qs, [make_filter(rb, re_, dlo, None)] * B, k)
         assert eng.last_search_launches == 4          # pack + tcgen05 pass + finalize + (flag-gated) exact re-run
+        redo = eng.last_dense_redo(B)                 # queries the tensor-core pass could not certify
+        assert (redo > 0) if expect_redo else (redo == 0), redo
         for b in range(B):
             oi, os_ = canon.search(hc.bf16_bits, qs[b], k, row_begin=rb, row_end=re_, ids=hc.ids, dates=hc.dates, date_lo=dlo)
             assert cnt[b] == len(oi) == k
@@ -58,7 +60,7 @@ def test_dense_uncertified_queries_fall_back_to_exact_scan(built):
         hc.bf16_bits[rows] = hc.bf16_bits[best]
         hc.bf16_bits[rows[::2], 5] ^= 1                      # half of them differ in one low bit
         hc.vectors[:] = synth.bf16_bits_to_f32(hc.bf16_bits).reshape(hc.vectors.shape)
-    run_case(spec, 69000, (32,), k=10, mutate=mutate)
+    run_case(spec, 69000, (32,), k=10, mutate=mutate, expect_redo=True)
 
 
 def test_mixed_filters_use_the_grouped_scan(built):
