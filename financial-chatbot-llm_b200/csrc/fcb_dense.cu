@@ -53,6 +53,8 @@ struct DenseParams {
     FcbCand *cta_top;                       // [grid][DN_N][32] sorted per-CTA lists
     FcbCand *pend;                          // [grid][DN_N][DN_PEND_CAP]
     int *error_flag;
+    float *debug_out;                       // diagnostic: raw accumulators [debug_rows, DN_N] (NULL in production)
+    int64_t debug_rows;
 };
 
 // ---- PTX wrappers -----------------------------------------------------------------------------
@@ -253,6 +255,10 @@ dense_topk_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
                 uint32_t v[32];
                 tmem_ld32(taddr + c, v);
                 asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                if (p.debug_out != nullptr && row - lo < p.debug_rows) {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) p.debug_out[(row - lo) * DN_N + c + j] = __uint_as_float(v[j]);
+                }
                 if (valid) {
 #pragma unroll
                     for (int j = 0; j < 32; ++j) {
@@ -391,10 +397,16 @@ __global__ void __launch_bounds__(256) dense_finalize_kernel(const __grid_consta
         __syncwarp();
         if (valid && rank == count - 1) s_kth = ms;
         __syncwarp();
-        const float worst = __shfl_sync(FCB_FULL, my_s, 31);
+        // first-pass scores are dot(x, q_bf16) / |x|: bring the worst kept one to cosine scale with 1 / |q|
+        double qq = 0.0;
+        for (int j = lane; j < p.dim; j += 32) qq = __fma_rn(qd[j], qd[j], qq);
+#pragma unroll
+        for (int off = 16; off >= 1; off >>= 1) qq += __shfl_xor_sync(FCB_FULL, qq, off);
+        const double nq = qq > 0.0 ? sqrt(qq) : 1.0;
+        const double worst = (double)__shfl_sync(FCB_FULL, my_s, 31) / nq;
         if (lane == 0) {
             p.out_counts[b] = count;
-            p.redo[b] = (nvalid == FCB_FUSED_CAND && !((double)worst + DN_CERT_MARGIN < s_kth)) ? 1 : 0;
+            p.redo[b] = (nvalid == FCB_FUSED_CAND && !(worst + DN_CERT_MARGIN < s_kth)) ? 1 : 0;
         }
     }
 }
@@ -473,6 +485,17 @@ int32_t fcb_dense_alloc(fcb_engine *e) {
 
 // Runs the tensor-core pass + finalize for `batch` (<= DN_N) queries sharing filter `f`.
 // `redo_out` receives the device pointer of the per-query "not certified" flags.
+static float *g_debug_out = nullptr;
+static int64_t g_debug_rows = 0;
+
+// Diagnostic: make the next batched-path call also dump the raw tensor-core accumulators of the
+// first `rows` rows of the segment into `out` (device float [rows, 256]); rows = 0 switches it off.
+extern "C" int32_t fcb_debug_dense_dump(float *out, int64_t rows) {
+    g_debug_out = rows > 0 ? out : nullptr;
+    g_debug_rows = rows > 0 ? rows : 0;
+    return FCB_OK;
+}
+
 int32_t fcb_search_dense(fcb_engine *e, const double *d_queries, const fcb_filter &f, int32_t batch, int32_t k,
                          uint64_t *d_out_ids, double *d_out_scores, int32_t *d_out_counts, cudaStream_t st,
                          const int32_t **redo_out) {
@@ -484,6 +507,7 @@ int32_t fcb_search_dense(fcb_engine *e, const double *d_queries, const fcb_filte
     p.inv_norm = e->inv_norm; p.id_rank = s.id_rank; p.dates = s.dates; p.cats = s.categories; p.filter = f;
     p.n_rows = s.n_rows; p.row_base = s.row_base; p.dim = s.dim;
     p.cta_top = d->cta_top; p.pend = d->pend; p.error_flag = d->error_flag;
+    p.debug_out = g_debug_out; p.debug_rows = g_debug_rows;
     const size_t smem = (size_t)DN_STAGES * DN_STAGE_BYTES + 4096;
     dense_topk_kernel<<<d->grid, DN_THREADS, smem, st>>>(d->map_x, d->map_q, p);
     FCB_CUDA(e, cudaGetLastError());

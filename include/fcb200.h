@@ -151,6 +151,11 @@ float fcb_last_search_ms(const fcb_engine *e);
  * -1 if the path is not active. Synchronises the device. Measurement aid. */
 int32_t fcb_last_dense_redo(fcb_engine *e, int32_t batch);
 
+/* Diagnostic for the batched tensor-core path: the next calls also dump the raw accumulators
+ * (un-normalised bf16 dot products) of the first `rows` rows of the segment into `out`
+ * (device float32 [rows, 256]); rows = 0 switches the dump off. Not for production use. */
+int32_t fcb_debug_dense_dump(float *out, int64_t rows);
+
 /* Number of kernels the last fcb_search / fcb_search_host call launched. Measurement aid. */
 int32_t fcb_last_search_launches(const fcb_engine *e);
 
