@@ -25,6 +25,7 @@
 // (or fewer than 32 rows qualified). Uncertified queries are re-run by the exact fp32-query scan
 // kernel in the same stream (device-side flag, no host round trip).
 #include <cuda.h>
+#include <stdlib.h>
 
 #include "fcb_internal.cuh"
 
@@ -40,7 +41,6 @@
 #define DN_TMEM_COLS 512
 #define DN_PEND_CAP 256                     // a query can receive at most 256 pushes per super-tile
 #define DN_SPIN_LIMIT (1u << 28)
-#define DN_CERT_MARGIN 1.0e-3               // ~30 sigma of the bf16-query first-pass error at dim 1536
 
 struct DenseParams {
     const float *inv_norm;
@@ -50,6 +50,8 @@ struct DenseParams {
     fcb_filter filter;                      // shared by the whole batch
     int64_t n_rows, row_base;
     int dim;
+    int n_queries;                          // real queries (columns beyond are zero padding and are ignored)
+    int n_eff;                              // UMMA N = n_queries rounded up to 32
     FcbCand *cta_top;                       // [grid][DN_N][32] sorted per-CTA lists
     FcbCand *pend;                          // [grid][DN_N][DN_PEND_CAP]
     int *error_flag;
@@ -197,7 +199,7 @@ dense_topk_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
                 for (int ks = 0; ks < k_stages; ++ks) {
                     mbar_wait(&empty_bar[stage], phase ^ 1, p.error_flag, 1);
                     unsigned char *sp = smem + stage * DN_STAGE_BYTES;
-                    mbar_expect_tx(&full_bar[stage], DN_STAGE_BYTES);
+                    mbar_expect_tx(&full_bar[stage], 2 * DN_A_BYTES + (uint32_t)p.n_eff * DN_BLOCK_K * 2);
                     tma_load_2d(sp, &map_x, ks * DN_BLOCK_K, row0, &full_bar[stage], hint_stream);
                     tma_load_2d(sp + DN_A_BYTES, &map_x, ks * DN_BLOCK_K, row0 + DN_BLOCK_M, &full_bar[stage], hint_stream);
                     tma_load_2d(sp + 2 * DN_A_BYTES, &map_q, ks * DN_BLOCK_K, 0, &full_bar[stage], hint_keep);
@@ -208,7 +210,7 @@ dense_topk_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
     } else if (warp == 1) {
         // ================= MMA issuer =================
         if (lane == 0) {
-            const uint32_t idesc = make_idesc_bf16(DN_BLOCK_M, DN_N);
+            const uint32_t idesc = make_idesc_bf16(DN_BLOCK_M, p.n_eff);
             int stage = 0;
             uint32_t phase = 0;
             int it = 0;
@@ -250,8 +252,10 @@ dense_topk_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
             mbar_wait(tmem_full, it & 1, p.error_flag, 4);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const uint32_t taddr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + acc * DN_N;
+            // ids ascending with the row (no id_rank): a later row never wins a tie, so ties need not be pushed
+            const bool push_ties = p.id_rank != nullptr;
 #pragma unroll 1
-            for (int c = 0; c < DN_N; c += 32) {
+            for (int c = 0; c < p.n_eff; c += 32) {
                 uint32_t v[32];
                 tmem_ld32(taddr + c, v);
                 asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
@@ -263,7 +267,8 @@ dense_topk_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
 #pragma unroll
                     for (int j = 0; j < 32; ++j) {
                         const float s = __uint_as_float(v[j]) * inv;
-                        if (s >= thr_s[c + j]) {
+                        const float t = thr_s[c + j];
+                        if ((s > t || (push_ties && s == t)) && c + j < p.n_queries) {
                             const int slot = atomicAdd(&cnt_s[c + j], 1);
                             my_pend[(size_t)(c + j) * DN_PEND_CAP + slot] = FcbCand{s, (uint32_t)row};
                         }
@@ -275,7 +280,7 @@ dense_topk_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
             __threadfence_block();
             asm volatile("bar.sync 1, 256;" ::: "memory");
             // fold pending entries into the sorted per-query lists; warp ew owns queries ew, ew+8, ...
-            for (int q = ew; q < DN_N; q += 8) {
+            for (int q = ew; q < p.n_queries; q += 8) {
                 const int n = cnt_s[q];
                 if (n == 0) continue;
                 FcbCand e = my_top[(size_t)q * FCB_FUSED_CAND + lane];
@@ -329,6 +334,7 @@ struct DenseFinalParams {
     double *out_scores;
     int32_t *out_counts;
     int32_t *redo;                          // [batch]: 1 = not certified, re-run exactly
+    int rigorous;                           // 1: Cauchy-Schwarz margin, 0: 8-sigma margin of the rounding model
 };
 
 __global__ void __launch_bounds__(256) dense_finalize_kernel(const __grid_constant__ DenseFinalParams p) {
@@ -397,16 +403,30 @@ __global__ void __launch_bounds__(256) dense_finalize_kernel(const __grid_consta
         __syncwarp();
         if (valid && rank == count - 1) s_kth = ms;
         __syncwarp();
-        // first-pass scores are dot(x, q_bf16) / |x|: bring the worst kept one to cosine scale with 1 / |q|
-        double qq = 0.0;
-        for (int j = lane; j < p.dim; j += 32) qq = __fma_rn(qd[j], qd[j], qq);
+        // First-pass scores are dot(x, q_bf16) / |x|: bring the worst kept one to cosine scale with 1 / |q|.
+        // Error of a first-pass score: |dot(x, q_bf16 - q)| / (|x||q|) <= rho := |q_bf16 - q| / |q| for ANY row
+        // (Cauchy-Schwarz; rho ~ 1.1e-3). For rows not aligned with the rounding-error vector the error behaves
+        // like rho / sqrt(dim); the default margin is 8 standard deviations of that model with a 3x variance
+        // allowance, the rigorous mode uses rho itself (more queries are then re-run by the exact scan).
+        double qq = 0.0, ee = 0.0;
+        for (int j = lane; j < p.dim; j += 32) {
+            const double qv = qd[j];
+            const double er = (double)__bfloat162float(__float2bfloat16_rn((float)qv)) - qv;
+            qq = __fma_rn(qv, qv, qq);
+            ee = __fma_rn(er, er, ee);
+        }
 #pragma unroll
-        for (int off = 16; off >= 1; off >>= 1) qq += __shfl_xor_sync(FCB_FULL, qq, off);
+        for (int off = 16; off >= 1; off >>= 1) {
+            qq += __shfl_xor_sync(FCB_FULL, qq, off);
+            ee += __shfl_xor_sync(FCB_FULL, ee, off);
+        }
         const double nq = qq > 0.0 ? sqrt(qq) : 1.0;
+        const double rho = sqrt(ee) / nq + 1e-6;                      // + float32 accumulation / norm rounding
+        const double margin = p.rigorous ? rho : 8.0 * rho * sqrt(3.0 / (double)p.dim) + 1e-6;
         const double worst = (double)__shfl_sync(FCB_FULL, my_s, 31) / nq;
         if (lane == 0) {
             p.out_counts[b] = count;
-            p.redo[b] = (nvalid == FCB_FUSED_CAND && !(worst + DN_CERT_MARGIN < s_kth)) ? 1 : 0;
+            p.redo[b] = (nvalid == FCB_FUSED_CAND && !(worst + margin < s_kth)) ? 1 : 0;
         }
     }
 }
@@ -437,7 +457,9 @@ static int32_t encode_map(fcb_engine *e, CUtensorMap *map, const void *base, uin
 }
 
 struct FcbDense {
-    CUtensorMap map_x, map_q;
+    CUtensorMap map_x;
+    CUtensorMap map_q[DN_N / 32];           // query tile maps for N = 32, 64, ..., 256
+    int rigorous = 0;
     __nv_bfloat16 *q_bf16 = nullptr;        // [DN_N, dim]
     FcbCand *cta_top = nullptr, *pend = nullptr;
     int32_t *redo = nullptr;
@@ -476,7 +498,10 @@ int32_t fcb_dense_alloc(fcb_engine *e) {
     }
     FCB_CUDA(e, cudaMemset(d->error_flag, 0, sizeof(int)));
     int32_t rc = encode_map(e, &d->map_x, s.vectors, (uint64_t)s.n_rows, (uint64_t)s.dim, DN_BLOCK_M);
-    if (rc == FCB_OK) rc = encode_map(e, &d->map_q, d->q_bf16, DN_N, (uint64_t)s.dim, DN_N);
+    for (int i = 0; i < DN_N / 32 && rc == FCB_OK; ++i)
+        rc = encode_map(e, &d->map_q[i], d->q_bf16, DN_N, (uint64_t)s.dim, 32 * (i + 1));
+    const char *rig = getenv("FCB_DENSE_RIGOROUS");
+    d->rigorous = rig && rig[0] == '1';
     if (rc != FCB_OK) { fcb_dense_free(e); return rc; }
     const size_t smem = (size_t)DN_STAGES * DN_STAGE_BYTES + 4096;
     FCB_CUDA(e, cudaFuncSetAttribute(dense_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -506,15 +531,17 @@ int32_t fcb_search_dense(fcb_engine *e, const double *d_queries, const fcb_filte
     DenseParams p{};
     p.inv_norm = e->inv_norm; p.id_rank = s.id_rank; p.dates = s.dates; p.cats = s.categories; p.filter = f;
     p.n_rows = s.n_rows; p.row_base = s.row_base; p.dim = s.dim;
+    p.n_queries = batch; p.n_eff = ((batch + 31) / 32) * 32;
     p.cta_top = d->cta_top; p.pend = d->pend; p.error_flag = d->error_flag;
     p.debug_out = g_debug_out; p.debug_rows = g_debug_rows;
     const size_t smem = (size_t)DN_STAGES * DN_STAGE_BYTES + 4096;
-    dense_topk_kernel<<<d->grid, DN_THREADS, smem, st>>>(d->map_x, d->map_q, p);
+    dense_topk_kernel<<<d->grid, DN_THREADS, smem, st>>>(d->map_x, d->map_q[p.n_eff / 32 - 1], p);
     FCB_CUDA(e, cudaGetLastError());
     DenseFinalParams fp{};
     fp.vectors = s.vectors; fp.ids = s.ids; fp.id_rank = s.id_rank; fp.queries = d_queries; fp.cta_top = d->cta_top;
     fp.n_lists = d->grid; fp.row_base = s.row_base; fp.dim = s.dim; fp.k = k;
     fp.out_ids = d_out_ids; fp.out_scores = d_out_scores; fp.out_counts = d_out_counts; fp.redo = d->redo;
+    fp.rigorous = d->rigorous;
     dense_finalize_kernel<<<batch, 256, 0, st>>>(fp);
     FCB_CUDA(e, cudaGetLastError());
     e->last_launches += 3;

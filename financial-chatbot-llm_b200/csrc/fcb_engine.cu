@@ -200,6 +200,13 @@ extern "C" int32_t fcb_load_shard(fcb_engine *e, const fcb_shard *s) {
     if (fcb_dense_eligible(e)) {
         const int32_t rc = fcb_dense_alloc(e);
         if (rc != FCB_OK) return rc;
+        // the flag-gated exact re-run gives every (possibly uncertified) query a full wave of CTAs
+        const size_t want = (size_t)e->max_batch * 2 * e->num_sms;
+        if (e->cand_lists < want) {
+            cudaFree(e->d_cand); e->d_cand = nullptr;
+            FCB_CUDA(e, cudaMalloc(&e->d_cand, want * FCB_FUSED_CAND * sizeof(FcbCand)));
+            e->cand_lists = want;
+        }
     }
     FCB_CUDA(e, cudaStreamSynchronize(e->stream));
     e->loaded = true;

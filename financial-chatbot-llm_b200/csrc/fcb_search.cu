@@ -267,7 +267,8 @@ static int32_t launch_fused(fcb_engine *e, ScanParams &p, int batch, int64_t max
     int64_t ctas = (groups + 2 * FCB_SCAN_WARPS - 1) / (2 * FCB_SCAN_WARPS);
     int64_t budget = (int64_t)e->cand_lists / batch;          // cand_lists >= max_batch >= batch
     const int64_t resident = (int64_t)e->num_sms * 2;
-    if (batch == 1 && budget > resident) budget = resident;   // one persistent wave for a lone query
+    // a lone query, or the flag-gated re-run of a few uncertified queries: one persistent wave each
+    if ((batch == 1 || p.only_if != nullptr) && budget > resident) budget = resident;
     if (ctas > budget) ctas = budget;
     if (ctas < 1) ctas = 1;
     const size_t smem = (size_t)p.dim * sizeof(float);
