@@ -11,11 +11,14 @@
 // per-CTA shared-memory cells with native 32-bit atomics: each value is split as
 // v = hi * 65536 + lo with lo in [-32768, 32767], so AGG_TILE <= 32768 rows can never overflow an
 // int32 cell whatever the int32 input; `hi` is zero for |v| < 32768 and then costs nothing.
-// Presence of a group (pandas lists observed groups only, even when their sum is 0) is a bitmap
-// tested before it is set. Cells are flushed to the dense int64 output with one 64-bit global
+// Values with |v| < 2^18 (every realistic amount) take ONE atomic; only larger ones pay the split.
+// Presence of a group (pandas lists observed groups only, even when their sum is 0) is a byte per
+// cell written with plain stores (all writers store 1). Cells are flushed to the dense int64 output with one 64-bit global
 // reduction per non-empty cell; very short pieces skip shared memory and reduce straight to global.
 // The month of a row is a table lookup: day -> month index, built once per CTA in shared memory
 // with the same civil-from-days arithmetic as the oracle.
+#include <stdlib.h>
+
 #include "fcb_internal.cuh"
 
 #define AGG_THREADS 256
@@ -36,6 +39,7 @@ struct AggParams {
     int64_t *sums;                         // [segs, n_categories, n_months]
     uint8_t *present;                      // same shape
     unsigned long long *dropped;           // rows outside the category / month window
+    int64_t small_piece;                   // pieces shorter than this reduce straight to the global cells
 };
 
 // months since 1970-01 of a day number (days since 1970-01-01), proleptic Gregorian
@@ -71,19 +75,43 @@ __device__ __forceinline__ int32_t floor_day(int32_t ts) {
     return d;
 }
 
+// one row into the CTA's shared cells (big pieces) or straight to the global cells (tiny pieces)
+__device__ __forceinline__ void agg_row(const AggParams &p, int32_t v, unsigned cat, int32_t date, bool use_global,
+                                        int32_t *c_lo, int32_t *c_hi, uint8_t *c_present, const uint16_t *month_tab,
+                                        int64_t *out_s, uint8_t *out_p, unsigned &dropped) {
+    const int32_t di = floor_day(date) - p.day0;
+    const unsigned mo = (unsigned)di < (unsigned)p.n_days ? month_tab[di] : 0xffffu;
+    if (cat >= (unsigned)p.n_categories || mo >= (unsigned)p.n_months) { ++dropped; return; }
+    const int cell = cat * p.n_months + mo;
+    if (use_global) {
+        atomicAdd(reinterpret_cast<unsigned long long *>(out_s + cell), (unsigned long long)(long long)v);
+        out_p[cell] = 1;
+        return;
+    }
+    // |v| < 2^18: AGG_TILE (4096) such values cannot overflow an int32 cell -> ONE native 32-bit shared atomic.
+    // Larger values are split v = hi * 65536 + lo16 so that no int32 input can overflow either cell.
+    if (v > -(1 << 18) && v < (1 << 18)) {
+        atomicAdd(&c_lo[cell], v);
+    } else {
+        const int32_t lo16 = (int32_t)(int16_t)(v & 0xffff);
+        atomicAdd(&c_lo[cell], lo16);
+        atomicAdd(&c_hi[cell], (int32_t)(((int64_t)v - lo16) >> 16));
+    }
+    if (!c_present[cell]) c_present[cell] = 1;             // plain byte store: every writer stores the same value
+}
+
 __global__ void __launch_bounds__(AGG_THREADS, 4) aggregate_kernel(const __grid_constant__ AggParams p) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int C = p.n_categories * p.n_months;
     int32_t *c_lo = reinterpret_cast<int32_t *>(smem_raw);             // [C]
     int32_t *c_hi = c_lo + C;                                          // [C]
-    uint32_t *c_present = reinterpret_cast<uint32_t *>(c_hi + C);      // [(C + 31) / 32]
-    uint16_t *month_tab = reinterpret_cast<uint16_t *>(c_present + (C + 31) / 32);   // [n_days]
+    uint16_t *month_tab = reinterpret_cast<uint16_t *>(c_hi + C);      // [n_days]
+    uint8_t *c_present = reinterpret_cast<uint8_t *>(month_tab + ((p.n_days + 1) & ~1));   // [C]
     __shared__ int64_t s_piece[2];
 
     const int tid = threadIdx.x;
     for (int i = tid; i < p.n_days; i += AGG_THREADS) month_tab[i] = (uint16_t)(month_of_day(p.day0 + i) - p.month_lo);
-    for (int i = tid; i < C; i += AGG_THREADS) { c_lo[i] = 0; c_hi[i] = 0; }
-    for (int i = tid; i < (C + 31) / 32; i += AGG_THREADS) c_present[i] = 0;
+    for (int i = tid; i < C; i += AGG_THREADS) { c_lo[i] = 0; c_hi[i] = 0; c_present[i] = 0; }
     __syncthreads();
 
     int64_t R0 = p.seg_offsets[p.seg_begin], R1 = p.seg_offsets[p.seg_end];
@@ -91,12 +119,14 @@ __global__ void __launch_bounds__(AGG_THREADS, 4) aggregate_kernel(const __grid_
     if (R1 > p.row_base + p.n_rows) R1 = p.row_base + p.n_rows;
     const int64_t n_tiles = R1 > R0 ? (R1 - R0 + AGG_TILE - 1) / AGG_TILE : 0;
     unsigned dropped = 0;
+    const int4 *cents4 = reinterpret_cast<const int4 *>(p.cents);
+    const int4 *dates4 = reinterpret_cast<const int4 *>(p.dates);
+    const uchar4 *cats4 = reinterpret_cast<const uchar4 *>(p.cats);
 
     for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x) {
         const int64_t a = R0 + t * AGG_TILE;
         const int64_t b = a + AGG_TILE < R1 ? a + AGG_TILE : R1;
-        // first user whose segment ends after a
-        if (tid == 0) {
+        if (tid == 0) {                                    // first user whose segment ends after a
             int64_t lo = p.seg_begin, hi = p.seg_end - 1;
             while (lo < hi) {
                 const int64_t mid = (lo + hi) >> 1;
@@ -114,39 +144,37 @@ __global__ void __launch_bounds__(AGG_THREADS, 4) aggregate_kernel(const __grid_
             const int64_t pb = uend < b ? uend : b;
             int64_t *out_s = p.sums + (u - p.seg_begin) * (int64_t)C;
             uint8_t *out_p = p.present + (u - p.seg_begin) * (int64_t)C;
-            const bool small = pb - pa < AGG_SMALL_PIECE;
-            for (int64_t r = pa + tid; r < pb; r += AGG_THREADS) {
-                const int64_t lr = r - p.row_base;
-                const int32_t v = p.cents[lr];
-                const unsigned cat = p.cats[lr];
-                const int32_t di = floor_day(p.dates[lr]) - p.day0;
-                const unsigned mo = (unsigned)di < (unsigned)p.n_days ? month_tab[di] : 0xffffu;
-                if (cat >= (unsigned)p.n_categories || mo >= (unsigned)p.n_months) { ++dropped; continue; }
-                const int cell = cat * p.n_months + mo;
-                if (small) {
-                    atomicAdd(reinterpret_cast<unsigned long long *>(out_s + cell), (unsigned long long)(long long)v);
-                    out_p[cell] = 1;
-                } else {
-                    const int32_t lo16 = (int32_t)(int16_t)(v & 0xffff);
-                    const int32_t hi16 = (int32_t)(((int64_t)v - lo16) >> 16);   // [-32768, 32768]
-                    atomicAdd(&c_lo[cell], lo16);
-                    if (hi16) atomicAdd(&c_hi[cell], hi16);
-                    const uint32_t bit = 1u << (cell & 31);
-                    if (!(c_present[cell >> 5] & bit)) atomicOr(&c_present[cell >> 5], bit);
+            const bool small = pb - pa < p.small_piece;
+            // local row range of the piece; quads aligned on the LOCAL row index so the 128-bit loads are aligned
+            const int64_t la = pa - p.row_base, lb = pb - p.row_base;
+            const int64_t q0 = la >> 2, q1 = (lb + 3) >> 2;            // quads [q0, q1) cover [la, lb)
+#pragma unroll 2
+            for (int64_t q = q0 + tid; q < q1; q += AGG_THREADS) {
+                const int64_t r = q << 2;
+                if (r >= la && r + 4 <= lb) {                           // interior quad: three vector loads
+                    const int4 v = __ldg(cents4 + q);
+                    const int4 d = __ldg(dates4 + q);
+                    const uchar4 c = __ldg(cats4 + q);
+                    agg_row(p, v.x, c.x, d.x, small, c_lo, c_hi, c_present, month_tab, out_s, out_p, dropped);
+                    agg_row(p, v.y, c.y, d.y, small, c_lo, c_hi, c_present, month_tab, out_s, out_p, dropped);
+                    agg_row(p, v.z, c.z, d.z, small, c_lo, c_hi, c_present, month_tab, out_s, out_p, dropped);
+                    agg_row(p, v.w, c.w, d.w, small, c_lo, c_hi, c_present, month_tab, out_s, out_p, dropped);
+                } else {                                                // ragged head / tail of the piece
+                    for (int64_t rr = r > la ? r : la; rr < r + 4 && rr < lb; ++rr)
+                        agg_row(p, p.cents[rr], p.cats[rr], p.dates[rr], small, c_lo, c_hi, c_present, month_tab, out_s,
+                                out_p, dropped);
                 }
             }
             if (!small) {
                 __syncthreads();
                 for (int c = tid; c < C; c += AGG_THREADS) {
-                    if (c_present[c >> 5] & (1u << (c & 31))) {
+                    if (c_present[c]) {
                         const long long s = (long long)c_hi[c] * 65536 + c_lo[c];
                         atomicAdd(reinterpret_cast<unsigned long long *>(out_s + c), (unsigned long long)s);
                         out_p[c] = 1;
-                        c_lo[c] = 0; c_hi[c] = 0;
+                        c_lo[c] = 0; c_hi[c] = 0; c_present[c] = 0;
                     }
                 }
-                __syncthreads();
-                for (int i = tid; i < (C + 31) / 32; i += AGG_THREADS) c_present[i] = 0;
                 __syncthreads();
             }
             pa = pb;
@@ -187,7 +215,9 @@ extern "C" int32_t fcb_aggregate(fcb_engine *e, int64_t seg_begin, int64_t seg_e
     p.day0 = first_day_of_month(month_lo);
     p.n_days = first_day_of_month(month_lo + n_months) - p.day0;
     p.sums = sums; p.present = present; p.dropped = (unsigned long long *)dropped;
-    const size_t smem = (size_t)C * 8 + (size_t)((C + 31) / 32) * 4 + (size_t)p.n_days * 2;
+    p.small_piece = AGG_SMALL_PIECE;
+    if (const char *knob = getenv("FCB_AGG_SMALL_PIECE")) p.small_piece = atoll(knob);   // tuning knob
+    const size_t smem = (size_t)C * 8 + (size_t)((p.n_days + 1) & ~1) * 2 + (size_t)C + 16;
     if (smem > 48 * 1024)
         FCB_CUDA(e, cudaFuncSetAttribute(aggregate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     aggregate_kernel<<<e->num_sms * 4, AGG_THREADS, smem, st>>>(p);
