@@ -165,6 +165,49 @@ __device__ __forceinline__ double fcb_canon_score_warp(const T *__restrict__ row
     return __ddiv_rn(dot, __dmul_rn(nr, nq));
 }
 
+// The same canonical score for FOUR rows at once (latency-oriented: the last CTA of the fused scan
+// re-scores 32 survivors with 8 warps). Per row the order of operations is exactly that of
+// fcb_canon_score_warp, so the results are bit-identical; the four chains only interleave. The
+// float64 query is read from shared memory and its sum of squares `qq` (same order: lane-strided
+// fma, xor butterfly) is computed once by the caller. rows[c] == nullptr skips a slot.
+template <typename T>
+__device__ __forceinline__ void fcb_canon_score_warp4(const T *const (&rows)[4], const double *__restrict__ q_s,
+                                                      double qq, int dim, int lane, double (&out)[4]) {
+    double dot[4] = {0.0, 0.0, 0.0, 0.0}, ss[4] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll 4
+    for (int j = lane; j < dim; j += FCB_WARP) {
+        const double qv = q_s[j];
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            const double x = rows[c] ? (double)fcb_to_float(rows[c][j]) : 0.0;
+            dot[c] = __fma_rn(x, qv, dot[c]);
+            ss[c] = __fma_rn(x, x, ss[c]);
+        }
+    }
+    double nq = __dsqrt_rn(qq);
+    if (nq == 0.0) nq = FCB_COS_EPS;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+#pragma unroll
+        for (int off = 16; off >= 1; off >>= 1) {
+            dot[c] = __dadd_rn(dot[c], __shfl_xor_sync(FCB_FULL, dot[c], off));
+            ss[c] = __dadd_rn(ss[c], __shfl_xor_sync(FCB_FULL, ss[c], off));
+        }
+        double nr = __dsqrt_rn(ss[c]);
+        if (nr == 0.0) nr = FCB_COS_EPS;
+        out[c] = __ddiv_rn(dot[c], __dmul_rn(nr, nq));
+    }
+}
+
+// sum of squares of the float64 query in the canonical order (lane-strided fma, xor butterfly)
+__device__ __forceinline__ double fcb_canon_qq_warp(const double *__restrict__ q, int dim, int lane) {
+    double qq = 0.0;
+    for (int j = lane; j < dim; j += FCB_WARP) qq = __fma_rn(q[j], q[j], qq);
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) qq = __dadd_rn(qq, __shfl_xor_sync(FCB_FULL, qq, off));
+    return qq;
+}
+
 // (score desc, id asc)
 __device__ __forceinline__ bool fcb_better64(double s1, uint64_t i1, double s2, uint64_t i2) {
     return s1 > s2 || (s1 == s2 && i1 < i2);

@@ -52,16 +52,30 @@ __device__ __forceinline__ void warp_insert(float &my_s, uint32_t &my_r, float s
     else if (lane > pos) { my_s = up_s; my_r = up_r; }
 }
 
-// Merge a sorted 32-entry list (entry i in lane i of `e`) into the warp's list.
+__device__ __forceinline__ bool cand_better(float s1, uint32_t r1, float s2, uint32_t r2,
+                                            const uint32_t *__restrict__ id_rank) {
+    if (s1 != s2) return s1 > s2;
+    return tie_key(r1, id_rank) < tie_key(r2, id_rank);
+}
+
+// Merge a sorted 32-entry list (entry i in lane i of `e`) into the warp's sorted list: lane i keeps the
+// better of mine[i] and other[31 - i] (a bitonic sequence holding the 32 best of the union), then a
+// 5-step bitonic merge restores best-first order. ~50 instructions instead of up to 32 insertions.
 __device__ __forceinline__ void warp_merge_list(float &my_s, uint32_t &my_r, FcbCand e,
                                                 const uint32_t *__restrict__ id_rank, int lane) {
-    float thr = __shfl_sync(FCB_FULL, my_s, 31);
-    for (int i = 0; i < FCB_FUSED_CAND; ++i) {
-        const float s = __shfl_sync(FCB_FULL, e.score, i);
-        const uint32_t r = __shfl_sync(FCB_FULL, e.row, i);
-        if (r == FCB_NO_ROW || !(s >= thr)) break;      // sorted: nothing further can enter
-        warp_insert(my_s, my_r, s, r, id_rank, lane);
-        thr = __shfl_sync(FCB_FULL, my_s, 31);
+    const float thr = __shfl_sync(FCB_FULL, my_s, 31);
+    const float top = __shfl_sync(FCB_FULL, e.score, 0);
+    const uint32_t top_r = __shfl_sync(FCB_FULL, e.row, 0);
+    if (top_r == FCB_NO_ROW || !(top >= thr)) return;          // nothing in `e` can enter
+    const float os = __shfl_sync(FCB_FULL, e.score, 31 - lane);
+    const uint32_t orow = __shfl_sync(FCB_FULL, e.row, 31 - lane);
+    if (cand_better(os, orow, my_s, my_r, id_rank)) { my_s = os; my_r = orow; }
+#pragma unroll
+    for (int d = 16; d >= 1; d >>= 1) {
+        const float ps = __shfl_xor_sync(FCB_FULL, my_s, d);
+        const uint32_t pr = __shfl_xor_sync(FCB_FULL, my_r, d);
+        const bool want_better = (lane & d) == 0;              // lower lane of the pair keeps the better entry
+        if (cand_better(ps, pr, my_s, my_r, id_rank) == want_better && (ps != my_s || pr != my_r)) { my_s = ps; my_r = pr; }
     }
 }
 
@@ -210,16 +224,31 @@ scan_topk_kernel(const __grid_constant__ ScanParams p) {
     }
     __syncthreads();
 
-    // ---- canonical float64 re-score of the 32 survivors (warp per candidate)
-    for (int c = warp; c < FCB_FUSED_CAND; c += FCB_SCAN_WARPS) {
-        const uint32_t row = m_s[0][c].row;
-        double sc = -INFINITY;
-        uint64_t id = UINT64_MAX;
-        if (row != FCB_NO_ROW) {
-            sc = fcb_canon_score_warp<T>(vec + (int64_t)row * p.dim, qd, p.dim, lane);
-            id = p.ids ? p.ids[row] : (uint64_t)(p.row_base + row);
+    // ---- canonical float64 re-score of the 32 survivors: the float64 query goes to shared memory,
+    //      each warp scores its 4 candidates with interleaved chains (one memory latency, not four)
+    double *qd_s = reinterpret_cast<double *>(smem_raw + (((size_t)p.dim * sizeof(float) + 15) & ~(size_t)15));
+    for (int i = tid; i < p.dim; i += FCB_SCAN_THREADS) qd_s[i] = qd[i];
+    __syncthreads();
+    {
+        const double qq = fcb_canon_qq_warp(qd_s, p.dim, lane);
+        const T *rows4[4];
+        uint32_t rr[4];
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            rr[c] = m_s[0][warp * 4 + c].row;
+            rows4[c] = rr[c] != FCB_NO_ROW ? vec + (int64_t)rr[c] * p.dim : nullptr;
         }
-        if (lane == 0) { f_score[c] = sc; f_id[c] = id; }
+        double sc4[4];
+        fcb_canon_score_warp4<T>(rows4, qd_s, qq, p.dim, lane, sc4);
+        if (lane < 4) {
+            double sc = sc4[0];
+            uint32_t row = rr[0];
+#pragma unroll
+            for (int c = 1; c < 4; ++c) if (lane == c) { sc = sc4[c]; row = rr[c]; }
+            const bool ok = row != FCB_NO_ROW;
+            f_score[warp * 4 + lane] = ok ? sc : -INFINITY;
+            f_id[warp * 4 + lane] = ok ? (p.ids ? p.ids[row] : (uint64_t)(p.row_base + row)) : UINT64_MAX;
+        }
     }
     __syncthreads();
     if (warp == 0) {
@@ -271,7 +300,8 @@ static int32_t launch_fused(fcb_engine *e, ScanParams &p, int batch, int64_t max
     if ((batch == 1 || p.only_if != nullptr) && budget > resident) budget = resident;
     if (ctas > budget) ctas = budget;
     if (ctas < 1) ctas = 1;
-    const size_t smem = (size_t)p.dim * sizeof(float);
+    // float32 query for the scan + float64 query for the last CTA's re-score
+    const size_t smem = (((size_t)p.dim * sizeof(float) + 15) & ~(size_t)15) + (size_t)p.dim * sizeof(double);
     auto kern = scan_topk_kernel<T, R>;
     if (smem > 48 * 1024) FCB_CUDA(e, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     kern<<<dim3((unsigned)ctas, (unsigned)batch), FCB_SCAN_THREADS, smem, st>>>(p);
