@@ -2,7 +2,7 @@
 // the replacement for client.query_points(...).points at reference tools/qdrant_tool.py:147-153.
 //
 // Fused path (k <= FCB_FUSED_MAX_K), ONE kernel per call:
-//   grid = (CTAs per query, batch). Each warp streams groups of R consecutive rows of the
+//   grid = (CTAs per query, batch). Each warp streams groups of R (2..8) consecutive rows of the
 //   user's CSR segment with 128-bit no-allocate loads (HBM-bound: 4*dim bytes per passing row),
 //   the date / category predicate is evaluated per row BEFORE its vector is fetched (rows that
 //   fail cost 5 bytes, not 4*dim), the float32 dot is reduced by warp shuffles, and the warp
@@ -11,6 +11,8 @@
 //   (atomic counter) merges the per-CTA lists, re-scores the 32 survivors in float64 with the
 //   canonical order of operations (bit-identical to oracle/canon.c), ranks them by
 //   (score desc, id asc) and writes the k results. No second launch, no host round trip.
+#include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "fcb_internal.cuh"
@@ -101,113 +103,16 @@ template <> struct RowDot<__nv_bfloat16> {
     }
 };
 
-template <typename T, int R>
-__global__ void __launch_bounds__(FCB_SCAN_THREADS, 2)
-scan_topk_kernel(const __grid_constant__ ScanParams p) {
-    constexpr int VEC = RowDot<T>::VEC;
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    float *q_s = reinterpret_cast<float *>(smem_raw);                 // [dim] float32 query
-    __shared__ FcbCand m_s[FCB_SCAN_WARPS][FCB_FUSED_CAND];
-    __shared__ double f_score[FCB_FUSED_CAND];
-    __shared__ uint64_t f_id[FCB_FUSED_CAND];
-    __shared__ int s_last;
-
+// Tail of the fused scan, executed by the LAST CTA of a query only.
+template <typename T>
+__device__ __noinline__ void scan_tail(const ScanParams &p, int b, unsigned char *smem_raw,
+                                       FcbCand (*m_s)[FCB_FUSED_CAND], double *f_score, uint64_t *f_id) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int b = blockIdx.y;
-    if (p.only_if != nullptr && p.only_if[b] == 0) return;      // block-uniform: re-run of uncertified queries only
-    const fcb_filter f = p.use_inline ? p.inl[b] : p.filters[b];
-    const double *__restrict__ qd = p.queries + (size_t)b * p.dim;
     const uint32_t *__restrict__ id_rank = p.id_rank;
-
-    for (int i = tid; i < p.dim; i += FCB_SCAN_THREADS) q_s[i] = (float)qd[i];
-    __syncthreads();
-
-    int64_t lo = f.row_begin - p.row_base, hi = f.row_end - p.row_base;
-    if (lo < 0) lo = 0;
-    if (hi > p.n_rows) hi = p.n_rows;
-    const int64_t nrows = hi > lo ? hi - lo : 0;
-    const int64_t ngroups = (nrows + R - 1) / R;
-    const bool has_date = f.date_lo != FCB_DATE_MIN || f.date_hi != FCB_DATE_MAX;
-    const bool has_cat = f.category_mask != FCB_ALL_CATEGORIES;
-    const int nv = p.dim / VEC;
+    const double *__restrict__ qd = p.queries + (size_t)b * p.dim;
     const T *__restrict__ vec = reinterpret_cast<const T *>(p.vectors);
-
-    float my_s = -INFINITY;
-    uint32_t my_r = FCB_NO_ROW;
-    float thr = -INFINITY;
-
-    // predicate of row (group g, lane) — evaluated one group ahead of the vector loads
-    auto load_pred = [&](int64_t g, bool &pass, float &inv) {
-        pass = false; inv = 0.f;
-        const int64_t row = lo + g * R + lane;
-        if (lane < R && row < hi) {
-            pass = true;
-            if (has_date) { const int64_t d = p.dates[row]; pass = d >= f.date_lo && d <= f.date_hi; }
-            if (pass && has_cat) { const unsigned c = p.cats[row]; pass = c < 64 && ((f.category_mask >> c) & 1ull); }
-            if (pass) inv = p.inv_norm[row];
-        }
-    };
-
-    const int64_t stride = (int64_t)gridDim.x * FCB_SCAN_WARPS;
-    int64_t g = (int64_t)blockIdx.x * FCB_SCAN_WARPS + warp;
-    bool pass = false; float inv = 0.f;
-    if (g < ngroups) load_pred(g, pass, inv);
-    while (g < ngroups) {
-        const int64_t gn = g + stride;
-        bool npass = false; float ninv = 0.f;
-        if (gn < ngroups) load_pred(gn, npass, ninv);
-
-        const unsigned pm = __ballot_sync(FCB_FULL, pass);
-        if (pm) {
-            const int64_t r0 = lo + g * R;
-            const uint4 *__restrict__ base = reinterpret_cast<const uint4 *>(vec + r0 * (int64_t)p.dim);
-            float acc[R];
-#pragma unroll
-            for (int r = 0; r < R; ++r) acc[r] = 0.f;
-#pragma unroll 4
-            for (int c = lane; c < nv; c += 32) {
-                float qv[VEC];
-#pragma unroll
-                for (int i = 0; i < VEC; i += 4)
-                    *reinterpret_cast<float4 *>(&qv[i]) = *reinterpret_cast<const float4 *>(&q_s[c * VEC + i]);
-#pragma unroll
-                for (int r = 0; r < R; ++r) {
-                    const uint4 v = fcb_ldg_stream(base + (int64_t)r * nv + c, (pm >> r) & 1u);
-                    acc[r] = RowDot<T>::dot(v, qv, acc[r]);
-                }
-            }
-#pragma unroll
-            for (int r = 0; r < R; ++r) acc[r] = fcb_warp_sum(acc[r]);
-#pragma unroll
-            for (int r = 0; r < R; ++r) {
-                const float s = acc[r] * __shfl_sync(FCB_FULL, inv, r);
-                if (((pm >> r) & 1u) && s >= thr) {
-                    warp_insert(my_s, my_r, s, (uint32_t)(r0 + r), id_rank, lane);
-                    thr = __shfl_sync(FCB_FULL, my_s, 31);
-                }
-            }
-        }
-        pass = npass; inv = ninv; g = gn;
-    }
-
-    // ---- CTA merge: 8 warp lists -> warp 0
-    m_s[warp][lane] = FcbCand{my_s, my_r};
-    __syncthreads();
-    if (warp == 0) {
-        for (int w = 1; w < FCB_SCAN_WARPS; ++w) warp_merge_list(my_s, my_r, m_s[w][lane], id_rank, lane);
-        p.cand[((size_t)b * gridDim.x + blockIdx.x) * FCB_FUSED_CAND + lane] = FcbCand{my_s, my_r};
-    }
-    __syncthreads();
-    if (tid == 0) {
-        __threadfence();
-        const unsigned prev = atomicAdd(&p.counters[b], 1u);
-        s_last = (prev == gridDim.x - 1);
-    }
-    __syncthreads();
-    if (!s_last) return;
-    __threadfence();
-
-    // ---- last CTA of this query: merge all per-CTA lists
+    float my_s;
+    uint32_t my_r;
     my_s = -INFINITY; my_r = FCB_NO_ROW;
     const FcbCand *lists = p.cand + (size_t)b * gridDim.x * FCB_FUSED_CAND;
     for (unsigned L = warp; L < gridDim.x; L += FCB_SCAN_WARPS) {
@@ -275,6 +180,124 @@ scan_topk_kernel(const __grid_constant__ ScanParams p) {
     }
 }
 
+#ifndef FCB_SCAN_MINCTAS
+#define FCB_SCAN_MINCTAS 2
+#endif
+
+// R = rows per warp step, U = unroll of the column loop: R * U independent 128-bit loads per lane in
+// flight. The streaming rate of this loop is sensitive to (R, U) — see profiles/r01_summary.md — so the
+// host picks the pair per storage type and dimension (launch_fused) from the instantiated set.
+template <typename T, int R, int U>
+__global__ void __launch_bounds__(FCB_SCAN_THREADS, FCB_SCAN_MINCTAS)
+scan_topk_kernel(const __grid_constant__ ScanParams p) {
+    constexpr int VEC = RowDot<T>::VEC;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    float *q_s = reinterpret_cast<float *>(smem_raw);                 // [dim] float32 query
+    __shared__ FcbCand m_s[FCB_SCAN_WARPS][FCB_FUSED_CAND];
+    __shared__ double f_score[FCB_FUSED_CAND];
+    __shared__ uint64_t f_id[FCB_FUSED_CAND];
+    __shared__ int s_last;
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int b = blockIdx.y;
+    if (p.only_if != nullptr && p.only_if[b] == 0) return;      // block-uniform: re-run of uncertified queries only
+    const fcb_filter f = p.use_inline ? p.inl[b] : p.filters[b];
+    const double *__restrict__ qd = p.queries + (size_t)b * p.dim;
+    const uint32_t *__restrict__ id_rank = p.id_rank;
+
+    for (int i = tid; i < p.dim; i += FCB_SCAN_THREADS) q_s[i] = (float)qd[i];
+    __syncthreads();
+
+    int64_t lo = f.row_begin - p.row_base, hi = f.row_end - p.row_base;
+    if (lo < 0) lo = 0;
+    if (hi > p.n_rows) hi = p.n_rows;
+    const int64_t nrows = hi > lo ? hi - lo : 0;
+    const int64_t ngroups = (nrows + R - 1) / R;
+    const bool has_date = f.date_lo != FCB_DATE_MIN || f.date_hi != FCB_DATE_MAX;
+    const bool has_cat = f.category_mask != FCB_ALL_CATEGORIES;
+    const int nv = p.dim / VEC;
+    const T *__restrict__ vec = reinterpret_cast<const T *>(p.vectors);
+
+    float my_s = -INFINITY;
+    uint32_t my_r = FCB_NO_ROW;
+    float thr = -INFINITY;
+
+    // predicate of row (group g, lane) — evaluated one group ahead of the vector loads
+    auto load_pred = [&](int64_t g, bool &pass, float &inv) {
+        pass = false; inv = 0.f;
+        const int64_t row = lo + g * R + lane;
+        if (lane < R && row < hi) {
+            pass = true;
+            if (has_date) { const int64_t d = p.dates[row]; pass = d >= f.date_lo && d <= f.date_hi; }
+            if (pass && has_cat) { const unsigned c = p.cats[row]; pass = c < 64 && ((f.category_mask >> c) & 1ull); }
+            if (pass) inv = p.inv_norm[row];
+        }
+    };
+
+    const int64_t stride = (int64_t)gridDim.x * FCB_SCAN_WARPS;
+    int64_t g = (int64_t)blockIdx.x * FCB_SCAN_WARPS + warp;
+    bool pass = false; float inv = 0.f;
+    if (g < ngroups) load_pred(g, pass, inv);
+    while (g < ngroups) {
+        const int64_t gn = g + stride;
+        bool npass = false; float ninv = 0.f;
+        if (gn < ngroups) load_pred(gn, npass, ninv);
+
+        const unsigned pm = __ballot_sync(FCB_FULL, pass);
+        if (pm) {
+            const int64_t r0 = lo + g * R;
+            const uint4 *__restrict__ base = reinterpret_cast<const uint4 *>(vec + r0 * (int64_t)p.dim);
+            float acc[R];
+#pragma unroll
+            for (int r = 0; r < R; ++r) acc[r] = 0.f;
+#pragma unroll U
+            for (int c = lane; c < nv; c += 32) {
+                float qv[VEC];
+#pragma unroll
+                for (int i = 0; i < VEC; i += 4)
+                    *reinterpret_cast<float4 *>(&qv[i]) = *reinterpret_cast<const float4 *>(&q_s[c * VEC + i]);
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    const uint4 v = fcb_ldg_stream(base + (int64_t)r * nv + c, (pm >> r) & 1u);
+                    acc[r] = RowDot<T>::dot(v, qv, acc[r]);
+                }
+            }
+#pragma unroll
+            for (int r = 0; r < R; ++r) acc[r] = fcb_warp_sum(acc[r]);
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                const float s = acc[r] * __shfl_sync(FCB_FULL, inv, r);
+                if (((pm >> r) & 1u) && s >= thr) {
+                    warp_insert(my_s, my_r, s, (uint32_t)(r0 + r), id_rank, lane);
+                    thr = __shfl_sync(FCB_FULL, my_s, 31);
+                }
+            }
+        }
+        pass = npass; inv = ninv; g = gn;
+    }
+
+    // ---- CTA merge: 8 warp lists -> warp 0
+    m_s[warp][lane] = FcbCand{my_s, my_r};
+    __syncthreads();
+    if (warp == 0) {
+        for (int w = 1; w < FCB_SCAN_WARPS; ++w) warp_merge_list(my_s, my_r, m_s[w][lane], id_rank, lane);
+        p.cand[((size_t)b * gridDim.x + blockIdx.x) * FCB_FUSED_CAND + lane] = FcbCand{my_s, my_r};
+    }
+    __syncthreads();
+    if (tid == 0) {
+        __threadfence();
+        const unsigned prev = atomicAdd(&p.counters[b], 1u);
+        s_last = (prev == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+
+    // ---- last CTA of this query: merge, re-score, rank, write. Kept out of line so that its register
+    //      needs (float64 chains) do not disturb the allocation / scheduling of the streaming loop above.
+    scan_tail<T>(p, b, smem_raw, m_s, f_score, f_id);
+}
+
 // ---- host side ------------------------------------------------------------------------------
 
 static int32_t check_search_args(fcb_engine *e, const void *queries, const fcb_filter *filters,
@@ -288,26 +311,55 @@ static int32_t check_search_args(fcb_engine *e, const void *queries, const fcb_f
     return FCB_OK;
 }
 
-template <typename T>
-static int32_t launch_fused(fcb_engine *e, ScanParams &p, int batch, int64_t max_rows, cudaStream_t st) {
-    constexpr int R = 4;
+template <typename T, int R, int U>
+static int32_t launch_fused_cfg(fcb_engine *e, ScanParams &p, int batch, int64_t max_rows, cudaStream_t st) {
     const int64_t groups = (max_rows + R - 1) / R;
     // >= 2 groups per warp when the segment allows; never more CTAs than the scratch holds
     int64_t ctas = (groups + 2 * FCB_SCAN_WARPS - 1) / (2 * FCB_SCAN_WARPS);
     int64_t budget = (int64_t)e->cand_lists / batch;          // cand_lists >= max_batch >= batch
-    const int64_t resident = (int64_t)e->num_sms * 2;
+    const int64_t resident = (int64_t)e->num_sms * FCB_SCAN_MINCTAS;
     // a lone query, or the flag-gated re-run of a few uncertified queries: one persistent wave each
     if ((batch == 1 || p.only_if != nullptr) && budget > resident) budget = resident;
     if (ctas > budget) ctas = budget;
     if (ctas < 1) ctas = 1;
     // float32 query for the scan + float64 query for the last CTA's re-score
     const size_t smem = (((size_t)p.dim * sizeof(float) + 15) & ~(size_t)15) + (size_t)p.dim * sizeof(double);
-    auto kern = scan_topk_kernel<T, R>;
+    auto kern = scan_topk_kernel<T, R, U>;
     if (smem > 48 * 1024) FCB_CUDA(e, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     kern<<<dim3((unsigned)ctas, (unsigned)batch), FCB_SCAN_THREADS, smem, st>>>(p);
     FCB_CUDA(e, cudaGetLastError());
     e->last_launches += 1;
     return FCB_OK;
+}
+
+// (R, U) per storage type and row length; FCB_SCAN_CFG="R,U" overrides for tuning runs.
+template <typename T>
+static int32_t launch_fused(fcb_engine *e, ScanParams &p, int batch, int64_t max_rows, cudaStream_t st) {
+    constexpr int VEC = 16 / (int)sizeof(T);
+    const int steps = (p.dim / VEC + 31) / 32;                // column-loop iterations per row
+    // Measured on B200 (profiles/r01_summary.md, "scan loop sweep"): 12 loads in flight per lane stream
+    // fastest; 16 (4x4, 2x8, 8x2 on 6 KB rows) fall off a cliff (10.8 ms vs 8.28 ms on 10M x 1536 fp32).
+    int R, U;
+    if (sizeof(T) == 4) {
+        if (steps % 6 == 0) { R = 2; U = 6; }
+        else if (steps % 3 == 0) { R = 4; U = 3; }
+        else if (steps % 4 == 0) { R = 2; U = 4; }
+        else { R = 4; U = 2; }
+    } else {
+        if (steps % 3 == 0) { R = 4; U = 3; }
+        else if (steps % 2 == 0) { R = 8; U = 2; }
+        else { R = 4; U = 2; }
+    }
+    static int env_r = -1, env_u = -1;
+    if (env_r < 0) {
+        env_r = 0;
+        if (const char *c = getenv("FCB_SCAN_CFG")) sscanf(c, "%d,%d", &env_r, &env_u);
+    }
+    if (env_r > 0) { R = env_r; U = env_u; }
+#define FCB_TRY(r, u) if (R == r && U == u) return launch_fused_cfg<T, r, u>(e, p, batch, max_rows, st)
+    FCB_TRY(2, 4); FCB_TRY(2, 6); FCB_TRY(2, 8); FCB_TRY(4, 2); FCB_TRY(4, 3); FCB_TRY(4, 4); FCB_TRY(8, 2);
+#undef FCB_TRY
+    return launch_fused_cfg<T, 4, 2>(e, p, batch, max_rows, st);
 }
 
 static int32_t search_device(fcb_engine *e, const double *d_queries, const fcb_filter *h_filters, int32_t batch,
