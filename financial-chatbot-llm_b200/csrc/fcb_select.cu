@@ -85,9 +85,9 @@ template <> struct KeyDot<__nv_bfloat16> {
     }
 };
 
-template <typename T>
+// R rows per warp step x U-fold unroll = R * U loads in flight per lane (12 streams fastest, see fcb_search.cu)
+template <typename T, int R, int U>
 __global__ void __launch_bounds__(FCB_SCAN_THREADS, 2) scan_keys_kernel(const __grid_constant__ KeyScanParams p) {
-    constexpr int R = 4;
     constexpr int VEC = KeyDot<T>::VEC;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float *q_s = reinterpret_cast<float *>(smem_raw);
@@ -126,7 +126,7 @@ __global__ void __launch_bounds__(FCB_SCAN_THREADS, 2) scan_keys_kernel(const __
         for (int r = 0; r < R; ++r) acc[r] = 0.f;
         if (pm) {
             const uint4 *__restrict__ base = reinterpret_cast<const uint4 *>(vec + r0 * (int64_t)p.dim);
-#pragma unroll 4
+#pragma unroll U
             for (int c = lane; c < nv; c += 32) {
                 float qv[VEC];
 #pragma unroll
@@ -281,11 +281,17 @@ static int32_t general_impl(fcb_engine *e, const double *d_query, const fcb_filt
         p.vectors = s.vectors; p.inv_norm = e->inv_norm; p.id_rank = s.id_rank; p.dates = s.dates; p.cats = s.categories;
         p.query = d_query; p.filter = f; p.n_rows = s.n_rows; p.row_base = s.row_base; p.dim = s.dim;
         p.keys = e->d_keys; p.state = e->d_sel;
-        const int64_t groups = (n + 3) / 4;
+        const int steps = (s.dim / KeyDot<T>::VEC + 31) / 32;
+        const bool six = steps % 6 == 0 && sizeof(T) == 4, three = steps % 3 == 0;
+        const int R = six ? 2 : 4;
+        const int64_t groups = (n + R - 1) / R;
         int64_t ctas = (groups + 2 * FCB_SCAN_WARPS - 1) / (2 * FCB_SCAN_WARPS);
         if (ctas > 2 * (int64_t)e->num_sms) ctas = 2 * (int64_t)e->num_sms;
         if (ctas < 1) ctas = 1;
-        scan_keys_kernel<T><<<(unsigned)ctas, FCB_SCAN_THREADS, (size_t)s.dim * sizeof(float), st>>>(p);
+        const size_t smem = (size_t)s.dim * sizeof(float);
+        if (six) scan_keys_kernel<T, 2, 6><<<(unsigned)ctas, FCB_SCAN_THREADS, smem, st>>>(p);
+        else if (three) scan_keys_kernel<T, 4, 3><<<(unsigned)ctas, FCB_SCAN_THREADS, smem, st>>>(p);
+        else scan_keys_kernel<T, 4, 2><<<(unsigned)ctas, FCB_SCAN_THREADS, smem, st>>>(p);
         FCB_CUDA(e, cudaGetLastError());
         int64_t sel_ctas = (n + SEL_THREADS * 16 - 1) / (SEL_THREADS * 16);
         if (sel_ctas > 4 * (int64_t)e->num_sms) sel_ctas = 4 * (int64_t)e->num_sms;
