@@ -174,7 +174,7 @@ template <typename T>
 __device__ __forceinline__ void fcb_canon_score_warp4(const T *const (&rows)[4], const double *__restrict__ q_s,
                                                       double qq, int dim, int lane, double (&out)[4]) {
     double dot[4] = {0.0, 0.0, 0.0, 0.0}, ss[4] = {0.0, 0.0, 0.0, 0.0};
-#pragma unroll 4
+#pragma unroll 8
     for (int j = lane; j < dim; j += FCB_WARP) {
         const double qv = q_s[j];
 #pragma unroll
@@ -202,6 +202,7 @@ __device__ __forceinline__ void fcb_canon_score_warp4(const T *const (&rows)[4],
 // sum of squares of the float64 query in the canonical order (lane-strided fma, xor butterfly)
 __device__ __forceinline__ double fcb_canon_qq_warp(const double *__restrict__ q, int dim, int lane) {
     double qq = 0.0;
+#pragma unroll 8
     for (int j = lane; j < dim; j += FCB_WARP) qq = __fma_rn(q[j], q[j], qq);
 #pragma unroll
     for (int off = 16; off >= 1; off >>= 1) qq = __dadd_rn(qq, __shfl_xor_sync(FCB_FULL, qq, off));

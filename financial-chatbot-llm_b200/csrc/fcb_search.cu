@@ -29,6 +29,7 @@ struct ScanParams {
     fcb_filter inl[FCB_INLINE_FILTERS];
     int use_inline;
     const int32_t *only_if;                // optional [batch]: run query b only where only_if[b] != 0
+    unsigned long long *timing;            // diagnostic: %globaltimer at phase boundaries (NULL in production)
     int64_t n_rows, row_base;
     int dim, k;
     FcbCand *cand;
@@ -37,6 +38,14 @@ struct ScanParams {
     double *out_scores;
     int32_t *out_counts;
 };
+
+__device__ __forceinline__ void stamp(const ScanParams &p, int slot) {
+    if (p.timing != nullptr && threadIdx.x == 0) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        p.timing[slot] = t;
+    }
+}
 
 __device__ __forceinline__ uint32_t tie_key(uint32_t row, const uint32_t *__restrict__ id_rank) {
     return (row == FCB_NO_ROW || id_rank == nullptr) ? row : id_rank[row];
@@ -69,6 +78,12 @@ __device__ __forceinline__ void warp_merge_list(float &my_s, uint32_t &my_r, Fcb
     const float top = __shfl_sync(FCB_FULL, e.score, 0);
     const uint32_t top_r = __shfl_sync(FCB_FULL, e.row, 0);
     if (top_r == FCB_NO_ROW || !(top >= thr)) return;          // nothing in `e` can enter
+    const int n_valid = __popc(__ballot_sync(FCB_FULL, e.row != FCB_NO_ROW));
+    if (n_valid <= 3) {                                        // short list (small segments): plain insertions
+        for (int i = 0; i < n_valid; ++i)
+            warp_insert(my_s, my_r, __shfl_sync(FCB_FULL, e.score, i), __shfl_sync(FCB_FULL, e.row, i), id_rank, lane);
+        return;
+    }
     const float os = __shfl_sync(FCB_FULL, e.score, 31 - lane);
     const uint32_t orow = __shfl_sync(FCB_FULL, e.row, 31 - lane);
     if (cand_better(os, orow, my_s, my_r, id_rank)) { my_s = os; my_r = orow; }
@@ -78,6 +93,39 @@ __device__ __forceinline__ void warp_merge_list(float &my_s, uint32_t &my_r, Fcb
         const uint32_t pr = __shfl_xor_sync(FCB_FULL, my_r, d);
         const bool want_better = (lane & d) == 0;              // lower lane of the pair keeps the better entry
         if (cand_better(ps, pr, my_s, my_r, id_rank) == want_better && (ps != my_s || pr != my_r)) { my_s = ps; my_r = pr; }
+    }
+}
+
+// Two independent merges in one instruction stream (no early exits, so the two shuffle chains
+// interleave): used by the last CTA, which has up to 2 * SMs lists to fold.
+__device__ __forceinline__ void warp_merge_list2(float &s0, uint32_t &r0, FcbCand e0, float &s1, uint32_t &r1, FcbCand e1,
+                                                 const uint32_t *__restrict__ id_rank, int lane) {
+    const float o0 = __shfl_sync(FCB_FULL, e0.score, 31 - lane), o1 = __shfl_sync(FCB_FULL, e1.score, 31 - lane);
+    const uint32_t q0 = __shfl_sync(FCB_FULL, e0.row, 31 - lane), q1 = __shfl_sync(FCB_FULL, e1.row, 31 - lane);
+    if (cand_better(o0, q0, s0, r0, id_rank)) { s0 = o0; r0 = q0; }
+    if (cand_better(o1, q1, s1, r1, id_rank)) { s1 = o1; r1 = q1; }
+#pragma unroll
+    for (int d = 16; d >= 1; d >>= 1) {
+        const float p0 = __shfl_xor_sync(FCB_FULL, s0, d), p1 = __shfl_xor_sync(FCB_FULL, s1, d);
+        const uint32_t t0 = __shfl_xor_sync(FCB_FULL, r0, d), t1 = __shfl_xor_sync(FCB_FULL, r1, d);
+        const bool want_better = (lane & d) == 0;
+        if (cand_better(p0, t0, s0, r0, id_rank) == want_better && (p0 != s0 || t0 != r0)) { s0 = p0; r0 = t0; }
+        if (cand_better(p1, t1, s1, r1, id_rank) == want_better && (p1 != s1 || t1 != r1)) { s1 = p1; r1 = t1; }
+    }
+}
+
+// 8 warp lists -> warp 0 through shared memory, as a 3-level tree (3 merges deep instead of 7).
+__device__ __forceinline__ void cta_merge_tree(float &my_s, uint32_t &my_r, FcbCand (*m_s)[FCB_FUSED_CAND],
+                                               const uint32_t *__restrict__ id_rank, int warp, int lane) {
+    m_s[warp][lane] = FcbCand{my_s, my_r};
+    __syncthreads();
+#pragma unroll
+    for (int stride = 1; stride < FCB_SCAN_WARPS; stride <<= 1) {
+        if ((warp & (2 * stride - 1)) == 0) {
+            warp_merge_list(my_s, my_r, m_s[warp + stride][lane], id_rank, lane);
+            m_s[warp][lane] = FcbCand{my_s, my_r};
+        }
+        __syncthreads();
     }
 }
 
@@ -115,19 +163,25 @@ __device__ __noinline__ void scan_tail(const ScanParams &p, int b, unsigned char
     uint32_t my_r;
     my_s = -INFINITY; my_r = FCB_NO_ROW;
     const FcbCand *lists = p.cand + (size_t)b * gridDim.x * FCB_FUSED_CAND;
-    for (unsigned L = warp; L < gridDim.x; L += FCB_SCAN_WARPS) {
-        const uint2 raw = __ldcg(reinterpret_cast<const uint2 *>(lists + (size_t)L * FCB_FUSED_CAND + lane));
-        const FcbCand e{__uint_as_float(raw.x), raw.y};
-        warp_merge_list(my_s, my_r, e, id_rank, lane);
+    {
+        float s1 = -INFINITY;
+        uint32_t r1 = FCB_NO_ROW;
+        unsigned L = warp;
+        for (; L + FCB_SCAN_WARPS < gridDim.x; L += 2 * FCB_SCAN_WARPS) {       // two lists per step
+            const uint2 a = __ldcg(reinterpret_cast<const uint2 *>(lists + (size_t)L * FCB_FUSED_CAND + lane));
+            const uint2 c = __ldcg(reinterpret_cast<const uint2 *>(lists + (size_t)(L + FCB_SCAN_WARPS) * FCB_FUSED_CAND + lane));
+            warp_merge_list2(my_s, my_r, FcbCand{__uint_as_float(a.x), a.y}, s1, r1, FcbCand{__uint_as_float(c.x), c.y},
+                             id_rank, lane);
+        }
+        if (L < gridDim.x) {
+            const uint2 a = __ldcg(reinterpret_cast<const uint2 *>(lists + (size_t)L * FCB_FUSED_CAND + lane));
+            warp_merge_list(my_s, my_r, FcbCand{__uint_as_float(a.x), a.y}, id_rank, lane);
+        }
+        warp_merge_list(my_s, my_r, FcbCand{s1, r1}, id_rank, lane);
     }
     __syncthreads();                       // m_s reuse: every warp finished reading it above
-    m_s[warp][lane] = FcbCand{my_s, my_r};
-    __syncthreads();
-    if (warp == 0) {
-        for (int w = 1; w < FCB_SCAN_WARPS; ++w) warp_merge_list(my_s, my_r, m_s[w][lane], id_rank, lane);
-        m_s[0][lane] = FcbCand{my_s, my_r};
-    }
-    __syncthreads();
+    cta_merge_tree(my_s, my_r, m_s, id_rank, warp, lane);
+    stamp(p, 5);
 
     // ---- canonical float64 re-score of the 32 survivors: the float64 query goes to shared memory,
     //      each warp scores its 4 candidates with interleaved chains (one memory latency, not four)
@@ -144,7 +198,9 @@ __device__ __noinline__ void scan_tail(const ScanParams &p, int b, unsigned char
             rows4[c] = rr[c] != FCB_NO_ROW ? vec + (int64_t)rr[c] * p.dim : nullptr;
         }
         double sc4[4];
+        stamp(p, 6);
         fcb_canon_score_warp4<T>(rows4, qd_s, qq, p.dim, lane, sc4);
+        stamp(p, 7);
         if (lane < 4) {
             double sc = sc4[0];
             uint32_t row = rr[0];
@@ -162,6 +218,7 @@ __device__ __noinline__ void scan_tail(const ScanParams &p, int b, unsigned char
         const double ms = f_score[lane];
         const uint64_t mi = f_id[lane];
         int rank = 0;
+#pragma unroll 8
         for (int j = 0; j < FCB_FUSED_CAND; ++j)
             rank += (m_s[0][j].row != FCB_NO_ROW) && fcb_better64(f_score[j], f_id[j], ms, mi);
         const int count = nvalid < p.k ? nvalid : p.k;
@@ -178,6 +235,7 @@ __device__ __noinline__ void scan_tail(const ScanParams &p, int b, unsigned char
             p.counters[b] = 0;             // ready for the next call
         }
     }
+    stamp(p, 8);
 }
 
 #ifndef FCB_SCAN_MINCTAS
@@ -205,8 +263,10 @@ scan_topk_kernel(const __grid_constant__ ScanParams p) {
     const double *__restrict__ qd = p.queries + (size_t)b * p.dim;
     const uint32_t *__restrict__ id_rank = p.id_rank;
 
+    if (blockIdx.x == 0) stamp(p, 0);
     for (int i = tid; i < p.dim; i += FCB_SCAN_THREADS) q_s[i] = (float)qd[i];
     __syncthreads();
+    if (blockIdx.x == 0) stamp(p, 1);
 
     int64_t lo = f.row_begin - p.row_base, hi = f.row_end - p.row_base;
     if (lo < 0) lo = 0;
@@ -276,13 +336,10 @@ scan_topk_kernel(const __grid_constant__ ScanParams p) {
         pass = npass; inv = ninv; g = gn;
     }
 
-    // ---- CTA merge: 8 warp lists -> warp 0
-    m_s[warp][lane] = FcbCand{my_s, my_r};
-    __syncthreads();
-    if (warp == 0) {
-        for (int w = 1; w < FCB_SCAN_WARPS; ++w) warp_merge_list(my_s, my_r, m_s[w][lane], id_rank, lane);
-        p.cand[((size_t)b * gridDim.x + blockIdx.x) * FCB_FUSED_CAND + lane] = FcbCand{my_s, my_r};
-    }
+    // ---- CTA merge: 8 warp lists -> warp 0 (tree through shared memory)
+    cta_merge_tree(my_s, my_r, m_s, id_rank, warp, lane);
+    if (blockIdx.x == 0) stamp(p, 2);
+    if (warp == 0) p.cand[((size_t)b * gridDim.x + blockIdx.x) * FCB_FUSED_CAND + lane] = FcbCand{my_s, my_r};
     __syncthreads();
     if (tid == 0) {
         __threadfence();
@@ -290,8 +347,10 @@ scan_topk_kernel(const __grid_constant__ ScanParams p) {
         s_last = (prev == gridDim.x - 1);
     }
     __syncthreads();
+    if (blockIdx.x == 0) stamp(p, 3);
     if (!s_last) return;
     __threadfence();
+    stamp(p, 4);
 
     // ---- last CTA of this query: merge, re-score, rank, write. Kept out of line so that its register
     //      needs (float64 chains) do not disturb the allocation / scheduling of the streaming loop above.
@@ -362,6 +421,15 @@ static int32_t launch_fused(fcb_engine *e, ScanParams &p, int batch, int64_t max
     return launch_fused_cfg<T, 4, 2>(e, p, batch, max_rows, st);
 }
 
+static unsigned long long *g_scan_timing = nullptr;
+
+// Diagnostic: the next fused-scan launches write %globaltimer (ns) at nine phase boundaries of
+// query 0 into `buf` (device uint64[9]); NULL switches it off.
+extern "C" int32_t fcb_debug_scan_timing(uint64_t *buf) {
+    g_scan_timing = reinterpret_cast<unsigned long long *>(buf);
+    return FCB_OK;
+}
+
 static int32_t search_device(fcb_engine *e, const double *d_queries, const fcb_filter *h_filters, int32_t batch,
                              int32_t k, uint64_t *d_out_ids, double *d_out_scores, int32_t *d_out_counts,
                              cudaStream_t st) {
@@ -386,6 +454,7 @@ static int32_t search_device(fcb_engine *e, const double *d_queries, const fcb_f
     p.n_rows = s.n_rows; p.row_base = s.row_base; p.dim = s.dim; p.k = k;
     p.cand = e->d_cand; p.counters = e->d_counters;
     p.out_ids = d_out_ids; p.out_scores = d_out_scores; p.out_counts = d_out_counts;
+    p.timing = g_scan_timing;
 
     // batched dense path: bf16 shard, a large batch whose filters are all the same, a segment big
     // enough to amortise the tensor-core pipeline. Uncertified queries are re-run by the exact scan below.

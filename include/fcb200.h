@@ -156,6 +156,12 @@ int32_t fcb_last_dense_redo(fcb_engine *e, int32_t batch);
  * (device float32 [rows, 256]); rows = 0 switches the dump off. Not for production use. */
 int32_t fcb_debug_dense_dump(float *out, int64_t rows);
 
+/* Diagnostic for the fused scan: while `buf` (device uint64[9]) is set, every launch writes the GPU
+ * global timer (ns) at nine phase boundaries of query 0 (kernel start, query staged, scan done,
+ * CTA list written, last CTA starts, lists merged, re-score starts / ends, results written).
+ * NULL switches it off. Not for production use. */
+int32_t fcb_debug_scan_timing(uint64_t *buf);
+
 /* Number of kernels the last fcb_search / fcb_search_host call launched. Measurement aid. */
 int32_t fcb_last_search_launches(const fcb_engine *e);
 
