@@ -72,8 +72,12 @@ static int32_t open_impl(fcb_engine *e, const fcb_config *cfg) {
     const size_t nf = (size_t)FCB_FILTER_SLOTS * e->max_batch;
     FCB_CUDA(e, cudaMalloc(&e->d_filters, nf * sizeof(fcb_filter)));
     FCB_CUDA(e, cudaMallocHost(&e->h_filters, nf * sizeof(fcb_filter)));
-    // fused path: one list per CTA; the launch never uses more than max(8 * SMs, max_batch) CTAs
-    e->cand_lists = (size_t)8 * e->num_sms;
+    // fused path: one 256-byte list per CTA. Every query of a batch may get a full persistent wave
+    // (2 CTAs per SM) when its segment is large — e.g. one resident whale per shard in a sharded batch —
+    // so size for max_batch full waves, capped at 64 Ki lists (16 MB).
+    e->cand_lists = (size_t)e->max_batch * 2 * e->num_sms;
+    if (e->cand_lists > 65536) e->cand_lists = 65536;
+    if (e->cand_lists < (size_t)8 * e->num_sms) e->cand_lists = (size_t)8 * e->num_sms;
     if (e->cand_lists < (size_t)e->max_batch) e->cand_lists = e->max_batch;
     FCB_CUDA(e, cudaMalloc(&e->d_cand, e->cand_lists * FCB_FUSED_CAND * sizeof(FcbCand)));
     FCB_CUDA(e, cudaMalloc(&e->d_counters, (size_t)e->max_batch * sizeof(unsigned)));
@@ -200,13 +204,6 @@ extern "C" int32_t fcb_load_shard(fcb_engine *e, const fcb_shard *s) {
     if (fcb_dense_eligible(e)) {
         const int32_t rc = fcb_dense_alloc(e);
         if (rc != FCB_OK) return rc;
-        // the flag-gated exact re-run gives every (possibly uncertified) query a full wave of CTAs
-        const size_t want = (size_t)e->max_batch * 2 * e->num_sms;
-        if (e->cand_lists < want) {
-            cudaFree(e->d_cand); e->d_cand = nullptr;
-            FCB_CUDA(e, cudaMalloc(&e->d_cand, want * FCB_FUSED_CAND * sizeof(FcbCand)));
-            e->cand_lists = want;
-        }
     }
     FCB_CUDA(e, cudaStreamSynchronize(e->stream));
     e->loaded = true;

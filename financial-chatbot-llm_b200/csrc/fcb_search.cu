@@ -377,8 +377,9 @@ static int32_t launch_fused_cfg(fcb_engine *e, ScanParams &p, int batch, int64_t
     int64_t ctas = (groups + 2 * FCB_SCAN_WARPS - 1) / (2 * FCB_SCAN_WARPS);
     int64_t budget = (int64_t)e->cand_lists / batch;          // cand_lists >= max_batch >= batch
     const int64_t resident = (int64_t)e->num_sms * FCB_SCAN_MINCTAS;
-    // a lone query, or the flag-gated re-run of a few uncertified queries: one persistent wave each
-    if ((batch == 1 || p.only_if != nullptr) && budget > resident) budget = resident;
+    // the grid is (CTAs per query, batch); queries whose segment misses this shard, or that the dense
+    // pass already certified, leave at once, so a large segment always gets up to one persistent wave
+    if (budget > resident) budget = resident;
     if (ctas > budget) ctas = budget;
     if (ctas < 1) ctas = 1;
     // float32 query for the scan + float64 query for the last CTA's re-score
