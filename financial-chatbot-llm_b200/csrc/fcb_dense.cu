@@ -311,6 +311,222 @@ dense_topk_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
     }
 }
 
+// ---------------------------------------------------------------------------------------------------
+// cta_group::2 variant: two CTAs of a cluster (an SM pair) run ONE 256-row UMMA per instruction. Each
+// CTA stages its own 128-row corpus tiles but only HALF of the query tile (the pair's MMA reads both
+// halves), and keeps two accumulators, so a query tile read from L2 now serves 512 corpus rows: the
+// L2->SM traffic per corpus byte drops from 1.0 to 0.5 byte — the bound of the 1-CTA kernel
+// (profiles/r01_summary.md). 4 stages of 48 KB. The leader CTA (cluster rank 0) issues every MMA; TMA
+// loads of both CTAs complete on the leader's full barrier; tcgen05.commit multicasts the stage-free
+// and accumulators-ready arrivals to both CTAs; both epilogues arrive remotely on the leader's
+// accumulators-drained barrier.
+#define DN2_STAGES 4
+#define DN2_STAGE_BYTES (2 * DN_A_BYTES + DN_B_BYTES / 2)   // 48 KB: A0, A1, half of B (max N = 256)
+#define DN2_SUPER_M 512
+
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tma_load_2d_2sm(void *dst, const CUtensorMap *map, int c0, int c1, uint64_t *bar, uint64_t hint) {
+    // executed by both CTAs; the peer bit of the barrier address is cleared so the bytes complete on CTA 0's barrier
+    asm volatile("cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint "
+                 "[%0], [%1, {%3, %4}], [%2], %5;"
+                 ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar) & 0xFEFFFFFFu), "r"(c0), "r"(c1), "l"(hint) : "memory");
+}
+__device__ __forceinline__ void umma_bf16_2sm(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                 "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+                 ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_commit_2sm(uint64_t *bar) {       // arrive on this barrier in BOTH CTAs of the pair
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(smem_u32(bar)), "h"((uint16_t)3) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_cta0(uint64_t *bar) {     // arrive on CTA 0's copy of the barrier
+    asm volatile("{\n\t.reg .b32 ra;\n\tmapa.shared::cluster.u32 ra, %0, %1;\n\t"
+                 "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n\t}"
+                 ::"r"(smem_u32(bar)), "r"(0) : "memory");
+}
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(DN_THREADS, 1)
+dense_topk2_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_q,
+                   const __grid_constant__ DenseParams p) {
+    extern __shared__ __align__(1024) unsigned char smem[];
+    uint64_t *full_bar = reinterpret_cast<uint64_t *>(smem + DN2_STAGES * DN2_STAGE_BYTES);
+    uint64_t *empty_bar = full_bar + DN2_STAGES;
+    uint64_t *tmem_full = empty_bar + DN2_STAGES;
+    uint64_t *tmem_empty = tmem_full + 1;
+    uint32_t *tmem_ptr = reinterpret_cast<uint32_t *>(tmem_empty + 1);
+    float *thr_s = reinterpret_cast<float *>(tmem_ptr + 2);          // [DN_N]
+    int *cnt_s = reinterpret_cast<int *>(thr_s + DN_N);              // [DN_N]
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const uint32_t cta_rank = cluster_ctarank();
+    const bool leader = cta_rank == 0;
+    const int pair = blockIdx.x >> 1, n_pairs = gridDim.x >> 1;
+    const fcb_filter f = p.filter;
+    int64_t lo = f.row_begin - p.row_base, hi = f.row_end - p.row_base;
+    if (lo < 0) lo = 0;
+    if (hi > p.n_rows) hi = p.n_rows;
+    const int64_t nrows = hi > lo ? hi - lo : 0;
+    const int n_super = (int)((nrows + DN2_SUPER_M - 1) / DN2_SUPER_M);
+    const int k_stages = p.dim / DN_BLOCK_K;
+    const int n_half = p.n_eff / 2;                                    // query rows this CTA stages
+
+    FcbCand *my_top = p.cta_top + (size_t)blockIdx.x * DN_N * FCB_FUSED_CAND;
+    FcbCand *my_pend = p.pend + (size_t)blockIdx.x * DN_N * DN_PEND_CAP;
+
+    if (warp == 0 && lane == 0) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_x) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_q) : "memory");
+    }
+    if (warp == 1 && lane == 0) {
+        for (int s = 0; s < DN2_STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+        mbar_init(tmem_full, 1);
+        mbar_init(tmem_empty, 512);                                    // 256 epilogue threads of each CTA
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 2) {
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_ptr)), "r"(DN_TMEM_COLS) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    }
+    for (int i = tid; i < DN_N; i += DN_THREADS) { thr_s[i] = -INFINITY; cnt_s[i] = 0; }
+    for (int i = tid; i < DN_N * FCB_FUSED_CAND; i += DN_THREADS) my_top[i] = FcbCand{-INFINITY, FCB_NO_ROW};
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    cluster_sync_all();                                                // barriers + TMEM of both CTAs are ready
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_base = *tmem_ptr;
+
+    if (warp == 0) {
+        // ================= TMA producer (both CTAs) =================
+        if (lane == 0) {
+            const uint64_t hint_stream = 0x12F0000000000000ull, hint_keep = 0x14F0000000000000ull;
+            const uint32_t stage_tx = 2u * (2u * DN_A_BYTES + (uint32_t)n_half * DN_BLOCK_K * 2u);   // both CTAs' bytes
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int st = pair; st < n_super; st += n_pairs) {
+                const int row0 = (int)(lo + (int64_t)st * DN2_SUPER_M) + (int)cta_rank * DN_BLOCK_M;
+                for (int ks = 0; ks < k_stages; ++ks) {
+                    mbar_wait(&empty_bar[stage], phase ^ 1, p.error_flag, 11);
+                    unsigned char *sp = smem + stage * DN2_STAGE_BYTES;
+                    if (leader) mbar_expect_tx(&full_bar[stage], stage_tx);
+                    tma_load_2d_2sm(sp, &map_x, ks * DN_BLOCK_K, row0, &full_bar[stage], hint_stream);
+                    tma_load_2d_2sm(sp + DN_A_BYTES, &map_x, ks * DN_BLOCK_K, row0 + 256, &full_bar[stage], hint_stream);
+                    tma_load_2d_2sm(sp + 2 * DN_A_BYTES, &map_q, ks * DN_BLOCK_K, (int)cta_rank * n_half, &full_bar[stage], hint_keep);
+                    if (++stage == DN2_STAGES) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ================= MMA issuer (leader CTA only) =================
+        if (leader && lane == 0) {
+            const uint32_t idesc = make_idesc_bf16(2 * DN_BLOCK_M, p.n_eff);
+            int stage = 0;
+            uint32_t phase = 0;
+            int it = 0;
+            for (int st = pair; st < n_super; st += n_pairs, ++it) {
+                mbar_wait(tmem_empty, (it & 1) ^ 1, p.error_flag, 12);
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                for (int ks = 0; ks < k_stages; ++ks) {
+                    mbar_wait(&full_bar[stage], phase, p.error_flag, 13);
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                    const uint32_t sa = smem_u32(smem + stage * DN2_STAGE_BYTES);
+                    const uint64_t a0 = make_sw128_desc(sa), a1 = make_sw128_desc(sa + DN_A_BYTES),
+                                   b = make_sw128_desc(sa + 2 * DN_A_BYTES);
+#pragma unroll
+                    for (int kk = 0; kk < DN_BLOCK_K / 16; ++kk) {
+                        umma_bf16_2sm(tmem_base, a0 + 2 * kk, b + 2 * kk, idesc, (ks | kk) != 0);
+                        umma_bf16_2sm(tmem_base + DN_N, a1 + 2 * kk, b + 2 * kk, idesc, (ks | kk) != 0);
+                    }
+                    umma_commit_2sm(&empty_bar[stage]);
+                    if (++stage == DN2_STAGES) { stage = 0; phase ^= 1; }
+                }
+                umma_commit_2sm(tmem_full);
+            }
+        }
+    } else if (warp >= 4) {
+        // ================= epilogue (both CTAs; TMEM lane = row of this CTA's half) =================
+        const int ew = warp - 4;
+        const int acc = ew >> 2;
+        const int lane_row = (warp & 3) * 32 + lane;
+        const bool has_date = f.date_lo != FCB_DATE_MIN || f.date_hi != FCB_DATE_MAX;
+        const bool has_cat = f.category_mask != FCB_ALL_CATEGORIES;
+        const bool push_ties = p.id_rank != nullptr;
+        int it = 0;
+        for (int st = pair; st < n_super; st += n_pairs, ++it) {
+            const int64_t row = lo + (int64_t)st * DN2_SUPER_M + acc * 256 + (int)cta_rank * DN_BLOCK_M + lane_row;
+            bool valid = row < hi;
+            if (valid && has_date) { const int64_t d = p.dates[row]; valid = d >= f.date_lo && d <= f.date_hi; }
+            if (valid && has_cat) { const unsigned c = p.cats[row]; valid = c < 64 && ((f.category_mask >> c) & 1ull); }
+            const float inv = valid ? p.inv_norm[row] : 0.f;
+
+            mbar_wait(tmem_full, it & 1, p.error_flag, 14);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const uint32_t taddr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + acc * DN_N;
+#pragma unroll 1
+            for (int c = 0; c < p.n_eff; c += 32) {
+                uint32_t v[32];
+                tmem_ld32(taddr + c, v);
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                if (p.debug_out != nullptr && row - lo < p.debug_rows) {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) p.debug_out[(row - lo) * DN_N + c + j] = __uint_as_float(v[j]);
+                }
+                if (valid) {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {
+                        const float s = __uint_as_float(v[j]) * inv;
+                        const float t = thr_s[c + j];
+                        if ((s > t || (push_ties && s == t)) && c + j < p.n_queries) {
+                            const int slot = atomicAdd(&cnt_s[c + j], 1);
+                            my_pend[(size_t)(c + j) * DN_PEND_CAP + slot] = FcbCand{s, (uint32_t)row};
+                        }
+                    }
+                }
+            }
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            mbar_arrive_cta0(tmem_empty);                              // the leader's MMA may overwrite both TMEMs
+            __threadfence_block();
+            asm volatile("bar.sync 1, 256;" ::: "memory");
+            for (int q = ew; q < p.n_queries; q += 8) {
+                const int n = cnt_s[q];
+                if (n == 0) continue;
+                FcbCand e = my_top[(size_t)q * FCB_FUSED_CAND + lane];
+                float thr = __shfl_sync(FCB_FULL, e.score, 31);
+                for (int base = 0; base < n; base += 32) {
+                    FcbCand pe{-INFINITY, FCB_NO_ROW};
+                    if (base + lane < n) pe = my_pend[(size_t)q * DN_PEND_CAP + base + lane];
+                    const int m = n - base < 32 ? n - base : 32;
+                    for (int j = 0; j < m; ++j) {
+                        const float s = __shfl_sync(FCB_FULL, pe.score, j);
+                        const uint32_t r = __shfl_sync(FCB_FULL, pe.row, j);
+                        if (s >= thr) {
+                            dn_insert(e.score, e.row, s, r, p.id_rank, lane);
+                            thr = __shfl_sync(FCB_FULL, e.score, 31);
+                        }
+                    }
+                }
+                my_top[(size_t)q * FCB_FUSED_CAND + lane] = e;
+                if (lane == 31) thr_s[q] = e.score;
+                if (lane == 0) cnt_s[q] = 0;
+            }
+            asm volatile("bar.sync 1, 256;" ::: "memory");
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    cluster_sync_all();                                                // nobody still targets the peer's barriers / TMEM
+    if (warp == 2) {
+        asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(DN_TMEM_COLS) : "memory");
+    }
+}
+
 // float64 queries -> bf16 [DN_N, dim], rows >= batch zero
 __global__ void __launch_bounds__(256) dense_pack_queries_kernel(const double *__restrict__ q, int batch, int dim,
                                                                  __nv_bfloat16 *__restrict__ out) {
@@ -458,8 +674,10 @@ static int32_t encode_map(fcb_engine *e, CUtensorMap *map, const void *base, uin
 
 struct FcbDense {
     CUtensorMap map_x;
-    CUtensorMap map_q[DN_N / 32];           // query tile maps for N = 32, 64, ..., 256
+    CUtensorMap map_q[DN_N / 32];           // query tile maps for N = 32, 64, ..., 256 (box rows = N)
+    CUtensorMap map_qh[DN_N / 32];          // ... box rows = N / 2 for the cta_group::2 kernel
     int rigorous = 0;
+    int two_cta = 1;
     __nv_bfloat16 *q_bf16 = nullptr;        // [DN_N, dim]
     FcbCand *cta_top = nullptr, *pend = nullptr;
     int32_t *redo = nullptr;
@@ -500,11 +718,17 @@ int32_t fcb_dense_alloc(fcb_engine *e) {
     int32_t rc = encode_map(e, &d->map_x, s.vectors, (uint64_t)s.n_rows, (uint64_t)s.dim, DN_BLOCK_M);
     for (int i = 0; i < DN_N / 32 && rc == FCB_OK; ++i)
         rc = encode_map(e, &d->map_q[i], d->q_bf16, DN_N, (uint64_t)s.dim, 32 * (i + 1));
+    for (int i = 0; i < DN_N / 32 && rc == FCB_OK; ++i)
+        rc = encode_map(e, &d->map_qh[i], d->q_bf16, DN_N, (uint64_t)s.dim, 16 * (i + 1));
     const char *rig = getenv("FCB_DENSE_RIGOROUS");
     d->rigorous = rig && rig[0] == '1';
+    const char *one = getenv("FCB_DENSE_1CTA");                     // tuning / fallback switch
+    d->two_cta = !(one && one[0] == '1') && (d->grid % 2 == 0);
     if (rc != FCB_OK) { fcb_dense_free(e); return rc; }
     const size_t smem = (size_t)DN_STAGES * DN_STAGE_BYTES + 4096;
     FCB_CUDA(e, cudaFuncSetAttribute(dense_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const size_t smem2 = (size_t)DN2_STAGES * DN2_STAGE_BYTES + 4096;
+    FCB_CUDA(e, cudaFuncSetAttribute(dense_topk2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
     return FCB_OK;
 }
 
@@ -535,7 +759,12 @@ int32_t fcb_search_dense(fcb_engine *e, const double *d_queries, const fcb_filte
     p.cta_top = d->cta_top; p.pend = d->pend; p.error_flag = d->error_flag;
     p.debug_out = g_debug_out; p.debug_rows = g_debug_rows;
     const size_t smem = (size_t)DN_STAGES * DN_STAGE_BYTES + 4096;
-    dense_topk_kernel<<<d->grid, DN_THREADS, smem, st>>>(d->map_x, d->map_q[p.n_eff / 32 - 1], p);
+    if (d->two_cta) {
+        const size_t smem2 = (size_t)DN2_STAGES * DN2_STAGE_BYTES + 4096;
+        dense_topk2_kernel<<<d->grid, DN_THREADS, smem2, st>>>(d->map_x, d->map_qh[p.n_eff / 32 - 1], p);
+    } else {
+        dense_topk_kernel<<<d->grid, DN_THREADS, smem, st>>>(d->map_x, d->map_q[p.n_eff / 32 - 1], p);
+    }
     FCB_CUDA(e, cudaGetLastError());
     DenseFinalParams fp{};
     fp.vectors = s.vectors; fp.ids = s.ids; fp.id_rank = s.id_rank; fp.queries = d_queries; fp.cta_top = d->cta_top;
