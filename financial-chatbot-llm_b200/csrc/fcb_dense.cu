@@ -364,6 +364,7 @@ dense_topk2_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
     uint32_t *tmem_ptr = reinterpret_cast<uint32_t *>(tmem_empty + 1);
     float *thr_s = reinterpret_cast<float *>(tmem_ptr + 2);          // [DN_N]
     int *cnt_s = reinterpret_cast<int *>(thr_s + DN_N);              // [DN_N]
+    float *thr_min_s = reinterpret_cast<float *>(cnt_s + DN_N);      // [DN_N / 32]: lowest threshold of each 32-query chunk
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const uint32_t cta_rank = cluster_ctarank();
@@ -396,6 +397,7 @@ dense_topk2_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
     }
     for (int i = tid; i < DN_N; i += DN_THREADS) { thr_s[i] = -INFINITY; cnt_s[i] = 0; }
+    if (tid < DN_N / 32) thr_min_s[tid] = -INFINITY;
     for (int i = tid; i < DN_N * FCB_FUSED_CAND; i += DN_THREADS) my_top[i] = FcbCand{-INFINITY, FCB_NO_ROW};
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
@@ -479,13 +481,20 @@ dense_topk2_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
                     for (int j = 0; j < 32; ++j) p.debug_out[(row - lo) * DN_N + c + j] = __uint_as_float(v[j]);
                 }
                 if (valid) {
+                    // chunk prefilter: the row's best raw score of these 32 queries against the chunk's lowest
+                    // threshold (inv >= 0, so max commutes with the scaling) — ~9 of 10 chunks stop here
+                    float mx = __uint_as_float(v[0]);
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) {
-                        const float s = __uint_as_float(v[j]) * inv;
-                        const float t = thr_s[c + j];
-                        if ((s > t || (push_ties && s == t)) && c + j < p.n_queries) {
-                            const int slot = atomicAdd(&cnt_s[c + j], 1);
-                            my_pend[(size_t)(c + j) * DN_PEND_CAP + slot] = FcbCand{s, (uint32_t)row};
+                    for (int j = 1; j < 32; ++j) mx = fmaxf(mx, __uint_as_float(v[j]));
+                    if (mx * inv >= thr_min_s[c >> 5]) {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) {
+                            const float s = __uint_as_float(v[j]) * inv;
+                            const float t = thr_s[c + j];
+                            if ((s > t || (push_ties && s == t)) && c + j < p.n_queries) {
+                                const int slot = atomicAdd(&cnt_s[c + j], 1);
+                                my_pend[(size_t)(c + j) * DN_PEND_CAP + slot] = FcbCand{s, (uint32_t)row};
+                            }
                         }
                     }
                 }
@@ -515,6 +524,13 @@ dense_topk2_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
                 my_top[(size_t)q * FCB_FUSED_CAND + lane] = e;
                 if (lane == 31) thr_s[q] = e.score;
                 if (lane == 0) cnt_s[q] = 0;
+            }
+            asm volatile("bar.sync 1, 256;" ::: "memory");
+            {   // warp ew refreshes the lowest threshold of query chunk ew (padding columns never qualify)
+                float t = (ew * 32 + lane < p.n_queries) ? thr_s[ew * 32 + lane] : INFINITY;
+#pragma unroll
+                for (int off = 16; off >= 1; off >>= 1) t = fminf(t, __shfl_xor_sync(FCB_FULL, t, off));
+                if (lane == 0) thr_min_s[ew] = t;
             }
             asm volatile("bar.sync 1, 256;" ::: "memory");
         }
