@@ -65,6 +65,7 @@ SIGNATURES = {
     "fcb_last_search_ms": (C.c_float, [C.c_void_p]),
     "fcb_last_search_launches": (C.c_int32, [C.c_void_p]),
     "fcb_debug_scan_timing": (C.c_int32, [C.c_void_p]),
+    "fcb_debug_dense_prof": (C.c_int32, [C.c_void_p]),
     "fcb_debug_dense_dump": (C.c_int32, [C.c_void_p, C.c_int64]),
     "fcb_last_dense_redo": (C.c_int32, [C.c_void_p, C.c_int32]),
     "fcb_aggregate": (C.c_int32, [C.c_void_p, C.c_int64, C.c_int64, C.c_int32, C.c_int32, C.c_int32,

@@ -57,6 +57,8 @@ struct DenseParams {
     int *error_flag;
     float *debug_out;                       // diagnostic: raw accumulators [debug_rows, DN_N] (NULL in production)
     int64_t debug_rows;
+    long long *prof;                        // diagnostic: per-role cycle counters of CTA 0 (NULL in production)
+    int n_stages;                           // cta_group::2 kernel: depth of the shared-memory ring (3 or 4)
 };
 
 // ---- PTX wrappers -----------------------------------------------------------------------------
@@ -316,11 +318,14 @@ dense_topk_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
 // CTA stages its own 128-row corpus tiles but only HALF of the query tile (the pair's MMA reads both
 // halves), and keeps two accumulators, so a query tile read from L2 now serves 512 corpus rows: the
 // L2->SM traffic per corpus byte drops from 1.0 to 0.5 byte — the bound of the 1-CTA kernel
-// (profiles/r01_summary.md). 4 stages of 48 KB. The leader CTA (cluster rank 0) issues every MMA; TMA
+// (profiles/r01_summary.md). 3 stages of 48 KB; the per-query sorted top-32 lists live in shared memory
+// (64 KB) so that folding the pending entries after a super-tile costs no global round trips. The leader CTA (cluster rank 0) issues every MMA; TMA
 // loads of both CTAs complete on the leader's full barrier; tcgen05.commit multicasts the stage-free
 // and accumulators-ready arrivals to both CTAs; both epilogues arrive remotely on the leader's
 // accumulators-drained barrier.
-#define DN2_STAGES 4
+#define DN2_THREADS 640                    // 4 service warps + 16 epilogue warps (two per TMEM lane quarter and accumulator)
+#define DN2_EPI_THREADS 512
+#define DN2_MAX_STAGES 4                   // 4 x 48 KB of stages when the per-query lists are small (batch <= 128), else 3
 #define DN2_STAGE_BYTES (2 * DN_A_BYTES + DN_B_BYTES / 2)   // 48 KB: A0, A1, half of B (max N = 256)
 #define DN2_SUPER_M 512
 
@@ -353,18 +358,20 @@ __device__ __forceinline__ void mbar_arrive_cta0(uint64_t *bar) {     // arrive 
                  ::"r"(smem_u32(bar)), "r"(0) : "memory");
 }
 
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(DN_THREADS, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(DN2_THREADS, 1)
 dense_topk2_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_q,
                    const __grid_constant__ DenseParams p) {
     extern __shared__ __align__(1024) unsigned char smem[];
-    uint64_t *full_bar = reinterpret_cast<uint64_t *>(smem + DN2_STAGES * DN2_STAGE_BYTES);
-    uint64_t *empty_bar = full_bar + DN2_STAGES;
-    uint64_t *tmem_full = empty_bar + DN2_STAGES;
+    const int n_stages = p.n_stages;
+    uint64_t *full_bar = reinterpret_cast<uint64_t *>(smem + n_stages * DN2_STAGE_BYTES);
+    uint64_t *empty_bar = full_bar + DN2_MAX_STAGES;
+    uint64_t *tmem_full = empty_bar + DN2_MAX_STAGES;
     uint64_t *tmem_empty = tmem_full + 1;
     uint32_t *tmem_ptr = reinterpret_cast<uint32_t *>(tmem_empty + 1);
-    float *thr_s = reinterpret_cast<float *>(tmem_ptr + 2);          // [DN_N]
+    float *thr_s = reinterpret_cast<float *>(smem + n_stages * DN2_STAGE_BYTES + 256);   // [DN_N], 16-byte aligned
     int *cnt_s = reinterpret_cast<int *>(thr_s + DN_N);              // [DN_N]
     float *thr_min_s = reinterpret_cast<float *>(cnt_s + DN_N);      // [DN_N / 32]: lowest threshold of each 32-query chunk
+    FcbCand *top_s = reinterpret_cast<FcbCand *>(smem + n_stages * DN2_STAGE_BYTES + 4096);   // [DN_N][32] sorted lists
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const uint32_t cta_rank = cluster_ctarank();
@@ -387,18 +394,18 @@ dense_topk2_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_q) : "memory");
     }
     if (warp == 1 && lane == 0) {
-        for (int s = 0; s < DN2_STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+        for (int s = 0; s < n_stages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
         mbar_init(tmem_full, 1);
-        mbar_init(tmem_empty, 512);                                    // 256 epilogue threads of each CTA
+        mbar_init(tmem_empty, 2 * DN2_EPI_THREADS);                    // the epilogue threads of both CTAs
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 2) {
         asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_ptr)), "r"(DN_TMEM_COLS) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
     }
-    for (int i = tid; i < DN_N; i += DN_THREADS) { thr_s[i] = -INFINITY; cnt_s[i] = 0; }
+    for (int i = tid; i < DN_N; i += DN2_THREADS) { thr_s[i] = -INFINITY; cnt_s[i] = 0; }
     if (tid < DN_N / 32) thr_min_s[tid] = -INFINITY;
-    for (int i = tid; i < DN_N * FCB_FUSED_CAND; i += DN_THREADS) my_top[i] = FcbCand{-INFINITY, FCB_NO_ROW};
+    for (int i = tid; i < p.n_eff * FCB_FUSED_CAND; i += DN2_THREADS) top_s[i] = FcbCand{-INFINITY, FCB_NO_ROW};
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     cluster_sync_all();                                                // barriers + TMEM of both CTAs are ready
@@ -412,18 +419,22 @@ dense_topk2_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
             const uint32_t stage_tx = 2u * (2u * DN_A_BYTES + (uint32_t)n_half * DN_BLOCK_K * 2u);   // both CTAs' bytes
             int stage = 0;
             uint32_t phase = 0;
+            long long w_empty = 0, t_begin = clock64();
             for (int st = pair; st < n_super; st += n_pairs) {
                 const int row0 = (int)(lo + (int64_t)st * DN2_SUPER_M) + (int)cta_rank * DN_BLOCK_M;
                 for (int ks = 0; ks < k_stages; ++ks) {
+                    const long long t0 = clock64();
                     mbar_wait(&empty_bar[stage], phase ^ 1, p.error_flag, 11);
+                    w_empty += clock64() - t0;
                     unsigned char *sp = smem + stage * DN2_STAGE_BYTES;
                     if (leader) mbar_expect_tx(&full_bar[stage], stage_tx);
                     tma_load_2d_2sm(sp, &map_x, ks * DN_BLOCK_K, row0, &full_bar[stage], hint_stream);
                     tma_load_2d_2sm(sp + DN_A_BYTES, &map_x, ks * DN_BLOCK_K, row0 + 256, &full_bar[stage], hint_stream);
                     tma_load_2d_2sm(sp + 2 * DN_A_BYTES, &map_q, ks * DN_BLOCK_K, (int)cta_rank * n_half, &full_bar[stage], hint_keep);
-                    if (++stage == DN2_STAGES) { stage = 0; phase ^= 1; }
+                    if (++stage == n_stages) { stage = 0; phase ^= 1; }
                 }
             }
+            if (p.prof && blockIdx.x == 0) { p.prof[0] = clock64() - t_begin; p.prof[1] = w_empty; }
         }
     } else if (warp == 1) {
         // ================= MMA issuer (leader CTA only) =================
@@ -432,11 +443,16 @@ dense_topk2_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
             int stage = 0;
             uint32_t phase = 0;
             int it = 0;
+            long long w_tmem = 0, w_full = 0, t_begin = clock64();
             for (int st = pair; st < n_super; st += n_pairs, ++it) {
+                long long t0 = clock64();
                 mbar_wait(tmem_empty, (it & 1) ^ 1, p.error_flag, 12);
+                w_tmem += clock64() - t0;
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 for (int ks = 0; ks < k_stages; ++ks) {
+                    t0 = clock64();
                     mbar_wait(&full_bar[stage], phase, p.error_flag, 13);
+                    w_full += clock64() - t0;
                     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                     const uint32_t sa = smem_u32(smem + stage * DN2_STAGE_BYTES);
                     const uint64_t a0 = make_sw128_desc(sa), a1 = make_sw128_desc(sa + DN_A_BYTES),
@@ -447,20 +463,23 @@ dense_topk2_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
                         umma_bf16_2sm(tmem_base + DN_N, a1 + 2 * kk, b + 2 * kk, idesc, (ks | kk) != 0);
                     }
                     umma_commit_2sm(&empty_bar[stage]);
-                    if (++stage == DN2_STAGES) { stage = 0; phase ^= 1; }
+                    if (++stage == n_stages) { stage = 0; phase ^= 1; }
                 }
                 umma_commit_2sm(tmem_full);
             }
+            if (p.prof && blockIdx.x == 0) { p.prof[2] = clock64() - t_begin; p.prof[3] = w_tmem; p.prof[4] = w_full; }
         }
     } else if (warp >= 4) {
         // ================= epilogue (both CTAs; TMEM lane = row of this CTA's half) =================
-        const int ew = warp - 4;
-        const int acc = ew >> 2;
+        const int ew = warp - 4;                           // 0..15
+        const int acc = (ew >> 2) & 1;                     // accumulator 0 / 1
+        const int col_half = ew >> 3;                      // which half of the query columns this warp scans
         const int lane_row = (warp & 3) * 32 + lane;
         const bool has_date = f.date_lo != FCB_DATE_MIN || f.date_hi != FCB_DATE_MAX;
         const bool has_cat = f.category_mask != FCB_ALL_CATEGORIES;
         const bool push_ties = p.id_rank != nullptr;
         int it = 0;
+        long long w_acc = 0, t_a = 0, t_b = 0, t_begin = clock64();
         for (int st = pair; st < n_super; st += n_pairs, ++it) {
             const int64_t row = lo + (int64_t)st * DN2_SUPER_M + acc * 256 + (int)cta_rank * DN_BLOCK_M + lane_row;
             bool valid = row < hi;
@@ -468,11 +487,15 @@ dense_topk2_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
             if (valid && has_cat) { const unsigned c = p.cats[row]; valid = c < 64 && ((f.category_mask >> c) & 1ull); }
             const float inv = valid ? p.inv_norm[row] : 0.f;
 
+            long long t0 = clock64();
             mbar_wait(tmem_full, it & 1, p.error_flag, 14);
+            long long t1 = clock64();
+            w_acc += t1 - t0;
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const uint32_t taddr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + acc * DN_N;
+            const int c_begin = col_half * (DN_N / 2), c_end = min(p.n_eff, c_begin + DN_N / 2);
 #pragma unroll 1
-            for (int c = 0; c < p.n_eff; c += 32) {
+            for (int c = c_begin; c < c_end; c += 32) {
                 uint32_t v[32];
                 tmem_ld32(taddr + c, v);
                 asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
@@ -480,21 +503,27 @@ dense_topk2_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
 #pragma unroll
                     for (int j = 0; j < 32; ++j) p.debug_out[(row - lo) * DN_N + c + j] = __uint_as_float(v[j]);
                 }
-                if (valid) {
-                    // chunk prefilter: the row's best raw score of these 32 queries against the chunk's lowest
-                    // threshold (inv >= 0, so max commutes with the scaling) — ~9 of 10 chunks stop here
-                    float mx = __uint_as_float(v[0]);
+                // branch-free pass mask of this row's 32 scores (thresholds: 8 broadcast 128-bit shared loads),
+                // then the rare survivors are pushed from an unrolled bit scan (no dynamic register indexing)
+                uint32_t mask = 0;
+                const float4 *t4 = reinterpret_cast<const float4 *>(thr_s + c);
 #pragma unroll
-                    for (int j = 1; j < 32; ++j) mx = fmaxf(mx, __uint_as_float(v[j]));
-                    if (mx * inv >= thr_min_s[c >> 5]) {
+                for (int j4 = 0; j4 < 8; ++j4) {
+                    const float4 t = t4[j4];
+                    const float s0 = __uint_as_float(v[4 * j4 + 0]) * inv, s1 = __uint_as_float(v[4 * j4 + 1]) * inv,
+                                s2 = __uint_as_float(v[4 * j4 + 2]) * inv, s3 = __uint_as_float(v[4 * j4 + 3]) * inv;
+                    const bool p0 = push_ties ? s0 >= t.x : s0 > t.x, p1 = push_ties ? s1 >= t.y : s1 > t.y,
+                               p2 = push_ties ? s2 >= t.z : s2 > t.z, p3 = push_ties ? s3 >= t.w : s3 > t.w;
+                    mask |= ((uint32_t)p0 | ((uint32_t)p1 << 1) | ((uint32_t)p2 << 2) | ((uint32_t)p3 << 3)) << (4 * j4);
+                }
+                const int left = p.n_queries - c;                      // padding columns never qualify
+                mask &= left >= 32 ? 0xffffffffu : ((1u << left) - 1u);
+                if (valid && mask) {
 #pragma unroll
-                        for (int j = 0; j < 32; ++j) {
-                            const float s = __uint_as_float(v[j]) * inv;
-                            const float t = thr_s[c + j];
-                            if ((s > t || (push_ties && s == t)) && c + j < p.n_queries) {
-                                const int slot = atomicAdd(&cnt_s[c + j], 1);
-                                my_pend[(size_t)(c + j) * DN_PEND_CAP + slot] = FcbCand{s, (uint32_t)row};
-                            }
+                    for (int j = 0; j < 32; ++j) {
+                        if (mask & (1u << j)) {
+                            const int slot = atomicAdd(&cnt_s[c + j], 1);
+                            my_pend[(size_t)(c + j) * DN_PEND_CAP + slot] = FcbCand{__uint_as_float(v[j]) * inv, (uint32_t)row};
                         }
                     }
                 }
@@ -502,41 +531,73 @@ dense_topk2_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
             asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
             mbar_arrive_cta0(tmem_empty);                              // the leader's MMA may overwrite both TMEMs
             __threadfence_block();
-            asm volatile("bar.sync 1, 256;" ::: "memory");
-            for (int q = ew; q < p.n_queries; q += 8) {
-                const int n = cnt_s[q];
-                if (n == 0) continue;
-                FcbCand e = my_top[(size_t)q * FCB_FUSED_CAND + lane];
-                float thr = __shfl_sync(FCB_FULL, e.score, 31);
-                for (int base = 0; base < n; base += 32) {
-                    FcbCand pe{-INFINITY, FCB_NO_ROW};
-                    if (base + lane < n) pe = my_pend[(size_t)q * DN_PEND_CAP + base + lane];
-                    const int m = n - base < 32 ? n - base : 32;
-                    for (int j = 0; j < m; ++j) {
-                        const float s = __shfl_sync(FCB_FULL, pe.score, j);
-                        const uint32_t r = __shfl_sync(FCB_FULL, pe.row, j);
-                        if (s >= thr) {
-                            dn_insert(e.score, e.row, s, r, p.id_rank, lane);
-                            thr = __shfl_sync(FCB_FULL, e.score, 31);
+            asm volatile("bar.sync 1, 512;" ::: "memory");
+            t0 = clock64();
+            t_a += t0 - t1;
+            // fold the pending entries into the sorted lists (shared memory). Lane i looks after query
+            // ew + 8 i; queries with pending entries are handled four at a time so that their (global,
+            // L2-resident) pending entries are fetched with one round trip instead of four.
+            {
+                const int my_q = ew + 16 * lane;
+                const int my_n = my_q < p.n_queries ? cnt_s[my_q] : 0;
+                unsigned todo = __ballot_sync(FCB_FULL, my_n > 0);
+                while (todo) {
+                    int qs[4], ns[4];
+                    FcbCand pe[4];
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        if (todo) {
+                            const int bit = __ffs(todo) - 1;
+                            todo &= todo - 1;
+                            qs[u] = ew + 16 * bit;
+                            ns[u] = __shfl_sync(FCB_FULL, my_n, bit);
+                        } else { qs[u] = -1; ns[u] = 0; }
+                        pe[u] = FcbCand{-INFINITY, FCB_NO_ROW};
+                        if (lane < ns[u]) pe[u] = my_pend[(size_t)qs[u] * DN_PEND_CAP + lane];
+                    }
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        if (qs[u] < 0) continue;
+                        const int q = qs[u], n = ns[u];
+                        FcbCand e = top_s[q * FCB_FUSED_CAND + lane];
+                        float thr = __shfl_sync(FCB_FULL, e.score, 31);
+                        for (int base = 0; base < n; base += 32) {
+                            FcbCand cur = pe[u];
+                            if (base > 0) {
+                                cur = FcbCand{-INFINITY, FCB_NO_ROW};
+                                if (base + lane < n) cur = my_pend[(size_t)q * DN_PEND_CAP + base + lane];
+                            }
+                            const int m = n - base < 32 ? n - base : 32;
+                            for (int j = 0; j < m; ++j) {
+                                const float s = __shfl_sync(FCB_FULL, cur.score, j);
+                                const uint32_t r = __shfl_sync(FCB_FULL, cur.row, j);
+                                if (s >= thr) {
+                                    dn_insert(e.score, e.row, s, r, p.id_rank, lane);
+                                    thr = __shfl_sync(FCB_FULL, e.score, 31);
+                                }
+                            }
                         }
+                        top_s[q * FCB_FUSED_CAND + lane] = e;
+                        if (lane == 31) thr_s[q] = e.score;
+                        if (lane == 0) cnt_s[q] = 0;
                     }
                 }
-                my_top[(size_t)q * FCB_FUSED_CAND + lane] = e;
-                if (lane == 31) thr_s[q] = e.score;
-                if (lane == 0) cnt_s[q] = 0;
             }
-            asm volatile("bar.sync 1, 256;" ::: "memory");
-            {   // warp ew refreshes the lowest threshold of query chunk ew (padding columns never qualify)
+            asm volatile("bar.sync 1, 512;" ::: "memory");
+            if (ew < DN_N / 32) {   // warp ew refreshes the lowest threshold of query chunk ew (padding columns never qualify)
                 float t = (ew * 32 + lane < p.n_queries) ? thr_s[ew * 32 + lane] : INFINITY;
 #pragma unroll
                 for (int off = 16; off >= 1; off >>= 1) t = fminf(t, __shfl_xor_sync(FCB_FULL, t, off));
                 if (lane == 0) thr_min_s[ew] = t;
             }
-            asm volatile("bar.sync 1, 256;" ::: "memory");
+            asm volatile("bar.sync 1, 512;" ::: "memory");
+            t_b += clock64() - t0;
         }
+        if (p.prof && blockIdx.x == 0 && tid == 128) { p.prof[5] = clock64() - t_begin; p.prof[6] = w_acc; p.prof[7] = t_a; p.prof[8] = t_b; p.prof[9] = it; }
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
+    for (int i = tid; i < p.n_eff * FCB_FUSED_CAND; i += DN2_THREADS) my_top[i] = top_s[i];   // hand the lists to dense_finalize_kernel
     cluster_sync_all();                                                // nobody still targets the peer's barriers / TMEM
     if (warp == 2) {
         asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(DN_TMEM_COLS) : "memory");
@@ -743,7 +804,7 @@ int32_t fcb_dense_alloc(fcb_engine *e) {
     if (rc != FCB_OK) { fcb_dense_free(e); return rc; }
     const size_t smem = (size_t)DN_STAGES * DN_STAGE_BYTES + 4096;
     FCB_CUDA(e, cudaFuncSetAttribute(dense_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    const size_t smem2 = (size_t)DN2_STAGES * DN2_STAGE_BYTES + 4096;
+    const size_t smem2 = (size_t)3 * DN2_STAGE_BYTES + 4096 + (size_t)DN_N * FCB_FUSED_CAND * sizeof(FcbCand);   // also covers 4 stages + 128 lists
     FCB_CUDA(e, cudaFuncSetAttribute(dense_topk2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
     return FCB_OK;
 }
@@ -752,6 +813,15 @@ int32_t fcb_dense_alloc(fcb_engine *e) {
 // `redo_out` receives the device pointer of the per-query "not certified" flags.
 static float *g_debug_out = nullptr;
 static int64_t g_debug_rows = 0;
+static long long *g_dense_prof = nullptr;
+
+// Diagnostic: per-role cycle counters of CTA 0 of the cta_group::2 kernel into `buf` (device int64[10]):
+// producer total / waiting for a free stage; MMA issuer total / waiting for drained accumulators / waiting
+// for a full stage; epilogue total / waiting for accumulators / scanning TMEM / folding candidates; super-tiles.
+extern "C" int32_t fcb_debug_dense_prof(int64_t *buf) {
+    g_dense_prof = reinterpret_cast<long long *>(buf);
+    return FCB_OK;
+}
 
 // Diagnostic: make the next batched-path call also dump the raw tensor-core accumulators of the
 // first `rows` rows of the segment into `out` (device float [rows, 256]); rows = 0 switches it off.
@@ -773,11 +843,12 @@ int32_t fcb_search_dense(fcb_engine *e, const double *d_queries, const fcb_filte
     p.n_rows = s.n_rows; p.row_base = s.row_base; p.dim = s.dim;
     p.n_queries = batch; p.n_eff = ((batch + 31) / 32) * 32;
     p.cta_top = d->cta_top; p.pend = d->pend; p.error_flag = d->error_flag;
-    p.debug_out = g_debug_out; p.debug_rows = g_debug_rows;
+    p.debug_out = g_debug_out; p.debug_rows = g_debug_rows; p.prof = g_dense_prof;
+    p.n_stages = p.n_eff <= 128 ? 4 : 3;                             // lists (n_eff x 256 B) + stages must fit 227 KB
     const size_t smem = (size_t)DN_STAGES * DN_STAGE_BYTES + 4096;
     if (d->two_cta) {
-        const size_t smem2 = (size_t)DN2_STAGES * DN2_STAGE_BYTES + 4096;
-        dense_topk2_kernel<<<d->grid, DN_THREADS, smem2, st>>>(d->map_x, d->map_qh[p.n_eff / 32 - 1], p);
+        const size_t smem2 = (size_t)p.n_stages * DN2_STAGE_BYTES + 4096 + (size_t)p.n_eff * FCB_FUSED_CAND * sizeof(FcbCand);
+        dense_topk2_kernel<<<d->grid, DN2_THREADS, smem2, st>>>(d->map_x, d->map_qh[p.n_eff / 32 - 1], p);
     } else {
         dense_topk_kernel<<<d->grid, DN_THREADS, smem, st>>>(d->map_x, d->map_q[p.n_eff / 32 - 1], p);
     }

@@ -156,6 +156,12 @@ int32_t fcb_last_dense_redo(fcb_engine *e, int32_t batch);
  * (device float32 [rows, 256]); rows = 0 switches the dump off. Not for production use. */
 int32_t fcb_debug_dense_dump(float *out, int64_t rows);
 
+/* Diagnostic for the batched tensor-core path (cta_group::2 kernel): while `buf` (device int64[10]) is
+ * set, CTA 0 writes per-role cycle counters: [0] producer total, [1] waiting for a free stage, [2] MMA
+ * issuer total, [3] waiting for drained accumulators, [4] waiting for a full stage, [5] epilogue total,
+ * [6] waiting for accumulators, [7] scanning TMEM, [8] folding candidates, [9] super-tiles. NULL = off. */
+int32_t fcb_debug_dense_prof(int64_t *buf);
+
 /* Diagnostic for the fused scan: while `buf` (device uint64[9]) is set, every launch writes the GPU
  * global timer (ns) at nine phase boundaries of query 0 (kernel start, query staged, scan done,
  * CTA list written, last CTA starts, lists merged, re-score starts / ends, results written).

@@ -18,9 +18,15 @@ if which == "cfg3":
     q = torch.from_numpy(np.stack([synth.query_vector(spec, 500 + i) for i in range(B)])).to(DEV)
     oi = torch.empty((B, 10), dtype=torch.int64, device=DEV); os_ = torch.empty((B, 10), dtype=torch.float64, device=DEV)
     oc = torch.empty(B, dtype=torch.int32, device=DEV)
+    from financial_chatbot_llm_b200 import _lib
+    prof = torch.zeros(10, dtype=torch.int64, device=DEV)
+    _lib.load().fcb_debug_dense_prof(prof.data_ptr())
     for i in range(steps):
         eng.search_device(q, [make_filter(0, rows)] * B, 10, oi, os_, oc)
     torch.cuda.synchronize()
+    names = ["producer total", "  wait free stage", "mma total", "  wait tmem drained", "  wait full stage", "epilogue total",
+             "  wait accumulators", "  scan tmem", "  fold candidates", "super-tiles"]
+    for n, v in zip(names, prof.cpu().tolist()): print(f"{n:24s} {v}")
 elif which == "cfg5":
     n, users = 1_000_000_000, 100_000
     spec = synth.SynthSpec(n_rows=n, dim=4, n_users=users, seed=5, zipf_a=1.1)
