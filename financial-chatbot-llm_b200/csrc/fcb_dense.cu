@@ -627,6 +627,7 @@ struct DenseFinalParams {
     double *out_scores;
     int32_t *out_counts;
     int32_t *redo;                          // [batch]: 1 = not certified, re-run exactly
+    int32_t *redo_list, *redo_count;        // compact list of those queries for the re-run launch
     int rigorous;                           // 1: Cauchy-Schwarz margin, 0: 8-sigma margin of the rounding model
 };
 
@@ -719,7 +720,9 @@ __global__ void __launch_bounds__(256) dense_finalize_kernel(const __grid_consta
         const double worst = (double)__shfl_sync(FCB_FULL, my_s, 31) / nq;
         if (lane == 0) {
             p.out_counts[b] = count;
-            p.redo[b] = (nvalid == FCB_FUSED_CAND && !(worst + margin < s_kth)) ? 1 : 0;
+            const int flag = (nvalid == FCB_FUSED_CAND && !(worst + margin < s_kth)) ? 1 : 0;
+            p.redo[b] = flag;
+            if (flag) p.redo_list[atomicAdd(p.redo_count, 1)] = b;
         }
     }
 }
@@ -757,7 +760,7 @@ struct FcbDense {
     int two_cta = 1;
     __nv_bfloat16 *q_bf16 = nullptr;        // [DN_N, dim]
     FcbCand *cta_top = nullptr, *pend = nullptr;
-    int32_t *redo = nullptr;
+    int32_t *redo = nullptr;                // [DN_N] flags, then [DN_N] compact list, then the count
     int *error_flag = nullptr;
     int grid = 0;
 };
@@ -785,7 +788,7 @@ int32_t fcb_dense_alloc(fcb_engine *e) {
     if (cudaMalloc(&d->q_bf16, (size_t)DN_N * s.dim * 2) != cudaSuccess ||
         cudaMalloc(&d->cta_top, lists * FCB_FUSED_CAND * sizeof(FcbCand)) != cudaSuccess ||
         cudaMalloc(&d->pend, lists * DN_PEND_CAP * sizeof(FcbCand)) != cudaSuccess ||
-        cudaMalloc(&d->redo, (size_t)DN_N * sizeof(int32_t)) != cudaSuccess ||
+        cudaMalloc(&d->redo, (size_t)(2 * DN_N + 1) * sizeof(int32_t)) != cudaSuccess ||
         cudaMalloc(&d->error_flag, sizeof(int)) != cudaSuccess) {
         cudaGetLastError();
         fcb_dense_free(e);
@@ -833,7 +836,7 @@ extern "C" int32_t fcb_debug_dense_dump(float *out, int64_t rows) {
 
 int32_t fcb_search_dense(fcb_engine *e, const double *d_queries, const fcb_filter &f, int32_t batch, int32_t k,
                          uint64_t *d_out_ids, double *d_out_scores, int32_t *d_out_counts, cudaStream_t st,
-                         const int32_t **redo_out) {
+                         const int32_t **redo_list_out, const int32_t **redo_count_out) {
     FcbDense *d = reinterpret_cast<FcbDense *>(e->dense);
     const fcb_shard &s = e->shard;
     if (!d) return fcb_fail(e, FCB_ERR_STATE, "fcb_search: batched path not initialised");
@@ -858,10 +861,13 @@ int32_t fcb_search_dense(fcb_engine *e, const double *d_queries, const fcb_filte
     fp.n_lists = d->grid; fp.row_base = s.row_base; fp.dim = s.dim; fp.k = k;
     fp.out_ids = d_out_ids; fp.out_scores = d_out_scores; fp.out_counts = d_out_counts; fp.redo = d->redo;
     fp.rigorous = d->rigorous;
+    fp.redo_list = d->redo + DN_N; fp.redo_count = d->redo + 2 * DN_N;
+    FCB_CUDA(e, cudaMemsetAsync(fp.redo_count, 0, sizeof(int32_t), st));
     dense_finalize_kernel<<<batch, 256, 0, st>>>(fp);
     FCB_CUDA(e, cudaGetLastError());
     e->last_launches += 3;
-    *redo_out = d->redo;
+    *redo_list_out = d->redo + DN_N;
+    *redo_count_out = d->redo + 2 * DN_N;
     return FCB_OK;
 }
 

@@ -88,7 +88,7 @@ int32_t fcb_dense_alloc(fcb_engine *e);
 void fcb_dense_free(fcb_engine *e);
 int32_t fcb_search_dense(fcb_engine *e, const double *d_queries, const fcb_filter &f, int32_t batch, int32_t k,
                          uint64_t *d_out_ids, double *d_out_scores, int32_t *d_out_counts, cudaStream_t st,
-                         const int32_t **redo_out);
+                         const int32_t **redo_list_out, const int32_t **redo_count_out);
 
 // error plumbing (fcb_engine.cu)
 int32_t fcb_fail(fcb_engine *e, int32_t code, const char *fmt, ...);

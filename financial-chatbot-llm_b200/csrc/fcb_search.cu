@@ -28,7 +28,8 @@ struct ScanParams {
     const fcb_filter *filters;             // device copy, used when !use_inline
     fcb_filter inl[FCB_INLINE_FILTERS];
     int use_inline;
-    const int32_t *only_if;                // optional [batch]: run query b only where only_if[b] != 0
+    const int32_t *redo_list;              // optional: device list of query indices to run (re-run of uncertified
+    const int32_t *redo_count;             //   queries of the dense path); grid.y rows then stride over that list
     unsigned long long *timing;            // diagnostic: %globaltimer at phase boundaries (NULL in production)
     int64_t n_rows, row_base;
     int dim, k;
@@ -246,19 +247,11 @@ __device__ __noinline__ void scan_tail(const ScanParams &p, int b, unsigned char
 // flight. The streaming rate of this loop is sensitive to (R, U) — see profiles/r01_summary.md — so the
 // host picks the pair per storage type and dimension (launch_fused) from the instantiated set.
 template <typename T, int R, int U>
-__global__ void __launch_bounds__(FCB_SCAN_THREADS, FCB_SCAN_MINCTAS)
-scan_topk_kernel(const __grid_constant__ ScanParams p) {
+__device__ __forceinline__ void scan_one_query(const ScanParams &p, const int b, unsigned char *smem_raw,
+                                               FcbCand (*m_s)[FCB_FUSED_CAND], double *f_score, uint64_t *f_id, int &s_last) {
     constexpr int VEC = RowDot<T>::VEC;
-    extern __shared__ __align__(16) unsigned char smem_raw[];
     float *q_s = reinterpret_cast<float *>(smem_raw);                 // [dim] float32 query
-    __shared__ FcbCand m_s[FCB_SCAN_WARPS][FCB_FUSED_CAND];
-    __shared__ double f_score[FCB_FUSED_CAND];
-    __shared__ uint64_t f_id[FCB_FUSED_CAND];
-    __shared__ int s_last;
-
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int b = blockIdx.y;
-    if (p.only_if != nullptr && p.only_if[b] == 0) return;      // block-uniform: re-run of uncertified queries only
     const fcb_filter f = p.use_inline ? p.inl[b] : p.filters[b];
     const double *__restrict__ qd = p.queries + (size_t)b * p.dim;
     const uint32_t *__restrict__ id_rank = p.id_rank;
@@ -357,6 +350,26 @@ scan_topk_kernel(const __grid_constant__ ScanParams p) {
     scan_tail<T>(p, b, smem_raw, m_s, f_score, f_id);
 }
 
+template <typename T, int R, int U>
+__global__ void __launch_bounds__(FCB_SCAN_THREADS, FCB_SCAN_MINCTAS)
+scan_topk_kernel(const __grid_constant__ ScanParams p) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    __shared__ FcbCand m_s[FCB_SCAN_WARPS][FCB_FUSED_CAND];
+    __shared__ double f_score[FCB_FUSED_CAND];
+    __shared__ uint64_t f_id[FCB_FUSED_CAND];
+    __shared__ int s_last;
+    if (p.redo_list == nullptr) {
+        scan_one_query<T, R, U>(p, blockIdx.y, smem_raw, m_s, f_score, f_id, s_last);
+    } else {
+        // re-run of the few queries the dense pass could not certify: grid.y rows stride over the device list
+        const int n = *p.redo_count;
+        for (int i = blockIdx.y; i < n; i += gridDim.y) {
+            scan_one_query<T, R, U>(p, p.redo_list[i], smem_raw, m_s, f_score, f_id, s_last);
+            __syncthreads();
+        }
+    }
+}
+
 // ---- host side ------------------------------------------------------------------------------
 
 static int32_t check_search_args(fcb_engine *e, const void *queries, const fcb_filter *filters,
@@ -372,6 +385,7 @@ static int32_t check_search_args(fcb_engine *e, const void *queries, const fcb_f
 
 template <typename T, int R, int U>
 static int32_t launch_fused_cfg(fcb_engine *e, ScanParams &p, int batch, int64_t max_rows, cudaStream_t st) {
+    const int grid_y = p.redo_list != nullptr && batch > 8 ? 8 : batch;   // re-run launch: 8 rows stride over the list
     const int64_t groups = (max_rows + R - 1) / R;
     // >= 2 groups per warp when the segment allows; never more CTAs than the scratch holds
     int64_t ctas = (groups + 2 * FCB_SCAN_WARPS - 1) / (2 * FCB_SCAN_WARPS);
@@ -386,7 +400,7 @@ static int32_t launch_fused_cfg(fcb_engine *e, ScanParams &p, int batch, int64_t
     const size_t smem = (((size_t)p.dim * sizeof(float) + 15) & ~(size_t)15) + (size_t)p.dim * sizeof(double);
     auto kern = scan_topk_kernel<T, R, U>;
     if (smem > 48 * 1024) FCB_CUDA(e, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    kern<<<dim3((unsigned)ctas, (unsigned)batch), FCB_SCAN_THREADS, smem, st>>>(p);
+    kern<<<dim3((unsigned)ctas, (unsigned)grid_y), FCB_SCAN_THREADS, smem, st>>>(p);
     FCB_CUDA(e, cudaGetLastError());
     e->last_launches += 1;
     return FCB_OK;
@@ -470,10 +484,9 @@ static int32_t search_device(fcb_engine *e, const double *d_queries, const fcb_f
         if (lo < 0) lo = 0;
         if (hi > s.n_rows) hi = s.n_rows;
         if (same && hi - lo >= 65536) {
-            const int32_t *redo = nullptr;
-            const int32_t rc = fcb_search_dense(e, d_queries, f0, batch, k, d_out_ids, d_out_scores, d_out_counts, st, &redo);
+            const int32_t rc = fcb_search_dense(e, d_queries, f0, batch, k, d_out_ids, d_out_scores, d_out_counts, st,
+                                                &p.redo_list, &p.redo_count);
             if (rc != FCB_OK) return rc;
-            p.only_if = redo;
         }
     }
 
