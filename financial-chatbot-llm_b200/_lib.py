@@ -72,6 +72,9 @@ SIGNATURES = {
                                   C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "fcb_merge_topk": (C.c_int32, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32,
                                    C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "fcb_shard_dates_sorted": (C.c_int32, [C.c_void_p]),
+    "fcb_synth_dates_sorted": (C.c_int32, [C.c_int32, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64,
+                                           C.c_int64, C.c_void_p]),
     "fcb_synth_vectors": (C.c_int32, [C.c_int32, C.c_void_p, C.c_int32, C.c_int64, C.c_int64,
                                       C.c_int32, C.c_uint64, C.c_int32, C.c_void_p]),
     "fcb_synth_columns": (C.c_int32, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,

@@ -183,6 +183,171 @@ __global__ void __launch_bounds__(AGG_THREADS, 4) aggregate_kernel(const __grid_
     if (dropped) atomicAdd(p.dropped, (unsigned long long)dropped);
 }
 
+// ---- date-ordered segments: no atomics on the hot path ---------------------------------------------
+// Transaction logs are appended in time order, so within a user the rows of one calendar month form
+// one contiguous run. A warp then only has to tell CATEGORIES apart: every lane owns a private
+// column of bins in shared memory (bins[category][lane], one bank per lane: conflict-free plain
+// load/add/store, no atomics), a run ends with a warp-shuffle reduction of the 16 (<= 32) bins and one
+// 64-bit global reduction per non-empty cell. Correct for ANY row order (a step that mixes months is
+// processed month by month, flushing in between) — only the speed relies on the order, so the host
+// selects this kernel when the load-time check found the dates non-decreasing within every user.
+#define AGS_WARP_ROWS 4096                 // consecutive rows one warp takes per task
+
+__global__ void __launch_bounds__(AGG_THREADS, 4) aggregate_sorted_kernel(const __grid_constant__ AggParams p) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int C = p.n_categories * p.n_months;
+    uint16_t *month_tab = reinterpret_cast<uint16_t *>(smem_raw);                                   // [n_days]
+    long long *bins_all = reinterpret_cast<long long *>(smem_raw + (((size_t)p.n_days * 2 + 15) & ~(size_t)15));
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    long long *bins = bins_all + (size_t)warp * p.n_categories * 32;                                // [n_categories][32]
+    for (int i = tid; i < p.n_days; i += AGG_THREADS) month_tab[i] = (uint16_t)(month_of_day(p.day0 + i) - p.month_lo);
+    for (int i = lane; i < p.n_categories * 32; i += 32) bins[i] = 0;
+    __syncthreads();
+
+    int64_t R0 = p.seg_offsets[p.seg_begin], R1 = p.seg_offsets[p.seg_end];
+    if (R0 < p.row_base) R0 = p.row_base;
+    if (R1 > p.row_base + p.n_rows) R1 = p.row_base + p.n_rows;
+    const int64_t n_tasks = R1 > R0 ? (R1 - R0 + AGS_WARP_ROWS - 1) / AGS_WARP_ROWS : 0;
+    const int4 *cents4 = reinterpret_cast<const int4 *>(p.cents);
+    const int4 *dates4 = reinterpret_cast<const int4 *>(p.dates);
+    const uchar4 *cats4 = reinterpret_cast<const uchar4 *>(p.cats);
+    unsigned dropped = 0;
+
+    int64_t cur_user = -1;
+    int cur_month = -1;
+    uint32_t seen = 0;                                              // categories this lane added to since the last flush
+
+    auto flush = [&]() {
+        if (cur_month >= 0) {
+            int64_t *out_s = p.sums + (cur_user - p.seg_begin) * (int64_t)C;
+            uint8_t *out_p = p.present + (cur_user - p.seg_begin) * (int64_t)C;
+            uint32_t any = seen;
+#pragma unroll
+            for (int off = 16; off >= 1; off >>= 1) any |= __shfl_xor_sync(FCB_FULL, any, off);
+            long long mine = 0;                                     // lane c ends up with the total of category c
+            for (int c = 0; c < p.n_categories; ++c) {
+                if (!((any >> c) & 1u)) continue;                   // warp-uniform
+                long long v = bins[c * 32 + lane];
+                bins[c * 32 + lane] = 0;
+#pragma unroll
+                for (int off = 16; off >= 1; off >>= 1) v += __shfl_xor_sync(FCB_FULL, v, off);
+                if (lane == c) mine = v;
+            }
+            if (lane < p.n_categories && ((any >> lane) & 1u)) {
+                const int cell = lane * p.n_months + cur_month;
+                atomicAdd(reinterpret_cast<unsigned long long *>(out_s + cell), (unsigned long long)mine);
+                out_p[cell] = 1;
+            }
+        }
+        seen = 0;
+    };
+
+    const int64_t n_warps = (int64_t)gridDim.x * (AGG_THREADS / 32);
+    for (int64_t t = (int64_t)blockIdx.x * (AGG_THREADS / 32) + warp; t < n_tasks; t += n_warps) {
+        const int64_t a = R0 + t * AGS_WARP_ROWS;
+        const int64_t b = a + AGS_WARP_ROWS < R1 ? a + AGS_WARP_ROWS : R1;
+        int64_t u;                                                  // first user whose segment ends after a
+        {
+            int64_t lo = p.seg_begin, hi = p.seg_end - 1;
+            while (lo < hi) {
+                const int64_t mid = (lo + hi) >> 1;
+                if (p.seg_offsets[mid + 1] > a) hi = mid; else lo = mid + 1;
+            }
+            u = lo;
+        }
+        int64_t pa = a;
+        while (pa < b) {
+            int64_t uend = p.seg_offsets[u + 1];
+            while (uend <= pa) { ++u; uend = p.seg_offsets[u + 1]; }
+            const int64_t pb = uend < b ? uend : b;
+            if (u != cur_user) { flush(); cur_user = u; cur_month = -1; }
+            const int64_t la = pa - p.row_base, lb = pb - p.row_base;
+            for (int64_t base = la & ~(int64_t)3; base < lb; base += 128) {
+                const int64_t r = base + 4 * lane;                  // this lane's quad of local rows
+                int v[4], m[4];
+                unsigned cat[4];
+                if (r + 4 <= p.n_rows && r < lb) {
+                    const int4 vv = __ldg(cents4 + (r >> 2));
+                    const int4 dd = __ldg(dates4 + (r >> 2));
+                    const uchar4 cc = __ldg(cats4 + (r >> 2));
+                    v[0] = vv.x; v[1] = vv.y; v[2] = vv.z; v[3] = vv.w;
+                    m[0] = dd.x; m[1] = dd.y; m[2] = dd.z; m[3] = dd.w;
+                    cat[0] = cc.x; cat[1] = cc.y; cat[2] = cc.z; cat[3] = cc.w;
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        const bool in = r + i < p.n_rows && r + i < lb;
+                        v[i] = in ? p.cents[r + i] : 0; m[i] = in ? p.dates[r + i] : 0; cat[i] = in ? p.cats[r + i] : 0;
+                    }
+                }
+                unsigned todo = 0;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const bool in = r + i >= la && r + i < lb;
+                    const int32_t di = floor_day(m[i]) - p.day0;
+                    const unsigned mo = (unsigned)di < (unsigned)p.n_days ? month_tab[di] : 0xffffu;
+                    const bool ok = in && cat[i] < (unsigned)p.n_categories && mo < (unsigned)p.n_months;
+                    if (in && !ok) ++dropped;
+                    m[i] = ok ? (int)mo : 0x7fffffff;
+                    if (ok) todo |= 1u << i;
+                }
+                // months present in this step, one at a time (normally one; two at a month boundary)
+                while (__any_sync(FCB_FULL, todo != 0)) {
+                    int mn = 0x7fffffff;
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) if ((todo >> i) & 1u) mn = min(mn, m[i]);
+#pragma unroll
+                    for (int off = 16; off >= 1; off >>= 1) mn = min(mn, __shfl_xor_sync(FCB_FULL, mn, off));
+                    if (mn != cur_month) { flush(); cur_month = mn; }
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        if (((todo >> i) & 1u) && m[i] == cur_month) {
+                            bins[cat[i] * 32 + lane] += (long long)v[i];
+                            seen |= 1u << cat[i];
+                            todo &= ~(1u << i);
+                        }
+                    }
+                }
+            }
+            pa = pb;
+        }
+    }
+    flush();
+    if (dropped) atomicAdd(p.dropped, (unsigned long long)dropped);
+}
+
+// non-decreasing dates within every user of [seg_begin, seg_end)? (load-time check; writes 0 on a violation)
+__global__ void __launch_bounds__(256) dates_sorted_kernel(const int64_t *__restrict__ seg_offsets, int64_t n_segs,
+                                                           const int32_t *__restrict__ dates, int64_t row_base,
+                                                           int64_t n_rows, int *__restrict__ sorted_flag) {
+    for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r + 1 < n_rows; r += (int64_t)gridDim.x * blockDim.x) {
+        if (dates[r] > dates[r + 1]) {
+            // a decrease is fine only across a user boundary: is global row (row_base + r + 1) a segment start?
+            const int64_t g = row_base + r + 1;
+            int64_t lo = 0, hi = n_segs;
+            while (lo < hi) { const int64_t mid = (lo + hi) >> 1; if (seg_offsets[mid] < g) lo = mid + 1; else hi = mid; }
+            if (!(lo <= n_segs && seg_offsets[lo] == g)) *sorted_flag = 0;
+        }
+    }
+}
+
+int32_t fcb_check_dates_sorted(fcb_engine *e) {
+    const fcb_shard &s = e->shard;
+    e->dates_sorted = 0;
+    if (!s.dates || !s.seg_offsets || s.n_segs <= 0) return FCB_OK;
+    int *flag = nullptr;
+    FCB_CUDA(e, cudaMalloc(&flag, sizeof(int)));
+    int one = 1;
+    FCB_CUDA(e, cudaMemcpyAsync(flag, &one, sizeof(int), cudaMemcpyHostToDevice, e->stream));
+    dates_sorted_kernel<<<e->num_sms * 8, 256, 0, e->stream>>>(s.seg_offsets, s.n_segs, s.dates, s.row_base, s.n_rows, flag);
+    int h = 0;
+    FCB_CUDA(e, cudaMemcpyAsync(&h, flag, sizeof(int), cudaMemcpyDeviceToHost, e->stream));
+    FCB_CUDA(e, cudaStreamSynchronize(e->stream));
+    cudaFree(flag);
+    e->dates_sorted = h;
+    return FCB_OK;
+}
+
 extern "C" int32_t fcb_aggregate(fcb_engine *e, int64_t seg_begin, int64_t seg_end, int32_t month_lo, int32_t n_months,
                                  int32_t n_categories, int64_t *sums, uint8_t *present, uint64_t *dropped, void *stream) {
     if (!e) return FCB_ERR_INVALID;
@@ -220,7 +385,17 @@ extern "C" int32_t fcb_aggregate(fcb_engine *e, int64_t seg_begin, int64_t seg_e
     const size_t smem = (size_t)C * 8 + (size_t)((p.n_days + 1) & ~1) * 2 + (size_t)C + 16;
     if (smem > 48 * 1024)
         FCB_CUDA(e, cudaFuncSetAttribute(aggregate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    aggregate_kernel<<<e->num_sms * 4, AGG_THREADS, smem, st>>>(p);
+    const char *force = getenv("FCB_AGG_KERNEL");                   // tuning: "atomic" / "sorted"
+    const bool sorted_ok = n_categories <= 32;
+    const bool use_sorted = sorted_ok && (force ? force[0] == 's' : e->dates_sorted != 0);
+    if (use_sorted) {
+        const size_t smem_s = (((size_t)p.n_days * 2 + 15) & ~(size_t)15) + (size_t)(AGG_THREADS / 32) * n_categories * 32 * 8;
+        if (smem_s > 48 * 1024)
+            FCB_CUDA(e, cudaFuncSetAttribute(aggregate_sorted_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_s));
+        aggregate_sorted_kernel<<<e->num_sms * 4, AGG_THREADS, smem_s, st>>>(p);
+    } else {
+        aggregate_kernel<<<e->num_sms * 4, AGG_THREADS, smem, st>>>(p);
+    }
     FCB_CUDA(e, cudaGetLastError());
     return FCB_OK;
 }

@@ -18,6 +18,8 @@ int32_t fcb_fail(fcb_engine *e, int32_t code, const char *fmt, ...) {
 
 extern "C" int32_t fcb_abi_version(void) { return FCB_ABI_VERSION; }
 
+extern "C" int32_t fcb_shard_dates_sorted(const fcb_engine *e) { return e && e->loaded ? e->dates_sorted : -1; }
+
 extern "C" const char *fcb_last_error(const fcb_engine *e) {
     return e ? e->err.c_str() : g_open_error.c_str();
 }
@@ -199,6 +201,10 @@ extern "C" int32_t fcb_load_shard(fcb_engine *e, const fcb_shard *s) {
     e->shard = *s;
     if (e->max_k > FCB_FUSED_MAX_K) {
         const int32_t rc = fcb_general_alloc(e);
+        if (rc != FCB_OK) return rc;
+    }
+    {
+        const int32_t rc = fcb_check_dates_sorted(e);
         if (rc != FCB_OK) return rc;
     }
     if (fcb_dense_eligible(e)) {

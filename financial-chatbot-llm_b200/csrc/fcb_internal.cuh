@@ -63,6 +63,7 @@ struct fcb_engine {
     uint64_t *d_sel_ids = nullptr;         // [kprime_max]
     int kprime_max = 0;
 
+    int dates_sorted = 0;                  // load-time check: dates non-decreasing within every user
     void *dense = nullptr;                 // FcbDense* (fcb_dense.cu): batched tensor-core path scratch
 
     float last_ms = -1.f;
@@ -81,6 +82,8 @@ int32_t fcb_general_alloc(fcb_engine *e);  // called by fcb_load_shard
 void fcb_general_free(fcb_engine *e);
 int32_t fcb_search_general(fcb_engine *e, const double *d_query, const fcb_filter &f, int32_t k,
                            uint64_t *d_out_ids, double *d_out_scores, int32_t *d_out_count, cudaStream_t st);
+
+int32_t fcb_check_dates_sorted(fcb_engine *e);   // fcb_aggregate.cu
 
 // batched tensor-core path (fcb_dense.cu)
 bool fcb_dense_eligible(const fcb_engine *e);

@@ -72,6 +72,18 @@ __global__ void __launch_bounds__(256) synth_columns_kernel(int32_t *__restrict_
     }
 }
 
+// dates non-decreasing within every user: row r of segment [a, b) gets DATE_BASE + floor((r - a) * span / (b - a))
+__global__ void __launch_bounds__(256) synth_dates_sorted_kernel(int32_t *__restrict__ dates, const int64_t *__restrict__ seg_offsets,
+                                                                 int64_t n_segs, int64_t row_lo, int64_t n_rows, uint64_t span) {
+    for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < n_rows; t += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t g = row_lo + t;
+        int64_t lo = 0, hi = n_segs - 1;                           // segment with seg_offsets[u] <= g < seg_offsets[u + 1]
+        while (lo < hi) { const int64_t mid = (lo + hi + 1) >> 1; if (seg_offsets[mid] <= g) lo = mid; else hi = mid - 1; }
+        const uint64_t a = (uint64_t)seg_offsets[lo], b = (uint64_t)seg_offsets[lo + 1];
+        dates[t] = (int32_t)(SYNTH_DATE_BASE + (int64_t)(((uint64_t)g - a) * span / (b - a)));
+    }
+}
+
 static int32_t synth_fail(const char *what, cudaError_t st) {
     return fcb_fail(nullptr, FCB_ERR_CUDA, "%s: %s", what, cudaGetErrorString(st));
 }
@@ -106,4 +118,18 @@ extern "C" int32_t fcb_synth_columns(int32_t device, int32_t *dates, uint8_t *ca
                                                                   (uint32_t)n_categories, (uint64_t)date_span_seconds);
     cudaError_t st = cudaGetLastError();
     return st == cudaSuccess ? FCB_OK : synth_fail("fcb_synth_columns", st);
+}
+
+extern "C" int32_t fcb_synth_dates_sorted(int32_t device, int32_t *dates, const int64_t *seg_offsets, int64_t n_segs,
+                                          int64_t row_lo, int64_t n_rows, int64_t date_span_seconds, void *stream) {
+    if (!dates || !seg_offsets || n_segs <= 0 || n_rows < 0 || date_span_seconds <= 0)
+        return fcb_fail(nullptr, FCB_ERR_INVALID, "fcb_synth_dates_sorted: bad argument");
+    if (n_rows == 0) return FCB_OK;
+    FcbDeviceGuard g(device);
+    if (!g.ok) return fcb_fail(nullptr, FCB_ERR_CUDA, "fcb_synth_dates_sorted: cannot select device %d", device);
+    const unsigned blocks = (unsigned)((n_rows + 255) / 256 < 148 * 16 ? (n_rows + 255) / 256 : 148 * 16);
+    synth_dates_sorted_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(dates, seg_offsets, n_segs, row_lo, n_rows,
+                                                                       (uint64_t)date_span_seconds);
+    cudaError_t st = cudaGetLastError();
+    return st == cudaSuccess ? FCB_OK : synth_fail("fcb_synth_dates_sorted", st);
 }

@@ -135,6 +135,11 @@ class Engine:
     def last_search_ms(self) -> float:
         return float(self._lib.fcb_last_search_ms(self._h))
 
+    @property
+    def dates_sorted(self) -> bool:
+        """True if the loaded shard's dates are non-decreasing within every user (atomic-free aggregation)."""
+        return int(self._lib.fcb_shard_dates_sorted(self._h)) == 1
+
     def last_dense_redo(self, batch: int) -> int:
         """Queries of the last batched tensor-core call answered by the exact re-run (-1: path inactive)."""
         return int(self._lib.fcb_last_dense_redo(self._h, batch))
@@ -182,3 +187,13 @@ def search_noalloc(device: int, shard: FcbShard, d_query, filt: FcbFilter, k: in
                                 C.c_void_p(stream), err, 256)
     if rc != _lib.FCB_OK:
         raise _lib.FcbError(rc, err.value.decode() or "fcb_search_noalloc failed")
+
+
+def synth_dates_sorted(dates, seg_offsets, row_lo: int, date_span_seconds: int) -> None:
+    """Fill CUDA int32 tensor ``dates`` (rows row_lo..) with time-ordered dates per user segment
+    (``seg_offsets``: CUDA int64 CSR offsets in global rows)."""
+    import torch
+    lib = _lib.load()
+    st = torch.cuda.current_stream(dates.device).cuda_stream
+    check(lib.fcb_synth_dates_sorted(dates.device.index, dates.data_ptr(), seg_offsets.data_ptr(),
+                                     seg_offsets.numel() - 1, row_lo, dates.numel(), date_span_seconds, C.c_void_p(st)))

@@ -163,6 +163,14 @@ def dates(spec: SynthSpec, row_lo: int, row_hi: int) -> np.ndarray:
     return (np.int64(DATE_BASE) + (h % U64(spec.date_span_seconds)).astype(np.int64)).astype(np.int32)
 
 
+def dates_sorted(spec: SynthSpec, offsets: np.ndarray, row_lo: int, row_hi: int) -> np.ndarray:
+    """Time-ordered variant: row r of user segment [a, b) gets DATE_BASE + floor((r - a) * span / (b - a))."""
+    rows = np.arange(row_lo, row_hi, dtype=np.int64)
+    u = row_users(offsets, rows)
+    a, b = offsets[u], offsets[u + 1]
+    return (np.int64(DATE_BASE) + (rows - a) * np.int64(spec.date_span_seconds) // (b - a)).astype(np.int32)
+
+
 def categories(spec: SynthSpec, row_lo: int, row_hi: int) -> np.ndarray:
     rows = np.arange(row_lo, row_hi, dtype=U64)
     return (hash_u64(spec.seed, S_CAT, rows) % U64(spec.n_categories)).astype(np.uint8)

@@ -200,6 +200,11 @@ int32_t fcb_merge_topk(int32_t device, const uint64_t *cand_ids, const double *c
                        int32_t batch, int32_t k, uint64_t *out_ids, double *out_scores,
                        int32_t *out_counts, void *stream);
 
+/* 1 if fcb_load_shard found metadata.date non-decreasing within every user segment (a time-ordered
+ * transaction log), 0 if not, -1 without a shard. fcb_aggregate then uses its atomic-free kernel; the
+ * result is the same either way. */
+int32_t fcb_shard_dates_sorted(const fcb_engine *e);
+
 /* Synthetic corpus (no counterpart in the reference, which has no ingestion code or data —
  * SURVEY.md §2 row 13, §8d): counter-based integer generator, bit-identical to
  * financial-chatbot-llm_b200/synth.py, writing straight into caller-owned device buffers. */
@@ -208,6 +213,11 @@ int32_t fcb_synth_vectors(int32_t device, void *out, int32_t dtype, int64_t row_
 int32_t fcb_synth_columns(int32_t device, int32_t *dates, uint8_t *categories, int32_t *cents,
                           int64_t row_lo, int64_t n_rows, uint64_t seed, int32_t n_categories,
                           int64_t date_span_seconds, void *stream);
+
+/* Variant of the date column for time-ordered logs: row r of user segment [a, b) gets
+ * DATE_BASE + floor((r - a) * span / (b - a)) (same integer recipe as synth.dates_sorted). */
+int32_t fcb_synth_dates_sorted(int32_t device, int32_t *dates, const int64_t *seg_offsets, int64_t n_segs,
+                               int64_t row_lo, int64_t n_rows, int64_t date_span_seconds, void *stream);
 
 #ifdef __cplusplus
 }

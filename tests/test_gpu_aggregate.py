@@ -142,3 +142,54 @@ def test_tool_shaped_json_groupby_equals_pandas_golden(built):
     assert out.startswith("data:")
     err = aggregate.create_financial_plot("not json", aggregate.PlotConfig(plot_type="bar", x_axis="a", y_axis="b", title="t", group_by="a"))
     assert err.startswith("Error creating plot:")
+
+
+def test_time_ordered_log_uses_the_atomic_free_kernel_and_matches_pandas(built):
+    """Dates non-decreasing within every user (the load-time check sees it) -> aggregate_sorted_kernel.
+    Same bit-exact answer as pandas; the device generator of ordered dates equals the host recipe."""
+    import torch
+    from financial_chatbot_llm_b200 import aggregate, synth
+    from financial_chatbot_llm_b200.engine import synth_dates_sorted
+    from oracle import groupby
+    sizes = np.array([1, 5, 40000, 3, 129, 4096, 4100, 2, 30000, 127, 128, 7000], dtype=np.int64)
+    off = np.zeros(len(sizes) + 1, dtype=np.int64)
+    np.cumsum(sizes, out=off[1:])
+    n = int(off[-1])
+    spec = synth.SynthSpec(n_rows=n, dim=4, n_users=len(sizes), seed=77)
+    d = synth.dates_sorted(spec, off, 0, n)
+    dd = torch.empty(n - 100, dtype=torch.int32, device="cuda")
+    synth_dates_sorted(dd, torch.from_numpy(off).cuda(), 100, spec.date_span_seconds)
+    assert np.array_equal(dd.cpu().numpy(), d[100:])
+    rng = np.random.default_rng(8)
+    v = rng.integers(-(2 ** 31), 2 ** 31, size=n, dtype=np.int64).astype(np.int32)
+    c = rng.integers(0, 16, size=n).astype(np.uint8)
+    eng, *_ = make_engine(spec, cents=v, dates=d, cats=c, offsets=off)
+    assert eng.dates_sorted
+    mlo, nm = month_window(d)
+    u, cat, mo, s = aggregate.groupby_user_category_month(eng, 0, len(sizes), mlo, nm, 16)
+    ser = groupby.groupby_user_category_month(synth.row_users(off, np.arange(n)), c, d, v)
+    idx = ser.index.to_frame(index=False)
+    assert u.tolist() == idx["user"].tolist() and cat.tolist() == idx["category"].tolist()
+    assert mo.tolist() == idx["month"].tolist() and s.tolist() == ser.tolist()
+    u2, _, _, s2 = aggregate.groupby_user_category_month(eng, 2, 9, mlo, nm, 16)
+    sel = (u >= 2) & (u < 9)
+    assert u2.tolist() == u[sel].tolist() and s2.tolist() == s[sel].tolist()
+    eng.close()
+
+
+def test_atomic_free_kernel_is_correct_for_any_row_order(built, monkeypatch):
+    """Forced onto shuffled dates the ordered-log kernel is slower, never wrong."""
+    from financial_chatbot_llm_b200 import aggregate, synth
+    from oracle import groupby
+    spec = synth.SynthSpec(n_rows=60000, dim=4, n_users=11, seed=78)
+    eng, off, d, c, v = make_engine(spec)
+    assert not eng.dates_sorted
+    mlo, nm = month_window(d)
+    monkeypatch.setenv("FCB_AGG_KERNEL", "sorted")
+    u, cat, mo, s = aggregate.groupby_user_category_month(eng, 0, spec.n_users, mlo, nm, 16)
+    monkeypatch.delenv("FCB_AGG_KERNEL")
+    ser = groupby.groupby_user_category_month(synth.row_users(off, np.arange(spec.n_rows)), c, d, v)
+    idx = ser.index.to_frame(index=False)
+    assert u.tolist() == idx["user"].tolist() and cat.tolist() == idx["category"].tolist()
+    assert mo.tolist() == idx["month"].tolist() and s.tolist() == ser.tolist()
+    eng.close()
