@@ -193,15 +193,24 @@ __global__ void __launch_bounds__(AGG_THREADS, 4) aggregate_kernel(const __grid_
 // selects this kernel when the load-time check found the dates non-decreasing within every user.
 #define AGS_WARP_ROWS 4096                 // consecutive rows one warp takes per task
 
+#define AGS_SMALL_PIECE 1024               // shorter pieces (tiny users): per-row 64-bit global reductions
+
 __global__ void __launch_bounds__(AGG_THREADS, 4) aggregate_sorted_kernel(const __grid_constant__ AggParams p) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int C = p.n_categories * p.n_months;
-    uint16_t *month_tab = reinterpret_cast<uint16_t *>(smem_raw);                                   // [n_days]
-    long long *bins_all = reinterpret_cast<long long *>(smem_raw + (((size_t)p.n_days * 2 + 15) & ~(size_t)15));
+    uint16_t *month_tab = reinterpret_cast<uint16_t *>(smem_raw);                                   // [n_days] day -> month
+    uint32_t *mstart = reinterpret_cast<uint32_t *>(smem_raw + (((size_t)p.n_days * 2 + 15) & ~(size_t)15));   // [n_months + 1]
+    long long *bins_all = reinterpret_cast<long long *>(reinterpret_cast<unsigned char *>(mstart) +
+                                                        (((size_t)(p.n_months + 1) * 4 + 15) & ~(size_t)15));
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     long long *bins = bins_all + (size_t)warp * p.n_categories * 32;                                // [n_categories][32]
     for (int i = tid; i < p.n_days; i += AGG_THREADS) month_tab[i] = (uint16_t)(month_of_day(p.day0 + i) - p.month_lo);
     for (int i = lane; i < p.n_categories * 32; i += 32) bins[i] = 0;
+    __syncthreads();
+    // seconds (relative to the window start) at which each month of the window begins
+    for (int i = tid; i < p.n_days; i += AGG_THREADS)
+        if (i == 0 || month_tab[i] != month_tab[i - 1]) mstart[month_tab[i]] = (uint32_t)i * 86400u;
+    if (tid == 0) mstart[p.n_months] = (uint32_t)p.n_days * 86400u;
     __syncthreads();
 
     int64_t R0 = p.seg_offsets[p.seg_begin], R1 = p.seg_offsets[p.seg_end];
@@ -211,35 +220,62 @@ __global__ void __launch_bounds__(AGG_THREADS, 4) aggregate_sorted_kernel(const 
     const int4 *cents4 = reinterpret_cast<const int4 *>(p.cents);
     const int4 *dates4 = reinterpret_cast<const int4 *>(p.dates);
     const uchar4 *cats4 = reinterpret_cast<const uchar4 *>(p.cats);
+    const int64_t t_window = (int64_t)p.day0 * 86400;
+    const uint32_t window_len = (uint32_t)p.n_days * 86400u;
     unsigned dropped = 0;
 
     int64_t cur_user = -1;
     int cur_month = -1;
+    uint32_t cur_base = 0, cur_len = 0;                             // the current run's month as [base, base + len) unix seconds (mod 2^32)
     uint32_t seen = 0;                                              // categories this lane added to since the last flush
 
+    // end of a (user, month) run: lane c sums row c of the warp's bin matrix (skewed column order: no bank
+    // conflicts), clears it, and issues the one 64-bit global reduction of that cell
     auto flush = [&]() {
-        if (cur_month >= 0) {
-            int64_t *out_s = p.sums + (cur_user - p.seg_begin) * (int64_t)C;
-            uint8_t *out_p = p.present + (cur_user - p.seg_begin) * (int64_t)C;
-            uint32_t any = seen;
+        uint32_t any = seen;
 #pragma unroll
-            for (int off = 16; off >= 1; off >>= 1) any |= __shfl_xor_sync(FCB_FULL, any, off);
-            long long mine = 0;                                     // lane c ends up with the total of category c
-            for (int c = 0; c < p.n_categories; ++c) {
-                if (!((any >> c) & 1u)) continue;                   // warp-uniform
-                long long v = bins[c * 32 + lane];
-                bins[c * 32 + lane] = 0;
-#pragma unroll
-                for (int off = 16; off >= 1; off >>= 1) v += __shfl_xor_sync(FCB_FULL, v, off);
-                if (lane == c) mine = v;
-            }
+        for (int off = 16; off >= 1; off >>= 1) any |= __shfl_xor_sync(FCB_FULL, any, off);
+        if (cur_month >= 0 && any != 0) {
+            __syncwarp();
             if (lane < p.n_categories && ((any >> lane) & 1u)) {
+                long long total = 0;
+#pragma unroll 8
+                for (int i = 0; i < 32; ++i) {
+                    const int col = (i + lane) & 31;
+                    total += bins[lane * 32 + col];
+                    bins[lane * 32 + col] = 0;
+                }
                 const int cell = lane * p.n_months + cur_month;
-                atomicAdd(reinterpret_cast<unsigned long long *>(out_s + cell), (unsigned long long)mine);
-                out_p[cell] = 1;
+                int64_t *out_s = p.sums + (cur_user - p.seg_begin) * (int64_t)C;
+                atomicAdd(reinterpret_cast<unsigned long long *>(out_s + cell), (unsigned long long)total);
+                p.present[(cur_user - p.seg_begin) * (int64_t)C + cell] = 1;
             }
+            __syncwarp();
         }
         seen = 0;
+    };
+    auto set_month = [&](int mo) {
+        cur_month = mo;
+        cur_base = mo >= 0 ? (uint32_t)t_window + mstart[mo] : 0;
+        cur_len = mo >= 0 ? mstart[mo + 1] - mstart[mo] : 0;
+    };
+
+    struct Quad { int4 v, d; uchar4 c; };
+    auto load_quad = [&](int64_t r, int64_t lb) {
+        Quad q;
+        q.v = make_int4(0, 0, 0, 0); q.d = make_int4(0, 0, 0, 0); q.c = make_uchar4(0, 0, 0, 0);
+        if (r < lb) {
+            if (r + 4 <= p.n_rows) {
+                q.v = __ldg(cents4 + (r >> 2)); q.d = __ldg(dates4 + (r >> 2)); q.c = __ldg(cats4 + (r >> 2));
+            } else {
+                int v[4] = {0, 0, 0, 0}, d[4] = {0, 0, 0, 0};
+                unsigned char c[4] = {0, 0, 0, 0};
+                for (int i = 0; i < 4 && r + i < p.n_rows; ++i) { v[i] = p.cents[r + i]; d[i] = p.dates[r + i]; c[i] = p.cats[r + i]; }
+                q.v = make_int4(v[0], v[1], v[2], v[3]); q.d = make_int4(d[0], d[1], d[2], d[3]);
+                q.c = make_uchar4(c[0], c[1], c[2], c[3]);
+            }
+        }
+        return q;
     };
 
     const int64_t n_warps = (int64_t)gridDim.x * (AGG_THREADS / 32);
@@ -260,45 +296,80 @@ __global__ void __launch_bounds__(AGG_THREADS, 4) aggregate_sorted_kernel(const 
             int64_t uend = p.seg_offsets[u + 1];
             while (uend <= pa) { ++u; uend = p.seg_offsets[u + 1]; }
             const int64_t pb = uend < b ? uend : b;
-            if (u != cur_user) { flush(); cur_user = u; cur_month = -1; }
             const int64_t la = pa - p.row_base, lb = pb - p.row_base;
-            for (int64_t base = la & ~(int64_t)3; base < lb; base += 128) {
-                const int64_t r = base + 4 * lane;                  // this lane's quad of local rows
-                int v[4], m[4];
-                unsigned cat[4];
-                if (r + 4 <= p.n_rows && r < lb) {
-                    const int4 vv = __ldg(cents4 + (r >> 2));
-                    const int4 dd = __ldg(dates4 + (r >> 2));
-                    const uchar4 cc = __ldg(cats4 + (r >> 2));
-                    v[0] = vv.x; v[1] = vv.y; v[2] = vv.z; v[3] = vv.w;
-                    m[0] = dd.x; m[1] = dd.y; m[2] = dd.z; m[3] = dd.w;
-                    cat[0] = cc.x; cat[1] = cc.y; cat[2] = cc.z; cat[3] = cc.w;
-                } else {
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) {
-                        const bool in = r + i < p.n_rows && r + i < lb;
-                        v[i] = in ? p.cents[r + i] : 0; m[i] = in ? p.dates[r + i] : 0; cat[i] = in ? p.cats[r + i] : 0;
-                    }
+            if (pb - pa < AGS_SMALL_PIECE) {
+                // tiny user: months change every few rows, a run is not worth setting up
+                int64_t *out_s = p.sums + (u - p.seg_begin) * (int64_t)C;
+                uint8_t *out_p = p.present + (u - p.seg_begin) * (int64_t)C;
+                for (int64_t r = la + lane; r < lb; r += 32) {
+                    const unsigned cat = p.cats[r];
+                    const uint64_t off_s = (uint64_t)((int64_t)p.dates[r] - t_window);
+                    const unsigned mo = off_s < window_len ? month_tab[(uint32_t)off_s / 86400u] : 0xffffu;
+                    if (cat >= (unsigned)p.n_categories || mo >= (unsigned)p.n_months) { ++dropped; continue; }
+                    const int cell = cat * p.n_months + mo;
+                    atomicAdd(reinterpret_cast<unsigned long long *>(out_s + cell), (unsigned long long)(long long)p.cents[r]);
+                    out_p[cell] = 1;
                 }
+                pa = pb;
+                continue;
+            }
+            if (u != cur_user) { flush(); cur_user = u; set_month(-1); }
+            int64_t base = la & ~(int64_t)3;
+            Quad nxt = load_quad(base + 4 * lane, lb);              // software pipeline: next step's columns in flight
+            for (; base < lb; base += 128) {
+                const int64_t r = base + 4 * lane;
+                const Quad q = nxt;
+                if (base + 128 < lb) nxt = load_quad(r + 128, lb);
+                const int v[4] = {q.v.x, q.v.y, q.v.z, q.v.w};
+                const int dts[4] = {q.d.x, q.d.y, q.d.z, q.d.w};
+                const unsigned cat[4] = {q.c.x, q.c.y, q.c.z, q.c.w};
+                // fast path: every row of the step lies in the current run's month and has a valid category.
+                // One wrapping 32-bit subtract + one unsigned compare per row against the month's
+                // [base, base + len) — exact modulo 2^32, so a date outside the window can never alias into it.
+                const bool interior = r >= la && r + 4 <= lb;
+                unsigned in_mask = interior ? 0xfu : 0u;
+                if (!interior) {
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) if (r + i >= la && r + i < lb) in_mask |= 1u << i;
+                }
+                bool same = true;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const bool hit = (uint32_t)dts[i] - cur_base < cur_len && cat[i] < (unsigned)p.n_categories;
+                    same = same && (hit || !((in_mask >> i) & 1u));
+                }
+                if (__all_sync(FCB_FULL, same)) {
+                    if (interior) {
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) { bins[cat[i] * 32 + lane] += (long long)v[i]; seen |= 1u << cat[i]; }
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            if ((in_mask >> i) & 1u) { bins[cat[i] * 32 + lane] += (long long)v[i]; seen |= 1u << cat[i]; }
+                        }
+                    }
+                    continue;
+                }
+                // a month boundary in this step: resolve months properly, one month at a time, flushing in between
+                int m[4];
                 unsigned todo = 0;
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
-                    const bool in = r + i >= la && r + i < lb;
-                    const int32_t di = floor_day(m[i]) - p.day0;
-                    const unsigned mo = (unsigned)di < (unsigned)p.n_days ? month_tab[di] : 0xffffu;
+                    const bool in = (in_mask >> i) & 1u;
+                    const uint64_t off_s = (uint64_t)((int64_t)dts[i] - t_window);
+                    const unsigned mo = off_s < window_len ? month_tab[(uint32_t)off_s / 86400u] : 0xffffu;
                     const bool ok = in && cat[i] < (unsigned)p.n_categories && mo < (unsigned)p.n_months;
                     if (in && !ok) ++dropped;
                     m[i] = ok ? (int)mo : 0x7fffffff;
                     if (ok) todo |= 1u << i;
                 }
-                // months present in this step, one at a time (normally one; two at a month boundary)
                 while (__any_sync(FCB_FULL, todo != 0)) {
                     int mn = 0x7fffffff;
 #pragma unroll
                     for (int i = 0; i < 4; ++i) if ((todo >> i) & 1u) mn = min(mn, m[i]);
 #pragma unroll
                     for (int off = 16; off >= 1; off >>= 1) mn = min(mn, __shfl_xor_sync(FCB_FULL, mn, off));
-                    if (mn != cur_month) { flush(); cur_month = mn; }
+                    if (mn != cur_month) { flush(); set_month(mn); }
 #pragma unroll
                     for (int i = 0; i < 4; ++i) {
                         if (((todo >> i) & 1u) && m[i] == cur_month) {
@@ -389,7 +460,8 @@ extern "C" int32_t fcb_aggregate(fcb_engine *e, int64_t seg_begin, int64_t seg_e
     const bool sorted_ok = n_categories <= 32;
     const bool use_sorted = sorted_ok && (force ? force[0] == 's' : e->dates_sorted != 0);
     if (use_sorted) {
-        const size_t smem_s = (((size_t)p.n_days * 2 + 15) & ~(size_t)15) + (size_t)(AGG_THREADS / 32) * n_categories * 32 * 8;
+        const size_t smem_s = (((size_t)p.n_days * 2 + 15) & ~(size_t)15) + (((size_t)(n_months + 1) * 4 + 15) & ~(size_t)15) +
+                              (size_t)(AGG_THREADS / 32) * n_categories * 32 * 8;
         if (smem_s > 48 * 1024)
             FCB_CUDA(e, cudaFuncSetAttribute(aggregate_sorted_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_s));
         aggregate_sorted_kernel<<<e->num_sms * 4, AGG_THREADS, smem_s, st>>>(p);

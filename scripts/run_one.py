@@ -27,13 +27,16 @@ if which == "cfg3":
     names = ["producer total", "  wait free stage", "mma total", "  wait tmem drained", "  wait full stage", "epilogue total",
              "  wait accumulators", "  scan tmem", "  fold candidates", "super-tiles"]
     for n, v in zip(names, prof.cpu().tolist()): print(f"{n:24s} {v}")
-elif which == "cfg5":
+elif which in ("cfg5", "cfg5s"):
     n, users = 1_000_000_000, 100_000
     spec = synth.SynthSpec(n_rows=n, dim=4, n_users=users, seed=5, zipf_a=1.1)
     d = torch.empty(n, dtype=torch.int32, device=DEV); c = torch.empty(n, dtype=torch.uint8, device=DEV)
     v = torch.empty(n, dtype=torch.int32, device=DEV)
     synth_columns(0, n, spec.seed, 16, spec.date_span_seconds, dates=d, categories=c, cents=v)
     off = synth.segment_offsets(spec)
+    if which == "cfg5s":
+        from financial_chatbot_llm_b200.engine import synth_dates_sorted
+        synth_dates_sorted(d, torch.from_numpy(off).to(DEV), 0, spec.date_span_seconds)
     eng = Engine(device=0, max_batch=1, max_k=1)
     eng.load_shard(torch.zeros((n, 4), dtype=torch.float32, device=DEV), dates=d, categories=c, cents=v,
                    seg_offsets=torch.from_numpy(off).to(DEV))
