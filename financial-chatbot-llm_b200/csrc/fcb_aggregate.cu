@@ -314,24 +314,13 @@ __global__ void __launch_bounds__(AGG_THREADS, 4) aggregate_sorted_kernel(const 
                 continue;
             }
             if (u != cur_user) { flush(); cur_user = u; set_month(-1); }
-            int64_t base = la & ~(int64_t)3;
-            Quad nxt = load_quad(base + 4 * lane, lb);              // software pipeline: next step's columns in flight
-            for (; base < lb; base += 128) {
-                const int64_t r = base + 4 * lane;
-                const Quad q = nxt;
-                if (base + 128 < lb) nxt = load_quad(r + 128, lb);
+
+            // one step of <= 128 rows whose rows `in_mask` belong to the piece: fast path if they all continue
+            // the current run, else resolve the months one at a time, flushing in between
+            auto step = [&](const Quad &q, unsigned in_mask) {
                 const int v[4] = {q.v.x, q.v.y, q.v.z, q.v.w};
                 const int dts[4] = {q.d.x, q.d.y, q.d.z, q.d.w};
                 const unsigned cat[4] = {q.c.x, q.c.y, q.c.z, q.c.w};
-                // fast path: every row of the step lies in the current run's month and has a valid category.
-                // One wrapping 32-bit subtract + one unsigned compare per row against the month's
-                // [base, base + len) — exact modulo 2^32, so a date outside the window can never alias into it.
-                const bool interior = r >= la && r + 4 <= lb;
-                unsigned in_mask = interior ? 0xfu : 0u;
-                if (!interior) {
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) if (r + i >= la && r + i < lb) in_mask |= 1u << i;
-                }
                 bool same = true;
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
@@ -339,18 +328,12 @@ __global__ void __launch_bounds__(AGG_THREADS, 4) aggregate_sorted_kernel(const 
                     same = same && (hit || !((in_mask >> i) & 1u));
                 }
                 if (__all_sync(FCB_FULL, same)) {
-                    if (interior) {
 #pragma unroll
-                        for (int i = 0; i < 4; ++i) { bins[cat[i] * 32 + lane] += (long long)v[i]; seen |= 1u << cat[i]; }
-                    } else {
-#pragma unroll
-                        for (int i = 0; i < 4; ++i) {
-                            if ((in_mask >> i) & 1u) { bins[cat[i] * 32 + lane] += (long long)v[i]; seen |= 1u << cat[i]; }
-                        }
+                    for (int i = 0; i < 4; ++i) {
+                        if ((in_mask >> i) & 1u) { bins[cat[i] * 32 + lane] += (long long)v[i]; seen |= 1u << cat[i]; }
                     }
-                    continue;
+                    return;
                 }
-                // a month boundary in this step: resolve months properly, one month at a time, flushing in between
                 int m[4];
                 unsigned todo = 0;
 #pragma unroll
@@ -379,7 +362,44 @@ __global__ void __launch_bounds__(AGG_THREADS, 4) aggregate_sorted_kernel(const 
                         }
                     }
                 }
+            };
+            auto ragged = [&](int64_t base) {                      // a step that may stick out of [la, lb) / the arrays
+                const int64_t r = base + 4 * lane;
+                unsigned in_mask = 0;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) if (r + i >= la && r + i < lb) in_mask |= 1u << i;
+                step(load_quad(r, lb), in_mask);
+            };
+
+            int64_t base = la & ~(int64_t)3;
+            if (base < la) { ragged(base); base += 128; }           // head: first quad not aligned with the piece
+            // full steps: all 128 rows inside the piece; plain pointer bumps, next step's columns already in flight
+            const int64_t full_end = lb - 127;                      // base < full_end  <=>  base + 128 <= lb
+            if (base < full_end) {
+                const int4 *pv = cents4 + (base >> 2) + lane, *pd = dates4 + (base >> 2) + lane;
+                const uchar4 *pc = cats4 + (base >> 2) + lane;
+                Quad nxt;
+                nxt.v = __ldg(pv); nxt.d = __ldg(pd); nxt.c = __ldg(pc);
+                for (; base < full_end; base += 128) {
+                    const Quad q = nxt;
+                    if (base + 128 < full_end) { pv += 32; pd += 32; pc += 32; nxt.v = __ldg(pv); nxt.d = __ldg(pd); nxt.c = __ldg(pc); }
+                    // inlined fast path (the compiler keeps it branch-light); anything else goes through step()
+                    const bool same =
+                        (uint32_t)q.d.x - cur_base < cur_len && (uint32_t)q.d.y - cur_base < cur_len &&
+                        (uint32_t)q.d.z - cur_base < cur_len && (uint32_t)q.d.w - cur_base < cur_len &&
+                        max(max((unsigned)q.c.x, (unsigned)q.c.y), max((unsigned)q.c.z, (unsigned)q.c.w)) < (unsigned)p.n_categories;
+                    if (__all_sync(FCB_FULL, same)) {
+                        bins[q.c.x * 32 + lane] += (long long)q.v.x;
+                        bins[q.c.y * 32 + lane] += (long long)q.v.y;
+                        bins[q.c.z * 32 + lane] += (long long)q.v.z;
+                        bins[q.c.w * 32 + lane] += (long long)q.v.w;
+                        seen |= (1u << q.c.x) | (1u << q.c.y) | (1u << q.c.z) | (1u << q.c.w);
+                    } else {
+                        step(q, 0xfu);
+                    }
+                }
             }
+            if (base < lb) ragged(base);                            // tail
             pa = pb;
         }
     }
