@@ -325,7 +325,7 @@ dense_topk_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
 // accumulators-drained barrier.
 #define DN2_THREADS 640                    // 4 service warps + 16 epilogue warps (two per TMEM lane quarter and accumulator)
 #define DN2_EPI_THREADS 512
-#define DN2_MAX_STAGES 4                   // 4 x 48 KB of stages when the per-query lists are small (batch <= 128), else 3
+#define DN2_MAX_STAGES 4                   // 4 x 48 KB of stages when the per-query lists are small (batch <= 96), else 3
 #define DN2_STAGE_BYTES (2 * DN_A_BYTES + DN_B_BYTES / 2)   // 48 KB: A0, A1, half of B (max N = 256)
 #define DN2_SUPER_M 512
 
@@ -807,7 +807,7 @@ int32_t fcb_dense_alloc(fcb_engine *e) {
     if (rc != FCB_OK) { fcb_dense_free(e); return rc; }
     const size_t smem = (size_t)DN_STAGES * DN_STAGE_BYTES + 4096;
     FCB_CUDA(e, cudaFuncSetAttribute(dense_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    const size_t smem2 = (size_t)3 * DN2_STAGE_BYTES + 4096 + (size_t)DN_N * FCB_FUSED_CAND * sizeof(FcbCand);   // also covers 4 stages + 128 lists
+    const size_t smem2 = (size_t)4 * DN2_STAGE_BYTES + 4096 + (size_t)96 * FCB_FUSED_CAND * sizeof(FcbCand);   // 4 stages + 96 lists >= 3 stages + 256 lists
     FCB_CUDA(e, cudaFuncSetAttribute(dense_topk2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
     return FCB_OK;
 }
@@ -847,7 +847,7 @@ int32_t fcb_search_dense(fcb_engine *e, const double *d_queries, const fcb_filte
     p.n_queries = batch; p.n_eff = ((batch + 31) / 32) * 32;
     p.cta_top = d->cta_top; p.pend = d->pend; p.error_flag = d->error_flag;
     p.debug_out = g_debug_out; p.debug_rows = g_debug_rows; p.prof = g_dense_prof;
-    p.n_stages = p.n_eff <= 128 ? 4 : 3;                             // lists (n_eff x 256 B) + stages must fit 227 KB
+    p.n_stages = p.n_eff <= 96 ? 4 : 3;                              // stages + 4 KB + lists (n_eff x 256 B) must fit 227 KB
     const size_t smem = (size_t)DN_STAGES * DN_STAGE_BYTES + 4096;
     if (d->two_cta) {
         const size_t smem2 = (size_t)p.n_stages * DN2_STAGE_BYTES + 4096 + (size_t)p.n_eff * FCB_FUSED_CAND * sizeof(FcbCand);
