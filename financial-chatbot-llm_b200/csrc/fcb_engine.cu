@@ -26,9 +26,7 @@ extern "C" const char *fcb_last_error(const fcb_engine *e) {
 
 static void free_host_staging(fcb_engine *e) {
     cudaFreeHost(e->h_q); cudaFree(e->d_q);
-    cudaFreeHost(e->h_ids); cudaFree(e->d_ids);
-    cudaFreeHost(e->h_scores); cudaFree(e->d_scores);
-    cudaFreeHost(e->h_counts); cudaFree(e->d_counts);
+    cudaFreeHost(e->h_ids); cudaFree(e->d_ids);          // one block each: ids | scores | counts
     e->h_q = e->d_q = nullptr; e->h_ids = e->d_ids = nullptr;
     e->h_scores = e->d_scores = nullptr; e->h_counts = e->d_counts = nullptr;
 }
@@ -192,12 +190,14 @@ extern "C" int32_t fcb_load_shard(fcb_engine *e, const fcb_shard *s) {
     const size_t B = e->max_batch, K = e->max_k;
     FCB_CUDA(e, cudaMallocHost(&e->h_q, B * s->dim * sizeof(double)));
     FCB_CUDA(e, cudaMalloc(&e->d_q, B * s->dim * sizeof(double)));
-    FCB_CUDA(e, cudaMallocHost(&e->h_ids, B * K * sizeof(uint64_t)));
-    FCB_CUDA(e, cudaMalloc(&e->d_ids, B * K * sizeof(uint64_t)));
-    FCB_CUDA(e, cudaMallocHost(&e->h_scores, B * K * sizeof(double)));
-    FCB_CUDA(e, cudaMalloc(&e->d_scores, B * K * sizeof(double)));
-    FCB_CUDA(e, cudaMallocHost(&e->h_counts, B * sizeof(int32_t)));
-    FCB_CUDA(e, cudaMalloc(&e->d_counts, B * sizeof(int32_t)));
+    // results of the host entry point: ONE block (ids | scores | counts) so that one copy brings them back
+    const size_t res_bytes = B * K * 16 + B * sizeof(int32_t);
+    FCB_CUDA(e, cudaMallocHost(&e->h_ids, res_bytes));
+    FCB_CUDA(e, cudaMalloc(&e->d_ids, res_bytes));
+    e->h_scores = reinterpret_cast<double *>(e->h_ids + B * K);
+    e->d_scores = reinterpret_cast<double *>(e->d_ids + B * K);
+    e->h_counts = reinterpret_cast<int32_t *>(e->h_scores + B * K);
+    e->d_counts = reinterpret_cast<int32_t *>(e->d_scores + B * K);
     e->shard = *s;
     if (e->max_k > FCB_FUSED_MAX_K) {
         const int32_t rc = fcb_general_alloc(e);

@@ -544,16 +544,18 @@ extern "C" int32_t fcb_search_host(fcb_engine *e, const double *queries, const f
     cudaStream_t st = e->stream;
     FCB_CUDA(e, cudaMemcpyAsync(e->d_q, e->h_q, qn * sizeof(double), cudaMemcpyHostToDevice, st));
     FCB_CUDA(e, cudaEventRecord(e->ev0, st));
-    rc = search_device(e, e->d_q, filters, batch, k, e->d_ids, e->d_scores, e->d_counts, st);
+    // results are laid out for THIS call's (batch, k) inside the one staging block: ids | scores | counts
+    uint64_t *d_ids = e->d_ids, *h_ids = e->h_ids;
+    double *d_scores = reinterpret_cast<double *>(d_ids + rn), *h_scores = reinterpret_cast<double *>(h_ids + rn);
+    int32_t *d_counts = reinterpret_cast<int32_t *>(d_scores + rn), *h_counts = reinterpret_cast<int32_t *>(h_scores + rn);
+    rc = search_device(e, e->d_q, filters, batch, k, d_ids, d_scores, d_counts, st);
     if (rc != FCB_OK) return rc;
     FCB_CUDA(e, cudaEventRecord(e->ev1, st));
-    FCB_CUDA(e, cudaMemcpyAsync(e->h_ids, e->d_ids, rn * sizeof(uint64_t), cudaMemcpyDeviceToHost, st));
-    FCB_CUDA(e, cudaMemcpyAsync(e->h_scores, e->d_scores, rn * sizeof(double), cudaMemcpyDeviceToHost, st));
-    FCB_CUDA(e, cudaMemcpyAsync(e->h_counts, e->d_counts, (size_t)batch * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    FCB_CUDA(e, cudaMemcpyAsync(h_ids, d_ids, rn * 16 + (size_t)batch * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
     FCB_CUDA(e, cudaStreamSynchronize(st));
-    memcpy(out_ids, e->h_ids, rn * sizeof(uint64_t));
-    memcpy(out_scores, e->h_scores, rn * sizeof(double));
-    memcpy(out_counts, e->h_counts, (size_t)batch * sizeof(int32_t));
+    memcpy(out_ids, h_ids, rn * sizeof(uint64_t));
+    memcpy(out_scores, h_scores, rn * sizeof(double));
+    memcpy(out_counts, h_counts, (size_t)batch * sizeof(int32_t));
     float ms = -1.f;
     if (cudaEventElapsedTime(&ms, e->ev0, e->ev1) == cudaSuccess) e->last_ms = ms;
     return FCB_OK;

@@ -92,7 +92,7 @@ class ShardMerger:
         else:
             if not self.gathered.is_cuda:
                 raise _lib.FcbError(_lib.FCB_ERR_CUDA, "the shard merge runs on the GPU only (no CPU path)")
-            cuda_merge(self.device.index, self.gathered, self.world, self.batch, self.k, self.merged)
+            cuda_merge(self.gathered.device.index, self.gathered, self.world, self.batch, self.k, self.merged)
 
 
 def shard_ranges(n_rows: int, world: int, offsets: Optional[np.ndarray] = None) -> List[tuple]:

@@ -212,12 +212,29 @@ def page_content(user: str, date: int, category: int, cents_v: int, row: int) ->
             f"{sign}${a // 100}.{a % 100:02d} merchant_{row % 9973:04d} (txn {row})")
 
 
+_MASK64 = (1 << 64) - 1
+
+
+def _hash_int(seed: int, stream: int, idx: int) -> int:
+    """hash_u64 for ONE index in plain Python integers (payloads of the k winners: no numpy overhead)."""
+    x = (((seed & _MASK64) ^ ((stream * int(_STREAM_MUL)) & _MASK64)) + idx * int(_GOLDEN)) & _MASK64
+    x ^= x >> 30
+    x = (x * int(_M1)) & _MASK64
+    x ^= x >> 27
+    x = (x * int(_M2)) & _MASK64
+    x ^= x >> 31
+    return x
+
+
 def payload_for_row(spec: SynthSpec, offsets: np.ndarray, uids: Sequence[str], row: int) -> dict:
-    """Payload dict in the layout the reference reads (tools/qdrant_tool.py:160-164)."""
-    u = int(row_users(offsets, np.array([row]))[0])
-    d = int(dates(spec, row, row + 1)[0])
-    c = int(categories(spec, row, row + 1)[0])
-    v = int(cents(spec, row, row + 1)[0])
+    """Payload dict in the layout the reference reads (tools/qdrant_tool.py:160-164). Same values as the
+    column generators (dates / categories / cents) for this row."""
+    u = int(np.searchsorted(offsets, row, side="right")) - 1
+    d = DATE_BASE + _hash_int(spec.seed, S_DATE, row) % spec.date_span_seconds
+    c = _hash_int(spec.seed, S_CAT, row) % spec.n_categories
+    h = _hash_int(spec.seed, S_CENTS, row)
+    mag = ((1024 + ((h >> 8) & 1023)) << ((h & 0xFF) % 18)) >> 10
+    v = -mag if ((h >> 40) & 7) == 0 else mag
     return {
         "page_content": page_content(uids[u], d, c, v, row),
         "metadata": {"user_id": uids[u], "date": d, "category": CATEGORIES[c % len(CATEGORIES)],
