@@ -116,6 +116,14 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t *v) {
                  : "r"(taddr) : "memory");
 }
 
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t *v) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+                 "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                   "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+                 : "r"(taddr) : "memory");
+}
+
 // shared-memory matrix descriptor, K-major, 128-byte swizzle (cute::UMMA::SmemDescriptor layout):
 // start>>4 [0,14) | LBO>>4 [16,30) = 1 (unused) | SBO>>4 [32,46) = 1024 B between 8-row groups |
 // version [46,48) = 1 | layout_type [61,64) = 2 (SWIZZLE_128B)
@@ -494,21 +502,17 @@ dense_topk2_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const uint32_t taddr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + acc * DN_N;
             const int c_begin = col_half * (DN_N / 2), c_end = min(p.n_eff, c_begin + DN_N / 2);
-#pragma unroll 1
-            for (int c = c_begin; c < c_end; c += 32) {
-                uint32_t v[32];
-                tmem_ld32(taddr + c, v);
-                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+            // one 16-column chunk of this row: branch-free pass mask (thresholds: 4 broadcast 128-bit shared loads),
+            // then the rare survivors are pushed from an unrolled bit scan (no dynamic register indexing)
+            auto process = [&](const uint32_t (&v)[16], const int c) {
                 if (p.debug_out != nullptr && row - lo < p.debug_rows) {
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) p.debug_out[(row - lo) * DN_N + c + j] = __uint_as_float(v[j]);
+                    for (int j = 0; j < 16; ++j) p.debug_out[(row - lo) * DN_N + c + j] = __uint_as_float(v[j]);
                 }
-                // branch-free pass mask of this row's 32 scores (thresholds: 8 broadcast 128-bit shared loads),
-                // then the rare survivors are pushed from an unrolled bit scan (no dynamic register indexing)
                 uint32_t mask = 0;
                 const float4 *t4 = reinterpret_cast<const float4 *>(thr_s + c);
 #pragma unroll
-                for (int j4 = 0; j4 < 8; ++j4) {
+                for (int j4 = 0; j4 < 4; ++j4) {
                     const float4 t = t4[j4];
                     const float s0 = __uint_as_float(v[4 * j4 + 0]) * inv, s1 = __uint_as_float(v[4 * j4 + 1]) * inv,
                                 s2 = __uint_as_float(v[4 * j4 + 2]) * inv, s3 = __uint_as_float(v[4 * j4 + 3]) * inv;
@@ -517,16 +521,31 @@ dense_topk2_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
                     mask |= ((uint32_t)p0 | ((uint32_t)p1 << 1) | ((uint32_t)p2 << 2) | ((uint32_t)p3 << 3)) << (4 * j4);
                 }
                 const int left = p.n_queries - c;                      // padding columns never qualify
-                mask &= left >= 32 ? 0xffffffffu : ((1u << left) - 1u);
+                mask &= left >= 16 ? 0xffffu : ((1u << (left > 0 ? left : 0)) - 1u);
                 if (valid && mask) {
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) {
+                    for (int j = 0; j < 16; ++j) {
                         if (mask & (1u << j)) {
                             const int slot = atomicAdd(&cnt_s[c + j], 1);
                             my_pend[(size_t)(c + j) * DN_PEND_CAP + slot] = FcbCand{__uint_as_float(v[j]) * inv, (uint32_t)row};
                         }
                     }
                 }
+            };
+            // double-buffered TMEM reads: the next chunk's tcgen05.ld is in flight while this chunk is scanned
+            uint32_t va[16], vb[16];
+            if (c_begin < c_end) {
+                tmem_ld16(taddr + c_begin, va);
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+            }
+#pragma unroll 1
+            for (int c = c_begin; c < c_end; c += 32) {                 // c_end - c_begin is a multiple of 32
+                tmem_ld16(taddr + c + 16, vb);
+                process(va, c);
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                if (c + 32 < c_end) tmem_ld16(taddr + c + 32, va);
+                process(vb, c + 16);
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
             }
             asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
             mbar_arrive_cta0(tmem_empty);                              // the leader's MMA may overwrite both TMEMs
