@@ -152,13 +152,16 @@ __global__ void __launch_bounds__(FCB_SCAN_THREADS, 2) scan_keys_kernel(const __
 }
 
 // (prefix, remaining) after `passes` completed radix passes; all threads of the CTA call this.
-// K' = min(kprime, n_pass). remaining == 0 means "nothing to select".
+// K' = min(kprime, n_pass). remaining == 0 means "nothing to select". `settled` is set once the score
+// bits (passes 0..3) are resolved AND every key of the final bucket is wanted (remaining == bucket size,
+// i.e. no tie straddles the cut): the tie-order passes 4..7 then have nothing to decide and are skipped.
 __device__ void resolve_state(const FcbSelectState *st, int passes, unsigned kprime, uint64_t &prefix,
-                              unsigned &remaining, unsigned *s_scan /* [256] */, unsigned *s_out /* [2] */) {
+                              unsigned &remaining, bool &settled, unsigned *s_scan /* [256] */, unsigned *s_out /* [3] */) {
     const int tid = threadIdx.x;
     unsigned rem = st->n_pass < kprime ? st->n_pass : kprime;
     uint64_t pre = 0;
-    for (int q = 0; q < passes && rem > 0; ++q) {
+    bool done = false;
+    for (int q = 0; q < passes && rem > 0 && !done; ++q) {
         // suffix-inclusive sums over digits 255..0 (Hillis-Steele on reversed index)
         const unsigned h = tid < 256 ? st->hist[q][255 - tid] : 0;       // position tid <-> digit 255 - tid
         if (tid < 256) s_scan[tid] = h;
@@ -172,33 +175,44 @@ __device__ void resolve_state(const FcbSelectState *st, int passes, unsigned kpr
         }
         if (tid < 256) {
             const unsigned incl = s_scan[tid], excl = incl - h;           // keys with a larger digit: excl
-            if (excl < rem && rem <= incl) { s_out[0] = 255 - tid; s_out[1] = rem - excl; }
+            if (excl < rem && rem <= incl) { s_out[0] = 255 - tid; s_out[1] = rem - excl; s_out[2] = h; }
         }
         __syncthreads();
         pre |= (uint64_t)s_out[0] << (56 - 8 * q);
         rem = s_out[1];
+        done = q >= 3 && rem == s_out[2];
         __syncthreads();
     }
     prefix = pre;
     remaining = rem;
+    settled = done;
 }
 
 __global__ void __launch_bounds__(SEL_THREADS) radix_hist_kernel(const uint64_t *__restrict__ keys, int64_t n,
                                                                  FcbSelectState *st, int pass, unsigned kprime) {
-    __shared__ unsigned s_scan[256], s_out[2], s_hist[256];
+    __shared__ unsigned s_scan[256], s_out[3], s_hist[256];
     uint64_t prefix;
     unsigned remaining;
-    resolve_state(st, pass, kprime, prefix, remaining, s_scan, s_out);
-    if (remaining == 0) return;
+    bool settled;
+    resolve_state(st, pass, kprime, prefix, remaining, settled, s_scan, s_out);
+    if (remaining == 0 || settled) return;
     const int tid = threadIdx.x;
     s_hist[tid] = 0;
     __syncthreads();
     const int shift = 56 - 8 * pass;
     const uint64_t himask = pass == 0 ? 0ull : ~0ull << (shift + 8);
+    // neighbouring keys usually share the digit (pass 0: sign + exponent bits of similar scores), so each
+    // thread counts runs locally and issues one shared atomic per run instead of one per key
+    unsigned cur = 0xffffffffu, run = 0;
     for (int64_t i = (int64_t)blockIdx.x * SEL_THREADS + tid; i < n; i += (int64_t)gridDim.x * SEL_THREADS) {
         const uint64_t key = keys[i];
-        if (key != 0ull && (key & himask) == prefix) atomicAdd(&s_hist[(unsigned)(key >> shift) & 255u], 1u);
+        if (key != 0ull && (key & himask) == prefix) {
+            const unsigned d = (unsigned)(key >> shift) & 255u;
+            if (d == cur) { ++run; }
+            else { if (run) atomicAdd(&s_hist[cur], run); cur = d; run = 1; }
+        }
     }
+    if (run) atomicAdd(&s_hist[cur], run);
     __syncthreads();
     if (s_hist[tid]) atomicAdd(&st->hist[pass][tid], s_hist[tid]);
 }
@@ -206,10 +220,11 @@ __global__ void __launch_bounds__(SEL_THREADS) radix_hist_kernel(const uint64_t 
 __global__ void __launch_bounds__(SEL_THREADS) compact_kernel(const uint64_t *__restrict__ keys, int64_t n, int64_t lo,
                                                               FcbSelectState *st, unsigned kprime,
                                                               uint32_t *__restrict__ sel_rows) {
-    __shared__ unsigned s_scan[256], s_out[2];
+    __shared__ unsigned s_scan[256], s_out[3];
     uint64_t thr;
     unsigned remaining;
-    resolve_state(st, 8, kprime, thr, remaining, s_scan, s_out);
+    bool settled;
+    resolve_state(st, 8, kprime, thr, remaining, settled, s_scan, s_out);   // settled: thr has zero tie bits = the whole bucket
     if (remaining == 0) return;                                    // nothing passed the filter
     for (int64_t i = (int64_t)blockIdx.x * SEL_THREADS + threadIdx.x; i < n; i += (int64_t)gridDim.x * SEL_THREADS) {
         const uint64_t key = keys[i];

@@ -140,9 +140,7 @@ def agg_bench(args):
     synth_columns(0, n, spec.seed, 16, spec.date_span_seconds, dates=d, categories=c, cents=v)
     off = synth.segment_offsets(spec)
     eng = Engine(device=0, max_batch=1, max_k=1)
-    dummy = torch.zeros((n, 4), dtype=torch.bfloat16, device=DEV) if False else None
-    # vectors are irrelevant for aggregation: a tiny aliasing buffer is not allowed (n rows are
-    # norm-scanned at load), so use an 8-byte/row bf16 dummy (dim 4 is not a multiple of 8 -> f32 dim 4)
+    # vectors are irrelevant for the aggregation but a shard needs them (row norms are scanned at load): 16 B/row of zeros
     vec = torch.zeros((n, 4), dtype=torch.float32, device=DEV)
     eng.load_shard(vec, dates=d, categories=c, cents=v, seg_offsets=torch.from_numpy(off).to(DEV))
     mlo = (2022 - 1970) * 12

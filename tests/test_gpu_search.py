@@ -29,8 +29,8 @@ def env(built):
 def oracle_search(hc, q, k, user=None, **kw):
     from oracle import canon
     rb, re_ = (0, hc.spec.n_rows) if user is None else (int(hc.offsets[user]), int(hc.offsets[user + 1]))
-    return canon.search(hc.vectors if kw.pop("vectors", None) is None else None, q, k, row_begin=rb, row_end=re_,
-                        ids=hc.ids, dates=hc.dates, categories=hc.categories, **kw)
+    return canon.search(hc.vectors, q, k, row_begin=rb, row_end=re_, ids=hc.ids, dates=hc.dates,
+                        categories=hc.categories, **kw)
 
 
 def run(eng, hc, q, k, user, date_lo=None, date_hi=None, category_mask=None):
