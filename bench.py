@@ -38,6 +38,9 @@ ROWS_PER_GPU = 10_000_000
 DIM = 1536
 K = 10
 SEED = 20240607
+# dram__bytes_read.sum + dram__bytes_write.sum per launch of scan_topk_kernel<float,2,6> on this workload, from the
+# `ncu --set full` capture committed as profiles/r01_final_scan_topk_f32_2x6_full_raw.csv (61.5206 GB + 4.27 MB)
+NCU_TRAFFIC_BYTES = 61_524_875_544   # 61.520607e9 + 4.268544e6
 
 
 def measured_peaks():
@@ -328,7 +331,7 @@ def run_b200(args):
         "dtype": "f32", "data": "synthetic", "config": workload_config(world),
         "p50_ms": per_step[len(per_step) // 2], "p99_ms": per_step[min(len(per_step) - 1, int(len(per_step) * 0.99))],
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": None, "kernel": "scan_topk_kernel<float,2,6>", "algorithmic_bytes_per_launch": alg_bytes,
+                     "traffic": NCU_TRAFFIC_BYTES if rows == ROWS_PER_GPU else None, "kernel": "scan_topk_kernel<float,2,6>", "algorithmic_bytes_per_launch": alg_bytes,
                      "kernel_ms": kern_ms, "peak_source": peak_src, "frac_of_nominal_8TBs": achieved / 8000.0},
         "e2e": {"value": B * e2e_steps / te, "unit": UNIT, "h2d_bytes_per_step": B * DIM * 8,
                 "d2h_bytes_per_step": B * (K * 16 + 4), "api": e2e_api,
