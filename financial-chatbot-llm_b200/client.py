@@ -113,6 +113,7 @@ class Collection:
         self.payload_fn = payload_fn
         self.n_total_rows = int(self.offsets[-1]) if n_total_rows is None else n_total_rows
         self.category_codes = category_codes or {}
+        self.point_id_fn: Optional[Callable[[int], Any]] = None   # global row -> original point id (non-integer ids)
         if ids_host is not None:
             ids_host = np.asarray(ids_host, dtype=np.uint64)
             self._id_order = np.argsort(ids_host, kind="stable")
@@ -190,6 +191,8 @@ class B200QdrantClient:
             if score_threshold is not None and s < score_threshold:
                 break
             pid = int(ids[0, j])
-            payload = col.payload_fn(col.row_of_id(pid)) if with_payload else None
-            points.append(ScoredPoint(id=pid, version=0, score=s, payload=payload, vector=None))
+            row = col.row_of_id(pid)
+            payload = col.payload_fn(row) if with_payload else None
+            points.append(ScoredPoint(id=col.point_id_fn(row) if col.point_id_fn else pid, version=0, score=s,
+                                      payload=payload, vector=None))
         return QueryResponse(points=points)

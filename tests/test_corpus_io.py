@@ -1,0 +1,85 @@
+"""On-disk corpus format: write points in the payload shape the reference reads, map them back, and (GPU)
+load them into an engine and search — results equal to the oracle over the same points."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+
+def make_points(n=900, dim=64, seed=5, uuid_ids=False):
+    from financial_chatbot_llm_b200 import synth
+    spec = synth.SynthSpec(n_rows=n, dim=dim, n_users=6, seed=seed)
+    hc = synth.make_host_corpus(spec)
+    rng = np.random.default_rng(seed)
+    order = rng.permutation(n)                                  # points arrive in arbitrary order
+    pts = []
+    for r in order:
+        pl = hc.payload(int(r))
+        pid = f"00000000-0000-4000-8000-{int(r):012x}" if uuid_ids else int(r) * 7 + 3
+        pts.append({"id": pid, "vector": hc.vectors[r].tolist(), "payload": pl})
+    return spec, hc, pts
+
+
+def test_write_and_map_roundtrip(tmp_path):
+    from financial_chatbot_llm_b200 import corpus_io, synth
+    spec, hc, pts = make_points()
+    man = corpus_io.write_corpus(str(tmp_path / "c"), pts, dim=spec.dim, categories=list(synth.CATEGORIES))
+    cf = corpus_io.CorpusFiles(str(tmp_path / "c"))
+    assert man["n_rows"] == 900 and cf.users == sorted(hc.users) and cf.offsets[-1] == 900
+    by_id = {p["id"]: p for p in pts}
+    ids = np.array(cf.columns["ids.u64"])
+    assert not man["ids_ascending"] and "id_rank.u32" in cf.columns
+    assert np.array_equal(np.argsort(np.argsort(ids)), np.array(cf.columns["id_rank.u32"]))
+    for row in (0, 17, 450, 899):
+        p = by_id[int(ids[row])]
+        u = int(np.searchsorted(cf.offsets, row, side="right") - 1)
+        assert cf.payload(row) == p["payload"] and p["payload"]["metadata"]["user_id"] == cf.users[u]
+        assert np.array_equal(cf.vectors[row], np.asarray(p["vector"], dtype=np.float32))
+        assert cf.columns["dates.i32"][row] == p["payload"]["metadata"]["date"]
+        assert cf.columns["cents.i32"][row] == p["payload"]["metadata"]["amount_cents"]
+        assert synth.CATEGORIES[cf.columns["categories.u8"][row]] == p["payload"]["metadata"]["category"]
+    # bf16 storage and UUID ids
+    spec2, hc2, pts2 = make_points(n=50, uuid_ids=True)
+    man2 = corpus_io.write_corpus(str(tmp_path / "u"), pts2, dim=spec2.dim, dtype="bfloat16")
+    cf2 = corpus_io.CorpusFiles(str(tmp_path / "u"))
+    assert man2["original_ids"] and cf2.point_ids is not None and cf2.vectors.dtype == np.uint16
+    with pytest.raises(ValueError):
+        corpus_io.write_corpus(str(tmp_path / "bad"), [{"id": 1, "vector": [0.0] * 3, "payload": pts[0]["payload"]}], dim=64)
+
+
+@pytest.mark.gpu
+def test_load_from_disk_and_search(tmp_path, built):
+    from financial_chatbot_llm_b200 import corpus_io, synth
+    from financial_chatbot_llm_b200 import qdrant_models as m
+    from financial_chatbot_llm_b200.client import B200QdrantClient
+    from financial_chatbot_llm_b200.engine import Engine
+    from oracle import canon
+    for uuid_ids, dtype in ((False, "float32"), (True, "bfloat16")):
+        spec, hc, pts = make_points(n=1500, dim=128, uuid_ids=uuid_ids)
+        d = str(tmp_path / f"c{int(uuid_ids)}")
+        corpus_io.write_corpus(d, pts, dim=spec.dim, dtype=dtype, categories=list(synth.CATEGORIES))
+        eng = Engine(device=0, max_batch=1, max_k=64)
+        col = corpus_io.load_collection(d, eng, chunk_rows=400)
+        cl = B200QdrantClient()
+        cl.attach_collection(col)
+        cf = col.files
+        vec = np.asarray(cf.vectors)
+        ids = np.array(cf.columns["ids.u64"])
+        t0 = int(np.median(cf.columns["dates.i32"]))
+        for u in (0, 3, 5):
+            q = synth.query_vector(spec, u)
+            flt = m.Filter(must=[m.FieldCondition(key="metadata.user_id", match=m.MatchValue(value=cf.users[u])),
+                                 m.FieldCondition(key="metadata.date", range=m.Range(gte=t0)),
+                                 m.FieldCondition(key="metadata.category", match=m.MatchAny(any=["Rent", "Dining", "Fuel", "Other", "Travel"]))])
+            pts_out = cl.query_points("transactions", query=q.tolist(), limit=20, query_filter=flt).points
+            cmask = sum(1 << cf.manifest["categories"].index(c) for c in ["Rent", "Dining", "Fuel", "Other", "Travel"])
+            oi, os_ = canon.search(vec, q, 20, row_begin=int(cf.offsets[u]), row_end=int(cf.offsets[u + 1]), ids=ids,
+                                   dates=np.array(cf.columns["dates.i32"]), categories=np.array(cf.columns["categories.u8"]),
+                                   date_lo=t0, category_mask=cmask)
+            rows = [int(np.flatnonzero(ids == i)[0]) for i in oi]
+            want_ids = [cf.point_ids[r] for r in rows] if uuid_ids else [int(i) for i in oi]
+            assert [p.id for p in pts_out] == want_ids
+            assert [p.score for p in pts_out] == os_.tolist()
+            assert all(p.payload == cf.payload(r) for p, r in zip(pts_out, rows))
+        eng.close()
