@@ -189,7 +189,7 @@ def load_collection(path: str, engine, *, name: str = "transactions", row_lo: in
     def col(fname, view=None):
         if fname not in cf.columns:
             return None
-        a = np.ascontiguousarray(cf.columns[fname][row_lo:row_hi])
+        a = np.array(cf.columns[fname][row_lo:row_hi])                 # copy: the memory map is read-only
         return torch.from_numpy(a.view(view) if view is not None else a).to(dev)
     ids = col("ids.u64", np.int64)
     id_rank = col("id_rank.u32", np.int32)
