@@ -1,0 +1,101 @@
+"""Resident engine + micro-batching (serving.py): many clients, one grouped launch per window.
+CPU: host logic with a fake engine. GPU: the real engine, results against the oracle."""
+import os
+import threading
+
+import numpy as np
+import pytest
+
+from financial_chatbot_llm_b200 import client, serving
+from financial_chatbot_llm_b200 import qdrant_models as m
+
+
+class FakeEngine:
+    dim, row_base, max_batch = 4, 0, 16
+
+    def __init__(self):
+        self.batches = []
+
+    def search_host(self, q, filters, k):
+        B = q.shape[0]
+        self.batches.append(B)
+        ids = np.full((B, k), np.iinfo(np.uint64).max, dtype=np.uint64)
+        sc = np.full((B, k), -np.inf)
+        cnt = np.zeros(B, dtype=np.int32)
+        for b, f in enumerate(filters):
+            rows = np.arange(f.row_begin, f.row_end, dtype=np.uint64)[:k]
+            ids[b, :rows.size] = rows
+            sc[b, :rows.size] = q[b, 0] - 0.01 * np.arange(rows.size)        # the query leaves a fingerprint in the score
+            cnt[b] = rows.size
+        return ids, sc, cnt
+
+
+def user_filter(u):
+    return m.Filter(must=[m.FieldCondition(key="metadata.user_id", match=m.MatchValue(value=u))])
+
+
+def test_micro_batching_host_logic(tmp_path):
+    eng = FakeEngine()
+    users = ["alice", "bob", "carol"]
+    col = client.Collection("transactions", eng, users, np.array([0, 3, 8, 20]),
+                            lambda row: {"page_content": f"txn {row}", "metadata": {"user_id": users[0 if row < 3 else 1 if row < 8 else 2]}})
+    addr = str(tmp_path / "engine.sock")
+    srv = serving.EngineServer(col, addr, window_us=20000).start()
+    errors, results = [], {}
+
+    def worker(i):
+        try:
+            cl = serving.EngineClient(url="http://ignored", api_key="x", address=addr)
+            for j in range(10):
+                u = users[(i + j) % 3]
+                pts = cl.query_points("transactions", query=[float(i * 100 + j), 0, 0, 0], limit=4, query_filter=user_filter(u)).points
+                results[(i, j)] = (u, [p.id for p in pts], pts[0].score, pts[0].payload["metadata"]["user_id"])
+            with pytest.raises(RuntimeError, match="not found"):
+                cl.query_points("missing", query=[0, 0, 0, 0])
+            cl.close()
+        except Exception as e:                                              # surfaced below
+            errors.append(repr(e))
+    threads = [threading.Thread(target=worker, args=(i,)) for i in range(8)]
+    [t.start() for t in threads]
+    [t.join(timeout=30) for t in threads]
+    srv.stop()
+    assert not errors, errors
+    assert len(results) == 80
+    for (i, j), (u, ids, s0, pu) in results.items():
+        lo = {"alice": 0, "bob": 3, "carol": 8}[u]
+        assert ids[0] == lo and len(ids) == (3 if u == "alice" else 4) and pu == u
+        assert s0 == float(i * 100 + j)                                    # each reply went back to ITS requester
+    assert srv.stats["requests"] == 80 and srv.stats["max_batch"] >= 2 and srv.stats["launches"] < 80
+    assert max(eng.batches) <= eng.max_batch
+
+
+@pytest.mark.gpu
+def test_server_with_real_engine_matches_oracle(tmp_path, built):
+    from financial_chatbot_llm_b200 import loader, synth
+    from financial_chatbot_llm_b200.engine import Engine
+    from oracle import canon
+    spec = synth.SynthSpec(n_rows=20000, dim=256, n_users=30, seed=61)
+    hc = synth.make_host_corpus(spec)
+    eng = Engine(device=0, max_batch=32, max_k=16)
+    col = loader.collection_from_host(hc, eng)
+    addr = str(tmp_path / "engine.sock")
+    srv = serving.EngineServer(col, addr, window_us=2000).start()
+    bad = []
+
+    def worker(i):
+        cl = serving.EngineClient(address=addr)
+        for j in range(15):
+            u = (3 * i + j) % 30
+            q = synth.query_vector(spec, 100 * i + j)
+            pts = cl.query_points("transactions", query=q.tolist(), limit=10, query_filter=user_filter(hc.users[u])).points
+            oi, os_ = canon.search(hc.vectors, q, 10, row_begin=int(hc.offsets[u]), row_end=int(hc.offsets[u + 1]))
+            if [p.id for p in pts] != oi.tolist() or [p.score for p in pts] != os_.tolist() or \
+                    any(p.payload != hc.payload(p.id) for p in pts):
+                bad.append((i, j))
+        cl.close()
+    threads = [threading.Thread(target=worker, args=(i,)) for i in range(12)]
+    [t.start() for t in threads]
+    [t.join(timeout=120) for t in threads]
+    srv.stop()
+    eng.close()
+    assert not bad and srv.stats["requests"] == 180 and srv.stats["max_batch"] >= 2
