@@ -59,6 +59,7 @@ struct DenseParams {
     int64_t debug_rows;
     long long *prof;                        // diagnostic: per-role cycle counters of CTA 0 (NULL in production)
     int n_stages;                           // cta_group::2 kernel: depth of the shared-memory ring (3 or 4)
+    unsigned *gthr;                         // [DN_N] best per-CTA 32nd-best score so far, order-preserving uint (cta_group::2 kernel)
 };
 
 // ---- PTX wrappers -----------------------------------------------------------------------------
@@ -135,6 +136,15 @@ __device__ __forceinline__ uint64_t make_sw128_desc(uint32_t smem_addr) {
 // [7,10) / [10,13), both K-major, N>>3 [17,23), M>>4 [24,29)
 __device__ __forceinline__ constexpr uint32_t make_idesc_bf16(int M, int N) {
     return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+// order-preserving float <-> uint (larger float = larger uint), for atomicMax on scores of either sign
+__device__ __forceinline__ unsigned dn_ord(float f) {
+    const unsigned u = __float_as_uint(f);
+    return u ^ ((u >> 31) ? 0xffffffffu : 0x80000000u);
+}
+__device__ __forceinline__ float dn_unord(unsigned o) {
+    return __uint_as_float(o ^ ((o >> 31) ? 0x80000000u : 0xffffffffu));
 }
 
 __device__ __forceinline__ uint32_t dn_tie_key(uint32_t row, const uint32_t *__restrict__ id_rank) {
@@ -411,7 +421,7 @@ dense_topk2_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
         asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_ptr)), "r"(DN_TMEM_COLS) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
     }
-    for (int i = tid; i < DN_N; i += DN2_THREADS) { thr_s[i] = -INFINITY; cnt_s[i] = 0; }
+    for (int i = tid; i < DN_N; i += DN2_THREADS) { thr_s[i] = i < p.n_queries ? -INFINITY : INFINITY; cnt_s[i] = 0; }   // padding never qualifies
     if (tid < DN_N / 32) thr_min_s[tid] = -INFINITY;
     for (int i = tid; i < p.n_eff * FCB_FUSED_CAND; i += DN2_THREADS) top_s[i] = FcbCand{-INFINITY, FCB_NO_ROW};
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -509,20 +519,28 @@ dense_topk2_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
 #pragma unroll
                     for (int j = 0; j < 16; ++j) p.debug_out[(row - lo) * DN_N + c + j] = __uint_as_float(v[j]);
                 }
-                uint32_t mask = 0;
+                // fast path: largest margin (score - threshold) of the 16 columns, one FFMA + max per element;
+                // only a row that has a survivor somewhere in the chunk computes the exact pass mask
                 const float4 *t4 = reinterpret_cast<const float4 *>(thr_s + c);
+                float dmax = -INFINITY;
 #pragma unroll
                 for (int j4 = 0; j4 < 4; ++j4) {
                     const float4 t = t4[j4];
-                    const float s0 = __uint_as_float(v[4 * j4 + 0]) * inv, s1 = __uint_as_float(v[4 * j4 + 1]) * inv,
-                                s2 = __uint_as_float(v[4 * j4 + 2]) * inv, s3 = __uint_as_float(v[4 * j4 + 3]) * inv;
-                    const bool p0 = push_ties ? s0 >= t.x : s0 > t.x, p1 = push_ties ? s1 >= t.y : s1 > t.y,
-                               p2 = push_ties ? s2 >= t.z : s2 > t.z, p3 = push_ties ? s3 >= t.w : s3 > t.w;
-                    mask |= ((uint32_t)p0 | ((uint32_t)p1 << 1) | ((uint32_t)p2 << 2) | ((uint32_t)p3 << 3)) << (4 * j4);
+                    const float d0 = fmaf(__uint_as_float(v[4 * j4 + 0]), inv, -t.x), d1 = fmaf(__uint_as_float(v[4 * j4 + 1]), inv, -t.y),
+                                d2 = fmaf(__uint_as_float(v[4 * j4 + 2]), inv, -t.z), d3 = fmaf(__uint_as_float(v[4 * j4 + 3]), inv, -t.w);
+                    dmax = fmaxf(fmaxf(dmax, fmaxf(d0, d1)), fmaxf(d2, d3));
                 }
-                const int left = p.n_queries - c;                      // padding columns never qualify
-                mask &= left >= 16 ? 0xffffu : ((1u << (left > 0 ? left : 0)) - 1u);
-                if (valid && mask) {
+                if (valid && dmax >= 0.f) {
+                    uint32_t mask = 0;
+#pragma unroll
+                    for (int j4 = 0; j4 < 4; ++j4) {
+                        const float4 t = t4[j4];
+                        const float s0 = __uint_as_float(v[4 * j4 + 0]) * inv, s1 = __uint_as_float(v[4 * j4 + 1]) * inv,
+                                    s2 = __uint_as_float(v[4 * j4 + 2]) * inv, s3 = __uint_as_float(v[4 * j4 + 3]) * inv;
+                        const bool p0 = push_ties ? s0 >= t.x : s0 > t.x, p1 = push_ties ? s1 >= t.y : s1 > t.y,
+                                   p2 = push_ties ? s2 >= t.z : s2 > t.z, p3 = push_ties ? s3 >= t.w : s3 > t.w;
+                        mask |= ((uint32_t)p0 | ((uint32_t)p1 << 1) | ((uint32_t)p2 << 2) | ((uint32_t)p3 << 3)) << (4 * j4);
+                    }
 #pragma unroll
                     for (int j = 0; j < 16; ++j) {
                         if (mask & (1u << j)) {
@@ -600,6 +618,20 @@ dense_topk2_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
                         if (lane == 31) thr_s[q] = e.score;
                         if (lane == 0) cnt_s[q] = 0;
                     }
+                }
+            }
+            asm volatile("bar.sync 1, 512;" ::: "memory");
+            // thresholds across CTAs: a CTA's 32nd-best score bounds the GLOBAL 32nd best from below, so every
+            // CTA may prune with the best such bound published so far (one ulp lower, so that a row tying with it
+            // still gets through — it may win the tie on id). Cuts the survivors per CTA by ~the number of CTAs.
+            {
+                const int q = (int)threadIdx.x - 128;                        // epilogue threads 0..511 <-> queries
+                if (q >= 0 && q < p.n_queries) {
+                    const float mine = thr_s[q];
+                    const unsigned om = dn_ord(mine);
+                    const unsigned g = max(atomicMax(&p.gthr[q], om), om);
+                    const float lowered = g > dn_ord(-INFINITY) ? dn_unord(g - 1) : -INFINITY;   // previous float in order
+                    thr_s[q] = fmaxf(mine, lowered);
                 }
             }
             asm volatile("bar.sync 1, 512;" ::: "memory");
@@ -779,6 +811,7 @@ struct FcbDense {
     int two_cta = 1;
     __nv_bfloat16 *q_bf16 = nullptr;        // [DN_N, dim]
     FcbCand *cta_top = nullptr, *pend = nullptr;
+    unsigned *gthr = nullptr;               // [DN_N] cross-CTA thresholds of the cta_group::2 kernel
     int32_t *redo = nullptr;                // [DN_N] flags, then [DN_N] compact list, then the count
     int *error_flag = nullptr;
     int grid = 0;
@@ -787,7 +820,7 @@ struct FcbDense {
 void fcb_dense_free(fcb_engine *e) {
     FcbDense *d = reinterpret_cast<FcbDense *>(e->dense);
     if (!d) return;
-    cudaFree(d->q_bf16); cudaFree(d->cta_top); cudaFree(d->pend); cudaFree(d->redo); cudaFree(d->error_flag);
+    cudaFree(d->q_bf16); cudaFree(d->cta_top); cudaFree(d->pend); cudaFree(d->redo); cudaFree(d->error_flag); cudaFree(d->gthr);
     delete d;
     e->dense = nullptr;
 }
@@ -808,6 +841,7 @@ int32_t fcb_dense_alloc(fcb_engine *e) {
         cudaMalloc(&d->cta_top, lists * FCB_FUSED_CAND * sizeof(FcbCand)) != cudaSuccess ||
         cudaMalloc(&d->pend, lists * DN_PEND_CAP * sizeof(FcbCand)) != cudaSuccess ||
         cudaMalloc(&d->redo, (size_t)(2 * DN_N + 1) * sizeof(int32_t)) != cudaSuccess ||
+        cudaMalloc(&d->gthr, (size_t)DN_N * sizeof(unsigned)) != cudaSuccess ||
         cudaMalloc(&d->error_flag, sizeof(int)) != cudaSuccess) {
         cudaGetLastError();
         fcb_dense_free(e);
@@ -866,6 +900,8 @@ int32_t fcb_search_dense(fcb_engine *e, const double *d_queries, const fcb_filte
     p.n_queries = batch; p.n_eff = ((batch + 31) / 32) * 32;
     p.cta_top = d->cta_top; p.pend = d->pend; p.error_flag = d->error_flag;
     p.debug_out = g_debug_out; p.debug_rows = g_debug_rows; p.prof = g_dense_prof;
+    p.gthr = d->gthr;
+    FCB_CUDA(e, cudaMemsetAsync(d->gthr, 0, (size_t)DN_N * sizeof(unsigned), st));   // 0 orders below every float
     p.n_stages = p.n_eff <= 96 ? 4 : 3;                              // stages + 4 KB + lists (n_eff x 256 B) must fit 227 KB
     const size_t smem = (size_t)DN_STAGES * DN_STAGE_BYTES + 4096;
     if (d->two_cta) {
