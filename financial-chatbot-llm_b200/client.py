@@ -9,14 +9,21 @@ server) and the same ``query_points`` call, and returns the same shape — but t
 search runs in libfcb200.so on a B200 over a resident, CSR-by-user corpus.
 
 Filter subset (anything else raises NotImplementedError — never a silent wrong answer):
-``Filter(must=[...])`` of ``FieldCondition`` on
+``Filter(must=[...], should=[...], must_not=[...])`` of ``FieldCondition`` on
   metadata.user_id  MatchValue(str)             -> the user's CSR segment
   metadata.date     Range(gte/gt/lte/lt)        -> inclusive int64 bounds fused into the scan
   metadata.category MatchValue / MatchAny       -> 64-bit category mask fused into the scan
+The device predicate is one conjunction (row range AND date range AND category mask). ``should`` (OR)
+and ``must_not`` (NOT) are rewritten on the host into a disjunction of such conjunctions — NOT of a
+date range is "before it OR after it", NOT of a user is "the rows before OR after the segment", NOT of
+a category set clears mask bits — every conjunct rides in the same grouped ``fcb_search`` call with a
+copy of the query, and the per-conjunct top-k lists are merged (duplicates dropped by point id; the
+scores of one row are bit-identical in every list). ``min_should`` and nested filters raise.
 Filters are read by attribute, so real qdrant-client model instances work too.
 """
 from __future__ import annotations
 
+import bisect
 import math
 from typing import Any, Callable, Dict, List, Optional, Sequence
 
@@ -27,17 +34,35 @@ from .engine import Engine, make_filter
 from .qdrant_models import QueryResponse, ScoredPoint
 
 USER_KEY, DATE_KEY, CATEGORY_KEY = "metadata.user_id", "metadata.date", "metadata.category"
+MAX_CONJUNCTS = 64                      # a should / must_not rewrite larger than this is refused
 
 
 class ParsedFilter:
-    __slots__ = ("user_id", "has_user", "date_lo", "date_hi", "category_values")
+    """One conjunction, still symbolic (no collection needed): user == / < / >, date bounds, category sets."""
+    __slots__ = ("user_id", "has_user", "user_lt", "user_gt", "date_lo", "date_hi", "category_values",
+                 "category_excluded")
 
     def __init__(self):
         self.user_id: Optional[str] = None
         self.has_user = False
+        self.user_lt: Optional[str] = None             # only users sorting strictly before this one
+        self.user_gt: Optional[str] = None             # only users sorting strictly after this one
         self.date_lo: Optional[int] = None
         self.date_hi: Optional[int] = None
         self.category_values: Optional[set] = None     # None = no category filter
+        self.category_excluded: set = set()
+
+    def copy(self) -> "ParsedFilter":
+        c = ParsedFilter()
+        for f in self.__slots__:
+            v = getattr(self, f)
+            setattr(c, f, set(v) if isinstance(v, set) else v)
+        return c
+
+    def impossible(self) -> bool:
+        return (self.has_user and self.user_id is None) or \
+               (self.date_lo is not None and self.date_hi is not None and self.date_lo > self.date_hi) or \
+               (self.category_values is not None and not (self.category_values - self.category_excluded))
 
 
 def _range_to_bounds(rng: Any):
@@ -59,38 +84,109 @@ def _range_to_bounds(rng: Any):
     return lo, hi
 
 
-def parse_filter(flt: Any) -> ParsedFilter:
-    """Resolve the qdrant filter model into the column predicate the kernels fuse."""
-    out = ParsedFilter()
-    if flt is None:
-        return out
-    for name in ("should", "must_not", "min_should"):
-        if getattr(flt, name, None):
-            raise NotImplementedError(f"Filter.{name} is not supported by the B200 engine")
-    for cond in (getattr(flt, "must", None) or []):
-        key = getattr(cond, "key", None)
-        match, rng = getattr(cond, "match", None), getattr(cond, "range", None)
-        if key is None or (match is None) == (rng is None):
-            raise NotImplementedError(f"unsupported condition {cond!r}")
-        if key == USER_KEY and match is not None and hasattr(match, "value"):
-            v = match.value
-            if out.has_user and out.user_id != v:
-                out.user_id = None            # two different users ANDed: nothing matches
+def _classify(cond: Any):
+    """-> ("user", str | None) | ("date", (lo, hi)) | ("category", set)"""
+    key = getattr(cond, "key", None)
+    match, rng = getattr(cond, "match", None), getattr(cond, "range", None)
+    if key is None or (match is None) == (rng is None):
+        raise NotImplementedError(f"unsupported condition {cond!r}")
+    if key == USER_KEY and match is not None and hasattr(match, "value"):
+        return "user", (match.value if isinstance(match.value, str) else None)
+    if key == DATE_KEY and rng is not None:
+        return "date", _range_to_bounds(rng)
+    if key == CATEGORY_KEY and match is not None:
+        return "category", ({match.value} if hasattr(match, "value") else set(getattr(match, "any")))
+    raise NotImplementedError(f"unsupported filter condition on key {key!r}")
+
+
+def _apply(pf: ParsedFilter, kind: str, arg: Any, negate: bool) -> List[ParsedFilter]:
+    """pf AND cond (or AND NOT cond) -> the conjuncts it becomes (0, 1 or 2)."""
+    out = pf.copy()
+    if kind == "user":
+        if not negate:
+            if arg is None or (out.has_user and out.user_id != arg):
+                out.user_id = None                     # non-string value / two different users ANDed: nothing matches
             else:
-                out.user_id = v if isinstance(v, str) else None
+                out.user_id = arg
             out.has_user = True
-        elif key == DATE_KEY and rng is not None:
-            lo, hi = _range_to_bounds(rng)
+            return [out]
+        if arg is None:                                # NOT (user == <non-string>): every row passes
+            return [out]
+        before, after = out, pf.copy()
+        before.user_lt = arg if before.user_lt is None else min(before.user_lt, arg)
+        after.user_gt = arg if after.user_gt is None else max(after.user_gt, arg)
+        return [before, after]
+    if kind == "date":
+        lo, hi = arg
+        if not negate:
             if lo is not None:
                 out.date_lo = lo if out.date_lo is None else max(out.date_lo, lo)
             if hi is not None:
                 out.date_hi = hi if out.date_hi is None else min(out.date_hi, hi)
-        elif key == CATEGORY_KEY and match is not None:
-            vals = {match.value} if hasattr(match, "value") else set(getattr(match, "any"))
-            out.category_values = vals if out.category_values is None else (out.category_values & vals)
-        else:
-            raise NotImplementedError(f"unsupported filter condition on key {key!r}")
-    return out
+            return [out]
+        alts = []
+        if lo is not None:                             # strictly before the range
+            a = pf.copy()
+            a.date_hi = lo - 1 if a.date_hi is None else min(a.date_hi, lo - 1)
+            alts.append(a)
+        if hi is not None:                             # strictly after it
+            a = pf.copy()
+            a.date_lo = hi + 1 if a.date_lo is None else max(a.date_lo, hi + 1)
+            alts.append(a)
+        return alts                                    # an unbounded range matches every dated row: NOT of it, none
+    if not negate:
+        out.category_values = set(arg) if out.category_values is None else (out.category_values & arg)
+    else:
+        out.category_excluded |= arg
+    return [out]
+
+
+def parse_filter_dnf(flt: Any) -> List[ParsedFilter]:
+    """The qdrant filter as a list of conjunctions whose UNION is the set of passing points
+    (qdrant semantics: every ``must``, at least one ``should`` when any is given, no ``must_not``)."""
+    if flt is None:
+        return [ParsedFilter()]
+    if getattr(flt, "min_should", None):
+        raise NotImplementedError("Filter.min_should is not supported by the B200 engine")
+    conj = [ParsedFilter()]
+    for cond in (getattr(flt, "must", None) or []):
+        kind, arg = _classify(cond)
+        conj = [c for pf in conj for c in _apply(pf, kind, arg, False)]
+    for cond in (getattr(flt, "must_not", None) or []):
+        kind, arg = _classify(cond)
+        conj = [c for pf in conj for c in _apply(pf, kind, arg, True) if not c.impossible()]
+        if len(conj) > MAX_CONJUNCTS:
+            raise NotImplementedError("must_not expands into too many conjunctions")
+    should = [_classify(c) for c in (getattr(flt, "should", None) or [])]
+    if should:
+        conj = [c for pf in conj for kind, arg in should for c in _apply(pf, kind, arg, False)]
+        if len(conj) > MAX_CONJUNCTS:
+            raise NotImplementedError("should x must_not expands into too many conjunctions")
+    return [c for c in conj if not c.impossible()]
+
+
+def parse_filter(flt: Any) -> ParsedFilter:
+    """The filter as ONE conjunction (what the reference's own filter always is, tools/qdrant_tool.py:98-131);
+    raises NotImplementedError when it needs more than one — use ``parse_filter_dnf`` for those."""
+    conj = parse_filter_dnf(flt)
+    if len(conj) > 1:
+        raise NotImplementedError("this filter needs several conjunctions; use parse_filter_dnf")
+    if not conj:                                       # nothing can match: an empty user segment says so
+        pf = ParsedFilter()
+        pf.has_user = True
+        return pf
+    return conj[0]
+
+
+def merge_conjunct_lists(ids: np.ndarray, scores: np.ndarray, counts: np.ndarray, k: int):
+    """Top-k of the UNION of per-conjunct top-k lists (rows of ids / scores, ``counts`` valid entries each):
+    duplicates dropped by id, order (score desc, id asc) as everywhere else. -> (ids[n], scores[n]), n <= k."""
+    all_ids = np.concatenate([ids[b, :int(counts[b])] for b in range(ids.shape[0])])
+    all_sc = np.concatenate([scores[b, :int(counts[b])] for b in range(ids.shape[0])])
+    all_ids, first = np.unique(all_ids, return_index=True)
+    all_sc = all_sc[first]
+    order = np.lexsort((all_ids, -all_sc))[:k]
+    return all_ids[order], all_sc[order]
 
 
 class Collection:
@@ -114,6 +210,7 @@ class Collection:
         self.n_total_rows = int(self.offsets[-1]) if n_total_rows is None else n_total_rows
         self.category_codes = category_codes or {}
         self.point_id_fn: Optional[Callable[[int], Any]] = None   # global row -> original point id (non-integer ids)
+        self.has_missing_category = False              # True when some rows carry no category (code >= 64 on the device)
         if ids_host is not None:
             ids_host = np.asarray(ids_host, dtype=np.uint64)
             self._id_order = np.argsort(ids_host, kind="stable")
@@ -128,6 +225,14 @@ class Collection:
         j = int(np.searchsorted(self._ids_sorted, np.uint64(pid)))
         return int(self._id_order[j]) + self.engine.row_base
 
+    def _mask_of(self, values) -> int:
+        mask = 0
+        for v in values:
+            c = self.category_codes.get(v)
+            if c is not None and 0 <= c < 64:
+                mask |= 1 << c
+        return mask
+
     def resolve(self, pf: ParsedFilter):
         """ParsedFilter -> FcbFilter for this collection."""
         if pf.has_user:
@@ -135,14 +240,50 @@ class Collection:
             rb, re_ = (0, 0) if u is None else (int(self.offsets[u]), int(self.offsets[u + 1]))
         else:
             rb, re_ = 0, self.n_total_rows
+        if pf.user_gt is not None:                     # users are sorted: "after user X" is a row suffix
+            rb = max(rb, int(self.offsets[bisect.bisect_right(self.users, pf.user_gt)]))
+        if pf.user_lt is not None:
+            re_ = min(re_, int(self.offsets[bisect.bisect_left(self.users, pf.user_lt)]))
+        re_ = max(re_, rb)
         mask = None
         if pf.category_values is not None:
-            mask = 0
-            for v in pf.category_values:
-                c = self.category_codes.get(v)
-                if c is not None and 0 <= c < 64:
-                    mask |= 1 << c
+            mask = self._mask_of(pf.category_values)
+        if pf.category_excluded:
+            if self.has_missing_category:
+                raise NotImplementedError("must_not on metadata.category needs every row to carry a category "
+                                          "(rows without one must pass, and the category mask cannot say so)")
+            excl = self._mask_of(pf.category_excluded)
+            if excl:
+                mask = (_lib.FCB_ALL_CATEGORIES if mask is None else mask) & ~excl
         return make_filter(rb, re_, pf.date_lo, pf.date_hi, mask)
+
+    def resolve_dnf(self, flt: Any) -> list:
+        """qdrant filter -> the FcbFilters whose union it selects (empty conjuncts dropped; may be [])."""
+        out = []
+        for pf in parse_filter_dnf(flt):
+            f = self.resolve(pf)
+            if f.row_begin < f.row_end and f.date_lo <= f.date_hi and f.category_mask != 0:
+                out.append(f)
+        return out
+
+    def search_union(self, search: Callable, q: np.ndarray, filters: list, k: int):
+        """Exact top-k over the union of ``filters`` for ONE query: all conjuncts in one grouped call
+        (chunked by the engine's batch limit). ``search(queries[B, dim], filters, k) -> ids, scores, counts``.
+        -> (ids[n], scores[n]) with n <= k."""
+        if not filters:
+            return np.zeros(0, dtype=np.uint64), np.zeros(0, dtype=np.float64)
+        if len(filters) == 1:
+            ids, sc, cn = search(q[None, :], filters, k)
+            n = int(cn[0])
+            return ids[0, :n], sc[0, :n]
+        parts = []
+        step = max(1, int(getattr(self.engine, "max_batch", len(filters))))
+        for lo in range(0, len(filters), step):
+            fl = filters[lo:lo + step]
+            parts.append(search(np.repeat(q[None, :], len(fl), axis=0), fl, k))
+        ids = np.concatenate([p[0] for p in parts]); sc = np.concatenate([p[1] for p in parts])
+        cn = np.concatenate([p[2] for p in parts])
+        return merge_conjunct_lists(ids, sc, cn, k)
 
 
 class B200QdrantClient:
@@ -182,15 +323,13 @@ class B200QdrantClient:
         k = int(limit) + skip
         if k < 1:
             return QueryResponse(points=[])
-        filt = col.resolve(parse_filter(query_filter))
-        ids, scores, counts = col.engine.search_host(q[None, :], [filt], k)
-        n = int(counts[0])
+        ids, scores = col.search_union(col.engine.search_host, q, col.resolve_dnf(query_filter), k)
         points: List[ScoredPoint] = []
-        for j in range(skip, n):
-            s = float(scores[0, j])
+        for j in range(skip, ids.shape[0]):
+            s = float(scores[j])
             if score_threshold is not None and s < score_threshold:
                 break
-            pid = int(ids[0, j])
+            pid = int(ids[j])
             row = col.row_of_id(pid)
             payload = col.payload_fn(row) if with_payload else None
             points.append(ScoredPoint(id=col.point_id_fn(row) if col.point_id_fn else pid, version=0, score=s,

@@ -13,6 +13,7 @@ Directory layout (all little-endian, no headers; ``manifest.json`` carries shape
   vectors.bin       [n_rows, dim] row-major
   ids.u64           [n_rows] point ids (absent: id = row)        id_rank.u32  (only if ids do not ascend)
   dates.i32  categories.u8  cents.i32  seg_offsets.i64 ([n_users + 1])
+                    (category code 255 = the row has no metadata.category: matches no category filter)
   users.json        user_id strings in segment order (ascending)
   point_ids.json    original point ids when they are not unsigned 64-bit integers (UUID strings)
   payload.blob / payload.off   UTF-8 JSON of each row's payload, and u64 offsets ([n_rows + 1])
@@ -28,6 +29,7 @@ import numpy as np
 from . import synth
 
 FORMAT_VERSION = 1
+NO_CATEGORY = 255                       # >= 64: passes when there is no category filter, never matches one
 _COLUMNS = {"ids.u64": np.uint64, "id_rank.u32": np.uint32, "dates.i32": np.int32, "categories.u8": np.uint8,
             "cents.i32": np.int32, "seg_offsets.i64": np.int64, "payload.off": np.uint64}
 
@@ -67,7 +69,7 @@ def write_corpus(path: str, points: Iterable[Dict[str, Any]], *, dim: int, dtype
     cat_code = {c: i for i, c in enumerate(cat_values)}
     vec = np.empty((n, dim), dtype=np.float32)
     dates = np.zeros(n, dtype=np.int32)
-    cats = np.zeros(n, dtype=np.uint8)
+    cats = np.full(n, NO_CATEGORY, dtype=np.uint8)
     cents = np.zeros(n, dtype=np.int32)
     raw_ids: List[Any] = []
     blobs: List[bytes] = []
@@ -125,7 +127,8 @@ def write_corpus(path: str, points: Iterable[Dict[str, Any]], *, dim: int, dtype
         with open(os.path.join(path, "point_ids.json"), "w") as f:
             json.dump(raw_ids, f)
     manifest = {"version": FORMAT_VERSION, "n_rows": n, "dim": dim, "dtype": dtype, "n_users": len(users),
-                "categories": cat_values, "ids_ascending": ascending, "original_ids": not int_ids}
+                "categories": cat_values, "ids_ascending": ascending, "original_ids": not int_ids,
+                "missing_category": bool(np.any(cats == NO_CATEGORY))}
     with open(os.path.join(path, "manifest.json"), "w") as f:
         json.dump(manifest, f, indent=1)
     return manifest
@@ -206,6 +209,7 @@ def load_collection(path: str, engine, *, name: str = "transactions", row_lo: in
     collection = Collection(name, engine, cf.users, cf.offsets, cf.payload, n_total_rows=cf.n_rows,
                             category_codes=codes, ids_host=ids_host)
     collection.files = cf
+    collection.has_missing_category = bool(cf.manifest.get("missing_category", False))
     if cf.point_ids is not None:                                      # UUID-style ids: hand the original id back to the caller
         collection.point_id_fn = lambda row: cf.point_ids[row]
     return collection

@@ -21,15 +21,15 @@ from typing import Any, Dict, List, Optional
 
 import numpy as np
 
-from .client import Collection, parse_filter
+from .client import Collection, merge_conjunct_lists
 from .qdrant_models import QueryResponse, ScoredPoint
 
 
 class _Request:
-    __slots__ = ("conn", "query", "filt", "k", "skip", "with_payload", "score_threshold", "lock")
+    __slots__ = ("conn", "query", "filts", "k", "skip", "with_payload", "score_threshold", "lock")
 
-    def __init__(self, conn, lock, query, filt, k, skip, with_payload, score_threshold):
-        self.conn, self.lock, self.query, self.filt, self.k = conn, lock, query, filt, k
+    def __init__(self, conn, lock, query, filts, k, skip, with_payload, score_threshold):
+        self.conn, self.lock, self.query, self.filts, self.k = conn, lock, query, filts, k
         self.skip, self.with_payload, self.score_threshold = skip, with_payload, score_threshold
 
 
@@ -99,8 +99,12 @@ class EngineServer:
                         with lock:
                             conn.send({"points": []})
                         continue
-                    filt = self.col.resolve(parse_filter(msg.get("query_filter")))
-                    self._q.put(_Request(conn, lock, q, filt, k, skip, bool(msg.get("with_payload", True)),
+                    filts = self.col.resolve_dnf(msg.get("query_filter"))   # should / must_not: several conjuncts
+                    if not filts:                                            # nothing can match
+                        with lock:
+                            conn.send({"points": []})
+                        continue
+                    self._q.put(_Request(conn, lock, q, filts, k, skip, bool(msg.get("with_payload", True)),
                                          msg.get("score_threshold")))
                 except Exception as e:                             # the caller's blanket except turns it into []
                     with lock:
@@ -135,17 +139,32 @@ class EngineServer:
 
     def _serve(self, k: int, reqs: List[_Request]) -> None:
         try:
-            ids, scores, counts = self.col.engine.search_host(np.stack([r.query for r in reqs]), [r.filt for r in reqs], k)
+            # one row per (request, conjunct); chunks of at most max_batch rows per launch
+            rows_q = [r.query for r in reqs for _ in r.filts]
+            rows_f = [f for r in reqs for f in r.filts]
+            parts = []
+            for lo in range(0, len(rows_f), self.max_batch):
+                parts.append(self.col.engine.search_host(np.stack(rows_q[lo:lo + self.max_batch]),
+                                                         rows_f[lo:lo + self.max_batch], k))
+                self.stats["launches"] += 1
+                self.stats["max_batch"] = max(self.stats["max_batch"], len(rows_f[lo:lo + self.max_batch]))
+            ids = np.concatenate([p[0] for p in parts]); scores = np.concatenate([p[1] for p in parts])
+            counts = np.concatenate([p[2] for p in parts])
             self.stats["requests"] += len(reqs)
-            self.stats["launches"] += 1
-            self.stats["max_batch"] = max(self.stats["max_batch"], len(reqs))
-            for b, r in enumerate(reqs):
+            at = 0
+            for r in reqs:
+                n = len(r.filts)
+                if n == 1:
+                    r_ids, r_sc = ids[at, :int(counts[at])], scores[at, :int(counts[at])]
+                else:
+                    r_ids, r_sc = merge_conjunct_lists(ids[at:at + n], scores[at:at + n], counts[at:at + n], k)
+                at += n
                 pts = []
-                for j in range(r.skip, int(counts[b])):
-                    s = float(scores[b, j])
+                for j in range(r.skip, r_ids.shape[0]):
+                    s = float(r_sc[j])
                     if r.score_threshold is not None and s < r.score_threshold:
                         break
-                    pid = int(ids[b, j])
+                    pid = int(r_ids[j])
                     row = self.col.row_of_id(pid)
                     pts.append({"id": self.col.point_id_fn(row) if self.col.point_id_fn else pid, "version": 0, "score": s,
                                 "payload": self.col.payload_fn(row) if r.with_payload else None, "vector": None})

@@ -20,7 +20,7 @@ from typing import Any, Callable, List, Optional, Sequence
 import numpy as np
 
 from . import _lib
-from .client import B200QdrantClient, Collection, parse_filter
+from .client import B200QdrantClient, Collection
 from .qdrant_models import QueryResponse, ScoredPoint
 
 
@@ -166,14 +166,13 @@ class ShardedB200Client(B200QdrantClient):
         k = int(limit) + skip
         if k < 1:
             return QueryResponse(points=[])
-        filt = col.resolve(parse_filter(query_filter))
-        ids, scores, counts = self._searchers[collection_name].search(q[None, :], [filt], k)
+        ids, scores = col.search_union(self._searchers[collection_name].search, q, col.resolve_dnf(query_filter), k)
         pts = []
-        for j in range(skip, int(counts[0])):
-            s = float(scores[0, j])
+        for j in range(skip, ids.shape[0]):
+            s = float(scores[j])
             if score_threshold is not None and s < score_threshold:
                 break
-            pid = int(ids[0, j])
+            pid = int(ids[j])
             pts.append(ScoredPoint(id=pid, version=0, score=s, vector=None,
                                    payload=col.payload_fn(col.row_of_id(pid)) if with_payload else None))
         return QueryResponse(points=pts)

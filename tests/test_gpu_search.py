@@ -257,3 +257,38 @@ def test_retrieve_transactions_end_to_end(env):
                          dates=hc.dates, date_lo=t0)
     assert out == [hc.payload(int(r))["page_content"] for r in oi] and len(out) == 10
     assert tools.retrieve_transactions(user_id="no-such-user", num_transactions=5) == []
+
+
+def test_should_and_must_not_filters_against_local_mode_model(env):
+    """OR / NOT filters are rewritten into several conjunctions that ride in one grouped launch and are
+    merged on the host (client.py); the selected points must be what the filter model selects."""
+    from financial_chatbot_llm_b200 import qdrant_models as m
+    from financial_chatbot_llm_b200 import synth
+    from financial_chatbot_llm_b200.client import B200QdrantClient
+    from oracle import local_mode
+    hc, eng, col = env
+    cl = B200QdrantClient()
+    cl.attach_collection(col)
+    payloads = [hc.payload(r) for r in range(hc.spec.n_rows)]
+    t1, t2 = int(np.percentile(hc.dates, 30)), int(np.percentile(hc.dates, 70))
+
+    def U(u): return m.FieldCondition(key="metadata.user_id", match=m.MatchValue(value=hc.users[u]))
+    def D(**kw): return m.FieldCondition(key="metadata.date", range=m.Range(**kw))
+    def C(*v): return m.FieldCondition(key="metadata.category", match=m.MatchAny(any=list(v)))
+    filters = [
+        m.Filter(must=[U(3)], must_not=[D(gte=t1, lte=t2)]),                       # before OR after the window
+        m.Filter(must_not=[U(0), U(7)]),                                           # everyone else's rows
+        m.Filter(should=[U(2), U(9), U(17)], must_not=[C("Rent", "Fuel")]),
+        m.Filter(must=[D(gte=t1)], should=[C("Dining"), D(lte=t2)], must_not=[U(5)]),   # overlapping conjuncts
+        m.Filter(must=[U(4)], must_not=[U(4)]),                                    # nothing
+    ]
+    for n_f, flt in enumerate(filters):
+        q = synth.query_vector(hc.spec, 50 + n_f)
+        pts = cl.query_points(collection_name="transactions", query=q.tolist(), limit=12, query_filter=flt).points
+        mask = local_mode.payload_mask(payloads, flt)
+        i_np, s_np = local_mode.search_columns(hc.vectors.copy(), hc.ids, mask, q, 12, inplace_renorm=True)
+        assert [p.id for p in pts] == i_np.tolist(), n_f
+        got = np.array([p.score for p in pts])
+        assert np.all(np.abs(got - s_np) <= REL_TOL_F32 * np.abs(s_np))
+        assert all(local_mode.check_filter(flt, p.payload) for p in pts)
+    assert cl.query_points("transactions", query=q.tolist(), limit=5, query_filter=filters[-1]).points == []

@@ -21,9 +21,70 @@ def test_range_bounds_are_inclusive_integers():
 
 def test_unsupported_filters_raise():
     with pytest.raises(NotImplementedError):
-        client.parse_filter(m.Filter(should=[m.FieldCondition(key="metadata.user_id", match=m.MatchValue(value="a"))]))
+        client.parse_filter(m.Filter(min_should=2, should=[m.FieldCondition(key="metadata.user_id", match=m.MatchValue(value="a"))]))
     with pytest.raises(NotImplementedError):
         client.parse_filter(m.Filter(must=[m.FieldCondition(key="metadata.amount", range=m.Range(gte=1))]))
+    with pytest.raises(NotImplementedError):                                   # two conjuncts do not fit ONE conjunction
+        client.parse_filter(m.Filter(must_not=[m.FieldCondition(key="metadata.date", range=m.Range(gte=5, lte=9))]))
+    # a single should is just a must; a filter nothing can pass resolves to an empty segment
+    pf = client.parse_filter(m.Filter(should=[m.FieldCondition(key="metadata.user_id", match=m.MatchValue(value="a"))]))
+    assert pf.has_user and pf.user_id == "a"
+    pf = client.parse_filter(m.Filter(must=[m.FieldCondition(key="metadata.user_id", match=m.MatchValue(value="a")),
+                                            m.FieldCondition(key="metadata.user_id", match=m.MatchValue(value="b"))]))
+    assert pf.has_user and pf.user_id is None
+
+
+def test_should_and_must_not_rewrite_selects_exactly_what_the_filter_model_selects():
+    """should / must_not become a union of conjunctions (row range AND date range AND category mask):
+    brute-force the union over a small table and compare with the oracle's per-payload filter check."""
+    from oracle import local_mode
+    rng = np.random.default_rng(7)
+    users = ["u%02d" % i for i in range(6)]
+    cats = ["Rent", "Fuel", "Dining", "Other"]
+    sizes = [5, 0, 9, 1, 7, 4]                                   # one user owns no rows
+    offsets = np.concatenate([[0], np.cumsum(sizes)])
+    n = int(offsets[-1])
+    row_user = np.repeat(np.arange(6), sizes)
+    dates = rng.integers(0, 30, n)
+    codes = rng.integers(0, 4, n)
+    payloads = [{"page_content": "x", "metadata": {"user_id": users[row_user[r]], "date": int(dates[r]),
+                                                   "category": cats[codes[r]]}} for r in range(n)]
+    col = client.Collection("t", FakeEngine(), users, offsets, lambda r: payloads[r],
+                            category_codes={c: i for i, c in enumerate(cats)})
+
+    def U(v): return m.FieldCondition(key="metadata.user_id", match=m.MatchValue(value=v))
+    def D(**kw): return m.FieldCondition(key="metadata.date", range=m.Range(**kw))
+    def C(*v): return m.FieldCondition(key="metadata.category", match=m.MatchAny(any=list(v)))
+    filters = [
+        m.Filter(must_not=[U("u02")]),
+        m.Filter(must_not=[U("u02"), U("u04"), U("zz")]),
+        m.Filter(must=[U("u02")], must_not=[D(gte=10, lte=20)]),
+        m.Filter(must_not=[D(gte=10)]), m.Filter(must_not=[D(lt=12.5)]), m.Filter(must_not=[D()]),
+        m.Filter(must_not=[C("Rent", "Fuel")]), m.Filter(must=[C("Rent", "Dining")], must_not=[C("Rent")]),
+        m.Filter(should=[U("u00"), U("u05"), U("u01")]),
+        m.Filter(must=[D(gte=5)], should=[C("Rent"), D(lte=8), U("u04")], must_not=[U("u02"), D(gte=15, lt=18)]),
+        m.Filter(must=[U("u02")], must_not=[U("u02")]), m.Filter(should=[]), m.Filter(must_not=[C("Nope")]),
+        m.Filter(must=[U("u04")], should=[D(lte=3), D(gte=25)], must_not=[C("Other")]),
+    ]
+    rows = np.arange(n)
+    for flt in filters:
+        got = np.zeros(n, dtype=bool)
+        for f in col.resolve_dnf(flt):
+            got |= (rows >= f.row_begin) & (rows < f.row_end) & (dates >= f.date_lo) & (dates <= f.date_hi) & \
+                   (((f.category_mask >> codes.astype(np.uint64)) & 1) == 1)
+        want = local_mode.payload_mask(payloads, flt)
+        assert np.array_equal(got, want), flt
+    # rows without a category must pass must_not(category): the mask cannot say that, so it is refused
+    col.has_missing_category = True
+    with pytest.raises(NotImplementedError):
+        col.resolve_dnf(m.Filter(must_not=[C("Rent")]))
+
+
+def test_union_of_conjunct_lists_drops_duplicates_and_keeps_the_order():
+    ids = np.array([[5, 9, 2, 0], [9, 7, 0, 0], [1, 0, 0, 0]], dtype=np.uint64)
+    sc = np.array([[0.9, 0.8, 0.8, 0], [0.8, 0.85, 0, 0], [0.8, 0, 0, 0]])
+    i, s = client.merge_conjunct_lists(ids, sc, np.array([3, 2, 1]), 4)
+    assert i.tolist() == [5, 7, 1, 2] and s.tolist() == [0.9, 0.85, 0.8, 0.8]
 
 
 class FakeEngine:
