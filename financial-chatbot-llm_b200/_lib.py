@@ -70,6 +70,8 @@ SIGNATURES = {
     "fcb_last_dense_redo": (C.c_int32, [C.c_void_p, C.c_int32]),
     "fcb_aggregate": (C.c_int32, [C.c_void_p, C.c_int64, C.c_int64, C.c_int32, C.c_int32, C.c_int32,
                                   C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "fcb_aggregate_hits": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32,
+                                       C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "fcb_merge_topk": (C.c_int32, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32,
                                    C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "fcb_shard_dates_sorted": (C.c_int32, [C.c_void_p]),

@@ -7,13 +7,17 @@ parses a JSON string with pandas (:29), computes
 path; the drawing is serial CPU work over a handful of groups and is out of
 scope (matplotlib is not installed here).
 
-Two entry levels:
+Three entry levels:
   * ``groupby_user_category_month``  — the bulk path: (user, category, UTC month) sums over the
     device-resident columns of a loaded shard (BASELINE config 5), in pandas' output order.
   * ``grouped_sum_json`` / ``create_financial_plot`` — the tool-shaped path: same arguments as the
     reference tool; the key column becomes the CSR segment, the value column integer cents, and
     the same CUDA kernel does the reduction. Values must be integers or exact cents (x.xx): the
     reference sums float64, this engine sums integers exactly — a deliberate strengthening.
+  * ``grouped_sum_retrieved`` / ``plot_retrieved`` — retrieval and group-by fused on the device (SURVEY.md
+    §8f.4): the agent's round trip retrieve_transactions -> JSON -> create_financial_plot collapses into one
+    search launch plus one tiny reduction launch over the returned points; nothing but the grouped sums
+    comes back to the host.
 """
 from __future__ import annotations
 
@@ -102,6 +106,89 @@ def grouped_sum_json(transactions_json: str, group_by: str, y_axis: str, device:
     return pd.Series(data, index=pd.Index(uniq, name=group_by), name=y_axis)
 
 
+def month_index(ts: int) -> int:
+    """Months since 1970-01 of a unix timestamp (UTC) — the device kernels' month key."""
+    import datetime as _dt
+    d = _dt.datetime.fromtimestamp(int(ts), _dt.timezone.utc)
+    return (d.year - 1970) * 12 + d.month - 1
+
+
+def month_label(mi: int) -> str:
+    return "%04d-%02d" % (1970 + mi // 12, mi % 12 + 1)
+
+
+def grouped_sum_retrieved(collection, query, query_filter, limit: int, group_by, y_axis: str = "amount_cents", *,
+                          month_lo: Optional[int] = None, n_months: Optional[int] = None):
+    """``groupby(group_by)[y_axis].sum()`` over the ``limit`` best points of a filtered search, without the
+    points leaving the GPU. ``group_by``: "category", "month" ("YYYY-MM", UTC) or ["category", "month"];
+    ``y_axis``: "amount_cents" (int64) or "amount" (cents / 100). The month window defaults to the filter's
+    date range (at most 240 months back from its upper bound, or from now). Returns the pandas Series the
+    reference's group-by would give for the retrieved transactions (ascending keys, observed groups only)."""
+    import time
+    import pandas as pd
+    import torch
+    from .client import parse_filter
+    keys = [group_by] if isinstance(group_by, str) else list(group_by)
+    if not keys or any(key not in ("category", "month") for key in keys) or len(set(keys)) != len(keys):
+        raise NotImplementedError(f"group_by {group_by!r}: the device columns offer 'category' and 'month'")
+    if y_axis not in ("amount_cents", "amount"):
+        raise NotImplementedError(f"y_axis {y_axis!r}: the device value column is the amount in integer cents")
+    eng = collection.engine
+    pf = parse_filter(query_filter)                         # one conjunction, like the reference's own filter
+    filt = collection.resolve(pf)
+    names = sorted(collection.category_codes, key=collection.category_codes.get)
+    n_cat = max(collection.category_codes.values()) + 1 if names else 1
+    if n_months is None or month_lo is None:
+        hi = month_index(pf.date_hi if pf.date_hi is not None else time.time())
+        lo = month_index(pf.date_lo) if pf.date_lo is not None else hi - 239
+        lo = max(lo, hi - min(239, 4096 // n_cat - 1))
+        month_lo, n_months = lo, hi - lo + 1
+    dev = torch.device("cuda", eng.device)
+    k = int(limit)
+    q = torch.from_numpy(np.ascontiguousarray(np.asarray(query, dtype=np.float64)[None, :])).to(dev)
+    ids = torch.empty((1, k), dtype=torch.int64, device=dev)
+    scores = torch.empty((1, k), dtype=torch.float64, device=dev)
+    counts = torch.empty(1, dtype=torch.int32, device=dev)
+    eng.search_device(q, [filt], k, ids, scores, counts)
+    sums, present, stats = eng.aggregate_hits(ids, counts, month_lo, n_months, n_cat)
+    sums, present, stats = sums[0].cpu().numpy(), present[0].cpu().numpy().astype(bool), stats.cpu().numpy()
+    if int(stats[0]):
+        raise ValueError(f"{int(stats[0])} retrieved rows fall outside the category/month window")
+    code_name = {c: n for n, c in collection.category_codes.items()}
+    rows = []                                                # (key tuple, cents) of the observed cells
+    for c, m in zip(*np.nonzero(present)):
+        rows.append(({"category": code_name.get(int(c), int(c)), "month": month_label(month_lo + int(m))}, int(sums[c, m])))
+    frame = pd.DataFrame([{**kv, y_axis: v} for kv, v in rows], columns=["category", "month", y_axis])
+    frame[y_axis] = frame[y_axis].astype(np.int64)
+    out = frame.groupby(keys if len(keys) > 1 else keys[0])[y_axis].sum()    # folds the cells of the key not grouped on
+    return out if y_axis == "amount_cents" else out.astype(np.float64) / 100.0
+
+
+def _render(grouped, plot_config: PlotConfig) -> str:
+    """The drawing half of tools/plot_tool.py:43-75 for an already grouped series (a JSON data URI when
+    matplotlib is not importable)."""
+    try:
+        import matplotlib
+        matplotlib.use("Agg")
+        import matplotlib.pyplot as plt
+    except ImportError:
+        body = json.dumps({"title": plot_config.title, "plot_type": plot_config.plot_type,
+                           "labels": [str(x) for x in grouped.index.tolist()],
+                           "values": [float(x) for x in grouped.tolist()]})
+        return "data:application/json;base64," + base64.b64encode(body.encode()).decode()
+    plt.figure(figsize=(10, 6))
+    if plot_config.plot_type == "bar":
+        grouped.plot(kind="bar")
+    else:
+        plt.pie(grouped, labels=grouped.index.astype(str).tolist(), autopct="%1.1f%%")
+    plt.title(plot_config.title)
+    plt.tight_layout()
+    buf = io.BytesIO()
+    plt.savefig(buf, format="png")
+    plt.close()
+    return "data:image/png;base64," + base64.b64encode(buf.getvalue()).decode("utf-8")
+
+
 def create_financial_plot(transactions_json: str, plot_config: PlotConfig) -> str:
     """Tool-shaped entry (reference tools/plot_tool.py:16-78) for the aggregating plot types.
     The group-by runs on the GPU; the figure itself is drawn only when matplotlib is importable,
@@ -109,27 +196,21 @@ def create_financial_plot(transactions_json: str, plot_config: PlotConfig) -> st
     reference's ``"Error creating plot: ..."`` string (:77-78)."""
     try:
         if plot_config.plot_type in ("bar", "pie") and plot_config.group_by and plot_config.y_axis:
-            grouped = grouped_sum_json(transactions_json, plot_config.group_by, plot_config.y_axis)
-            try:
-                import matplotlib
-                matplotlib.use("Agg")
-                import matplotlib.pyplot as plt
-            except ImportError:
-                body = json.dumps({"title": plot_config.title, "plot_type": plot_config.plot_type,
-                                   "labels": [str(x) for x in grouped.index.tolist()],
-                                   "values": [float(x) for x in grouped.tolist()]})
-                return "data:application/json;base64," + base64.b64encode(body.encode()).decode()
-            plt.figure(figsize=(10, 6))
-            if plot_config.plot_type == "bar":
-                grouped.plot(kind="bar")
-            else:
-                plt.pie(grouped, labels=grouped.index.astype(str).tolist(), autopct="%1.1f%%")
-            plt.title(plot_config.title)
-            plt.tight_layout()
-            buf = io.BytesIO()
-            plt.savefig(buf, format="png")
-            plt.close()
-            return "data:image/png;base64," + base64.b64encode(buf.getvalue()).decode("utf-8")
+            return _render(grouped_sum_json(transactions_json, plot_config.group_by, plot_config.y_axis), plot_config)
+        raise NotImplementedError(f"plot_type {plot_config.plot_type!r} without group_by/y_axis has no "
+                                  "reduction and is not part of the GPU path")
+    except Exception as e:
+        return f"Error creating plot: {str(e)}"
+
+
+def plot_retrieved(collection, query, query_filter, limit: int, plot_config: PlotConfig) -> str:
+    """``create_financial_plot`` over the transactions a retrieval selects, with both steps on the device:
+    same ``PlotConfig`` and same return convention, but the first argument is the retrieval (collection, query
+    vector, qdrant filter, limit) instead of its JSON."""
+    try:
+        if plot_config.plot_type in ("bar", "pie") and plot_config.group_by and plot_config.y_axis:
+            return _render(grouped_sum_retrieved(collection, query, query_filter, limit, plot_config.group_by,
+                                                 plot_config.y_axis), plot_config)
         raise NotImplementedError(f"plot_type {plot_config.plot_type!r} without group_by/y_axis has no "
                                   "reduction and is not part of the GPU path")
     except Exception as e:

@@ -491,3 +491,149 @@ extern "C" int32_t fcb_aggregate(fcb_engine *e, int64_t seg_begin, int64_t seg_e
     FCB_CUDA(e, cudaGetLastError());
     return FCB_OK;
 }
+
+// ---- group-by over the points a search just returned ------------------------------
+// One CTA per query: each returned point id is mapped back to its row (ids absent: id - row_base; ids
+// ascending: binary search; otherwise binary search through the inverse of id_rank), the row's cents are
+// added to the CTA's shared [category, month] cells with 64-bit shared-memory atomics (at most 10000
+// points per query: latency-bound, not a bandwidth problem), and the cells are written out densely.
+struct AggHitsParams {
+    const uint64_t *hit_ids;               // [batch, k] as written by fcb_search
+    const int32_t *hit_counts;             // [batch]
+    int k;
+    const uint64_t *ids;                   // shard columns (device)
+    const uint32_t *row_of_rank;           // inverse of id_rank, or NULL when the ids ascend with the rows
+    const int32_t *dates;
+    const uint8_t *cats;
+    const int32_t *cents;
+    int64_t row_base, n_rows;
+    int32_t month_lo, n_months, n_categories;
+    int64_t *sums;                         // [batch, n_categories, n_months]
+    uint8_t *present;
+    unsigned long long *stats;             // [0] rows outside the window, [1] points not resident in this shard
+};
+
+__global__ void __launch_bounds__(256) aggregate_hits_kernel(const __grid_constant__ AggHitsParams p) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int C = p.n_categories * p.n_months;
+    unsigned long long *cells = reinterpret_cast<unsigned long long *>(smem_raw);   // [C]
+    uint8_t *seen = reinterpret_cast<uint8_t *>(cells + C);                          // [C]
+    const int tid = threadIdx.x, b = blockIdx.x;
+    for (int c = tid; c < C; c += blockDim.x) { cells[c] = 0; seen[c] = 0; }
+    __syncthreads();
+    int n = p.hit_counts[b];
+    if (n > p.k) n = p.k;
+    unsigned dropped = 0, absent = 0;
+    for (int j = tid; j < n; j += blockDim.x) {
+        const uint64_t id = p.hit_ids[(int64_t)b * p.k + j];
+        int64_t row = -1;
+        if (!p.ids) {
+            const int64_t r = (int64_t)id - p.row_base;
+            if (id <= (uint64_t)INT64_MAX && r >= 0 && r < p.n_rows) row = r;
+        } else {
+            int64_t lo = 0, hi = p.n_rows;                          // first position whose id is >= the point's
+            while (lo < hi) {
+                const int64_t mid = (lo + hi) >> 1;
+                const uint64_t at = p.ids[p.row_of_rank ? (int64_t)p.row_of_rank[mid] : mid];
+                if (at < id) lo = mid + 1; else hi = mid;
+            }
+            if (lo < p.n_rows) {
+                const int64_t r = p.row_of_rank ? (int64_t)p.row_of_rank[lo] : lo;
+                if (p.ids[r] == id) row = r;
+            }
+        }
+        if (row < 0) { ++absent; continue; }
+        const unsigned cat = p.cats[row];
+        const int32_t mo = month_of_day(floor_day(p.dates[row])) - p.month_lo;
+        if (cat >= (unsigned)p.n_categories || mo < 0 || mo >= p.n_months) { ++dropped; continue; }
+        const int cell = cat * p.n_months + mo;
+        atomicAdd(&cells[cell], (unsigned long long)(long long)p.cents[row]);
+        seen[cell] = 1;
+    }
+    __syncthreads();
+    for (int c = tid; c < C; c += blockDim.x) {
+        p.sums[(int64_t)b * C + c] = (int64_t)cells[c];
+        p.present[(int64_t)b * C + c] = seen[c];
+    }
+    if (dropped) atomicAdd(p.stats, (unsigned long long)dropped);
+    if (absent) atomicAdd(p.stats + 1, (unsigned long long)absent);
+}
+
+__global__ void __launch_bounds__(256) invert_rank_kernel(const uint32_t *__restrict__ id_rank, int64_t n_rows,
+                                                          uint32_t *__restrict__ row_of_rank, unsigned *__restrict__ bad) {
+    for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < n_rows; r += (int64_t)gridDim.x * blockDim.x) {
+        const uint32_t k = id_rank[r];
+        if ((int64_t)k < n_rows) row_of_rank[k] = (uint32_t)r; else atomicAdd(bad, 1u);
+    }
+}
+
+__global__ void __launch_bounds__(256) count_unset_kernel(const uint32_t *__restrict__ row_of_rank, int64_t n_rows,
+                                                          unsigned *__restrict__ bad) {
+    for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < n_rows; r += (int64_t)gridDim.x * blockDim.x)
+        if (row_of_rank[r] == 0xffffffffu) atomicAdd(bad, 1u);
+}
+
+// the inverse of id_rank, built on first use (ids that do not ascend with the rows)
+static int32_t build_row_of_rank(fcb_engine *e, cudaStream_t st) {
+    const fcb_shard &s = e->shard;
+    if (s.n_rows >= 0xffffffffLL) return fcb_fail(e, FCB_ERR_UNSUPPORTED, "fcb_aggregate_hits: too many rows for a 32-bit row map");
+    uint32_t *map = nullptr;
+    unsigned *bad = nullptr;
+    if (cudaMalloc(&map, (size_t)s.n_rows * sizeof(uint32_t)) != cudaSuccess || cudaMalloc(&bad, sizeof(unsigned)) != cudaSuccess) {
+        cudaGetLastError();
+        cudaFree(map);
+        return fcb_fail(e, FCB_ERR_NOMEM, "fcb_aggregate_hits: cannot allocate the %zu-byte row map", (size_t)s.n_rows * 4);
+    }
+    cudaMemsetAsync(map, 0xff, (size_t)s.n_rows * sizeof(uint32_t), st);
+    cudaMemsetAsync(bad, 0, sizeof(unsigned), st);
+    invert_rank_kernel<<<e->num_sms * 8, 256, 0, st>>>(s.id_rank, s.n_rows, map, bad);
+    count_unset_kernel<<<e->num_sms * 8, 256, 0, st>>>(map, s.n_rows, bad);
+    unsigned h_bad = 0;
+    cudaMemcpyAsync(&h_bad, bad, sizeof(unsigned), cudaMemcpyDeviceToHost, st);
+    const cudaError_t err = cudaStreamSynchronize(st);
+    cudaFree(bad);
+    if (err != cudaSuccess || h_bad) {
+        cudaFree(map);
+        if (err != cudaSuccess) return fcb_fail(e, FCB_ERR_CUDA, "fcb_aggregate_hits: %s", cudaGetErrorString(err));
+        return fcb_fail(e, FCB_ERR_UNSUPPORTED, "fcb_aggregate_hits: id_rank is not a permutation of this shard's rows");
+    }
+    e->row_of_rank = map;
+    return FCB_OK;
+}
+
+extern "C" int32_t fcb_aggregate_hits(fcb_engine *e, const uint64_t *hit_ids, const int32_t *hit_counts, int32_t batch,
+                                      int32_t k, int32_t month_lo, int32_t n_months, int32_t n_categories, int64_t *sums,
+                                      uint8_t *present, uint64_t *stats, void *stream) {
+    if (!e) return FCB_ERR_INVALID;
+    if (!e->loaded) return fcb_fail(e, FCB_ERR_STATE, "fcb_aggregate_hits: no shard loaded");
+    const fcb_shard &s = e->shard;
+    if (!s.dates || !s.categories || !s.cents)
+        return fcb_fail(e, FCB_ERR_STATE, "fcb_aggregate_hits: the shard needs dates, categories and cents");
+    if (!hit_ids || !hit_counts || !sums || !present || !stats)
+        return fcb_fail(e, FCB_ERR_INVALID, "fcb_aggregate_hits: NULL argument");
+    if (batch < 0 || k < 1) return fcb_fail(e, FCB_ERR_INVALID, "fcb_aggregate_hits: need batch >= 0 and k >= 1");
+    if (n_months < 1 || n_months > AGG_MAX_MONTHS || n_categories < 1 || n_categories > 64 ||
+        (int64_t)n_months * n_categories > AGG_MAX_CELLS)
+        return fcb_fail(e, FCB_ERR_UNSUPPORTED, "fcb_aggregate_hits: need 1..%d months, 1..64 categories, <= %d cells per query",
+                        AGG_MAX_MONTHS, AGG_MAX_CELLS);
+    FcbDeviceGuard g(e->device);
+    if (!g.ok) return fcb_fail(e, FCB_ERR_CUDA, "fcb_aggregate_hits: cannot select device %d", e->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    FCB_CUDA(e, cudaMemsetAsync(stats, 0, 2 * sizeof(uint64_t), st));
+    if (batch == 0) return FCB_OK;
+    if (s.id_rank && !e->row_of_rank) {
+        const int32_t rc = build_row_of_rank(e, st);
+        if (rc != FCB_OK) return rc;
+    }
+    AggHitsParams p{};
+    p.hit_ids = hit_ids; p.hit_counts = hit_counts; p.k = k;
+    p.ids = s.ids; p.row_of_rank = s.id_rank ? e->row_of_rank : nullptr;
+    p.dates = s.dates; p.cats = s.categories; p.cents = s.cents;
+    p.row_base = s.row_base; p.n_rows = s.n_rows;
+    p.month_lo = month_lo; p.n_months = n_months; p.n_categories = n_categories;
+    p.sums = sums; p.present = present; p.stats = (unsigned long long *)stats;
+    const size_t smem = (size_t)n_months * n_categories * 9;
+    aggregate_hits_kernel<<<batch, 256, smem, st>>>(p);
+    FCB_CUDA(e, cudaGetLastError());
+    return FCB_OK;
+}

@@ -38,6 +38,7 @@ extern "C" int32_t fcb_close(fcb_engine *e) {
         cudaDeviceSynchronize();
         free_host_staging(e);
         cudaFree(e->inv_norm);
+        cudaFree(e->row_of_rank);
         fcb_general_free(e);
         fcb_dense_free(e);
         cudaFree(e->d_filters);
@@ -171,6 +172,7 @@ extern "C" int32_t fcb_load_shard(fcb_engine *e, const fcb_shard *s) {
 
     e->loaded = false;
     cudaFree(e->inv_norm); e->inv_norm = nullptr;
+    cudaFree(e->row_of_rank); e->row_of_rank = nullptr;
     fcb_general_free(e);
     fcb_dense_free(e);
     free_host_staging(e);

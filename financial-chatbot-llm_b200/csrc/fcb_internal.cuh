@@ -64,6 +64,7 @@ struct fcb_engine {
     int kprime_max = 0;
 
     int dates_sorted = 0;                  // load-time check: dates non-decreasing within every user
+    uint32_t *row_of_rank = nullptr;       // inverse of shard.id_rank, built by fcb_aggregate_hits on first use
     void *dense = nullptr;                 // FcbDense* (fcb_dense.cu): batched tensor-core path scratch
 
     float last_ms = -1.f;

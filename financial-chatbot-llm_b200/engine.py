@@ -131,6 +131,24 @@ class Engine:
                                       C.c_void_p(stream)), self._h)
         return sums, present, dropped
 
+    def aggregate_hits(self, hit_ids, hit_counts, month_lo: int, n_months: int, n_categories: int,
+                       stream: Optional[int] = None):
+        """fcb_aggregate_hits: (category, month) sums over the points a search returned. ``hit_ids`` int64/uint64
+        CUDA [B, k] and ``hit_counts`` int32 CUDA [B] as written by ``search_device``. Returns CUDA tensors
+        (sums int64 [B, C, M], present uint8 [B, C, M], stats int64 [2]); asynchronous on torch's current stream."""
+        import torch
+        dev = torch.device("cuda", self.device)
+        B, k = hit_ids.shape
+        sums = torch.empty((B, n_categories, n_months), dtype=torch.int64, device=dev)
+        present = torch.empty((B, n_categories, n_months), dtype=torch.uint8, device=dev)
+        stats = torch.empty(2, dtype=torch.int64, device=dev)
+        if stream is None:
+            stream = torch.cuda.current_stream(self.device).cuda_stream
+        check(self._lib.fcb_aggregate_hits(self._h, hit_ids.data_ptr(), hit_counts.data_ptr(), B, k, month_lo, n_months,
+                                           n_categories, sums.data_ptr(), present.data_ptr(), stats.data_ptr(),
+                                           C.c_void_p(stream)), self._h)
+        return sums, present, stats
+
     @property
     def last_search_ms(self) -> float:
         return float(self._lib.fcb_last_search_ms(self._h))

@@ -187,6 +187,22 @@ int32_t fcb_aggregate(fcb_engine *e, int64_t seg_begin, int64_t seg_end, int32_t
                       int32_t n_months, int32_t n_categories, int64_t *sums, uint8_t *present,
                       uint64_t *dropped, void *stream);
 
+/* Group-by over the points a search just returned: the reference's agent feeds the
+ * output of retrieve_transactions (tools/qdrant_tool.py:147-170) back through JSON into
+ * transactions.groupby(...)[...].sum() (tools/plot_tool.py:29,45,52); here the ids fcb_search wrote stay on
+ * the device and their rows' cents are summed per (category, UTC calendar month) directly.
+ *   hit_ids / hit_counts   device outputs of fcb_search for `batch` queries with this `k` (same stream, or ordered
+ *                          after it)
+ *   sums / present         device int64 / uint8 [batch, n_categories, n_months], written densely (see fcb_aggregate)
+ *   stats                  device uint64 [2]: [0] returned points whose category / month fall outside the window,
+ *                          [1] returned points that are not rows of this shard (a sharded search returns points of
+ *                          other shards too: each rank sums its own, the per-rank sums add up)
+ * Window limits as for fcb_aggregate. When the shard's ids do not ascend with the rows (id_rank given), the first
+ * call builds a 4-byte-per-row inverse map: it allocates and synchronises once. Asynchronous on `stream`. */
+int32_t fcb_aggregate_hits(fcb_engine *e, const uint64_t *hit_ids, const int32_t *hit_counts, int32_t batch,
+                           int32_t k, int32_t month_lo, int32_t n_months, int32_t n_categories, int64_t *sums,
+                           uint8_t *present, uint64_t *stats, void *stream);
+
 /* The exchange step of the sharded search (north_star: "each shard computes a local top-k and the
  * k x shards candidates are merged after a small NCCL allgather"). No counterpart in the
  * reference, whose Qdrant server merges its own segments internally. Inputs are the

@@ -6,6 +6,7 @@
    k10000     whale, k = 10000 (general-k path)
    bf16-b1    10M x 1536 bf16 whale, batch 1
    cfg5       1B-row aggregation (user x category x month), 100k users
+   fused      whale, k = 10000 retrieval + (category, month) group-by of the returned points, both on the device
 Timing: CUDA events on the launching stream, >= 3 warm-ups, inputs >> L2 (or stated)."""
 import argparse
 import json
@@ -131,6 +132,32 @@ def search_bench(args):
     torch.cuda.empty_cache()
 
 
+def fused_bench(args):
+    rows, dim, k = args.rows, 1536, 10000
+    spec = synth.SynthSpec(n_rows=rows, dim=dim, seed=1, n_users=1)
+    eng = Engine(device=0, max_batch=1, max_k=k)
+    loader.collection_synthetic(spec, eng)
+    qs = [torch.from_numpy(synth.query_vector(spec, i)[None, :]).to(DEV) for i in range(8)]
+    oi = torch.empty((1, k), dtype=torch.int64, device=DEV); os_ = torch.empty((1, k), dtype=torch.float64, device=DEV)
+    oc = torch.empty(1, dtype=torch.int32, device=DEV)
+    fall = [make_filter(0, rows, synth.DATE_BASE, None)]
+    mlo = (2022 - 1970) * 12
+    ms_s, _ = timed(lambda i: eng.search_device(qs[i % 8], fall, k, oi, os_, oc), args.steps)
+    out = {}
+    def both(i):
+        eng.search_device(qs[i % 8], fall, k, oi, os_, oc)
+        out["r"] = eng.aggregate_hits(oi, oc, mlo, 24, 16)
+    ms, p50 = timed(both, args.steps)
+    sums, present, stats = out["r"]
+    torch.cuda.synchronize()
+    total = int(eng._keep[5][oi[0].long()].long().sum().item())      # ids = rows here: the cents of the returned points
+    emit("fused: whale, k=10000 retrieval + (category, month) group-by of the returned points", ms, p50,
+         rows * dim * 4 + rows * 4 + rows * 8, qps=1e3 / ms, search_only_ms=ms_s, groupby_ms=ms - ms_s,
+         checksum_ok=bool(int(sums.sum().item()) == total and int(stats.sum().item()) == 0), groups=int(present.sum().item()))
+    eng.close(); del eng
+    torch.cuda.empty_cache()
+
+
 def agg_bench(args):
     n, users = args.agg_rows, 100_000
     spec = synth.SynthSpec(n_rows=n, dim=4, n_users=users, seed=5, zipf_a=1.1)
@@ -178,6 +205,8 @@ if __name__ == "__main__":
     ap.add_argument("--only", default="")
     a = ap.parse_args()
     graft.build()
+    if a.only in ("", "fused"):
+        fused_bench(a)
     if a.only in ("", "agg"):
         agg_bench(a)
     if a.only in ("", "search"):

@@ -193,3 +193,52 @@ def test_atomic_free_kernel_is_correct_for_any_row_order(built, monkeypatch):
     assert u.tolist() == idx["user"].tolist() and cat.tolist() == idx["category"].tolist()
     assert mo.tolist() == idx["month"].tolist() and s.tolist() == ser.tolist()
     eng.close()
+
+
+@pytest.mark.parametrize("id_layout", ["rows", "ascending", "permuted"])
+def test_group_by_over_retrieved_points_equals_pandas_on_their_payloads(built, id_layout):
+    """Retrieval + group-by fused on the device (fcb_aggregate_hits) vs the reference's round trip: take the
+    payloads query_points returns, build the DataFrame, groupby(...)[...].sum() (tools/plot_tool.py:29,45)."""
+    import dataclasses
+    import pandas as pd
+    from financial_chatbot_llm_b200 import aggregate, loader, synth
+    from financial_chatbot_llm_b200 import qdrant_models as m
+    from financial_chatbot_llm_b200.client import B200QdrantClient
+    from financial_chatbot_llm_b200.engine import Engine
+    spec = synth.SynthSpec(n_rows=20000, dim=64, n_users=7, seed=31)
+    hc = synth.make_host_corpus(spec)
+    if id_layout == "ascending":
+        hc = dataclasses.replace(hc, ids=(np.arange(spec.n_rows, dtype=np.uint64) * np.uint64(3) + np.uint64(10 ** 9)))
+    elif id_layout == "permuted":
+        hc = dataclasses.replace(hc, ids=np.random.default_rng(5).permutation(spec.n_rows).astype(np.uint64) + np.uint64(77))
+    eng = Engine(device=0, max_batch=1, max_k=2000)
+    col = loader.collection_from_host(hc, eng, with_ids=id_layout != "rows")
+    cl = B200QdrantClient()
+    cl.attach_collection(col)
+    t0 = int(np.percentile(hc.dates, 35))
+    for u, limit in [(2, 10), (4, 700), (0, 2000)]:
+        q = synth.query_vector(spec, 90 + u)
+        flt = m.Filter(must=[m.FieldCondition(key="metadata.user_id", match=m.MatchValue(value=hc.users[u])),
+                             m.FieldCondition(key="metadata.date", range=m.Range(gte=t0))])
+        pts = cl.query_points("transactions", query=q.tolist(), limit=limit, query_filter=flt).points
+        assert len(pts) == min(limit, int(np.sum(hc.dates[hc.offsets[u]:hc.offsets[u + 1]] >= t0)))
+        frame = pd.DataFrame([p.payload["metadata"] for p in pts])
+        frame["month"] = pd.to_datetime(frame["date"], unit="s", utc=True).dt.strftime("%Y-%m")
+        frame["amount"] = frame["amount_cents"] / 100.0
+        for keys in ("category", "month", ["category", "month"], ["month", "category"]):
+            want = frame.groupby(keys)["amount_cents"].sum()
+            got = aggregate.grouped_sum_retrieved(col, q, flt, limit, keys, "amount_cents")
+            assert got.index.tolist() == want.index.tolist() and got.tolist() == want.tolist(), (id_layout, u, keys)
+        got = aggregate.grouped_sum_retrieved(col, q, flt, limit, "category", "amount")
+        want = frame.groupby("category")["amount_cents"].sum() / 100.0
+        assert got.index.tolist() == want.index.tolist() and got.tolist() == want.tolist()
+    # the tool-shaped wrapper: same return convention as create_financial_plot
+    out = aggregate.plot_retrieved(col, q, flt, 50, aggregate.PlotConfig(plot_type="bar", x_axis="category",
+                                                                        y_axis="amount", title="t", group_by="category"))
+    assert out.startswith("data:")
+    assert aggregate.plot_retrieved(col, q, flt, 50, aggregate.PlotConfig(plot_type="bar", x_axis="x", y_axis="amount",
+                                                                          title="t", group_by="merchant")).startswith("Error creating plot")
+    # an unknown user retrieves nothing: empty series, no error
+    none = m.Filter(must=[m.FieldCondition(key="metadata.user_id", match=m.MatchValue(value="nobody"))])
+    assert len(aggregate.grouped_sum_retrieved(col, q, none, 10, "category")) == 0
+    eng.close()
