@@ -12,7 +12,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "csrc", "libfcb200.so")
+LIB_PATH = os.environ.get("FCB_LIB_PATH") or os.path.join(_HERE, "csrc", "libfcb200.so")   # override: A/B of two builds
 
 FCB_OK = 0
 FCB_ERR_INVALID, FCB_ERR_CUDA, FCB_ERR_NOMEM, FCB_ERR_STATE, FCB_ERR_UNSUPPORTED = -1, -2, -3, -4, -5

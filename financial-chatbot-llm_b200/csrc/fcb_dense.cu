@@ -59,7 +59,8 @@ struct DenseParams {
     int64_t debug_rows;
     long long *prof;                        // diagnostic: per-role cycle counters of CTA 0 (NULL in production)
     int n_stages;                           // cta_group::2 kernel: depth of the shared-memory ring (3 or 4)
-    unsigned *gthr;                         // [DN_N] best per-CTA 32nd-best score so far, order-preserving uint (cta_group::2 kernel)
+    unsigned *gtop;                         // [DN_N][gt_stride] best score of every CTA's list, order-preserving uint (cta_group::2 kernel)
+    int gt_stride;
 };
 
 // ---- PTX wrappers -----------------------------------------------------------------------------
@@ -383,12 +384,13 @@ dense_topk2_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
     const int n_stages = p.n_stages;
     uint64_t *full_bar = reinterpret_cast<uint64_t *>(smem + n_stages * DN2_STAGE_BYTES);
     uint64_t *empty_bar = full_bar + DN2_MAX_STAGES;
-    uint64_t *tmem_full = empty_bar + DN2_MAX_STAGES;
-    uint64_t *tmem_empty = tmem_full + 1;
-    uint32_t *tmem_ptr = reinterpret_cast<uint32_t *>(tmem_empty + 1);
+    uint64_t *tmem_full = empty_bar + DN2_MAX_STAGES;                 // [2]: one per accumulator set
+    uint64_t *tmem_empty = tmem_full + 2;                             // [2]
+    uint32_t *tmem_ptr = reinterpret_cast<uint32_t *>(tmem_empty + 2);
     float *thr_s = reinterpret_cast<float *>(smem + n_stages * DN2_STAGE_BYTES + 256);   // [DN_N], 16-byte aligned
     int *cnt_s = reinterpret_cast<int *>(thr_s + DN_N);              // [DN_N]
-    float *thr_min_s = reinterpret_cast<float *>(cnt_s + DN_N);      // [DN_N / 32]: lowest threshold of each 32-query chunk
+    float *gb_s = reinterpret_cast<float *>(cnt_s + DN_N);           // [DN_N] cross-CTA bound of each query (written by the gossip warps)
+    volatile int *gb_seq = reinterpret_cast<volatile int *>(gb_s + DN_N);   // super-tiles this CTA has published; -1 = finished
     FcbCand *top_s = reinterpret_cast<FcbCand *>(smem + n_stages * DN2_STAGE_BYTES + 4096);   // [DN_N][32] sorted lists
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -403,6 +405,10 @@ dense_topk2_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
     const int n_super = (int)((nrows + DN2_SUPER_M - 1) / DN2_SUPER_M);
     const int k_stages = p.dim / DN_BLOCK_K;
     const int n_half = p.n_eff / 2;                                    // query rows this CTA stages
+    // TMEM: 512 columns. Up to 128 queries the two accumulators of a super-tile take 256 of them, so there are two
+    // SETS and the MMAs of super-tile t + 1 run while the epilogue still scans super-tile t; above, one set.
+    const bool dbuf = p.n_eff <= DN_N / 2;
+    const uint32_t acc_stride = dbuf ? DN_N / 2 : DN_N;
 
     FcbCand *my_top = p.cta_top + (size_t)blockIdx.x * DN_N * FCB_FUSED_CAND;
     FcbCand *my_pend = p.pend + (size_t)blockIdx.x * DN_N * DN_PEND_CAP;
@@ -413,8 +419,10 @@ dense_topk2_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
     }
     if (warp == 1 && lane == 0) {
         for (int s = 0; s < n_stages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
-        mbar_init(tmem_full, 1);
-        mbar_init(tmem_empty, 2 * DN2_EPI_THREADS);                    // the epilogue threads of both CTAs
+        for (int a = 0; a < 2; ++a) {
+            mbar_init(&tmem_full[a], 1);
+            mbar_init(&tmem_empty[a], 2 * DN2_EPI_THREADS);            // the epilogue threads of both CTAs
+        }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 2) {
@@ -422,7 +430,8 @@ dense_topk2_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
     }
     for (int i = tid; i < DN_N; i += DN2_THREADS) { thr_s[i] = i < p.n_queries ? -INFINITY : INFINITY; cnt_s[i] = 0; }   // padding never qualifies
-    if (tid < DN_N / 32) thr_min_s[tid] = -INFINITY;
+    for (int i = tid; i < DN_N; i += DN2_THREADS) gb_s[i] = -INFINITY;
+    if (tid == 0) *gb_seq = 0;
     for (int i = tid; i < p.n_eff * FCB_FUSED_CAND; i += DN2_THREADS) top_s[i] = FcbCand{-INFINITY, FCB_NO_ROW};
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
@@ -464,7 +473,9 @@ dense_topk2_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
             long long w_tmem = 0, w_full = 0, t_begin = clock64();
             for (int st = pair; st < n_super; st += n_pairs, ++it) {
                 long long t0 = clock64();
-                mbar_wait(tmem_empty, (it & 1) ^ 1, p.error_flag, 12);
+                const int set = dbuf ? (it & 1) : 0, use = dbuf ? (it >> 1) : it;     // accumulator set and how often it was used
+                const uint32_t acc0 = tmem_base + set * DN_N, acc1 = acc0 + acc_stride;
+                mbar_wait(&tmem_empty[set], (use & 1) ^ 1, p.error_flag, 12);
                 w_tmem += clock64() - t0;
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 for (int ks = 0; ks < k_stages; ++ks) {
@@ -477,15 +488,55 @@ dense_topk2_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
                                    b = make_sw128_desc(sa + 2 * DN_A_BYTES);
 #pragma unroll
                     for (int kk = 0; kk < DN_BLOCK_K / 16; ++kk) {
-                        umma_bf16_2sm(tmem_base, a0 + 2 * kk, b + 2 * kk, idesc, (ks | kk) != 0);
-                        umma_bf16_2sm(tmem_base + DN_N, a1 + 2 * kk, b + 2 * kk, idesc, (ks | kk) != 0);
+                        umma_bf16_2sm(acc0, a0 + 2 * kk, b + 2 * kk, idesc, (ks | kk) != 0);
+                        umma_bf16_2sm(acc1, a1 + 2 * kk, b + 2 * kk, idesc, (ks | kk) != 0);
                     }
                     umma_commit_2sm(&empty_bar[stage]);
                     if (++stage == n_stages) { stage = 0; phase ^= 1; }
                 }
-                umma_commit_2sm(tmem_full);
+                umma_commit_2sm(&tmem_full[set]);
             }
             if (p.prof && blockIdx.x == 0) { p.prof[2] = clock64() - t_begin; p.prof[3] = w_tmem; p.prof[4] = w_full; }
+        }
+    } else if (warp == 2 || warp == 3) {
+        // ================= gossip warps: cross-CTA pruning bound, off everybody's critical path =================
+        // Every CTA publishes the best score of each of its lists (p.gtop[query][cta]). The CTAs' best rows are distinct
+        // rows, so any value that at least 32 of them reach bounds the final global 32nd best from below. Lane l takes
+        // the maximum over CTAs l, l + 32, ...; the minimum of the 32 lane maxima is reached by one CTA in every lane's
+        // group, i.e. by >= 32 rows. With ~148 CTAs this lets through only ~4x the rows an exact global threshold would
+        // (a CTA's own 32nd best: ~150x), which keeps the epilogue's slow path and the fold rare. Lowered one ulp so
+        // that a row tying with it still gets through (it may win the tie on id). Stale reads are harmless: every
+        // value ever published is a valid bound.
+        int seen = 0;
+        for (;;) {
+            const int seq = *gb_seq;
+            if (seq < 0) break;
+            if (seq < seen + (seen < 4 ? 1 : 4)) { __nanosleep(500); continue; }   // early super-tiles move the bound most
+            seen = seq;
+#pragma unroll 1
+            for (int q0 = (warp - 2) * 8; q0 < p.n_queries; q0 += 16) {      // 8 queries per round trip, the two warps alternate
+                unsigned m[8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u) {                                // 40 independent L2 loads in flight per lane
+                    const int qq = q0 + u < p.n_queries ? q0 + u : q0;
+                    const unsigned *g = p.gtop + (size_t)qq * p.gt_stride;
+                    unsigned mm = 0;
+#pragma unroll
+                    for (int t = 0; t < 5; ++t) {
+                        const int c = lane + 32 * t;
+                        const unsigned v = c < (int)gridDim.x ? __ldcg(g + c) : 0u;
+                        mm = max(mm, v);
+                    }
+                    m[u] = mm;
+                }
+#pragma unroll
+                for (int u = 0; u < 8; ++u) {
+                    unsigned v = m[u];
+#pragma unroll
+                    for (int off = 16; off >= 1; off >>= 1) v = min(v, __shfl_xor_sync(FCB_FULL, v, off));
+                    if (lane == 0 && q0 + u < p.n_queries && v > dn_ord(-INFINITY)) gb_s[q0 + u] = dn_unord(v - 1);
+                }
+            }
         }
     } else if (warp >= 4) {
         // ================= epilogue (both CTAs; TMEM lane = row of this CTA's half) =================
@@ -506,12 +557,14 @@ dense_topk2_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
             const float inv = valid ? p.inv_norm[row] : 0.f;
 
             long long t0 = clock64();
-            mbar_wait(tmem_full, it & 1, p.error_flag, 14);
+            const int set = dbuf ? (it & 1) : 0, use = dbuf ? (it >> 1) : it;
+            mbar_wait(&tmem_full[set], use & 1, p.error_flag, 14);
             long long t1 = clock64();
             w_acc += t1 - t0;
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            const uint32_t taddr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + acc * DN_N;
-            const int c_begin = col_half * (DN_N / 2), c_end = min(p.n_eff, c_begin + DN_N / 2);
+            const uint32_t taddr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + set * DN_N + acc * acc_stride;
+            const int c_half = dbuf ? DN_N / 4 : DN_N / 2;                 // columns per warp: half of an accumulator's width
+            const int c_begin = col_half * c_half, c_end = min(p.n_eff, c_begin + c_half);
             // one 16-column chunk of this row: branch-free pass mask (thresholds: 4 broadcast 128-bit shared loads),
             // then the rare survivors are pushed from an unrolled bit scan (no dynamic register indexing)
             auto process = [&](const uint32_t (&v)[16], const int c) {
@@ -566,7 +619,7 @@ dense_topk2_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
                 asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
             }
             asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-            mbar_arrive_cta0(tmem_empty);                              // the leader's MMA may overwrite both TMEMs
+            mbar_arrive_cta0(&tmem_empty[set]);                        // the leader's MMA may overwrite this set in both TMEMs
             __threadfence_block();
             asm volatile("bar.sync 1, 512;" ::: "memory");
             t0 = clock64();
@@ -615,35 +668,26 @@ dense_topk2_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
                             }
                         }
                         top_s[q * FCB_FUSED_CAND + lane] = e;
-                        if (lane == 31) thr_s[q] = e.score;
+                        if (lane == 31) thr_s[q] = fmaxf(thr_s[q], e.score);   // never below a cross-CTA bound adopted earlier
                         if (lane == 0) cnt_s[q] = 0;
                     }
                 }
             }
             asm volatile("bar.sync 1, 512;" ::: "memory");
-            // thresholds across CTAs: a CTA's 32nd-best score bounds the GLOBAL 32nd best from below, so every
-            // CTA may prune with the best such bound published so far (one ulp lower, so that a row tying with it
-            // still gets through — it may win the tie on id). Cuts the survivors per CTA by ~the number of CTAs.
+            // thresholds across CTAs: publish the BEST first-pass score of each of this CTA's lists, adopt the bound the
+            // gossip warps derived from everybody's (see there). A bound is never lowered.
             {
                 const int q = (int)threadIdx.x - 128;                        // epilogue threads 0..511 <-> queries
                 if (q >= 0 && q < p.n_queries) {
-                    const float mine = thr_s[q];
-                    const unsigned om = dn_ord(mine);
-                    const unsigned g = max(atomicMax(&p.gthr[q], om), om);
-                    const float lowered = g > dn_ord(-INFINITY) ? dn_unord(g - 1) : -INFINITY;   // previous float in order
-                    thr_s[q] = fmaxf(mine, lowered);
+                    __stcg(&p.gtop[(size_t)q * p.gt_stride + blockIdx.x], dn_ord(top_s[q * FCB_FUSED_CAND].score));
+                    thr_s[q] = fmaxf(thr_s[q], *reinterpret_cast<volatile float *>(gb_s + q));
                 }
-            }
-            asm volatile("bar.sync 1, 512;" ::: "memory");
-            if (ew < DN_N / 32) {   // warp ew refreshes the lowest threshold of query chunk ew (padding columns never qualify)
-                float t = (ew * 32 + lane < p.n_queries) ? thr_s[ew * 32 + lane] : INFINITY;
-#pragma unroll
-                for (int off = 16; off >= 1; off >>= 1) t = fminf(t, __shfl_xor_sync(FCB_FULL, t, off));
-                if (lane == 0) thr_min_s[ew] = t;
+                if (q == 0) *gb_seq = it + 1;
             }
             asm volatile("bar.sync 1, 512;" ::: "memory");
             t_b += clock64() - t0;
         }
+        if (tid == 128) *gb_seq = -1;                                  // the gossip warps may stop
         if (p.prof && blockIdx.x == 0 && tid == 128) { p.prof[5] = clock64() - t_begin; p.prof[6] = w_acc; p.prof[7] = t_a; p.prof[8] = t_b; p.prof[9] = it; }
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -811,7 +855,8 @@ struct FcbDense {
     int two_cta = 1;
     __nv_bfloat16 *q_bf16 = nullptr;        // [DN_N, dim]
     FcbCand *cta_top = nullptr, *pend = nullptr;
-    unsigned *gthr = nullptr;               // [DN_N] cross-CTA thresholds of the cta_group::2 kernel
+    unsigned *gtop = nullptr;               // [DN_N][gt_stride] per-CTA best scores of the cta_group::2 kernel
+    int gt_stride = 0;
     int32_t *redo = nullptr;                // [DN_N] flags, then [DN_N] compact list, then the count
     int *error_flag = nullptr;
     int grid = 0;
@@ -820,7 +865,7 @@ struct FcbDense {
 void fcb_dense_free(fcb_engine *e) {
     FcbDense *d = reinterpret_cast<FcbDense *>(e->dense);
     if (!d) return;
-    cudaFree(d->q_bf16); cudaFree(d->cta_top); cudaFree(d->pend); cudaFree(d->redo); cudaFree(d->error_flag); cudaFree(d->gthr);
+    cudaFree(d->q_bf16); cudaFree(d->cta_top); cudaFree(d->pend); cudaFree(d->redo); cudaFree(d->error_flag); cudaFree(d->gtop);
     delete d;
     e->dense = nullptr;
 }
@@ -836,12 +881,13 @@ int32_t fcb_dense_alloc(fcb_engine *e) {
     FcbDense *d = new FcbDense();
     e->dense = d;
     d->grid = e->num_sms;
+    d->gt_stride = ((d->grid + 31) / 32) * 32;
     const size_t lists = (size_t)d->grid * DN_N;
     if (cudaMalloc(&d->q_bf16, (size_t)DN_N * s.dim * 2) != cudaSuccess ||
         cudaMalloc(&d->cta_top, lists * FCB_FUSED_CAND * sizeof(FcbCand)) != cudaSuccess ||
         cudaMalloc(&d->pend, lists * DN_PEND_CAP * sizeof(FcbCand)) != cudaSuccess ||
         cudaMalloc(&d->redo, (size_t)(2 * DN_N + 1) * sizeof(int32_t)) != cudaSuccess ||
-        cudaMalloc(&d->gthr, (size_t)DN_N * sizeof(unsigned)) != cudaSuccess ||
+        cudaMalloc(&d->gtop, (size_t)DN_N * d->gt_stride * sizeof(unsigned)) != cudaSuccess ||
         cudaMalloc(&d->error_flag, sizeof(int)) != cudaSuccess) {
         cudaGetLastError();
         fcb_dense_free(e);
@@ -900,8 +946,8 @@ int32_t fcb_search_dense(fcb_engine *e, const double *d_queries, const fcb_filte
     p.n_queries = batch; p.n_eff = ((batch + 31) / 32) * 32;
     p.cta_top = d->cta_top; p.pend = d->pend; p.error_flag = d->error_flag;
     p.debug_out = g_debug_out; p.debug_rows = g_debug_rows; p.prof = g_dense_prof;
-    p.gthr = d->gthr;
-    FCB_CUDA(e, cudaMemsetAsync(d->gthr, 0, (size_t)DN_N * sizeof(unsigned), st));   // 0 orders below every float
+    p.gtop = d->gtop; p.gt_stride = d->gt_stride;
+    FCB_CUDA(e, cudaMemsetAsync(d->gtop, 0, (size_t)DN_N * d->gt_stride * sizeof(unsigned), st));   // 0 orders below every float
     p.n_stages = p.n_eff <= 96 ? 4 : 3;                              // stages + 4 KB + lists (n_eff x 256 B) must fit 227 KB
     const size_t smem = (size_t)DN_STAGES * DN_STAGE_BYTES + 4096;
     if (d->two_cta) {
