@@ -62,6 +62,7 @@ struct fcb_engine {
     double *d_sel_scores = nullptr;        // [kprime_max] canonical float64 scores
     uint64_t *d_sel_ids = nullptr;         // [kprime_max]
     int kprime_max = 0;
+    bool sel_clean = false;                // the selection state is all zero (left so by the one-launch direct path)
 
     int dates_sorted = 0;                  // load-time check: dates non-decreasing within every user
     uint32_t *row_of_rank = nullptr;       // inverse of shard.id_rank, built by fcb_aggregate_hits on first use

@@ -11,7 +11,11 @@
 //                            Keys are L2-resident for segments up to ~15M rows.
 //   3. compact_kernel        rows with key >= threshold -> candidate list (exactly K' rows)
 //   4. rescore_kernel        canonical float64 score per candidate (one warp each)
-//   5. rank_scatter_kernel   rank by (score desc, id asc) and write the first k
+//   5. sort_chunks_kernel    the candidates sorted by (score desc, id asc) in chunks of 1024 (bitonic, shared memory);
+//                            up to 1024 candidates this writes the results and ends the query
+//   6. rank_merge_kernel     more than one chunk: rank = position in the own chunk + binary searches in the others
+// Segments that fit the candidate buffer whole (an ordinary tenant asked for "everything", the tool's
+// default call) skip steps 1-4: direct_rescore_kernel scores every passing row in float64 right away.
 #include "fcb_internal.cuh"
 
 #define SEL_THREADS 256
@@ -31,6 +35,7 @@ void fcb_general_free(fcb_engine *e) {
 
 int32_t fcb_general_alloc(fcb_engine *e) {
     e->kprime_max = kprime_for(e->max_k);
+    e->sel_clean = false;
     const size_t n = (size_t)e->shard.n_rows, kp = (size_t)e->kprime_max;
     if (cudaMalloc(&e->d_keys, n * sizeof(uint64_t)) != cudaSuccess ||
         cudaMalloc(&e->d_sel, sizeof(FcbSelectState)) != cudaSuccess ||
@@ -250,34 +255,141 @@ __global__ void __launch_bounds__(SEL_THREADS) rescore_kernel(const T *__restric
     if (lane == 0) { sel_scores[w] = sc; sel_ids[w] = ids ? ids[row] : (uint64_t)(row_base + row); }
 }
 
-__global__ void __launch_bounds__(128) rank_scatter_kernel(const FcbSelectState *st, unsigned kprime, int k,
-                                                           const double *__restrict__ sel_scores,
-                                                           const uint64_t *__restrict__ sel_ids, uint64_t *__restrict__ out_ids,
-                                                           double *__restrict__ out_scores, int32_t *__restrict__ out_count) {
-    __shared__ double t_s[512];
-    __shared__ uint64_t t_i[512];
-    const unsigned n_sel = st->n_pass < kprime ? st->n_pass : kprime;
+#define SORT_CHUNK 1024
+
+// bitonic sort of `width` (a power of two) entries in shared memory by (score desc, id asc); all threads of the CTA call it
+__device__ __forceinline__ void sel_sort_chunk(double *s_s, uint64_t *s_i, unsigned width) {
+    for (unsigned size = 2; size <= width; size <<= 1) {
+        for (unsigned stride = size >> 1; stride > 0; stride >>= 1) {
+            for (unsigned t = threadIdx.x; t < width / 2; t += blockDim.x) {
+                const unsigned pos = 2 * t - (t & (stride - 1)), mate = pos + stride;
+                const bool first_better = (pos & size) == 0;      // this block is ordered best-first, the next one worst-first
+                const double sa = s_s[pos], sb = s_s[mate];
+                const uint64_t ia = s_i[pos], ib = s_i[mate];
+                if (first_better ? fcb_better64(sb, ib, sa, ia) : fcb_better64(sa, ia, sb, ib)) {
+                    s_s[pos] = sb; s_i[pos] = ib; s_s[mate] = sa; s_i[mate] = ia;
+                }
+            }
+            __syncthreads();
+        }
+    }
+}
+
+// load up to 1024 candidates starting at `base`, sort them; returns how many are real (padding sorts last)
+__device__ __forceinline__ unsigned sel_load_sorted(double *s_s, uint64_t *s_i, const double *sel_scores, const uint64_t *sel_ids,
+                                                    unsigned base, unsigned n_sel) {
+    const unsigned here = n_sel > base ? (n_sel - base < SORT_CHUNK ? n_sel - base : SORT_CHUNK) : 0;
+    unsigned width = 2;                                            // power of two covering the chunk's entries
+    while (width < here) width <<= 1;
+    for (unsigned t = threadIdx.x; t < width; t += blockDim.x) {
+        const bool in = t < here;
+        s_s[t] = in ? __ldcg(sel_scores + base + t) : -INFINITY;      // written by other CTAs of this launch (direct path)
+        s_i[t] = in ? __ldcg(sel_ids + base + t) : UINT64_MAX;
+    }
+    __syncthreads();
+    sel_sort_chunk(s_s, s_i, width);
+    return here;
+}
+
+// the first k of a sorted chunk -> outputs, tail padded, count set (the query's only chunk)
+__device__ __forceinline__ void sel_write_single(const double *s_s, const uint64_t *s_i, unsigned n_sel, int k, uint64_t *out_ids,
+                                                 double *out_scores, int32_t *out_count) {
     const unsigned count = n_sel < (unsigned)k ? n_sel : (unsigned)k;
-    const unsigned i = blockIdx.x * 128 + threadIdx.x;
+    if (threadIdx.x == 0) *out_count = (int32_t)count;
+    for (unsigned t = threadIdx.x; t < (unsigned)k; t += blockDim.x) {
+        out_ids[t] = t < count ? s_i[t] : UINT64_MAX;
+        out_scores[t] = t < count ? s_s[t] : -INFINITY;
+    }
+}
+
+// Sorts candidates [1024 * blockIdx.x, +1024) by (score desc, id asc) in shared memory. `single` (the host knows
+// that at most one chunk can exist): writes the first k straight to the outputs, pads the tail and sets the count.
+__global__ void __launch_bounds__(SORT_CHUNK / 2) sort_chunks_kernel(const FcbSelectState *st, unsigned cap, int k, int single,
+                                                                     double *__restrict__ sel_scores, uint64_t *__restrict__ sel_ids,
+                                                                     uint64_t *__restrict__ out_ids, double *__restrict__ out_scores,
+                                                                     int32_t *__restrict__ out_count) {
+    __shared__ double s_s[SORT_CHUNK];
+    __shared__ uint64_t s_i[SORT_CHUNK];
+    const unsigned n_sel = st->n_pass < cap ? st->n_pass : cap;
+    const unsigned base = blockIdx.x * SORT_CHUNK;
+    if (!single && base >= n_sel) return;
+    const unsigned here = sel_load_sorted(s_s, s_i, sel_scores, sel_ids, base, n_sel);
+    if (single) {
+        sel_write_single(s_s, s_i, n_sel, k, out_ids, out_scores, out_count);
+    } else {
+        for (unsigned t = threadIdx.x; t < here; t += blockDim.x) { sel_scores[base + t] = s_s[t]; sel_ids[base + t] = s_i[t]; }
+    }
+}
+
+// Several sorted chunks: an entry's rank is its position in its own chunk plus, for every other chunk, the number of
+// entries there that rank before it (binary search; ids are unique, so the order is strict). Writes the first k.
+__global__ void __launch_bounds__(256) rank_merge_kernel(const FcbSelectState *st, unsigned cap, int k,
+                                                         const double *__restrict__ sel_scores, const uint64_t *__restrict__ sel_ids,
+                                                         uint64_t *__restrict__ out_ids, double *__restrict__ out_scores,
+                                                         int32_t *__restrict__ out_count) {
+    const unsigned n_sel = st->n_pass < cap ? st->n_pass : cap;
+    const unsigned count = n_sel < (unsigned)k ? n_sel : (unsigned)k;
+    const unsigned i = blockIdx.x * 256 + threadIdx.x;
     if (i == 0) *out_count = (int32_t)count;
     if (i >= count && i < (unsigned)k) { out_ids[i] = UINT64_MAX; out_scores[i] = -INFINITY; }   // pad the tail
-    if (blockIdx.x * 128 >= n_sel) return;
-    const bool mine = i < n_sel;
-    const double ms = mine ? sel_scores[i] : 0.0;
-    const uint64_t mi = mine ? sel_ids[i] : 0;
-    unsigned rank = 0;
-    for (unsigned base = 0; base < n_sel; base += 512) {
-        __syncthreads();
-        for (unsigned t = threadIdx.x; t < 512; t += 128) {
-            const unsigned j = base + t;
-            t_s[t] = j < n_sel ? sel_scores[j] : -INFINITY;
-            t_i[t] = j < n_sel ? sel_ids[j] : UINT64_MAX;
+    if (i >= n_sel) return;
+    const double ms = sel_scores[i];
+    const uint64_t mi = sel_ids[i];
+    const unsigned own = i / SORT_CHUNK;
+    unsigned rank = i % SORT_CHUNK;
+    for (unsigned c = 0, lo0 = 0; lo0 < n_sel; ++c, lo0 += SORT_CHUNK) {
+        if (c == own) continue;
+        unsigned lo = lo0, hi = lo0 + SORT_CHUNK < n_sel ? lo0 + SORT_CHUNK : n_sel;
+        while (lo < hi) {                                          // first entry of the chunk that does NOT rank before mine
+            const unsigned mid = (lo + hi) >> 1;
+            if (fcb_better64(sel_scores[mid], sel_ids[mid], ms, mi)) lo = mid + 1; else hi = mid;
         }
-        __syncthreads();
-        const unsigned lim = n_sel - base < 512 ? n_sel - base : 512;
-        for (unsigned t = 0; t < lim; ++t) rank += fcb_better64(t_s[t], t_i[t], ms, mi);
+        rank += lo - lo0;
     }
-    if (mine && rank < (unsigned)k) { out_ids[rank] = mi; out_scores[rank] = ms; }
+    if (rank < (unsigned)k) { out_ids[rank] = mi; out_scores[rank] = ms; }
+}
+
+// A segment that fits the candidate buffer whole: predicate + canonical float64 score for every row, one warp each.
+// `fused` (at most 1024 rows): the CTA that finishes last also sorts the candidates, writes the results and leaves the
+// selection state zeroed — the whole query is this one launch.
+template <typename T>
+__global__ void __launch_bounds__(SEL_THREADS) direct_rescore_kernel(const T *__restrict__ vectors, const uint64_t *__restrict__ ids,
+                                                                     const int32_t *__restrict__ dates, const uint8_t *__restrict__ cats,
+                                                                     const fcb_filter f, int64_t row_base, int64_t lo, int64_t hi, int dim,
+                                                                     const double *__restrict__ q, FcbSelectState *st,
+                                                                     double *__restrict__ sel_scores, uint64_t *__restrict__ sel_ids,
+                                                                     int fused, int k, uint64_t *__restrict__ out_ids,
+                                                                     double *__restrict__ out_scores, int32_t *__restrict__ out_count) {
+    const int lane = threadIdx.x & 31;
+    const bool has_date = dates && (f.date_lo != FCB_DATE_MIN || f.date_hi != FCB_DATE_MAX);
+    const bool has_cat = cats && f.category_mask != FCB_ALL_CATEGORIES;
+    const int64_t warps = (int64_t)gridDim.x * (SEL_THREADS / 32);
+    for (int64_t row = lo + (int64_t)blockIdx.x * (SEL_THREADS / 32) + (threadIdx.x >> 5); row < hi; row += warps) {
+        bool pass = true;
+        if (has_date) { const int64_t d = dates[row]; pass = d >= f.date_lo && d <= f.date_hi; }
+        if (pass && has_cat) { const unsigned c = cats[row]; pass = c < 64 && ((f.category_mask >> c) & 1ull); }
+        if (!pass) continue;
+        const double sc = fcb_canon_score_warp<T>(vectors + row * dim, q, dim, lane);
+        if (lane == 0) {
+            const unsigned slot = atomicAdd(&st->n_pass, 1u);
+            sel_scores[slot] = sc;
+            sel_ids[slot] = ids ? ids[row] : (uint64_t)(row_base + row);
+        }
+    }
+    if (!fused) return;
+    __shared__ double s_s[SORT_CHUNK];
+    __shared__ uint64_t s_i[SORT_CHUNK];
+    __shared__ unsigned s_last;
+    __threadfence();                                               // this CTA's candidates before its ticket
+    __syncthreads();
+    if (threadIdx.x == 0) s_last = atomicAdd(&st->n_selected, 1u) == gridDim.x - 1;
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    const unsigned n_sel = *reinterpret_cast<volatile unsigned *>(&st->n_pass);
+    sel_load_sorted(s_s, s_i, sel_scores, sel_ids, 0, n_sel);      // plain loads are fine: written by other CTAs before their tickets
+    sel_write_single(s_s, s_i, n_sel, k, out_ids, out_scores, out_count);
+    if (threadIdx.x == 0) { st->n_pass = 0; st->n_selected = 0; }  // the state stays clean for the next query
 }
 
 template <typename T>
@@ -290,8 +402,24 @@ static int32_t general_impl(fcb_engine *e, const double *d_query, const fcb_filt
     if (hi > s.n_rows) hi = s.n_rows;
     const int64_t n = hi > lo ? hi - lo : 0;
 
-    FCB_CUDA(e, cudaMemsetAsync(e->d_sel, 0, sizeof(FcbSelectState), st));
-    if (n > 0) {
+    const bool direct = n > 0 && n <= (int64_t)e->kprime_max;         // the whole segment fits the candidate buffer
+    const bool fused = direct && n <= SORT_CHUNK;                      // one launch does it all and leaves the state clean
+    if (!(fused && e->sel_clean)) FCB_CUDA(e, cudaMemsetAsync(e->d_sel, 0, sizeof(FcbSelectState), st));
+    e->sel_clean = fused;
+    unsigned cap = kprime;                                             // how many candidates can exist
+    if (direct) {
+        // score every passing row in float64 right away
+        cap = (unsigned)n;
+        int64_t ctas = (n + SEL_THREADS / 32 - 1) / (SEL_THREADS / 32);
+        if (ctas > 8 * (int64_t)e->num_sms) ctas = 8 * (int64_t)e->num_sms;
+        direct_rescore_kernel<T><<<(unsigned)ctas, SEL_THREADS, 0, st>>>((const T *)s.vectors, s.ids, s.dates, s.categories, f,
+                                                                        s.row_base, lo, hi, s.dim, d_query, e->d_sel,
+                                                                        e->d_sel_scores, e->d_sel_ids, fused ? 1 : 0, k,
+                                                                        d_out_ids, d_out_scores, d_out_count);
+        FCB_CUDA(e, cudaGetLastError());
+        e->last_launches += 1;
+        if (fused) return FCB_OK;
+    } else if (n > 0) {
         KeyScanParams p{};
         p.vectors = s.vectors; p.inv_norm = e->inv_norm; p.id_rank = s.id_rank; p.dates = s.dates; p.cats = s.categories;
         p.query = d_query; p.filter = f; p.n_rows = s.n_rows; p.row_base = s.row_base; p.dim = s.dim;
@@ -319,11 +447,18 @@ static int32_t general_impl(fcb_engine *e, const double *d_query, const fcb_filt
         FCB_CUDA(e, cudaGetLastError());
         e->last_launches += 11;
     }
-    const unsigned span = kprime > (unsigned)k ? kprime : (unsigned)k;
-    rank_scatter_kernel<<<(span + 127) / 128, 128, 0, st>>>(e->d_sel, kprime, k, e->d_sel_scores, e->d_sel_ids, d_out_ids,
-                                                          d_out_scores, d_out_count);
-    FCB_CUDA(e, cudaGetLastError());
+    // order the candidates: one sorted chunk ends the query, several are merged by rank
+    const bool single = cap <= SORT_CHUNK;
+    sort_chunks_kernel<<<single ? 1 : (cap + SORT_CHUNK - 1) / SORT_CHUNK, SORT_CHUNK / 2, 0, st>>>(
+        e->d_sel, cap, k, single ? 1 : 0, e->d_sel_scores, e->d_sel_ids, d_out_ids, d_out_scores, d_out_count);
     e->last_launches += 1;
+    if (!single) {
+        const unsigned span = cap > (unsigned)k ? cap : (unsigned)k;
+        rank_merge_kernel<<<(span + 255) / 256, 256, 0, st>>>(e->d_sel, cap, k, e->d_sel_scores, e->d_sel_ids, d_out_ids,
+                                                            d_out_scores, d_out_count);
+        e->last_launches += 1;
+    }
+    FCB_CUDA(e, cudaGetLastError());
     return FCB_OK;
 }
 

@@ -1,4 +1,4 @@
-"""Run ONE secondary workload a few times (for ncu): python scripts/run_one.py cfg3|cfg5|cfg2b [steps]"""
+"""Run ONE secondary workload a few times (for ncu): python scripts/run_one.py cfg3|cfg5|cfg5s|cfg2b|k10000 [steps]"""
 import os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
@@ -42,6 +42,17 @@ elif which in ("cfg5", "cfg5s"):
                    seg_offsets=torch.from_numpy(off).to(DEV))
     for i in range(steps):
         eng.aggregate(0, users, (2022 - 1970) * 12, 24, 16)
+    torch.cuda.synchronize()
+elif which == "k10000":
+    rows, dim, k = 10_000_000, 1536, 10000
+    spec = synth.SynthSpec(n_rows=rows, dim=dim, seed=1, n_users=1)
+    eng = Engine(device=0, max_batch=1, max_k=k)
+    loader.collection_synthetic(spec, eng, with_cents=False)
+    q = torch.from_numpy(synth.query_vector(spec, 1)[None, :]).to(DEV)
+    oi = torch.empty((1, k), dtype=torch.int64, device=DEV); os_ = torch.empty((1, k), dtype=torch.float64, device=DEV)
+    oc = torch.empty(1, dtype=torch.int32, device=DEV)
+    for i in range(steps):
+        eng.search_device(q, [make_filter(0, rows, synth.DATE_BASE, None)], k, oi, os_, oc)
     torch.cuda.synchronize()
 elif which == "cfg2b":
     rows, dim = 10_000_000, 1536

@@ -41,7 +41,7 @@ def test_k_sweep_on_whale_segment(env):
     hc, eng, _ = env
     for k in (17, 64, 100, 1000, 10000):
         assert check(eng, hc, k, k, 0) == k
-    assert eng.last_search_launches == 12
+    assert eng.last_search_launches == 13               # key scan, 8 radix passes, compact, re-score, chunk sort, rank merge
 
 
 def test_k_larger_than_segment_and_filters(env):
@@ -53,6 +53,28 @@ def test_k_larger_than_segment_and_filters(env):
     check(eng, hc, 3, 2000, 0, date_lo=t0, category_mask=(1 << 4) | (1 << 5))
     check(eng, hc, 4, 50, 5, category_mask=1 << 0)
     assert check(eng, hc, 5, 100, 2, date_lo=2 ** 40) == 0  # nothing passes
+
+
+def test_segments_that_fit_the_candidate_buffer_take_the_direct_path(env):
+    """The tool's default call (limit 10000) against an ordinary tenant: every passing row is scored in float64
+    straight away (no key scan, no radix select), then sorted — ONE launch up to 1024 rows, 3 above."""
+    hc, eng, _ = env
+    sizes = np.diff(hc.offsets)
+    small = int(np.argmin(np.where(sizes > 0, sizes, 1 << 30)))
+    big = int(np.argmax(np.where(sizes <= 10000, sizes, -1)))
+    assert sizes[big] > 1024
+    t0 = int(np.percentile(hc.dates, 40))
+    for k in (10000, 1500, 100, 17):
+        assert check(eng, hc, 7, k, big) == min(k, sizes[big])
+        assert eng.last_search_launches == 3
+        check(eng, hc, 8, k, big, date_lo=t0, category_mask=0b1011011)
+    if sizes[small] <= 1024:
+        for rep in range(3):                                  # back to back: the state is left clean by the launch itself
+            assert check(eng, hc, 9 + rep, 10000, small) == sizes[small]
+            assert eng.last_search_launches == 1
+        check(eng, hc, 9, 20, small, date_lo=t0)
+        check(eng, hc, 7, 64, big)                              # and the other paths still start from a clean state
+        assert check(eng, hc, 9, 10000, small) == sizes[small]
 
 
 def test_batch_of_general_queries(env):
@@ -90,6 +112,17 @@ def test_ties_across_the_cut_with_permuted_ids(built):
         gi, gs, cnt = eng.search_host(q[None, :], [make_filter(0, 6000)], k)
         oi, os_ = canon.search(vec, q, k, ids=ids)
         assert cnt[0] == k and gi[0].tolist() == oi.tolist() and gs[0].tolist() == os_.tolist()
+    eng.close()
+    # the same corpus through the direct path (the segment fits the candidate buffer): ties inside and across sorted chunks
+    eng = Engine(device=0, max_batch=1, max_k=10000)
+    eng.load_shard(torch.from_numpy(vec).to(dev), ids=torch.from_numpy(ids.view(np.int64)).to(dev),
+                   id_rank=torch.from_numpy(rank.astype(np.int32)).to(dev))
+    for k in (45, 1000, 6000, 10000):
+        gi, gs, cnt = eng.search_host(q[None, :], [make_filter(0, 6000)], k)
+        oi, os_ = canon.search(vec, q, k, ids=ids)
+        n = min(k, 6000)
+        assert cnt[0] == n and gi[0, :n].tolist() == oi.tolist() and gs[0, :n].tolist() == os_.tolist()
+        assert eng.last_search_launches == 3
     eng.close()
 
 
