@@ -63,6 +63,9 @@ struct fcb_engine {
     uint64_t *d_sel_ids = nullptr;         // [kprime_max]
     int kprime_max = 0;
     bool sel_clean = false;                // the selection state is all zero (left so by the one-launch direct path)
+    unsigned *d_bsel = nullptr;            // [max_batch][2] (candidates, tickets) of the batched direct path, kept at zero between calls
+    double *d_bsel_scores = nullptr;       // [max_batch][1024]
+    uint64_t *d_bsel_ids = nullptr;        // [max_batch][1024]
 
     int dates_sorted = 0;                  // load-time check: dates non-decreasing within every user
     uint32_t *row_of_rank = nullptr;       // inverse of shard.id_rank, built by fcb_aggregate_hits on first use
@@ -82,6 +85,10 @@ struct FcbSelectState {
 
 int32_t fcb_general_alloc(fcb_engine *e);  // called by fcb_load_shard
 void fcb_general_free(fcb_engine *e);
+// every query's segment has at most 1024 rows: the whole batch in one launch (filters already clipped and on the device)
+int32_t fcb_search_general_small_batch(fcb_engine *e, const double *d_queries, const fcb_filter *d_filters, int32_t batch,
+                                       int32_t k, int64_t max_rows, uint64_t *d_out_ids, double *d_out_scores,
+                                       int32_t *d_out_counts, cudaStream_t st);
 int32_t fcb_search_general(fcb_engine *e, const double *d_query, const fcb_filter &f, int32_t k,
                            uint64_t *d_out_ids, double *d_out_scores, int32_t *d_out_count, cudaStream_t st);
 

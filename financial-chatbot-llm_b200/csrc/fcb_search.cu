@@ -451,6 +451,34 @@ static int32_t search_device(fcb_engine *e, const double *d_queries, const fcb_f
     const fcb_shard &s = e->shard;
     e->last_launches = 0;
     if (k > FCB_FUSED_MAX_K) {
+        // a batch of small segments (every one fits one sorted chunk): ONE launch for all of them
+        if (batch > 1 && e->d_bsel) {
+            int64_t max_rows = 0;
+            for (int b = 0; b < batch; ++b) {
+                int64_t lo = h_filters[b].row_begin - s.row_base, hi = h_filters[b].row_end - s.row_base;
+                if (lo < 0) lo = 0;
+                if (hi > s.n_rows) hi = s.n_rows;
+                if (hi - lo > max_rows) max_rows = hi - lo;
+            }
+            if (max_rows <= 1024) {
+                const int slot = e->filter_slot;
+                e->filter_slot = (slot + 1) % FCB_FILTER_SLOTS;
+                FCB_CUDA(e, cudaEventSynchronize(e->filter_ev[slot]));      // slot's previous copy has drained
+                fcb_filter *stage = e->h_filters + (size_t)slot * e->max_batch;
+                fcb_filter *d_f = e->d_filters + (size_t)slot * e->max_batch;
+                for (int b = 0; b < batch; ++b) {
+                    fcb_filter f = h_filters[b];
+                    const bool has_date = f.date_lo != FCB_DATE_MIN || f.date_hi != FCB_DATE_MAX;
+                    const bool has_cat = f.category_mask != FCB_ALL_CATEGORIES;
+                    if ((has_date && !s.dates) || (has_cat && !s.categories) || f.date_lo > f.date_hi) f.row_end = f.row_begin;
+                    stage[b] = f;
+                }
+                FCB_CUDA(e, cudaMemcpyAsync(d_f, stage, (size_t)batch * sizeof(fcb_filter), cudaMemcpyHostToDevice, st));
+                FCB_CUDA(e, cudaEventRecord(e->filter_ev[slot], st));
+                return fcb_search_general_small_batch(e, d_queries, d_f, batch, k, max_rows, d_out_ids, d_out_scores,
+                                                      d_out_counts, st);
+            }
+        }
         // general-k path: one query at a time, stream-ordered (fcb_select.cu)
         for (int b = 0; b < batch; ++b) {
             fcb_filter f = h_filters[b];

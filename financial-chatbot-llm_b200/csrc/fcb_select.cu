@@ -19,6 +19,7 @@
 #include "fcb_internal.cuh"
 
 #define SEL_THREADS 256
+#define SORT_CHUNK 1024                    // candidates sorted per CTA (bitonic, shared memory)
 
 static inline int kprime_for(int k) {
     int margin = k / 16;
@@ -29,6 +30,8 @@ static inline int kprime_for(int k) {
 void fcb_general_free(fcb_engine *e) {
     cudaFree(e->d_keys); cudaFree(e->d_sel); cudaFree(e->d_sel_rows);
     cudaFree(e->d_sel_scores); cudaFree(e->d_sel_ids);
+    cudaFree(e->d_bsel); cudaFree(e->d_bsel_scores); cudaFree(e->d_bsel_ids);
+    e->d_bsel = nullptr; e->d_bsel_scores = nullptr; e->d_bsel_ids = nullptr;
     e->d_keys = nullptr; e->d_sel = nullptr; e->d_sel_rows = nullptr;
     e->d_sel_scores = nullptr; e->d_sel_ids = nullptr; e->kprime_max = 0;
 }
@@ -46,6 +49,17 @@ int32_t fcb_general_alloc(fcb_engine *e) {
         fcb_general_free(e);
         return fcb_fail(e, FCB_ERR_NOMEM, "fcb_load_shard: cannot allocate general-k scratch (%zu bytes of keys)",
                         n * sizeof(uint64_t));
+    }
+    if (e->max_batch > 1) {                                            // batched direct path: 16 KB of candidates per query
+        const size_t b = (size_t)e->max_batch;
+        if (cudaMalloc(&e->d_bsel, b * 2 * sizeof(unsigned)) != cudaSuccess ||
+            cudaMalloc(&e->d_bsel_scores, b * SORT_CHUNK * sizeof(double)) != cudaSuccess ||
+            cudaMalloc(&e->d_bsel_ids, b * SORT_CHUNK * sizeof(uint64_t)) != cudaSuccess ||
+            cudaMemset(e->d_bsel, 0, b * 2 * sizeof(unsigned)) != cudaSuccess) {
+            cudaGetLastError();
+            fcb_general_free(e);
+            return fcb_fail(e, FCB_ERR_NOMEM, "fcb_load_shard: cannot allocate the batched general-k scratch");
+        }
     }
     return FCB_OK;
 }
@@ -255,8 +269,6 @@ __global__ void __launch_bounds__(SEL_THREADS) rescore_kernel(const T *__restric
     if (lane == 0) { sel_scores[w] = sc; sel_ids[w] = ids ? ids[row] : (uint64_t)(row_base + row); }
 }
 
-#define SORT_CHUNK 1024
-
 // bitonic sort of `width` (a power of two) entries in shared memory by (score desc, id asc); all threads of the CTA call it
 __device__ __forceinline__ void sel_sort_chunk(double *s_s, uint64_t *s_i, unsigned width) {
     for (unsigned size = 2; size <= width; size <<= 1) {
@@ -390,6 +402,77 @@ __global__ void __launch_bounds__(SEL_THREADS) direct_rescore_kernel(const T *__
     sel_load_sorted(s_s, s_i, sel_scores, sel_ids, 0, n_sel);      // plain loads are fine: written by other CTAs before their tickets
     sel_write_single(s_s, s_i, n_sel, k, out_ids, out_scores, out_count);
     if (threadIdx.x == 0) { st->n_pass = 0; st->n_selected = 0; }  // the state stays clean for the next query
+}
+
+// The same for a whole batch of small segments: blockIdx.y = query, every query has its own counters and candidate
+// buffer; the last CTA of each query sorts and writes that query's results and re-zeroes its counters.
+template <typename T>
+__global__ void __launch_bounds__(SEL_THREADS) direct_batch_kernel(const T *__restrict__ vectors, const uint64_t *__restrict__ ids,
+                                                                   const int32_t *__restrict__ dates, const uint8_t *__restrict__ cats,
+                                                                   const fcb_filter *__restrict__ filters, int64_t row_base, int64_t n_rows,
+                                                                   int dim, const double *__restrict__ queries, unsigned *__restrict__ bsel,
+                                                                   double *__restrict__ bsel_scores, uint64_t *__restrict__ bsel_ids, int k,
+                                                                   uint64_t *__restrict__ out_ids, double *__restrict__ out_scores,
+                                                                   int32_t *__restrict__ out_counts) {
+    __shared__ double s_s[SORT_CHUNK];
+    __shared__ uint64_t s_i[SORT_CHUNK];
+    __shared__ unsigned s_last;
+    const int b = blockIdx.y, lane = threadIdx.x & 31;
+    const fcb_filter f = filters[b];
+    int64_t lo = f.row_begin - row_base, hi = f.row_end - row_base;
+    if (lo < 0) lo = 0;
+    if (hi > n_rows) hi = n_rows;
+    const bool has_date = dates && (f.date_lo != FCB_DATE_MIN || f.date_hi != FCB_DATE_MAX);
+    const bool has_cat = cats && f.category_mask != FCB_ALL_CATEGORIES;
+    unsigned *my = bsel + 2 * b;
+    double *my_scores = bsel_scores + (size_t)b * SORT_CHUNK;
+    uint64_t *my_ids = bsel_ids + (size_t)b * SORT_CHUNK;
+    const double *q = queries + (size_t)b * dim;
+    const int64_t warps = (int64_t)gridDim.x * (SEL_THREADS / 32);
+    for (int64_t row = lo + (int64_t)blockIdx.x * (SEL_THREADS / 32) + (threadIdx.x >> 5); row < hi; row += warps) {
+        bool pass = true;
+        if (has_date) { const int64_t d = dates[row]; pass = d >= f.date_lo && d <= f.date_hi; }
+        if (pass && has_cat) { const unsigned c = cats[row]; pass = c < 64 && ((f.category_mask >> c) & 1ull); }
+        if (!pass) continue;
+        const double sc = fcb_canon_score_warp<T>(vectors + row * dim, q, dim, lane);
+        if (lane == 0) {
+            const unsigned slot = atomicAdd(&my[0], 1u);
+            my_scores[slot] = sc;
+            my_ids[slot] = ids ? ids[row] : (uint64_t)(row_base + row);
+        }
+    }
+    __threadfence();                                               // this CTA's candidates before its ticket
+    __syncthreads();
+    if (threadIdx.x == 0) s_last = atomicAdd(&my[1], 1u) == gridDim.x - 1;
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    const unsigned n_sel = *reinterpret_cast<volatile unsigned *>(&my[0]);
+    sel_load_sorted(s_s, s_i, my_scores, my_ids, 0, n_sel);
+    sel_write_single(s_s, s_i, n_sel, k, out_ids + (size_t)b * k, out_scores + (size_t)b * k, out_counts + b);
+    if (threadIdx.x == 0) { my[0] = 0; my[1] = 0; }
+}
+
+int32_t fcb_search_general_small_batch(fcb_engine *e, const double *d_queries, const fcb_filter *d_filters, int32_t batch,
+                                       int32_t k, int64_t max_rows, uint64_t *d_out_ids, double *d_out_scores,
+                                       int32_t *d_out_counts, cudaStream_t st) {
+    const fcb_shard &s = e->shard;
+    if (!e->d_bsel) return fcb_fail(e, FCB_ERR_STATE, "fcb_search: batched general-k scratch missing");
+    int64_t per_query = (max_rows + SEL_THREADS / 32 - 1) / (SEL_THREADS / 32);
+    if (per_query < 1) per_query = 1;
+    const dim3 grid((unsigned)per_query, (unsigned)batch);
+    if (s.dtype == FCB_DTYPE_F32)
+        direct_batch_kernel<float><<<grid, SEL_THREADS, 0, st>>>((const float *)s.vectors, s.ids, s.dates, s.categories, d_filters,
+                                                                 s.row_base, s.n_rows, s.dim, d_queries, e->d_bsel, e->d_bsel_scores,
+                                                                 e->d_bsel_ids, k, d_out_ids, d_out_scores, d_out_counts);
+    else
+        direct_batch_kernel<__nv_bfloat16><<<grid, SEL_THREADS, 0, st>>>((const __nv_bfloat16 *)s.vectors, s.ids, s.dates, s.categories,
+                                                                         d_filters, s.row_base, s.n_rows, s.dim, d_queries, e->d_bsel,
+                                                                         e->d_bsel_scores, e->d_bsel_ids, k, d_out_ids, d_out_scores,
+                                                                         d_out_counts);
+    FCB_CUDA(e, cudaGetLastError());
+    e->last_launches += 1;
+    return FCB_OK;
 }
 
 template <typename T>

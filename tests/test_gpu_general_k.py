@@ -139,3 +139,29 @@ def test_bf16_general_k(built):
     oi, os_ = canon.search(hc.bf16_bits, q, 2048, row_begin=0, row_end=int(hc.offsets[1]))
     assert ids[0, :cnt[0]].tolist() == oi.tolist() and sc[0, :cnt[0]].tolist() == os_.tolist()
     eng.close()
+
+
+def test_batch_of_small_tenants_is_one_launch(env):
+    """A micro-batch of default-limit calls against ordinary tenants (<= 1024 rows each): one launch scores, sorts and
+    writes every query (blockIdx.y = query); repeated calls prove that the per-query counters are left clean."""
+    from financial_chatbot_llm_b200 import synth
+    from financial_chatbot_llm_b200.engine import make_filter
+    from oracle import canon
+    hc, eng, _ = env
+    users = [5, 8, 6, 7]
+    assert all(hc.offsets[u + 1] - hc.offsets[u] <= 1024 for u in users)
+    t0 = int(np.percentile(hc.dates, 55))
+    for rep, k in enumerate((10000, 50, 10000)):
+        qs = np.stack([synth.query_vector(hc.spec, 70 + rep * 4 + i) for i in range(4)])
+        kw = [dict(), dict(date_lo=t0), dict(category_mask=0b110101), dict(date_lo=2 ** 40)]     # the last one: nothing passes
+        fl = [make_filter(int(hc.offsets[u]), int(hc.offsets[u + 1]), w.get("date_lo"), None, w.get("category_mask"))
+              for u, w in zip(users, kw)]
+        ids, sc, cnt = eng.search_host(qs, fl, k)
+        assert eng.last_search_launches == 1
+        for i, (u, w) in enumerate(zip(users, kw)):
+            oi, os_ = canon.search(hc.vectors, qs[i], k, row_begin=int(hc.offsets[u]), row_end=int(hc.offsets[u + 1]),
+                                   ids=hc.ids, dates=hc.dates, categories=hc.categories, **w)
+            n = int(cnt[i])
+            assert n == len(oi) and ids[i, :n].tolist() == oi.tolist() and sc[i, :n].tolist() == os_.tolist()
+            assert (ids[i, n:] == np.iinfo(np.uint64).max).all() and np.isneginf(sc[i, n:]).all()
+    assert cnt[3] == 0
