@@ -193,9 +193,31 @@ __global__ void __launch_bounds__(AGG_THREADS, 4) aggregate_kernel(const __grid_
 // selects this kernel when the load-time check found the dates non-decreasing within every user.
 #define AGS_WARP_ROWS 4096                 // consecutive rows one warp takes per task
 
-#define AGS_SMALL_PIECE 1024               // shorter pieces (tiny users): per-row 64-bit global reductions
+#ifndef AGS_AHEAD
+#define AGS_AHEAD 1                        // steps of columns each warp keeps in flight (ring of AGS_AHEAD + 1 slots: power of two)
+#endif
+#ifndef AGS_CTAS
+#define AGS_CTAS 4
+#endif
+#define AGS_SLOT_BYTES 1152                // one step of one warp: 32 x (16 B cents + 16 B dates + 4 B categories)
 
-__global__ void __launch_bounds__(AGG_THREADS, 4) aggregate_sorted_kernel(const __grid_constant__ AggParams p) {
+__device__ __forceinline__ void ags_cp16(void *dst, const void *src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void ags_cp4(void *dst, const void *src) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(src) : "memory");
+}
+#ifndef AGS_ROUND
+#define AGS_ROUND 8                        // rows per lane and round of the small-user path
+#endif
+#ifndef AGS_TABLE_USER
+#define AGS_TABLE_USER 8192                // users shorter than this: per-warp [category, month] table instead of runs
+#endif
+#ifndef AGS_SMALL_PIECE
+#define AGS_SMALL_PIECE 1024               // shorter pieces (tiny users): per-row 64-bit global reductions
+#endif
+
+__global__ void __launch_bounds__(AGG_THREADS, AGS_CTAS) aggregate_sorted_kernel(const __grid_constant__ AggParams p) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int C = p.n_categories * p.n_months;
     uint16_t *month_tab = reinterpret_cast<uint16_t *>(smem_raw);                                   // [n_days] day -> month
@@ -204,6 +226,8 @@ __global__ void __launch_bounds__(AGG_THREADS, 4) aggregate_sorted_kernel(const 
                                                         (((size_t)(p.n_months + 1) * 4 + 15) & ~(size_t)15));
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     long long *bins = bins_all + (size_t)warp * p.n_categories * 32;                                // [n_categories][32]
+    const bool table_ok = C * 9 <= p.n_categories * 32 * 8;        // the table (lo, hi, presence) fits the warp's bin matrix
+    unsigned char *ring = reinterpret_cast<unsigned char *>(bins_all + (size_t)(AGG_THREADS / 32) * p.n_categories * 32);   // per-warp cp.async rings
     for (int i = tid; i < p.n_days; i += AGG_THREADS) month_tab[i] = (uint16_t)(month_of_day(p.day0 + i) - p.month_lo);
     for (int i = lane; i < p.n_categories * 32; i += 32) bins[i] = 0;
     __syncthreads();
@@ -297,8 +321,64 @@ __global__ void __launch_bounds__(AGG_THREADS, 4) aggregate_sorted_kernel(const 
             while (uend <= pa) { ++u; uend = p.seg_offsets[u + 1]; }
             const int64_t pb = uend < b ? uend : b;
             const int64_t la = pa - p.row_base, lb = pb - p.row_base;
+            if (table_ok && uend - p.seg_offsets[u] < AGS_TABLE_USER) {
+                // small user (a month is only a few dozen rows, runs are not worth setting up): the warp's bin matrix,
+                // empty between runs, serves as a private [category, month] table — 32-bit shared atomics (one per row for
+                // |v| < 2^18, a lo/hi split otherwise; a piece has at most 4096 rows, so no cell can overflow), then the
+                // present cells go out once: plain stores when the piece is the whole user, 64-bit reductions otherwise
+                if (cur_month >= 0) flush();
+                cur_user = -1; set_month(-1);
+                __syncwarp();
+                int32_t *t_lo = reinterpret_cast<int32_t *>(bins), *t_hi = t_lo + C;
+                uint8_t *t_p = reinterpret_cast<uint8_t *>(t_hi + C);
+                // AGS_ROUND x 32 rows per round: all 3 x AGS_ROUND column loads of a lane are in flight before the first is used (a warp that
+                // loads one row per lane at a time streams ~1 TB/s across the GPU, latency-bound)
+                for (int64_t r0 = la + lane; r0 < lb; r0 += 32 * AGS_ROUND) {
+                    int32_t vv[AGS_ROUND], dd[AGS_ROUND];
+                    unsigned cc[AGS_ROUND];
+#pragma unroll
+                    for (int j = 0; j < AGS_ROUND; ++j) {
+                        const int64_t r = r0 + 32 * j;
+                        const bool in = r < lb;
+                        vv[j] = in ? p.cents[r] : 0; dd[j] = in ? p.dates[r] : 0; cc[j] = in ? (unsigned)p.cats[r] : 0x100u;
+                    }
+#pragma unroll
+                    for (int j = 0; j < AGS_ROUND; ++j) {
+                        if (cc[j] == 0x100u) continue;                       // past the piece
+                        const uint64_t off_s = (uint64_t)((int64_t)dd[j] - t_window);
+                        const unsigned mo = off_s < window_len ? month_tab[(uint32_t)off_s / 86400u] : 0xffffu;
+                        if (cc[j] >= (unsigned)p.n_categories || mo >= (unsigned)p.n_months) { ++dropped; continue; }
+                        const int cell = cc[j] * p.n_months + mo;
+                        const int32_t v = vv[j];
+                        if (v > -(1 << 18) && v < (1 << 18)) {
+                            atomicAdd(&t_lo[cell], v);
+                        } else {
+                            const int32_t lo16 = (int32_t)(int16_t)(v & 0xffff);
+                            atomicAdd(&t_lo[cell], lo16);
+                            atomicAdd(&t_hi[cell], (int32_t)(((int64_t)v - lo16) >> 16));
+                        }
+                        if (!t_p[cell]) t_p[cell] = 1;
+                    }
+                }
+                __syncwarp();
+                const bool whole = pa == p.seg_offsets[u] && pb == uend;    // nobody else adds to this user's cells
+                int64_t *out_s = p.sums + (u - p.seg_begin) * (int64_t)C;
+                uint8_t *out_p = p.present + (u - p.seg_begin) * (int64_t)C;
+                for (int c = lane; c < C; c += 32) {
+                    if (t_p[c]) {
+                        const long long total = (long long)t_hi[c] * 65536 + t_lo[c];
+                        if (whole) out_s[c] = total;
+                        else atomicAdd(reinterpret_cast<unsigned long long *>(out_s + c), (unsigned long long)total);
+                        out_p[c] = 1;
+                        t_lo[c] = 0; t_hi[c] = 0; t_p[c] = 0;
+                    }
+                }
+                __syncwarp();
+                pa = pb;
+                continue;
+            }
             if (pb - pa < AGS_SMALL_PIECE) {
-                // tiny user: months change every few rows, a run is not worth setting up
+                // tiny piece of a large user (a task boundary): months change every few rows, a run is not worth setting up
                 int64_t *out_s = p.sums + (u - p.seg_begin) * (int64_t)C;
                 uint8_t *out_p = p.present + (u - p.seg_begin) * (int64_t)C;
                 for (int64_t r = la + lane; r < lb; r += 32) {
@@ -376,28 +456,54 @@ __global__ void __launch_bounds__(AGG_THREADS, 4) aggregate_sorted_kernel(const 
             // full steps: all 128 rows inside the piece; plain pointer bumps, next step's columns already in flight
             const int64_t full_end = lb - 127;                      // base < full_end  <=>  base + 128 <= lb
             if (base < full_end) {
-                const int4 *pv = cents4 + (base >> 2) + lane, *pd = dates4 + (base >> 2) + lane;
-                const uchar4 *pc = cats4 + (base >> 2) + lane;
-                Quad nxt;
-                nxt.v = __ldg(pv); nxt.d = __ldg(pd); nxt.c = __ldg(pc);
-                for (; base < full_end; base += 128) {
-                    const Quad q = nxt;
-                    if (base + 128 < full_end) { pv += 32; pd += 32; pc += 32; nxt.v = __ldg(pv); nxt.d = __ldg(pd); nxt.c = __ldg(pc); }
-                    // inlined fast path (the compiler keeps it branch-light); anything else goes through step()
+                // 32-bit step counter and 32-bit offsets from the task's first quad (one IMAD.WIDE per load instead of
+                // predicated 64-bit pointer bumps); the next step's columns are always in flight (the last step re-reads
+                // itself, so the prefetch needs no predicate); categories stay ONE raw 32-bit register until they are
+                // used, so nothing waits for the load inside the step that issued it
+                const int n_full = (int)((full_end - base + 127) >> 7);
+                const int4 *tv = cents4 + (base >> 2) + lane, *td = dates4 + (base >> 2) + lane;
+                const uint32_t *tc = reinterpret_cast<const uint32_t *>(p.cats) + (base >> 2) + lane;
+                char *bl = reinterpret_cast<char *>(bins + lane);   // this lane's column; a category's bin is 256 bytes further per code
+                // Columns travel global -> shared with cp.async, AGS_AHEAD steps ahead, into this warp's ring of
+                // AGS_AHEAD + 1 slots (a lane only ever reads what it copied itself, so no warp barrier is involved): data in
+                // flight costs shared memory instead of registers.
+                unsigned char *my_ring = ring + (size_t)warp * (AGS_AHEAD + 1) * AGS_SLOT_BYTES;
+                auto issue = [&](int j) {
+                    const int nx = min(j, n_full - 1) * 32;          // past the end: re-read the last step (harmless, no predicate)
+                    unsigned char *slot = my_ring + (size_t)(j & AGS_AHEAD) * AGS_SLOT_BYTES;
+                    ags_cp16(slot + lane * 16, tv + nx);
+                    ags_cp16(slot + 512 + lane * 16, td + nx);
+                    ags_cp4(slot + 1024 + lane * 4, tc + nx);
+                    asm volatile("cp.async.commit_group;" ::: "memory");
+                };
+#pragma unroll
+                for (int j = 0; j < AGS_AHEAD; ++j) issue(j);
+                for (int it = 0; it < n_full; ++it) {
+                    asm volatile("cp.async.wait_group %0;" ::"n"(AGS_AHEAD - 1) : "memory");
+                    const unsigned char *slot = my_ring + (size_t)(it & AGS_AHEAD) * AGS_SLOT_BYTES;
+                    const int4 v = *reinterpret_cast<const int4 *>(slot + lane * 16);
+                    const int4 d = *reinterpret_cast<const int4 *>(slot + 512 + lane * 16);
+                    const uint32_t c = *reinterpret_cast<const uint32_t *>(slot + 1024 + lane * 4);
+                    issue(it + AGS_AHEAD);                            // into the slot read one step ago
+                    const unsigned c0 = c & 0xffu, c1 = (c >> 8) & 0xffu, c2 = (c >> 16) & 0xffu, c3 = c >> 24;
                     const bool same =
-                        (uint32_t)q.d.x - cur_base < cur_len && (uint32_t)q.d.y - cur_base < cur_len &&
-                        (uint32_t)q.d.z - cur_base < cur_len && (uint32_t)q.d.w - cur_base < cur_len &&
-                        max(max((unsigned)q.c.x, (unsigned)q.c.y), max((unsigned)q.c.z, (unsigned)q.c.w)) < (unsigned)p.n_categories;
+                        (uint32_t)d.x - cur_base < cur_len && (uint32_t)d.y - cur_base < cur_len &&
+                        (uint32_t)d.z - cur_base < cur_len && (uint32_t)d.w - cur_base < cur_len &&
+                        max(max(c0, c1), max(c2, c3)) < (unsigned)p.n_categories;
                     if (__all_sync(FCB_FULL, same)) {
-                        bins[q.c.x * 32 + lane] += (long long)q.v.x;
-                        bins[q.c.y * 32 + lane] += (long long)q.v.y;
-                        bins[q.c.z * 32 + lane] += (long long)q.v.z;
-                        bins[q.c.w * 32 + lane] += (long long)q.v.w;
-                        seen |= (1u << q.c.x) | (1u << q.c.y) | (1u << q.c.z) | (1u << q.c.w);
+                        *reinterpret_cast<long long *>(bl + (c0 << 8)) += (long long)v.x;
+                        *reinterpret_cast<long long *>(bl + (c & 0xff00u)) += (long long)v.y;
+                        *reinterpret_cast<long long *>(bl + ((c >> 8) & 0xff00u)) += (long long)v.z;
+                        *reinterpret_cast<long long *>(bl + (c3 << 8)) += (long long)v.w;
+                        seen |= (1u << c0) | (1u << c1) | (1u << c2) | (1u << c3);
                     } else {
+                        Quad q;
+                        q.v = v; q.d = d; q.c = make_uchar4((unsigned char)c0, (unsigned char)c1, (unsigned char)c2, (unsigned char)c3);
                         step(q, 0xfu);
                     }
                 }
+                asm volatile("cp.async.wait_group 0;" ::: "memory");  // the re-reads past the end must land before the ring is reused
+                base += (int64_t)n_full * 128;
             }
             if (base < lb) ragged(base);                            // tail
             pa = pb;
@@ -481,10 +587,11 @@ extern "C" int32_t fcb_aggregate(fcb_engine *e, int64_t seg_begin, int64_t seg_e
     const bool use_sorted = sorted_ok && (force ? force[0] == 's' : e->dates_sorted != 0);
     if (use_sorted) {
         const size_t smem_s = (((size_t)p.n_days * 2 + 15) & ~(size_t)15) + (((size_t)(n_months + 1) * 4 + 15) & ~(size_t)15) +
-                              (size_t)(AGG_THREADS / 32) * n_categories * 32 * 8;
+                              (size_t)(AGG_THREADS / 32) * n_categories * 32 * 8 +
+                              (size_t)(AGG_THREADS / 32) * (AGS_AHEAD + 1) * AGS_SLOT_BYTES;
         if (smem_s > 48 * 1024)
             FCB_CUDA(e, cudaFuncSetAttribute(aggregate_sorted_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_s));
-        aggregate_sorted_kernel<<<e->num_sms * 4, AGG_THREADS, smem_s, st>>>(p);
+        aggregate_sorted_kernel<<<e->num_sms * AGS_CTAS, AGG_THREADS, smem_s, st>>>(p);
     } else {
         aggregate_kernel<<<e->num_sms * 4, AGG_THREADS, smem, st>>>(p);
     }
