@@ -100,6 +100,63 @@ __device__ __forceinline__ void agg_row(const AggParams &p, int32_t v, unsigned 
     if (!c_present[cell]) c_present[cell] = 1;             // plain byte store: every writer stores the same value
 }
 
+#ifndef AGS_ROUND
+#define AGS_ROUND 8                        // rows per lane and round of the small-user path
+#endif
+#ifndef AGS_TABLE_USER
+#define AGS_TABLE_USER 8192                // users shorter than this: per-warp [category, month] table
+#endif
+
+// One small user's piece [la, lb) (local rows) on ONE warp: a private [category, month] table in shared memory (t_lo, t_hi,
+// t_p: all zero on entry and on exit) fed with 32-bit shared atomics — one per row for |v| < 2^18, a lo/hi split otherwise; a
+// piece has at most 4096 rows, so no cell can overflow. AGS_ROUND x 32 rows per round, all column loads of a lane in flight
+// before the first is used (one row per lane at a time streams ~1 TB/s across the GPU, latency-bound). The present cells go
+// out once: plain stores when the piece is the whole user (`whole`), 64-bit reductions otherwise.
+__device__ __forceinline__ void agg_warp_table(const AggParams &p, int64_t la, int64_t lb, bool whole, int64_t user, int32_t *t_lo,
+                                               int32_t *t_hi, uint8_t *t_p, const uint16_t *month_tab, int lane, unsigned &dropped) {
+    const int C = p.n_categories * p.n_months;
+    for (int64_t r0 = la + lane; r0 < lb; r0 += 32 * AGS_ROUND) {
+        int32_t vv[AGS_ROUND], dd[AGS_ROUND];
+        unsigned cc[AGS_ROUND];
+#pragma unroll
+        for (int j = 0; j < AGS_ROUND; ++j) {
+            const int64_t r = r0 + 32 * j;
+            const bool in = r < lb;
+            vv[j] = in ? p.cents[r] : 0; dd[j] = in ? p.dates[r] : 0; cc[j] = in ? (unsigned)p.cats[r] : 0x100u;
+        }
+#pragma unroll
+        for (int j = 0; j < AGS_ROUND; ++j) {
+            if (cc[j] == 0x100u) continue;                       // past the piece
+            const int32_t di = floor_day(dd[j]) - p.day0;
+            const unsigned mo = (unsigned)di < (unsigned)p.n_days ? month_tab[di] : 0xffffu;
+            if (cc[j] >= (unsigned)p.n_categories || mo >= (unsigned)p.n_months) { ++dropped; continue; }
+            const int cell = cc[j] * p.n_months + mo;
+            const int32_t v = vv[j];
+            if (v > -(1 << 18) && v < (1 << 18)) {
+                atomicAdd(&t_lo[cell], v);
+            } else {
+                const int32_t lo16 = (int32_t)(int16_t)(v & 0xffff);
+                atomicAdd(&t_lo[cell], lo16);
+                atomicAdd(&t_hi[cell], (int32_t)(((int64_t)v - lo16) >> 16));
+            }
+            if (!t_p[cell]) t_p[cell] = 1;
+        }
+    }
+    __syncwarp();
+    int64_t *out_s = p.sums + (user - p.seg_begin) * (int64_t)C;
+    uint8_t *out_p = p.present + (user - p.seg_begin) * (int64_t)C;
+    for (int c = lane; c < C; c += 32) {
+        if (t_p[c]) {
+            const long long total = (long long)t_hi[c] * 65536 + t_lo[c];
+            if (whole) out_s[c] = total;
+            else atomicAdd(reinterpret_cast<unsigned long long *>(out_s + c), (unsigned long long)total);
+            out_p[c] = 1;
+            t_lo[c] = 0; t_hi[c] = 0; t_p[c] = 0;
+        }
+    }
+    __syncwarp();
+}
+
 __global__ void __launch_bounds__(AGG_THREADS, 4) aggregate_kernel(const __grid_constant__ AggParams p) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int C = p.n_categories * p.n_months;
@@ -207,12 +264,6 @@ __device__ __forceinline__ void ags_cp16(void *dst, const void *src) {
 __device__ __forceinline__ void ags_cp4(void *dst, const void *src) {
     asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(src) : "memory");
 }
-#ifndef AGS_ROUND
-#define AGS_ROUND 8                        // rows per lane and round of the small-user path
-#endif
-#ifndef AGS_TABLE_USER
-#define AGS_TABLE_USER 8192                // users shorter than this: per-warp [category, month] table instead of runs
-#endif
 #ifndef AGS_SMALL_PIECE
 #define AGS_SMALL_PIECE 1024               // shorter pieces (tiny users): per-row 64-bit global reductions
 #endif
@@ -330,50 +381,8 @@ __global__ void __launch_bounds__(AGG_THREADS, AGS_CTAS) aggregate_sorted_kernel
                 cur_user = -1; set_month(-1);
                 __syncwarp();
                 int32_t *t_lo = reinterpret_cast<int32_t *>(bins), *t_hi = t_lo + C;
-                uint8_t *t_p = reinterpret_cast<uint8_t *>(t_hi + C);
-                // AGS_ROUND x 32 rows per round: all 3 x AGS_ROUND column loads of a lane are in flight before the first is used (a warp that
-                // loads one row per lane at a time streams ~1 TB/s across the GPU, latency-bound)
-                for (int64_t r0 = la + lane; r0 < lb; r0 += 32 * AGS_ROUND) {
-                    int32_t vv[AGS_ROUND], dd[AGS_ROUND];
-                    unsigned cc[AGS_ROUND];
-#pragma unroll
-                    for (int j = 0; j < AGS_ROUND; ++j) {
-                        const int64_t r = r0 + 32 * j;
-                        const bool in = r < lb;
-                        vv[j] = in ? p.cents[r] : 0; dd[j] = in ? p.dates[r] : 0; cc[j] = in ? (unsigned)p.cats[r] : 0x100u;
-                    }
-#pragma unroll
-                    for (int j = 0; j < AGS_ROUND; ++j) {
-                        if (cc[j] == 0x100u) continue;                       // past the piece
-                        const uint64_t off_s = (uint64_t)((int64_t)dd[j] - t_window);
-                        const unsigned mo = off_s < window_len ? month_tab[(uint32_t)off_s / 86400u] : 0xffffu;
-                        if (cc[j] >= (unsigned)p.n_categories || mo >= (unsigned)p.n_months) { ++dropped; continue; }
-                        const int cell = cc[j] * p.n_months + mo;
-                        const int32_t v = vv[j];
-                        if (v > -(1 << 18) && v < (1 << 18)) {
-                            atomicAdd(&t_lo[cell], v);
-                        } else {
-                            const int32_t lo16 = (int32_t)(int16_t)(v & 0xffff);
-                            atomicAdd(&t_lo[cell], lo16);
-                            atomicAdd(&t_hi[cell], (int32_t)(((int64_t)v - lo16) >> 16));
-                        }
-                        if (!t_p[cell]) t_p[cell] = 1;
-                    }
-                }
-                __syncwarp();
-                const bool whole = pa == p.seg_offsets[u] && pb == uend;    // nobody else adds to this user's cells
-                int64_t *out_s = p.sums + (u - p.seg_begin) * (int64_t)C;
-                uint8_t *out_p = p.present + (u - p.seg_begin) * (int64_t)C;
-                for (int c = lane; c < C; c += 32) {
-                    if (t_p[c]) {
-                        const long long total = (long long)t_hi[c] * 65536 + t_lo[c];
-                        if (whole) out_s[c] = total;
-                        else atomicAdd(reinterpret_cast<unsigned long long *>(out_s + c), (unsigned long long)total);
-                        out_p[c] = 1;
-                        t_lo[c] = 0; t_hi[c] = 0; t_p[c] = 0;
-                    }
-                }
-                __syncwarp();
+                agg_warp_table(p, la, lb, pa == p.seg_offsets[u] && pb == uend, u, t_lo, t_hi, reinterpret_cast<uint8_t *>(t_hi + C),
+                               month_tab, lane, dropped);
                 pa = pb;
                 continue;
             }
