@@ -314,6 +314,36 @@ __device__ __forceinline__ void sel_write_single(const double *s_s, const uint64
     }
 }
 
+// A query's only chunk (<= 1024 candidates starting at sel_*[0]) -> results. Up to SEL_RANK_MAX candidates no sort at all:
+// each warp takes candidates w, w + warps, ... and counts, 32 at a time, how many others rank before it — that count IS its
+// output position (ids are unique, the order is strict). A bitonic step costs ~0.25 us of barrier + shared-memory latency
+// whatever the width (28 steps for 128 entries: 7 us, more than scoring them); the counting pass of a typical tenant takes
+// well under a microsecond. Above SEL_RANK_MAX the bitonic sort wins (the counting is quadratic).
+#define SEL_RANK_MAX 384
+__device__ __forceinline__ void sel_finish_single(double *s_s, uint64_t *s_i, const double *sel_scores, const uint64_t *sel_ids,
+                                                  unsigned n_sel, int k, uint64_t *out_ids, double *out_scores, int32_t *out_count) {
+    if (n_sel > SEL_RANK_MAX) {
+        sel_load_sorted(s_s, s_i, sel_scores, sel_ids, 0, n_sel);
+        sel_write_single(s_s, s_i, n_sel, k, out_ids, out_scores, out_count);
+        return;
+    }
+    const unsigned count = n_sel < (unsigned)k ? n_sel : (unsigned)k;
+    for (unsigned t = threadIdx.x; t < n_sel; t += blockDim.x) { s_s[t] = __ldcg(sel_scores + t); s_i[t] = __ldcg(sel_ids + t); }
+    if (threadIdx.x == 0) *out_count = (int32_t)count;
+    for (unsigned t = count + threadIdx.x; t < (unsigned)k; t += blockDim.x) { out_ids[t] = UINT64_MAX; out_scores[t] = -INFINITY; }
+    __syncthreads();
+    const unsigned lane = threadIdx.x & 31, warps = blockDim.x >> 5;
+    for (unsigned e = threadIdx.x >> 5; e < n_sel; e += warps) {
+        const double ms = s_s[e];
+        const uint64_t mi = s_i[e];
+        unsigned before = 0;
+        for (unsigned j = lane; j < n_sel; j += 32) before += fcb_better64(s_s[j], s_i[j], ms, mi);
+#pragma unroll
+        for (int off = 16; off >= 1; off >>= 1) before += __shfl_xor_sync(FCB_FULL, before, off);
+        if (lane == 0 && before < (unsigned)k) { out_ids[before] = mi; out_scores[before] = ms; }
+    }
+}
+
 // Sorts candidates [1024 * blockIdx.x, +1024) by (score desc, id asc) in shared memory. `single` (the host knows
 // that at most one chunk can exist): writes the first k straight to the outputs, pads the tail and sets the count.
 __global__ void __launch_bounds__(SORT_CHUNK / 2) sort_chunks_kernel(const FcbSelectState *st, unsigned cap, int k, int single,
@@ -325,10 +355,9 @@ __global__ void __launch_bounds__(SORT_CHUNK / 2) sort_chunks_kernel(const FcbSe
     const unsigned n_sel = st->n_pass < cap ? st->n_pass : cap;
     const unsigned base = blockIdx.x * SORT_CHUNK;
     if (!single && base >= n_sel) return;
+    if (single) { sel_finish_single(s_s, s_i, sel_scores, sel_ids, n_sel, k, out_ids, out_scores, out_count); return; }
     const unsigned here = sel_load_sorted(s_s, s_i, sel_scores, sel_ids, base, n_sel);
-    if (single) {
-        sel_write_single(s_s, s_i, n_sel, k, out_ids, out_scores, out_count);
-    } else {
+    {
         for (unsigned t = threadIdx.x; t < here; t += blockDim.x) { sel_scores[base + t] = s_s[t]; sel_ids[base + t] = s_i[t]; }
     }
 }
@@ -399,8 +428,7 @@ __global__ void __launch_bounds__(SEL_THREADS) direct_rescore_kernel(const T *__
     if (!s_last) return;
     __threadfence();
     const unsigned n_sel = *reinterpret_cast<volatile unsigned *>(&st->n_pass);
-    sel_load_sorted(s_s, s_i, sel_scores, sel_ids, 0, n_sel);      // plain loads are fine: written by other CTAs before their tickets
-    sel_write_single(s_s, s_i, n_sel, k, out_ids, out_scores, out_count);
+    sel_finish_single(s_s, s_i, sel_scores, sel_ids, n_sel, k, out_ids, out_scores, out_count);
     if (threadIdx.x == 0) { st->n_pass = 0; st->n_selected = 0; }  // the state stays clean for the next query
 }
 
@@ -448,8 +476,7 @@ __global__ void __launch_bounds__(SEL_THREADS) direct_batch_kernel(const T *__re
     if (!s_last) return;
     __threadfence();
     const unsigned n_sel = *reinterpret_cast<volatile unsigned *>(&my[0]);
-    sel_load_sorted(s_s, s_i, my_scores, my_ids, 0, n_sel);
-    sel_write_single(s_s, s_i, n_sel, k, out_ids + (size_t)b * k, out_scores + (size_t)b * k, out_counts + b);
+    sel_finish_single(s_s, s_i, my_scores, my_ids, n_sel, k, out_ids + (size_t)b * k, out_scores + (size_t)b * k, out_counts + b);
     if (threadIdx.x == 0) { my[0] = 0; my[1] = 0; }
 }
 

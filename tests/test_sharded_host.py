@@ -44,7 +44,8 @@ class FakeEngine:
             rb, re_ = max(f.row_begin, lo), min(f.row_end, hi)
             oi, os_ = (np.zeros(0, np.uint64), np.zeros(0)) if re_ <= rb else canon.search(
                 self.hc.vectors, dq[b].numpy(), k, row_begin=rb, row_end=re_, ids=self.hc.ids,
-                dates=self.hc.dates, date_lo=None if f.date_lo < -2 ** 62 else f.date_lo)
+                dates=self.hc.dates, date_lo=None if f.date_lo < -2 ** 62 else f.date_lo,
+                date_hi=None if f.date_hi > 2 ** 62 else f.date_hi)
             counts[b] = len(oi)
             ids[b, :len(oi)] = torch.from_numpy(oi.view(np.int64))
             scores[b, :len(oi)] = torch.from_numpy(os_)
@@ -87,6 +88,15 @@ def worker(rank, world, port, ret):
             m.FieldCondition(key="metadata.user_id", match=m.MatchValue(value=hc.users[3]))])).points
         oi, _ = canon.search(hc.vectors, qs[1], 5, row_begin=int(hc.offsets[3]), row_end=int(hc.offsets[4]))
         ok &= [p.id for p in pts] == oi.tolist() and all(p.payload["metadata"]["user_id"] == hc.users[3] for p in pts)
+        # OR / NOT filters: several conjuncts ride in one collective search and are merged on the host (client.py)
+        from oracle import local_mode
+        flt = m.Filter(should=[m.FieldCondition(key="metadata.user_id", match=m.MatchValue(value=hc.users[u])) for u in (1, su, 5)],
+                       must_not=[m.FieldCondition(key="metadata.date", range=m.Range(gte=t0 - 40 * 86400, lte=t0 + 40 * 86400))])
+        pts = cl.query_points("transactions", query=qs[2].tolist(), limit=9, query_filter=flt).points
+        mask = local_mode.payload_mask([hc.payload(r) for r in range(spec.n_rows)], flt)
+        rows = np.flatnonzero(mask)
+        want = sorted(((-float(canon.scores(hc.vectors[r:r + 1], qs[2])[0]), int(hc.ids[r])) for r in rows))[:9]
+        ok &= [p.id for p in pts] == [w[1] for w in want] and len(pts) == 9
         ret[rank] = (bool(ok), bool(straddles))
     finally:
         dist.destroy_process_group()
