@@ -331,7 +331,7 @@ def run_b200(args):
         "dtype": "f32", "data": "synthetic", "config": workload_config(world),
         "p50_ms": per_step[len(per_step) // 2], "p99_ms": per_step[min(len(per_step) - 1, int(len(per_step) * 0.99))],
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": NCU_TRAFFIC_BYTES if rows == ROWS_PER_GPU else None, "kernel": "scan_topk_kernel<float,2,6>", "algorithmic_bytes_per_launch": alg_bytes,
+                     "traffic": NCU_TRAFFIC_BYTES if rows == ROWS_PER_GPU else None, "kernel": "scan_topk_kernel<float,%d,%d>" % (eng.scan_config if eng.scan_config != (0, 0) else (2, 6)), "algorithmic_bytes_per_launch": alg_bytes,
                      "kernel_ms": kern_ms, "peak_source": peak_src, "frac_of_nominal_8TBs": achieved / 8000.0},
         "e2e": {"value": B * e2e_steps / te, "unit": UNIT, "h2d_bytes_per_step": B * DIM * 8,
                 "d2h_bytes_per_step": B * (K * 16 + 4), "api": e2e_api,

@@ -64,6 +64,7 @@ SIGNATURES = {
                                        C.c_char_p, C.c_int32]),
     "fcb_last_search_ms": (C.c_float, [C.c_void_p]),
     "fcb_last_search_launches": (C.c_int32, [C.c_void_p]),
+    "fcb_scan_config": (C.c_int32, [C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
     "fcb_debug_scan_timing": (C.c_int32, [C.c_void_p]),
     "fcb_debug_dense_prof": (C.c_int32, [C.c_void_p]),
     "fcb_debug_dense_dump": (C.c_int32, [C.c_void_p, C.c_int64]),

@@ -171,6 +171,7 @@ extern "C" int32_t fcb_load_shard(fcb_engine *e, const fcb_shard *s) {
     if (!g.ok) return fcb_fail(e, FCB_ERR_CUDA, "fcb_load_shard: cannot select device %d", e->device);
 
     e->loaded = false;
+    e->scan_r = e->scan_u = 0;
     cudaFree(e->inv_norm); e->inv_norm = nullptr;
     cudaFree(e->row_of_rank); e->row_of_rank = nullptr;
     fcb_general_free(e);
@@ -211,6 +212,10 @@ extern "C" int32_t fcb_load_shard(fcb_engine *e, const fcb_shard *s) {
     }
     if (fcb_dense_eligible(e)) {
         const int32_t rc = fcb_dense_alloc(e);
+        if (rc != FCB_OK) return rc;
+    }
+    {
+        const int32_t rc = fcb_tune_scan(e);                   // large shards: pick the scan's loop shape by measurement
         if (rc != FCB_OK) return rc;
     }
     FCB_CUDA(e, cudaStreamSynchronize(e->stream));

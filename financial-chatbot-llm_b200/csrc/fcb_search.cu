@@ -406,13 +406,33 @@ static int32_t launch_fused_cfg(fcb_engine *e, ScanParams &p, int batch, int64_t
     return FCB_OK;
 }
 
-// (R, U) per storage type and row length; FCB_SCAN_CFG="R,U" overrides for tuning runs.
+template <typename T>
+static int32_t dispatch_fused(int R, int U, fcb_engine *e, ScanParams &p, int batch, int64_t max_rows, cudaStream_t st) {
+#define FCB_TRY(r, u) if (R == r && U == u) return launch_fused_cfg<T, r, u>(e, p, batch, max_rows, st)
+    FCB_TRY(2, 4); FCB_TRY(2, 6); FCB_TRY(2, 8); FCB_TRY(4, 2); FCB_TRY(4, 3); FCB_TRY(4, 4); FCB_TRY(8, 2);
+#undef FCB_TRY
+    return launch_fused_cfg<T, 4, 2>(e, p, batch, max_rows, st);
+}
+
+// (R, U) = rows per warp step x unroll of the column loop = loads in flight per lane. Which pair streams fastest depends on
+// the storage type, the row length AND on incidental code generation: on B200 12 loads in flight usually win and 16 fall
+// off a cliff (10.8 vs 8.28 ms on 10M x 1536 fp32), but the best pair for bf16 x 1024 moved from (8,2) to (4,2) between two
+// builds of the same loop (5.0 vs 3.76 ms). So fcb_load_shard MEASURES the candidates on the shard itself (fcb_tune_scan,
+// shards of at least 1M rows: ~20 scans) and the engine keeps the winner; every pair computes bit-identical results.
+// FCB_SCAN_CFG="R,U" forces a pair, FCB_SCAN_TUNE=0 keeps the table below (what won the last offline sweep).
+static int g_env_r = -1, g_env_u = -1, g_env_tune = -1;
+static void read_scan_env() {
+    if (g_env_r >= 0) return;
+    g_env_r = 0;
+    if (const char *c = getenv("FCB_SCAN_CFG")) sscanf(c, "%d,%d", &g_env_r, &g_env_u);
+    const char *t = getenv("FCB_SCAN_TUNE");
+    g_env_tune = !(t && t[0] == '0');
+}
+
 template <typename T>
 static int32_t launch_fused(fcb_engine *e, ScanParams &p, int batch, int64_t max_rows, cudaStream_t st) {
     constexpr int VEC = 16 / (int)sizeof(T);
     const int steps = (p.dim / VEC + 31) / 32;                // column-loop iterations per row
-    // Measured on B200 (profiles/r01_summary.md, "scan loop sweep"): 12 loads in flight per lane stream
-    // fastest; 16 (4x4, 2x8, 8x2 on 6 KB rows) fall off a cliff (10.8 ms vs 8.28 ms on 10M x 1536 fp32).
     int R, U;
     if (sizeof(T) == 4) {
         if (steps % 6 == 0) { R = 2; U = 6; }
@@ -421,19 +441,12 @@ static int32_t launch_fused(fcb_engine *e, ScanParams &p, int batch, int64_t max
         else { R = 4; U = 2; }
     } else {
         if (steps % 3 == 0) { R = 4; U = 3; }
-        else if (steps % 2 == 0) { R = 8; U = 2; }
         else { R = 4; U = 2; }
     }
-    static int env_r = -1, env_u = -1;
-    if (env_r < 0) {
-        env_r = 0;
-        if (const char *c = getenv("FCB_SCAN_CFG")) sscanf(c, "%d,%d", &env_r, &env_u);
-    }
-    if (env_r > 0) { R = env_r; U = env_u; }
-#define FCB_TRY(r, u) if (R == r && U == u) return launch_fused_cfg<T, r, u>(e, p, batch, max_rows, st)
-    FCB_TRY(2, 4); FCB_TRY(2, 6); FCB_TRY(2, 8); FCB_TRY(4, 2); FCB_TRY(4, 3); FCB_TRY(4, 4); FCB_TRY(8, 2);
-#undef FCB_TRY
-    return launch_fused_cfg<T, 4, 2>(e, p, batch, max_rows, st);
+    read_scan_env();
+    if (g_env_r > 0) { R = g_env_r; U = g_env_u; }
+    else if (e->scan_r > 0) { R = e->scan_r; U = e->scan_u; }
+    return dispatch_fused<T>(R, U, e, p, batch, max_rows, st);
 }
 
 static unsigned long long *g_scan_timing = nullptr;
@@ -548,6 +561,68 @@ static int32_t search_device(fcb_engine *e, const double *d_queries, const fcb_f
     }
     if (s.dtype == FCB_DTYPE_F32) return launch_fused<float>(e, p, batch, max_rows, st);
     return launch_fused<__nv_bfloat16>(e, p, batch, max_rows, st);
+}
+
+// Called by fcb_load_shard: time every (R, U) candidate on a full-shard scan with a pseudo-random query (results discarded)
+// and keep the fastest for this shard. Needs the host-call staging buffers (query, results), so it runs after they exist.
+int32_t fcb_tune_scan(fcb_engine *e) {
+    const fcb_shard &s = e->shard;
+    e->scan_r = e->scan_u = 0;
+    read_scan_env();
+    if (!g_env_tune || g_env_r > 0 || s.n_rows < (1 << 20) || !e->d_q || !e->d_ids) return FCB_OK;
+    uint64_t x = 0x9E3779B97F4A7C15ull;                       // splitmix64: any query without ties will do
+    for (int i = 0; i < s.dim; ++i) {
+        x += 0x9E3779B97F4A7C15ull;
+        uint64_t z = x;
+        z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull; z = (z ^ (z >> 27)) * 0x94D049BB133111EBull; z ^= z >> 31;
+        e->h_q[i] = (double)(int64_t)(z >> 11) / 9007199254740992.0 - 0.5;
+    }
+    cudaStream_t st = e->stream;
+    FCB_CUDA(e, cudaMemcpyAsync(e->d_q, e->h_q, (size_t)s.dim * sizeof(double), cudaMemcpyHostToDevice, st));
+    const int k = e->max_k < 10 ? e->max_k : 10;
+    ScanParams p{};
+    p.vectors = s.vectors; p.inv_norm = e->inv_norm; p.ids = s.ids; p.id_rank = s.id_rank;
+    p.dates = s.dates; p.cats = s.categories; p.queries = e->d_q;
+    p.n_rows = s.n_rows; p.row_base = s.row_base; p.dim = s.dim; p.k = k;
+    p.cand = e->d_cand; p.counters = e->d_counters;
+    p.out_ids = e->d_ids;
+    p.out_scores = reinterpret_cast<double *>(e->d_ids + k);
+    p.out_counts = reinterpret_cast<int32_t *>(p.out_scores + k);
+    p.use_inline = true;
+    p.inl[0] = fcb_filter{s.row_base, s.row_base + s.n_rows, FCB_DATE_MIN, FCB_DATE_MAX, FCB_ALL_CATEGORIES};
+    static const int cand[][2] = {{2, 4}, {2, 6}, {2, 8}, {4, 2}, {4, 3}, {4, 4}, {8, 2}};
+    cudaEvent_t ev_a = nullptr, ev_b = nullptr;
+    FCB_CUDA(e, cudaEventCreate(&ev_a));
+    FCB_CUDA(e, cudaEventCreate(&ev_b));
+    float best = 1e30f;
+    int best_r = 0, best_u = 0;
+    int32_t rc = FCB_OK;
+    for (const auto &c : cand) {
+        auto run = [&]() { return s.dtype == FCB_DTYPE_F32 ? dispatch_fused<float>(c[0], c[1], e, p, 1, s.n_rows, st)
+                                                           : dispatch_fused<__nv_bfloat16>(c[0], c[1], e, p, 1, s.n_rows, st); };
+        rc = run();                                             // warm-up (instruction cache, clocks)
+        if (rc != FCB_OK) break;
+        cudaEventRecord(ev_a, st);
+        for (int i = 0; i < 2 && rc == FCB_OK; ++i) rc = run();
+        cudaEventRecord(ev_b, st);
+        if (rc != FCB_OK) break;
+        if (cudaEventSynchronize(ev_b) != cudaSuccess) { rc = fcb_fail(e, FCB_ERR_CUDA, "fcb_load_shard: scan tuning failed"); break; }
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, ev_a, ev_b);
+        if (ms < best) { best = ms; best_r = c[0]; best_u = c[1]; }
+    }
+    cudaEventDestroy(ev_a);
+    cudaEventDestroy(ev_b);
+    e->last_launches = 0;
+    if (rc != FCB_OK) return rc;
+    e->scan_r = best_r; e->scan_u = best_u;
+    return FCB_OK;
+}
+
+extern "C" int32_t fcb_scan_config(const fcb_engine *e, int32_t *r, int32_t *u) {
+    if (!e || !r || !u) return FCB_ERR_INVALID;
+    *r = e->scan_r; *u = e->scan_u;
+    return FCB_OK;
 }
 
 extern "C" int32_t fcb_search(fcb_engine *e, const double *queries, const fcb_filter *filters, int32_t batch,

@@ -150,6 +150,13 @@ class Engine:
         return sums, present, stats
 
     @property
+    def scan_config(self):
+        """(rows per warp step, unroll) of the fused scan measured fastest on the loaded shard; (0, 0) = table default."""
+        r, u = C.c_int32(0), C.c_int32(0)
+        check(self._lib.fcb_scan_config(self._h, C.byref(r), C.byref(u)), self._h)
+        return int(r.value), int(u.value)
+
+    @property
     def last_search_ms(self) -> float:
         return float(self._lib.fcb_last_search_ms(self._h))
 

@@ -168,6 +168,12 @@ int32_t fcb_debug_dense_prof(int64_t *buf);
  * NULL switches it off. Not for production use. */
 int32_t fcb_debug_scan_timing(uint64_t *buf);
 
+/* The loop shape of the fused scan kernel in use for this engine's shard: rows per warp step (*r) and unroll of the
+ * column loop (*u); fcb_load_shard measures the candidates on shards of at least 1M rows and keeps the fastest (every
+ * shape computes bit-identical results). Both 0: not measured (small shard, FCB_SCAN_TUNE=0 or FCB_SCAN_CFG set) — the
+ * built-in table decides per call. Measurement aid; no counterpart in the reference. */
+int32_t fcb_scan_config(const fcb_engine *e, int32_t *r, int32_t *u);
+
 /* Number of kernels the last fcb_search / fcb_search_host call launched. Measurement aid. */
 int32_t fcb_last_search_launches(const fcb_engine *e);
 

@@ -27,6 +27,8 @@ def big(built):
     spec = synth.SynthSpec(n_rows=N, dim=DIM, seed=20240607, n_users=1)
     eng = Engine(device=0, max_batch=2, max_k=16)
     col = loader.collection_synthetic(spec, eng, with_cents=False)
+    # a shard this size has its scan loop shape measured at load (fcb_tune_scan); every shape gives bit-identical results
+    assert eng.scan_config in {(2, 4), (2, 6), (2, 8), (4, 2), (4, 3), (4, 4), (8, 2)}
     yield spec, eng, col
     eng.close()
     torch.cuda.empty_cache()
