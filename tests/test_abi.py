@@ -52,3 +52,24 @@ def test_product_never_imports_the_oracle():
                 src = open(os.path.join(dirpath, f)).read()
                 assert not re.search(r"^\s*(from|import)\s+oracle\b", src, flags=re.M), f
                 assert "libcanon" not in src, f
+
+
+def test_plain_c_caller_compiles_and_links(built, tmp_path):
+    """The boundary is a C ABI: the header compiles as C99 and as C++, and examples/ffi_demo.c (a host with no Python
+    and no CUDA headers) compiles and links against the library. Running it needs a GPU (tests/test_gpu_search.py)."""
+    import subprocess
+    from financial_chatbot_llm_b200 import _lib
+    root = ROOT
+    inc = os.path.join(root, "include")
+    for compiler, std in (("gcc", "-std=c99"), ("g++", "-std=c++11")):
+        src = tmp_path / ("hdr.c" if compiler == "gcc" else "hdr.cpp")
+        src.write_text('#include "fcb200.h"\nint main(void) { return (int)sizeof(fcb_filter) - 40; }\n')
+        subprocess.run([compiler, std, "-Wall", "-Werror", "-I", inc, "-fsyntax-only", str(src)], check=True)
+    cuda_lib = "/usr/local/cuda/lib64"
+    if not os.path.exists(os.path.join(cuda_lib, "libcudart.so")):
+        pytest.skip("no libcudart to link the demo against")
+    lib_dir = os.path.dirname(_lib.LIB_PATH)
+    out = tmp_path / "ffi_demo"
+    subprocess.run(["gcc", "-std=c99", "-Wall", "-Werror", "-I", inc, os.path.join(root, "examples", "ffi_demo.c"), "-L", lib_dir,
+                    "-lfcb200", "-L", cuda_lib, "-lcudart", "-Wl,-rpath," + lib_dir, "-o", str(out)], check=True)
+    assert out.exists()
