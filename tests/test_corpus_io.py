@@ -48,6 +48,33 @@ def test_write_and_map_roundtrip(tmp_path):
         corpus_io.write_corpus(str(tmp_path / "bad"), [{"id": 1, "vector": [0.0] * 3, "payload": pts[0]["payload"]}], dim=64)
 
 
+def test_rows_without_a_category_get_their_own_code(tmp_path):
+    """A payload without metadata.category must not alias the first category: code 255 matches no category filter
+    (the kernels test c < 64), and the manifest says so — must_not on the category is then refused, never wrong."""
+    from financial_chatbot_llm_b200 import client, corpus_io
+    from financial_chatbot_llm_b200 import qdrant_models as m
+    spec, hc, pts = make_points(n=40, dim=8)
+    for p in pts[::5]:
+        del p["payload"]["metadata"]["category"]
+    man = corpus_io.write_corpus(str(tmp_path / "m"), pts, dim=spec.dim)
+    cf = corpus_io.CorpusFiles(str(tmp_path / "m"))
+    cats = np.array(cf.columns["categories.u8"])
+    assert man["missing_category"] and int((cats == corpus_io.NO_CATEGORY).sum()) == 8
+    assert all(("category" in cf.payload(r)["metadata"]) == (cats[r] != corpus_io.NO_CATEGORY) for r in range(40))
+    assert cats[cats != corpus_io.NO_CATEGORY].max() < len(man["categories"])
+
+    class NoEngine:
+        dim, row_base, max_batch = 8, 0, 4
+    col = client.Collection("t", NoEngine(), cf.users, cf.offsets, cf.payload,
+                            category_codes={c: i for i, c in enumerate(man["categories"])})
+    col.has_missing_category = bool(man["missing_category"])           # what load_collection sets
+    some = man["categories"][0]
+    f = col.resolve_dnf(m.Filter(must=[m.FieldCondition(key="metadata.category", match=m.MatchValue(value=some))]))
+    assert len(f) == 1 and f[0].category_mask == 1                      # a positive filter is fine: code 255 never passes it
+    with pytest.raises(NotImplementedError):
+        col.resolve_dnf(m.Filter(must_not=[m.FieldCondition(key="metadata.category", match=m.MatchValue(value=some))]))
+
+
 @pytest.mark.gpu
 def test_load_from_disk_and_search(tmp_path, built):
     from financial_chatbot_llm_b200 import corpus_io, synth

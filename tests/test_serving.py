@@ -69,6 +69,35 @@ def test_micro_batching_host_logic(tmp_path):
     assert max(eng.batches) <= eng.max_batch
 
 
+def test_or_and_not_filters_through_the_server(tmp_path):
+    """should / must_not requests become several query rows of the same grouped launch; the server merges them per request."""
+    eng = FakeEngine()
+    users = ["alice", "bob", "carol"]
+    col = client.Collection("transactions", eng, users, np.array([0, 3, 8, 20]),
+                            lambda row: {"page_content": f"txn {row}", "metadata": {"user_id": users[0 if row < 3 else 1 if row < 8 else 2]}})
+    addr = str(tmp_path / "engine2.sock")
+    srv = serving.EngineServer(col, addr, window_us=1000).start()
+    try:
+        cl = serving.EngineClient(address=addr)
+        U = lambda u: m.FieldCondition(key="metadata.user_id", match=m.MatchValue(value=u))
+        # alice OR carol: two conjuncts; each list is scored q0 - 0.01 * position, so the merge interleaves them by score, id
+        pts = cl.query_points("transactions", query=[5.0, 0, 0, 0], limit=5, query_filter=m.Filter(should=[U("alice"), U("carol")])).points
+        assert [p.id for p in pts] == [0, 8, 1, 9, 2] and [p.payload["metadata"]["user_id"] for p in pts] == ["alice", "carol"] * 2 + ["alice"]
+        assert eng.batches[-1] == 2
+        # NOT bob: the rows before and after bob's segment
+        pts = cl.query_points("transactions", query=[5.0, 0, 0, 0], limit=3, query_filter=m.Filter(must_not=[U("bob")])).points
+        assert [p.id for p in pts] == [0, 8, 1]
+        # nothing can match: answered without a launch
+        n = len(eng.batches)
+        assert cl.query_points("transactions", query=[5.0, 0, 0, 0], limit=3, query_filter=m.Filter(must=[U("bob")], must_not=[U("bob")])).points == []
+        assert len(eng.batches) == n
+        with pytest.raises(RuntimeError, match="NotImplementedError"):
+            cl.query_points("transactions", query=[5.0, 0, 0, 0], query_filter=m.Filter(min_should=2, should=[U("alice")]))
+        cl.close()
+    finally:
+        srv.stop()
+
+
 @pytest.mark.gpu
 def test_server_with_real_engine_matches_oracle(tmp_path, built):
     from financial_chatbot_llm_b200 import loader, synth
