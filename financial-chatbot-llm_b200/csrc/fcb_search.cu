@@ -591,28 +591,38 @@ int32_t fcb_tune_scan(fcb_engine *e) {
     p.use_inline = true;
     p.inl[0] = fcb_filter{s.row_base, s.row_base + s.n_rows, FCB_DATE_MIN, FCB_DATE_MAX, FCB_ALL_CATEGORIES};
     static const int cand[][2] = {{2, 4}, {2, 6}, {2, 8}, {4, 2}, {4, 3}, {4, 4}, {8, 2}};
-    cudaEvent_t ev_a = nullptr, ev_b = nullptr;
-    FCB_CUDA(e, cudaEventCreate(&ev_a));
-    FCB_CUDA(e, cudaEventCreate(&ev_b));
-    float best = 1e30f;
-    int best_r = 0, best_u = 0;
+    // Two rounds over all candidates, each launch timed on its own, a candidate's score = its FASTEST launch: the clocks
+    // drift under the power cap right after a load, and a single noisy interval once picked a shape 9 % slower.
+    constexpr int N_CAND = sizeof(cand) / sizeof(cand[0]);
+    cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};
+    for (auto &x : ev) FCB_CUDA(e, cudaEventCreate(&x));
+    float fastest[N_CAND];
+    for (float &f : fastest) f = 1e30f;
     int32_t rc = FCB_OK;
-    for (const auto &c : cand) {
-        auto run = [&]() { return s.dtype == FCB_DTYPE_F32 ? dispatch_fused<float>(c[0], c[1], e, p, 1, s.n_rows, st)
-                                                           : dispatch_fused<__nv_bfloat16>(c[0], c[1], e, p, 1, s.n_rows, st); };
-        rc = run();                                             // warm-up (instruction cache, clocks)
-        if (rc != FCB_OK) break;
-        cudaEventRecord(ev_a, st);
-        for (int i = 0; i < 2 && rc == FCB_OK; ++i) rc = run();
-        cudaEventRecord(ev_b, st);
-        if (rc != FCB_OK) break;
-        if (cudaEventSynchronize(ev_b) != cudaSuccess) { rc = fcb_fail(e, FCB_ERR_CUDA, "fcb_load_shard: scan tuning failed"); break; }
-        float ms = 0.f;
-        cudaEventElapsedTime(&ms, ev_a, ev_b);
-        if (ms < best) { best = ms; best_r = c[0]; best_u = c[1]; }
+    for (int round = 0; round < 2 && rc == FCB_OK; ++round) {
+        for (int ci = 0; ci < N_CAND && rc == FCB_OK; ++ci) {
+            const int r = cand[ci][0], u = cand[ci][1];
+            auto run = [&]() { return s.dtype == FCB_DTYPE_F32 ? dispatch_fused<float>(r, u, e, p, 1, s.n_rows, st)
+                                                               : dispatch_fused<__nv_bfloat16>(r, u, e, p, 1, s.n_rows, st); };
+            rc = run();                                         // warm-up (instruction cache, clocks)
+            for (int i = 0; i < 2 && rc == FCB_OK; ++i) {
+                cudaEventRecord(ev[i], st);
+                rc = run();
+            }
+            cudaEventRecord(ev[2], st);
+            if (rc != FCB_OK) break;
+            if (cudaEventSynchronize(ev[2]) != cudaSuccess) { rc = fcb_fail(e, FCB_ERR_CUDA, "fcb_load_shard: scan tuning failed"); break; }
+            for (int i = 0; i < 2; ++i) {
+                float ms = 1e30f;
+                if (cudaEventElapsedTime(&ms, ev[i], ev[i + 1]) == cudaSuccess && ms < fastest[ci]) fastest[ci] = ms;
+            }
+        }
     }
-    cudaEventDestroy(ev_a);
-    cudaEventDestroy(ev_b);
+    for (auto &x : ev) cudaEventDestroy(x);
+    int best_r = 0, best_u = 0;
+    float best = 1e30f;
+    for (int ci = 0; ci < N_CAND; ++ci)
+        if (fastest[ci] < best) { best = fastest[ci]; best_r = cand[ci][0]; best_u = cand[ci][1]; }
     e->last_launches = 0;
     if (rc != FCB_OK) return rc;
     e->scan_r = best_r; e->scan_u = best_u;
