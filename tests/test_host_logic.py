@@ -156,3 +156,55 @@ def test_retrieve_transactions_behaviour():
     assert tools.retrieve_transactions(user_id="bob") == []
     with pytest.raises(Exception):
         tools.RetrievalIntent(num_transactions=10001)
+
+
+def test_random_filters_rewrite_equals_the_filter_model():
+    """300 seeded random must / should / must_not combinations over the three keys (including unknown users, unknown
+    categories, empty and inverted ranges, fractional bounds): the union of the rewritten conjunctions selects exactly the
+    rows the oracle's per-payload check selects, or the rewrite refuses (too many conjunctions) — never a wrong set."""
+    from oracle import local_mode
+    rng = np.random.default_rng(2024)
+    users = ["u%02d" % i for i in range(8)]
+    cats = ["Rent", "Fuel", "Dining", "Other", "Travel"]
+    sizes = [4, 0, 7, 1, 9, 3, 0, 6]
+    offsets = np.concatenate([[0], np.cumsum(sizes)])
+    n = int(offsets[-1])
+    row_user = np.repeat(np.arange(8), sizes)
+    dates = rng.integers(-5, 40, n)
+    codes = rng.integers(0, 5, n)
+    payloads = [{"page_content": "x", "metadata": {"user_id": users[row_user[r]], "date": int(dates[r]),
+                                                   "category": cats[codes[r]]}} for r in range(n)]
+    col = client.Collection("t", FakeEngine(), users, offsets, lambda r: payloads[r],
+                            category_codes={c: i for i, c in enumerate(cats)})
+
+    def cond():
+        kind = rng.integers(0, 3)
+        if kind == 0:
+            return m.FieldCondition(key="metadata.user_id", match=m.MatchValue(value=str(rng.choice(users + ["zz", "a"]))))
+        if kind == 1:
+            kw = {}
+            for name in ("gte", "gt", "lte", "lt"):
+                if rng.random() < 0.4:
+                    kw[name] = float(rng.integers(-8, 45)) + float(rng.choice([0.0, 0.5]))
+            return m.FieldCondition(key="metadata.date", range=m.Range(**kw))
+        pick = [str(c) for c in rng.choice(cats + ["Nope"], size=int(rng.integers(1, 4)), replace=False)]
+        return m.FieldCondition(key="metadata.category", match=m.MatchAny(any=pick) if len(pick) > 1 or rng.random() < 0.5
+                                else m.MatchValue(value=pick[0]))
+    rows = np.arange(n)
+    checked = refused = 0
+    for _ in range(300):
+        flt = m.Filter(must=[cond() for _ in range(rng.integers(0, 3))] or None,
+                       should=[cond() for _ in range(rng.integers(0, 4))] or None,
+                       must_not=[cond() for _ in range(rng.integers(0, 4))] or None)
+        try:
+            conj = col.resolve_dnf(flt)
+        except NotImplementedError:
+            refused += 1
+            continue
+        got = np.zeros(n, dtype=bool)
+        for f in conj:
+            got |= (rows >= f.row_begin) & (rows < f.row_end) & (dates >= f.date_lo) & (dates <= f.date_hi) & \
+                   (((f.category_mask >> codes.astype(np.uint64)) & 1) == 1)
+        assert np.array_equal(got, local_mode.payload_mask(payloads, flt)), flt
+        checked += 1
+    assert checked > 250 and refused < 50
