@@ -669,10 +669,18 @@ extern "C" int32_t fcb_search_host(fcb_engine *e, const double *queries, const f
     memcpy(out_ids, h_ids, rn * sizeof(uint64_t));
     memcpy(out_scores, h_scores, rn * sizeof(double));
     memcpy(out_counts, h_counts, (size_t)batch * sizeof(int32_t));
-    float ms = -1.f;
-    if (cudaEventElapsedTime(&ms, e->ev0, e->ev1) == cudaSuccess) e->last_ms = ms;
+    e->last_ms = -2.f;                                          // measured by ev0 / ev1; read out on demand
     return FCB_OK;
 }
 
-extern "C" float fcb_last_search_ms(const fcb_engine *e) { return e ? e->last_ms : -1.f; }
+extern "C" float fcb_last_search_ms(const fcb_engine *e) {
+    if (!e) return -1.f;
+    if (e->last_ms == -2.f) {                                   // the host call left its two events behind
+        fcb_engine *m = const_cast<fcb_engine *>(e);
+        float ms = -1.f;
+        FcbDeviceGuard g(e->device);
+        m->last_ms = g.ok && cudaEventElapsedTime(&ms, e->ev0, e->ev1) == cudaSuccess ? ms : -1.f;
+    }
+    return e->last_ms;
+}
 extern "C" int32_t fcb_last_search_launches(const fcb_engine *e) { return e ? e->last_launches : 0; }
