@@ -42,7 +42,7 @@ int main(void) {
     double query[DIM];
     for (int d = 0; d < DIM; ++d) query[d] = vectors[2000][d] + 0.01 * d;   /* close to row 2000 */
 
-    fcb_config cfg = {0, 1, 16, 0};                               /* device 0, max_batch 1, max_k 16 */
+    fcb_config cfg = {0, 1, FCB_MAX_K, 0};                        /* device 0, max_batch 1, max_k 10000 = the tool's default limit */
     fcb_engine *eng = NULL;
     if (fcb_open(&cfg, &eng) != 0) { fprintf(stderr, "fcb_open failed\n"); return 1; }
 

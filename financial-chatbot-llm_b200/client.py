@@ -201,7 +201,8 @@ class Collection:
 
     def __init__(self, name: str, engine: Engine, users: Sequence[str], offsets: np.ndarray,
                  payload_fn: Callable[[int], Dict[str, Any]], *, n_total_rows: Optional[int] = None,
-                 category_codes: Optional[Dict[Any, int]] = None, ids_host: Optional[np.ndarray] = None):
+                 category_codes: Optional[Dict[Any, int]] = None, ids_host: Optional[np.ndarray] = None,
+                 ids_row_base: Optional[int] = None):
         self.name, self.engine = name, engine
         self.users = list(users)
         self.user_index = {u: i for i, u in enumerate(self.users)}
@@ -211,6 +212,10 @@ class Collection:
         self.category_codes = category_codes or {}
         self.point_id_fn: Optional[Callable[[int], Any]] = None   # global row -> original point id (non-integer ids)
         self.has_missing_category = False              # True when some rows carry no category (code >= 64 on the device)
+        self.has_missing_date = False                  # True when some rows carry no date (stored as INT32_MIN, corpus_io.NO_DATE)
+        # ids_host[i] = point id of GLOBAL row ids_row_base + i (default: this engine's shard). A sharded
+        # collection needs the ids of EVERY shard here: the merged answer names points of other ranks too.
+        self._ids_row_base = int(getattr(engine, "row_base", 0) if ids_row_base is None else ids_row_base)
         if ids_host is not None:
             ids_host = np.asarray(ids_host, dtype=np.uint64)
             self._id_order = np.argsort(ids_host, kind="stable")
@@ -219,11 +224,18 @@ class Collection:
             self._id_order = self._ids_sorted = None
 
     def row_of_id(self, pid: int) -> int:
-        """Global row of a returned point id."""
+        """Global row of a returned point id. Raises KeyError for an id this collection's id map does not
+        hold (never a neighbouring row: that would hand out another transaction's payload)."""
         if self._ids_sorted is None:
-            return int(pid)
+            row = int(pid)
+            if not 0 <= row < self.n_total_rows:
+                raise KeyError(f"point id {pid} is not a row of collection {self.name!r}")
+            return row
         j = int(np.searchsorted(self._ids_sorted, np.uint64(pid)))
-        return int(self._id_order[j]) + self.engine.row_base
+        if j >= self._ids_sorted.shape[0] or int(self._ids_sorted[j]) != int(pid):
+            raise KeyError(f"point id {pid} is not in the id map of collection {self.name!r} "
+                           f"(a sharded collection needs the ids of all shards: ids_host=<all ids>, ids_row_base=0)")
+        return int(self._id_order[j]) + self._ids_row_base
 
     def _mask_of(self, values) -> int:
         mask = 0
@@ -255,7 +267,15 @@ class Collection:
             excl = self._mask_of(pf.category_excluded)
             if excl:
                 mask = (_lib.FCB_ALL_CATEGORIES if mask is None else mask) & ~excl
-        return make_filter(rb, re_, pf.date_lo, pf.date_hi, mask)
+        date_lo = pf.date_lo
+        if self.has_missing_date and (pf.date_lo is not None or pf.date_hi is not None):
+            # rows without metadata.date sit at INT32_MIN: Qdrant's Range never matches a missing key (and must_not on it
+            # passes). A lower bound above the sentinel keeps them out; an upper bound would let them in -> refuse.
+            if pf.date_hi is not None:
+                raise NotImplementedError("Range(lte/lt) and must_not on metadata.date need every row to carry a date "
+                                          "(this corpus has rows without one)")
+            date_lo = max(int(pf.date_lo), -(2 ** 31) + 1)
+        return make_filter(rb, re_, date_lo, pf.date_hi, mask)
 
     def resolve_dnf(self, flt: Any) -> list:
         """qdrant filter -> the FcbFilters whose union it selects (empty conjuncts dropped; may be [])."""

@@ -30,6 +30,9 @@ from . import synth
 
 FORMAT_VERSION = 1
 NO_CATEGORY = 255                       # >= 64: passes when there is no category filter, never matches one
+NO_DATE = -(2 ** 31)                    # row without metadata.date: Qdrant's Range never matches a missing key. The adapter
+                                        # keeps every lower bound above this value and refuses upper bounds / must_not on the
+                                        # date while such rows exist (manifest "missing_date"), so the sentinel never passes
 _COLUMNS = {"ids.u64": np.uint64, "id_rank.u32": np.uint32, "dates.i32": np.int32, "categories.u8": np.uint8,
             "cents.i32": np.int32, "seg_offsets.i64": np.int64, "payload.off": np.uint64}
 
@@ -73,6 +76,7 @@ def write_corpus(path: str, points: Iterable[Dict[str, Any]], *, dim: int, dtype
     cents = np.zeros(n, dtype=np.int32)
     raw_ids: List[Any] = []
     blobs: List[bytes] = []
+    missing_date = False
     for r, i in enumerate(order):
         p = pts[i]
         v = np.asarray(p["vector"], dtype=np.float32)
@@ -80,10 +84,14 @@ def write_corpus(path: str, points: Iterable[Dict[str, Any]], *, dim: int, dtype
             raise ValueError(f"point {p.get('id')!r}: vector length {v.shape} != {dim}")
         vec[r] = v
         md = p["payload"]["metadata"]
-        d = int(md.get("date", 0))
-        if not -(2 ** 31) <= d < 2 ** 31:
-            raise ValueError(f"metadata.date {d} does not fit int32 unix seconds")
-        dates[r] = d
+        if md.get("date") is None:
+            dates[r] = NO_DATE
+            missing_date = True
+        else:
+            d = int(md["date"])
+            if not NO_DATE < d < 2 ** 31:
+                raise ValueError(f"metadata.date {d} does not fit int32 unix seconds")
+            dates[r] = d
         c = md.get("category")
         if c is not None:
             if c not in cat_code:
@@ -128,7 +136,7 @@ def write_corpus(path: str, points: Iterable[Dict[str, Any]], *, dim: int, dtype
             json.dump(raw_ids, f)
     manifest = {"version": FORMAT_VERSION, "n_rows": n, "dim": dim, "dtype": dtype, "n_users": len(users),
                 "categories": cat_values, "ids_ascending": ascending, "original_ids": not int_ids,
-                "missing_category": bool(np.any(cats == NO_CATEGORY))}
+                "missing_category": bool(np.any(cats == NO_CATEGORY)), "missing_date": missing_date}
     with open(os.path.join(path, "manifest.json"), "w") as f:
         json.dump(manifest, f, indent=1)
     return manifest
@@ -204,12 +212,14 @@ def load_collection(path: str, engine, *, name: str = "transactions", row_lo: in
     offs = torch.from_numpy(cf.offsets).to(dev)
     engine.load_shard(vec, ids=ids, id_rank=id_rank, dates=dates, categories=cats, cents=cents, seg_offsets=offs,
                       row_base=row_lo)
-    ids_host = np.array(cf.columns["ids.u64"][row_lo:row_hi]) if "ids.u64" in cf.columns else None
+    # id -> row map over the WHOLE corpus (8 host bytes per row): a sharded search returns points of other shards too
+    ids_host = np.array(cf.columns["ids.u64"]) if "ids.u64" in cf.columns else None
     codes = {c: i for i, c in enumerate(cf.manifest["categories"])}
     collection = Collection(name, engine, cf.users, cf.offsets, cf.payload, n_total_rows=cf.n_rows,
-                            category_codes=codes, ids_host=ids_host)
+                            category_codes=codes, ids_host=ids_host, ids_row_base=0)
     collection.files = cf
     collection.has_missing_category = bool(cf.manifest.get("missing_category", False))
+    collection.has_missing_date = bool(cf.manifest.get("missing_date", False))
     if cf.point_ids is not None:                                      # UUID-style ids: hand the original id back to the caller
         collection.point_id_fn = lambda row: cf.point_ids[row]
     return collection

@@ -23,7 +23,10 @@ def make_filter(row_begin: int, row_end: int, date_lo: Optional[int] = None,
 
 
 class Engine:
-    def __init__(self, device: int = 0, max_batch: int = 1, max_k: int = 16):
+    def __init__(self, device: int = 0, max_batch: int = 1, max_k: int = _lib.FCB_MAX_K):
+        """``max_k`` defaults to FCB_MAX_K = 10000: the reference's default call (num_transactions=None) asks for
+        limit=10000 (tools/qdrant_tool.py:145); an engine opened with a smaller max_k refuses that call, and the
+        tool's blanket ``except`` would turn the refusal into ``[]``. Costs 8 bytes of scratch per shard row."""
         self._lib = _lib.load()
         self._h = C.c_void_p()
         cfg = FcbConfig(device, max_batch, max_k, 0)

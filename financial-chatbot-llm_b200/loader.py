@@ -51,8 +51,10 @@ def collection_from_host(hc: "synth.HostCorpus", engine: Engine, *, name: str = 
     offs = torch.from_numpy(hc.offsets).to(dev)
     engine.load_shard(vec, ids=ids, id_rank=id_rank, dates=dates, categories=cats, cents=cents,
                       seg_offsets=offs, row_base=row_lo)
+    # the host-side id -> row map covers the WHOLE corpus (a sharded search returns points of other shards too);
+    # only this shard's slice of the ids went to the device
     return Collection(name, engine, hc.users, hc.offsets, hc.payload, n_total_rows=hc.spec.n_rows,
-                      category_codes=CATEGORY_CODES, ids_host=ids_host)
+                      category_codes=CATEGORY_CODES, ids_host=hc.ids if with_ids else None, ids_row_base=0)
 
 
 def collection_synthetic(spec: "synth.SynthSpec", engine: Engine, *, name: str = "transactions",

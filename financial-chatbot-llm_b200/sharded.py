@@ -173,6 +173,7 @@ class ShardedB200Client(B200QdrantClient):
             if score_threshold is not None and s < score_threshold:
                 break
             pid = int(ids[j])
-            pts.append(ScoredPoint(id=pid, version=0, score=s, vector=None,
-                                   payload=col.payload_fn(col.row_of_id(pid)) if with_payload else None))
+            row = col.row_of_id(pid)                   # KeyError (never a wrong row) if the id map lacks another shard's ids
+            pts.append(ScoredPoint(id=col.point_id_fn(row) if col.point_id_fn else pid, version=0, score=s, vector=None,
+                                   payload=col.payload_fn(row) if with_payload else None))
         return QueryResponse(points=pts)

@@ -75,6 +75,38 @@ def test_rows_without_a_category_get_their_own_code(tmp_path):
         col.resolve_dnf(m.Filter(must_not=[m.FieldCondition(key="metadata.category", match=m.MatchValue(value=some))]))
 
 
+def test_rows_without_a_date_never_match_a_range(tmp_path):
+    """A payload without metadata.date: Qdrant's Range never matches a missing key. Such rows are stored at INT32_MIN
+    (corpus_io.NO_DATE), lower bounds stay above it, and upper bounds / must_not on the date are refused — checked
+    against the oracle's per-payload filter."""
+    from financial_chatbot_llm_b200 import client, corpus_io
+    from financial_chatbot_llm_b200 import qdrant_models as m
+    from oracle import local_mode
+    spec, hc, pts = make_points(n=40, dim=8)
+    for p in pts[::4]:
+        del p["payload"]["metadata"]["date"]
+    man = corpus_io.write_corpus(str(tmp_path / "d"), pts, dim=spec.dim)
+    cf = corpus_io.CorpusFiles(str(tmp_path / "d"))
+    dates = np.array(cf.columns["dates.i32"])
+    assert man["missing_date"] and int((dates == corpus_io.NO_DATE).sum()) == 10
+
+    class NoEngine:
+        dim, row_base, max_batch = 8, 0, 4
+    col = client.Collection("t", NoEngine(), cf.users, cf.offsets, cf.payload)
+    col.has_missing_date = bool(man["missing_date"])                    # what load_collection sets
+    payloads = [cf.payload(r) for r in range(40)]
+    for gte in (-(2 ** 40), -(2 ** 31), int(np.median(dates[dates != corpus_io.NO_DATE]))):
+        flt = m.Filter(must=[m.FieldCondition(key="metadata.date", range=m.Range(gte=gte))])
+        (f,) = col.resolve_dnf(flt)
+        got = (dates >= f.date_lo) & (dates <= f.date_hi)
+        assert np.array_equal(got, local_mode.payload_mask(payloads, flt)) and not got[dates == corpus_io.NO_DATE].any()
+    for bad in (m.Filter(must=[m.FieldCondition(key="metadata.date", range=m.Range(lte=2 ** 30))]),
+                m.Filter(must_not=[m.FieldCondition(key="metadata.date", range=m.Range(gte=0))])):
+        with pytest.raises(NotImplementedError):
+            col.resolve_dnf(bad)
+    assert len(col.resolve_dnf(None)) == 1                              # no date condition: every row passes
+
+
 @pytest.mark.gpu
 def test_load_from_disk_and_search(tmp_path, built):
     from financial_chatbot_llm_b200 import corpus_io, synth

@@ -119,3 +119,32 @@ def test_shard_ranges_cover_and_align():
     assert r[0][0] == 0 and r[-1][1] == 100000 and all(a[1] == b[0] for a, b in zip(r, r[1:]))
     assert all(c in set(off.tolist()) for _, c in r)
     assert sharded.packed_len(64, 10) == 1312
+
+
+def test_row_of_id_global_map_and_miss():
+    """A sharded answer names points of every shard: the id -> row map must be global, and an id it does not hold
+    raises (round-1 fault: searchsorted's neighbour was returned, i.e. another transaction's payload)."""
+    from financial_chatbot_llm_b200.client import Collection
+
+    class Eng:
+        row_base, dim = 1000, 8
+    ids_all = (np.arange(3000, dtype=np.uint64) * 7 + 5)[::-1].copy()          # descending: row != id, rank != row
+    users, offsets = ["u0", "u1"], np.array([0, 1500, 3000])
+    col = Collection("t", Eng(), users, offsets, lambda row: {"row": row}, n_total_rows=3000,
+                     ids_host=ids_all, ids_row_base=0)
+    for row in (0, 999, 1000, 1999, 2000, 2999):
+        assert col.row_of_id(int(ids_all[row])) == row
+    with pytest.raises(KeyError):
+        col.row_of_id(6)                                                       # between two ids
+    with pytest.raises(KeyError):
+        col.row_of_id(10 ** 9)                                                 # beyond the last id
+    # a map over the local slice only: local ids resolve, ids of other shards raise instead of aliasing
+    loc = Collection("t", Eng(), users, offsets, lambda row: {"row": row}, n_total_rows=3000, ids_host=ids_all[1000:2000])
+    assert loc.row_of_id(int(ids_all[1500])) == 1500
+    with pytest.raises(KeyError):
+        loc.row_of_id(int(ids_all[5]))
+    # ids == row numbers (no id column): range-checked
+    plain = Collection("t", Eng(), users, offsets, lambda row: {"row": row}, n_total_rows=3000)
+    assert plain.row_of_id(2999) == 2999
+    with pytest.raises(KeyError):
+        plain.row_of_id(3000)
