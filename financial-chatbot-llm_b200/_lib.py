@@ -69,6 +69,7 @@ SIGNATURES = {
     "fcb_debug_dense_prof": (C.c_int32, [C.c_void_p]),
     "fcb_debug_dense_dump": (C.c_int32, [C.c_void_p, C.c_int64]),
     "fcb_last_dense_redo": (C.c_int32, [C.c_void_p, C.c_int32]),
+    "fcb_exact_reruns": (C.c_int64, [C.c_void_p]),
     "fcb_aggregate": (C.c_int32, [C.c_void_p, C.c_int64, C.c_int64, C.c_int32, C.c_int32, C.c_int32,
                                   C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "fcb_aggregate_hits": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32,

@@ -27,7 +27,10 @@
 #include <cuda.h>
 #include <stdlib.h>
 
+#include <cuda_fp16.h>
+
 #include "fcb_internal.cuh"
+#include "fcb_topk.cuh"
 
 #define DN_THREADS 384
 #define DN_BLOCK_M 128
@@ -58,6 +61,7 @@ struct DenseParams {
     float *debug_out;                       // diagnostic: raw accumulators [debug_rows, DN_N] (NULL in production)
     int64_t debug_rows;
     long long *prof;                        // diagnostic: per-role cycle counters of CTA 0 (NULL in production)
+    int q_is_bf16;                          // format of the packed query tile: 1 = bfloat16, 0 = float16 (8x finer rounding)
     int n_stages;                           // cta_group::2 kernel: depth of the shared-memory ring (3 or 4)
     unsigned *gtop;                         // [DN_N][gt_stride] best score of every CTA's list, order-preserving uint (cta_group::2 kernel)
     int gt_stride;
@@ -133,10 +137,11 @@ __device__ __forceinline__ uint64_t make_sw128_desc(uint32_t smem_addr) {
     return (uint64_t)((smem_addr & 0x3FFFF) >> 4) | ((uint64_t)1 << 16) | ((uint64_t)(1024 >> 4) << 32) |
            ((uint64_t)1 << 46) | ((uint64_t)2 << 61);
 }
-// instruction descriptor (cute::UMMA::InstrDescriptor): c_format F32 (1) [4,6), a/b format BF16 (1)
-// [7,10) / [10,13), both K-major, N>>3 [17,23), M>>4 [24,29)
-__device__ __forceinline__ constexpr uint32_t make_idesc_bf16(int M, int N) {
-    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+// instruction descriptor (cute::UMMA::InstrDescriptor): c_format F32 (1) [4,6), a_format [7,10) = BF16 (1: the corpus),
+// b_format [10,13) = F16 (0) or BF16 (1) for the query tile (kind::f16 takes the two operand formats independently),
+// both K-major, N>>3 [17,23), M>>4 [24,29)
+__device__ __forceinline__ constexpr uint32_t make_idesc(int M, int N, int b_is_bf16) {
+    return (1u << 4) | (1u << 7) | ((uint32_t)(b_is_bf16 ? 1 : 0) << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
 
 // order-preserving float <-> uint (larger float = larger uint), for atomicMax on scores of either sign
@@ -146,20 +151,6 @@ __device__ __forceinline__ unsigned dn_ord(float f) {
 }
 __device__ __forceinline__ float dn_unord(unsigned o) {
     return __uint_as_float(o ^ ((o >> 31) ? 0x80000000u : 0xffffffffu));
-}
-
-__device__ __forceinline__ uint32_t dn_tie_key(uint32_t row, const uint32_t *__restrict__ id_rank) {
-    return (row == FCB_NO_ROW || id_rank == nullptr) ? row : id_rank[row];
-}
-__device__ __forceinline__ void dn_insert(float &my_s, uint32_t &my_r, float s, uint32_t r,
-                                          const uint32_t *__restrict__ id_rank, int lane) {
-    bool mine_better = my_s > s;
-    if (my_s == s) mine_better = dn_tie_key(my_r, id_rank) < dn_tie_key(r, id_rank);
-    const int pos = __popc(__ballot_sync(FCB_FULL, mine_better));
-    const float up_s = __shfl_up_sync(FCB_FULL, my_s, 1);
-    const uint32_t up_r = __shfl_up_sync(FCB_FULL, my_r, 1);
-    if (lane == pos) { my_s = s; my_r = r; }
-    else if (lane > pos) { my_s = up_s; my_r = up_r; }
 }
 
 __global__ void __launch_bounds__(DN_THREADS, 1)
@@ -231,7 +222,7 @@ dense_topk_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
     } else if (warp == 1) {
         // ================= MMA issuer =================
         if (lane == 0) {
-            const uint32_t idesc = make_idesc_bf16(DN_BLOCK_M, p.n_eff);
+            const uint32_t idesc = make_idesc(DN_BLOCK_M, p.n_eff, p.q_is_bf16);
             int stage = 0;
             uint32_t phase = 0;
             int it = 0;
@@ -314,7 +305,7 @@ dense_topk_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
                         const float s = __shfl_sync(FCB_FULL, pe.score, j);
                         const uint32_t r = __shfl_sync(FCB_FULL, pe.row, j);
                         if (s >= thr) {
-                            dn_insert(e.score, e.row, s, r, p.id_rank, lane);
+                            fcb_warp_insert(e.score, e.row, s, r, p.id_rank, lane);
                             thr = __shfl_sync(FCB_FULL, e.score, 31);
                         }
                     }
@@ -466,7 +457,7 @@ dense_topk2_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
     } else if (warp == 1) {
         // ================= MMA issuer (leader CTA only) =================
         if (leader && lane == 0) {
-            const uint32_t idesc = make_idesc_bf16(2 * DN_BLOCK_M, p.n_eff);
+            const uint32_t idesc = make_idesc(2 * DN_BLOCK_M, p.n_eff, p.q_is_bf16);
             int stage = 0;
             uint32_t phase = 0;
             int it = 0;
@@ -662,7 +653,7 @@ dense_topk2_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
                                 const float s = __shfl_sync(FCB_FULL, cur.score, j);
                                 const uint32_t r = __shfl_sync(FCB_FULL, cur.row, j);
                                 if (s >= thr) {
-                                    dn_insert(e.score, e.row, s, r, p.id_rank, lane);
+                                    fcb_warp_insert(e.score, e.row, s, r, p.id_rank, lane);
                                     thr = __shfl_sync(FCB_FULL, e.score, 31);
                                 }
                             }
@@ -699,13 +690,39 @@ dense_topk2_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
     }
 }
 
-// float64 queries -> bf16 [DN_N, dim], rows >= batch zero
+// float64 queries -> the 16-bit query tile [DN_N, dim] of the tensor-core pass, rows >= batch zero. One CTA per row.
+// float16 (default): h = fl16(alpha q) with alpha = 256 / |q| — unit-norm components of a 1536-vector sit around
+// 0.025, so alpha puts them near 6: far from float16's subnormals (6e-5) and its maximum (65504); the 11-bit
+// significand rounds 8x finer than bfloat16's 8 bits. bfloat16: h = bf16(q), alpha = 1. The first-pass scores are in
+// "h units" either way (the kernel only compares them with each other); dense_finalize_kernel divides by alpha |q| and
+// measures the rounding error |h / alpha - q| / |q| from the stored tile itself.
 __global__ void __launch_bounds__(256) dense_pack_queries_kernel(const double *__restrict__ q, int batch, int dim,
-                                                                 __nv_bfloat16 *__restrict__ out) {
-    const int64_t total = (int64_t)DN_N * dim;
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-        const int b = (int)(i / dim);
-        out[i] = __float2bfloat16_rn(b < batch ? (float)q[i] : 0.f);
+                                                                 uint16_t *__restrict__ out, double *__restrict__ alpha_out,
+                                                                 int q_is_bf16) {
+    __shared__ double s_part[8];
+    const int b = blockIdx.x, tid = threadIdx.x;
+    uint16_t *row = out + (size_t)b * dim;
+    if (b >= batch) {
+        for (int j = tid; j < dim; j += 256) row[j] = 0;
+        return;
+    }
+    const double *qb = q + (size_t)b * dim;
+    double alpha = 1.0;
+    if (!q_is_bf16) {
+        double ss = 0.0;
+        for (int j = tid; j < dim; j += 256) ss = fma(qb[j], qb[j], ss);
+#pragma unroll
+        for (int off = 16; off >= 1; off >>= 1) ss += __shfl_xor_sync(FCB_FULL, ss, off);
+        if ((tid & 31) == 0) s_part[tid >> 5] = ss;
+        __syncthreads();
+        double tot = 0.0;
+        for (int w = 0; w < 8; ++w) tot += s_part[w];
+        alpha = tot > 0.0 ? 256.0 / sqrt(tot) : 0.0;
+    }
+    if (tid == 0) alpha_out[b] = alpha;
+    for (int j = tid; j < dim; j += 256) {
+        const float v = (float)(qb[j] * alpha);
+        row[j] = q_is_bf16 ? __bfloat16_as_ushort(__float2bfloat16_rn(v)) : __half_as_ushort(__float2half_rn(v));
     }
 }
 
@@ -723,48 +740,25 @@ struct DenseFinalParams {
     int32_t *out_counts;
     int32_t *redo;                          // [batch]: 1 = not certified, re-run exactly
     int32_t *redo_list, *redo_count;        // compact list of those queries for the re-run launch
-    int rigorous;                           // 1: Cauchy-Schwarz margin, 0: 8-sigma margin of the rounding model
+    int rigorous;                           // 1 (default): worst-case margin, 0: 8-sigma margin of the rounding model (A/B only)
+    const uint16_t *q_packed;               // the query tile the tensor-core pass used
+    const double *alpha;                    // [batch] its scale
+    int q_is_bf16;
 };
 
 __global__ void __launch_bounds__(256) dense_finalize_kernel(const __grid_constant__ DenseFinalParams p) {
     __shared__ FcbCand m_s[8][FCB_FUSED_CAND];
     __shared__ double f_score[FCB_FUSED_CAND];
     __shared__ uint64_t f_id[FCB_FUSED_CAND];
-    __shared__ double s_kth;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int b = blockIdx.x;
     const __nv_bfloat16 *vec = reinterpret_cast<const __nv_bfloat16 *>(p.vectors);
     const double *qd = p.queries + (size_t)b * p.dim;
     float my_s = -INFINITY;
     uint32_t my_r = FCB_NO_ROW;
-    for (int L = warp; L < p.n_lists; L += 8) {
-        const FcbCand e = p.cta_top[((size_t)L * DN_N + b) * FCB_FUSED_CAND + lane];
-        float thr = __shfl_sync(FCB_FULL, my_s, 31);
-        for (int i = 0; i < FCB_FUSED_CAND; ++i) {
-            const float s = __shfl_sync(FCB_FULL, e.score, i);
-            const uint32_t r = __shfl_sync(FCB_FULL, e.row, i);
-            if (r == FCB_NO_ROW || !(s >= thr)) break;
-            dn_insert(my_s, my_r, s, r, p.id_rank, lane);
-            thr = __shfl_sync(FCB_FULL, my_s, 31);
-        }
-    }
-    m_s[warp][lane] = FcbCand{my_s, my_r};
-    __syncthreads();
-    if (warp == 0) {
-        for (int w = 1; w < 8; ++w) {
-            const FcbCand e = m_s[w][lane];
-            float thr = __shfl_sync(FCB_FULL, my_s, 31);
-            for (int i = 0; i < FCB_FUSED_CAND; ++i) {
-                const float s = __shfl_sync(FCB_FULL, e.score, i);
-                const uint32_t r = __shfl_sync(FCB_FULL, e.row, i);
-                if (r == FCB_NO_ROW || !(s >= thr)) break;
-                dn_insert(my_s, my_r, s, r, p.id_rank, lane);
-                thr = __shfl_sync(FCB_FULL, my_s, 31);
-            }
-        }
-        m_s[0][lane] = FcbCand{my_s, my_r};
-    }
-    __syncthreads();
+    for (int L = warp; L < p.n_lists; L += 8)
+        fcb_warp_merge_list(my_s, my_r, p.cta_top[((size_t)L * DN_N + b) * FCB_FUSED_CAND + lane], p.id_rank, lane);
+    fcb_cta_merge_tree(my_s, my_r, m_s, p.id_rank, warp, lane);
     for (int c = warp; c < FCB_FUSED_CAND; c += 8) {
         const uint32_t row = m_s[0][c].row;
         double sc = -INFINITY;
@@ -777,30 +771,31 @@ __global__ void __launch_bounds__(256) dense_finalize_kernel(const __grid_consta
     }
     __syncthreads();
     if (warp == 0) {
-        const bool valid = m_s[0][lane].row != FCB_NO_ROW;
-        const int nvalid = __popc(__ballot_sync(FCB_FULL, valid));
-        const double ms = f_score[lane];
-        const uint64_t mi = f_id[lane];
-        int rank = 0;
-        for (int j = 0; j < FCB_FUSED_CAND; ++j)
-            rank += (m_s[0][j].row != FCB_NO_ROW) && fcb_better64(f_score[j], f_id[j], ms, mi);
-        const int count = nvalid < p.k ? nvalid : p.k;
-        if (valid && rank < p.k) { p.out_ids[(size_t)b * p.k + rank] = mi; p.out_scores[(size_t)b * p.k + rank] = ms; }
-        if (lane >= count && lane < p.k) { p.out_ids[(size_t)b * p.k + lane] = UINT64_MAX; p.out_scores[(size_t)b * p.k + lane] = -INFINITY; }
-        // certificate: the exact k-th score must clear the worst kept first-pass score by the margin
-        if (lane == 0) s_kth = -INFINITY;
-        __syncwarp();
-        if (valid && rank == count - 1) s_kth = ms;
-        __syncwarp();
-        // First-pass scores are dot(x, q_bf16) / |x|: bring the worst kept one to cosine scale with 1 / |q|.
-        // Error of a first-pass score: |dot(x, q_bf16 - q)| / (|x||q|) <= rho := |q_bf16 - q| / |q| for ANY row
-        // (Cauchy-Schwarz; rho ~ 1.1e-3). For rows not aligned with the rounding-error vector the error behaves
-        // like rho / sqrt(dim); the default margin is 8 standard deviations of that model with a 3x variance
-        // allowance, the rigorous mode uses rho itself (more queries are then re-run by the exact scan).
+        double kth;
+        int nvalid;
+        fcb_rank_and_write(m_s[0], f_score, f_id, p.k, lane, p.out_ids + (size_t)b * p.k, p.out_scores + (size_t)b * p.k,
+                           p.out_counts + b, kth, nvalid);
+        // Certificate. First-pass score of a row: a = fl32(acc * inv32) with acc the tensor-core accumulator of x . h
+        // (h = the 16-bit query tile, ~ alpha q). In cosine units, a / (alpha |q|) differs from the row's cosine by at most
+        //   rho      = |h / alpha - q| / |q|       rounding of the query tile, for ANY row (Cauchy-Schwarz); measured here
+        //                                          from the tile itself: ~1.4e-4 for float16, ~1.1e-3 for bfloat16
+        //   eps_acc  = (dim / 16) * 17 * 2^-23     the accumulator: every UMMA K-step adds 16 exact products to it; the
+        //                                          model is one truncation to 24 significant bits (relative to the largest
+        //                                          addend, itself <= |x||h|) per addend and step — 2.0e-4 at dim 1536.
+        //                                          tests/test_gpu_dense.py measures the real error against this bound.
+        //   eps_inv  = (n / 2 + 8) * 2^-24         inverse norm (float32 sum of squares, rsqrtf) and the final product
+        // A row that is not among the 32 survivors has a <= the worst kept one, so the answer is certified when the exact
+        // k-th score clears worst + margin (or fewer than 32 rows qualified). The legacy margin (FCB_DENSE_RIGOROUS=0, for
+        // A/B runs only) is 8 standard deviations of a statistical model of rho.
         double qq = 0.0, ee = 0.0;
+        const double alpha = p.alpha[b];
+        const double ialpha = alpha > 0.0 ? 1.0 / alpha : 0.0;
+        const uint16_t *hq = p.q_packed + (size_t)b * p.dim;
         for (int j = lane; j < p.dim; j += 32) {
             const double qv = qd[j];
-            const double er = (double)__bfloat162float(__float2bfloat16_rn((float)qv)) - qv;
+            const double hv = p.q_is_bf16 ? (double)__bfloat162float(__ushort_as_bfloat16(hq[j]))
+                                          : (double)__half2float(__ushort_as_half(hq[j]));
+            const double er = hv * ialpha - qv;
             qq = __fma_rn(qv, qv, qq);
             ee = __fma_rn(er, er, ee);
         }
@@ -809,13 +804,18 @@ __global__ void __launch_bounds__(256) dense_finalize_kernel(const __grid_consta
             qq += __shfl_xor_sync(FCB_FULL, qq, off);
             ee += __shfl_xor_sync(FCB_FULL, ee, off);
         }
-        const double nq = qq > 0.0 ? sqrt(qq) : 1.0;
-        const double rho = sqrt(ee) / nq + 1e-6;                      // + float32 accumulation / norm rounding
-        const double margin = p.rigorous ? rho : 8.0 * rho * sqrt(3.0 / (double)p.dim) + 1e-6;
-        const double worst = (double)__shfl_sync(FCB_FULL, my_s, 31) / nq;
+        const double nq = sqrt(qq);
+        const double rho = nq > 0.0 ? sqrt(ee) / nq : 1.0;
+        const double n_chain = (double)(p.dim / 32 + 8);
+        const double eps_acc = (double)(p.dim / 16) * 17.0 * 1.1920928955078125e-7 * (1.0 + rho);
+        const double eps_inv = (0.5 * n_chain + 8.0) * 5.9604644775390625e-8;
+        const double margin = p.rigorous ? rho * (1.0 + 1e-9) + eps_acc + eps_inv + 1e-12
+                                         : 8.0 * rho * sqrt(3.0 / (double)p.dim) + 1e-6;
+        const float worst32 = __shfl_sync(FCB_FULL, my_s, 31);
+        const bool domain = alpha > 0.0 && nq > 8.9e-16 && nq < 1.1e15 && isfinite(worst32);
+        const double worst = domain ? (double)worst32 * ialpha / nq : 0.0;
         if (lane == 0) {
-            p.out_counts[b] = count;
-            const int flag = (nvalid == FCB_FUSED_CAND && !(worst + margin < s_kth)) ? 1 : 0;
+            const int flag = (nvalid == FCB_FUSED_CAND && !(domain && worst + margin < kth)) ? 1 : 0;
             p.redo[b] = flag;
             if (flag) p.redo_list[atomicAdd(p.redo_count, 1)] = b;
         }
@@ -853,7 +853,9 @@ struct FcbDense {
     CUtensorMap map_qh[DN_N / 32];          // ... box rows = N / 2 for the cta_group::2 kernel
     int rigorous = 0;
     int two_cta = 1;
-    __nv_bfloat16 *q_bf16 = nullptr;        // [DN_N, dim]
+    uint16_t *q_bf16 = nullptr;             // [DN_N, dim] the 16-bit query tile (float16 or bfloat16)
+    double *alpha = nullptr;                // [DN_N] its per-query scale
+    int q_is_bf16 = 0;
     FcbCand *cta_top = nullptr, *pend = nullptr;
     unsigned *gtop = nullptr;               // [DN_N][gt_stride] per-CTA best scores of the cta_group::2 kernel
     int gt_stride = 0;
@@ -865,7 +867,7 @@ struct FcbDense {
 void fcb_dense_free(fcb_engine *e) {
     FcbDense *d = reinterpret_cast<FcbDense *>(e->dense);
     if (!d) return;
-    cudaFree(d->q_bf16); cudaFree(d->cta_top); cudaFree(d->pend); cudaFree(d->redo); cudaFree(d->error_flag); cudaFree(d->gtop);
+    cudaFree(d->q_bf16); cudaFree(d->alpha); cudaFree(d->cta_top); cudaFree(d->pend); cudaFree(d->redo); cudaFree(d->error_flag); cudaFree(d->gtop);
     delete d;
     e->dense = nullptr;
 }
@@ -884,6 +886,7 @@ int32_t fcb_dense_alloc(fcb_engine *e) {
     d->gt_stride = ((d->grid + 31) / 32) * 32;
     const size_t lists = (size_t)d->grid * DN_N;
     if (cudaMalloc(&d->q_bf16, (size_t)DN_N * s.dim * 2) != cudaSuccess ||
+        cudaMalloc(&d->alpha, (size_t)DN_N * sizeof(double)) != cudaSuccess ||
         cudaMalloc(&d->cta_top, lists * FCB_FUSED_CAND * sizeof(FcbCand)) != cudaSuccess ||
         cudaMalloc(&d->pend, lists * DN_PEND_CAP * sizeof(FcbCand)) != cudaSuccess ||
         cudaMalloc(&d->redo, (size_t)(2 * DN_N + 1) * sizeof(int32_t)) != cudaSuccess ||
@@ -899,8 +902,10 @@ int32_t fcb_dense_alloc(fcb_engine *e) {
         rc = encode_map(e, &d->map_q[i], d->q_bf16, DN_N, (uint64_t)s.dim, 32 * (i + 1));
     for (int i = 0; i < DN_N / 32 && rc == FCB_OK; ++i)
         rc = encode_map(e, &d->map_qh[i], d->q_bf16, DN_N, (uint64_t)s.dim, 16 * (i + 1));
-    const char *rig = getenv("FCB_DENSE_RIGOROUS");
-    d->rigorous = rig && rig[0] == '1';
+    const char *rig = getenv("FCB_DENSE_RIGOROUS");                 // "0": the statistical margin of round 1 (A/B runs only)
+    d->rigorous = !(rig && rig[0] == '0');
+    const char *qf = getenv("FCB_DENSE_QFMT");                      // "bf16": bfloat16 query tile instead of float16
+    d->q_is_bf16 = qf && qf[0] == 'b';
     const char *one = getenv("FCB_DENSE_1CTA");                     // tuning / fallback switch
     d->two_cta = !(one && one[0] == '1') && (d->grid % 2 == 0);
     if (rc != FCB_OK) { fcb_dense_free(e); return rc; }
@@ -939,14 +944,14 @@ int32_t fcb_search_dense(fcb_engine *e, const double *d_queries, const fcb_filte
     FcbDense *d = reinterpret_cast<FcbDense *>(e->dense);
     const fcb_shard &s = e->shard;
     if (!d) return fcb_fail(e, FCB_ERR_STATE, "fcb_search: batched path not initialised");
-    dense_pack_queries_kernel<<<e->num_sms, 256, 0, st>>>(d_queries, batch, s.dim, d->q_bf16);
+    dense_pack_queries_kernel<<<DN_N, 256, 0, st>>>(d_queries, batch, s.dim, d->q_bf16, d->alpha, d->q_is_bf16);
     DenseParams p{};
     p.inv_norm = e->inv_norm; p.id_rank = s.id_rank; p.dates = s.dates; p.cats = s.categories; p.filter = f;
     p.n_rows = s.n_rows; p.row_base = s.row_base; p.dim = s.dim;
     p.n_queries = batch; p.n_eff = ((batch + 31) / 32) * 32;
     p.cta_top = d->cta_top; p.pend = d->pend; p.error_flag = d->error_flag;
     p.debug_out = g_debug_out; p.debug_rows = g_debug_rows; p.prof = g_dense_prof;
-    p.gtop = d->gtop; p.gt_stride = d->gt_stride;
+    p.gtop = d->gtop; p.gt_stride = d->gt_stride; p.q_is_bf16 = d->q_is_bf16;
     FCB_CUDA(e, cudaMemsetAsync(d->gtop, 0, (size_t)DN_N * d->gt_stride * sizeof(unsigned), st));   // 0 orders below every float
     p.n_stages = p.n_eff <= 96 ? 4 : 3;                              // stages + 4 KB + lists (n_eff x 256 B) must fit 227 KB
     const size_t smem = (size_t)DN_STAGES * DN_STAGE_BYTES + 4096;
@@ -961,7 +966,7 @@ int32_t fcb_search_dense(fcb_engine *e, const double *d_queries, const fcb_filte
     fp.vectors = s.vectors; fp.ids = s.ids; fp.id_rank = s.id_rank; fp.queries = d_queries; fp.cta_top = d->cta_top;
     fp.n_lists = d->grid; fp.row_base = s.row_base; fp.dim = s.dim; fp.k = k;
     fp.out_ids = d_out_ids; fp.out_scores = d_out_scores; fp.out_counts = d_out_counts; fp.redo = d->redo;
-    fp.rigorous = d->rigorous;
+    fp.rigorous = d->rigorous; fp.q_packed = d->q_bf16; fp.alpha = d->alpha; fp.q_is_bf16 = d->q_is_bf16;
     fp.redo_list = d->redo + DN_N; fp.redo_count = d->redo + 2 * DN_N;
     FCB_CUDA(e, cudaMemsetAsync(fp.redo_count, 0, sizeof(int32_t), st));
     dense_finalize_kernel<<<batch, 256, 0, st>>>(fp);

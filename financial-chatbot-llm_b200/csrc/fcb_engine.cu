@@ -39,6 +39,7 @@ extern "C" int32_t fcb_close(fcb_engine *e) {
         free_host_staging(e);
         cudaFree(e->inv_norm);
         cudaFree(e->row_of_rank);
+        fcb_exact_free(e);
         fcb_general_free(e);
         fcb_dense_free(e);
         cudaFree(e->d_filters);
@@ -120,9 +121,13 @@ extern "C" int32_t fcb_open(const fcb_config *cfg, fcb_engine **out) {
 // ---- inverse row norms ------------------------------------------------------------------
 // One warp per row, 128-bit loads, float32 accumulation: the first-pass ranking only needs
 // ~1e-6 relative accuracy (the float64 rescore recomputes norms canonically).
+// Also counts the rows whose squared norm is outside [2^-100, 2^100] or not finite (zero rows are fine: they score 0 in
+// both passes): the float32 first pass has no error bound for those, so a shard holding any sends every query to the
+// exact float64 path (fcb_exact.cu).
 template <typename T>
 __global__ void __launch_bounds__(256) inv_norm_kernel(const T *__restrict__ vectors, int64_t n_rows,
-                                                       int dim, float *__restrict__ inv_norm) {
+                                                       int dim, float *__restrict__ inv_norm,
+                                                       unsigned long long *__restrict__ out_of_domain) {
     constexpr int VEC = 16 / sizeof(T);
     const int lane = threadIdx.x & 31;
     const int64_t warp0 = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
@@ -131,8 +136,10 @@ __global__ void __launch_bounds__(256) inv_norm_kernel(const T *__restrict__ vec
     for (int64_t r = warp0; r < n_rows; r += nwarps) {
         const uint4 *p = reinterpret_cast<const uint4 *>(vectors + r * (int64_t)dim);
         float ss = 0.f;
+        unsigned nz = 0;                                       // any non-zero element (sign bits masked)
         for (int c = lane; c < nv; c += 32) {
             const uint4 v = fcb_ldg_stream(p + c, true);
+            nz |= (v.x | v.y | v.z | v.w) & (sizeof(T) == 4 ? 0x7fffffffu : 0x7fff7fffu);
             if (sizeof(T) == 4) {
                 const float a = __uint_as_float(v.x), b = __uint_as_float(v.y),
                             cc = __uint_as_float(v.z), d = __uint_as_float(v.w);
@@ -147,7 +154,12 @@ __global__ void __launch_bounds__(256) inv_norm_kernel(const T *__restrict__ vec
             }
         }
         ss = fcb_warp_sum(ss);
-        if (lane == 0) inv_norm[r] = ss > 0.f ? rsqrtf(ss) : 0.f;
+        nz = __reduce_or_sync(FCB_FULL, nz);
+        if (lane == 0) {
+            inv_norm[r] = ss > 0.f ? rsqrtf(ss) : 0.f;
+            // a true zero row is fine; a sum of squares that underflowed to zero is not
+            if (!((ss == 0.f && nz == 0) || (ss >= 7.8886091e-31f && ss <= 1.2676506e30f))) atomicAdd(out_of_domain, 1ull);
+        }
     }
 }
 
@@ -174,6 +186,7 @@ extern "C" int32_t fcb_load_shard(fcb_engine *e, const fcb_shard *s) {
     e->scan_r = e->scan_u = 0;
     cudaFree(e->inv_norm); e->inv_norm = nullptr;
     cudaFree(e->row_of_rank); e->row_of_rank = nullptr;
+    fcb_exact_free(e);
     fcb_general_free(e);
     fcb_dense_free(e);
     free_host_staging(e);
@@ -183,18 +196,24 @@ extern "C" int32_t fcb_load_shard(fcb_engine *e, const fcb_shard *s) {
                         (size_t)s->n_rows * sizeof(float));
     }
     const int blocks = e->num_sms * 8;
+    unsigned long long *d_ood = nullptr;
+    FCB_CUDA(e, cudaMalloc(&d_ood, sizeof(unsigned long long)));
+    FCB_CUDA(e, cudaMemsetAsync(d_ood, 0, sizeof(unsigned long long), e->stream));
     if (s->dtype == FCB_DTYPE_F32)
-        inv_norm_kernel<float><<<blocks, 256, 0, e->stream>>>((const float *)s->vectors, s->n_rows, s->dim, e->inv_norm);
+        inv_norm_kernel<float><<<blocks, 256, 0, e->stream>>>((const float *)s->vectors, s->n_rows, s->dim, e->inv_norm, d_ood);
     else
         inv_norm_kernel<__nv_bfloat16><<<blocks, 256, 0, e->stream>>>((const __nv_bfloat16 *)s->vectors, s->n_rows,
-                                                                       s->dim, e->inv_norm);
+                                                                       s->dim, e->inv_norm, d_ood);
     FCB_CUDA(e, cudaGetLastError());
+    FCB_CUDA(e, cudaMemcpyAsync(&e->rows_out_of_domain, d_ood, sizeof(unsigned long long), cudaMemcpyDeviceToHost, e->stream));
+    FCB_CUDA(e, cudaStreamSynchronize(e->stream));
+    cudaFree(d_ood);
 
     const size_t B = e->max_batch, K = e->max_k;
     FCB_CUDA(e, cudaMallocHost(&e->h_q, B * s->dim * sizeof(double)));
     FCB_CUDA(e, cudaMalloc(&e->d_q, B * s->dim * sizeof(double)));
     // results of the host entry point: ONE block (ids | scores | counts) so that one copy brings them back
-    const size_t res_bytes = B * K * 16 + B * sizeof(int32_t);
+    const size_t res_bytes = B * K * 16 + 2 * B * sizeof(int32_t);        // ... | certificate flags
     FCB_CUDA(e, cudaMallocHost(&e->h_ids, res_bytes));
     FCB_CUDA(e, cudaMalloc(&e->d_ids, res_bytes));
     e->h_scores = reinterpret_cast<double *>(e->h_ids + B * K);
@@ -204,6 +223,10 @@ extern "C" int32_t fcb_load_shard(fcb_engine *e, const fcb_shard *s) {
     e->shard = *s;
     if (e->max_k > FCB_FUSED_MAX_K) {
         const int32_t rc = fcb_general_alloc(e);
+        if (rc != FCB_OK) return rc;
+    }
+    {
+        const int32_t rc = fcb_exact_alloc(e);                  // after the general-k scratch: shares its key buffer
         if (rc != FCB_OK) return rc;
     }
     {

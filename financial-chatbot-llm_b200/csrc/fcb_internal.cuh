@@ -71,6 +71,9 @@ struct fcb_engine {
     int scan_r = 0, scan_u = 0;            // fused scan: the (rows per step, unroll) pair measured fastest on this shard (0 = not yet)
     uint32_t *row_of_rank = nullptr;       // inverse of shard.id_rank, built by fcb_aggregate_hits on first use
     void *dense = nullptr;                 // FcbDense* (fcb_dense.cu): batched tensor-core path scratch
+    void *exact = nullptr;                 // FcbExact* (fcb_exact.cu): exact float64 fallback scratch + certificate flags
+    unsigned long long rows_out_of_domain = 0;   // rows whose norm is outside [2^-50, 2^50] (or not finite): the float32
+                                           //   first pass has no error bound for them, every query takes the exact path
 
     float last_ms = -1.f;
     int last_launches = 0;
@@ -91,7 +94,7 @@ int32_t fcb_search_general_small_batch(fcb_engine *e, const double *d_queries, c
                                        int32_t k, int64_t max_rows, uint64_t *d_out_ids, double *d_out_scores,
                                        int32_t *d_out_counts, cudaStream_t st);
 int32_t fcb_search_general(fcb_engine *e, const double *d_query, const fcb_filter &f, int32_t k,
-                           uint64_t *d_out_ids, double *d_out_scores, int32_t *d_out_count, cudaStream_t st);
+                           uint64_t *d_out_ids, double *d_out_scores, int32_t *d_out_count, int32_t *d_flag, cudaStream_t st);
 
 int32_t fcb_check_dates_sorted(fcb_engine *e);   // fcb_aggregate.cu
 int32_t fcb_tune_scan(fcb_engine *e);            // fcb_search.cu: measure the scan's (R, U) candidates on the loaded shard
@@ -103,6 +106,14 @@ void fcb_dense_free(fcb_engine *e);
 int32_t fcb_search_dense(fcb_engine *e, const double *d_queries, const fcb_filter &f, int32_t batch, int32_t k,
                          uint64_t *d_out_ids, double *d_out_scores, int32_t *d_out_counts, cudaStream_t st,
                          const int32_t **redo_list_out, const int32_t **redo_count_out);
+
+// exact float64 fallback (fcb_exact.cu): answers the queries whose certificate flag a fast path set
+int32_t fcb_exact_alloc(fcb_engine *e);
+void fcb_exact_free(fcb_engine *e);
+int32_t *fcb_exact_flags(fcb_engine *e);   // device [max_batch]
+int32_t fcb_exact_enqueue(fcb_engine *e, const double *d_queries, const fcb_filter *d_filters, const fcb_filter *inl,
+                          int filters_mode, int32_t batch, int32_t k, const int32_t *d_flags, uint64_t *d_out_ids,
+                          double *d_out_scores, int32_t *d_out_counts, cudaStream_t st);
 
 // error plumbing (fcb_engine.cu)
 int32_t fcb_fail(fcb_engine *e, int32_t code, const char *fmt, ...);

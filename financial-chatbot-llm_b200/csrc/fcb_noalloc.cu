@@ -35,6 +35,7 @@
 #include <mutex>
 
 #include "fcb_internal.cuh"
+#include "fcb_topk.cuh"
 
 #define FCB_NOALLOC_MAX_K 16
 #define FCB_NOALLOC_MAX_DIM 8192
@@ -65,35 +66,59 @@ struct NoallocParams {
     int32_t *out_count;
 };
 
-__device__ __forceinline__ uint32_t na_tie_key(uint32_t row, const uint32_t *__restrict__ id_rank) {
-    return (row == FCB_NO_ROW || id_rank == nullptr) ? row : id_rank[row];
-}
-
-__device__ __forceinline__ void na_insert(float &my_s, uint32_t &my_r, float s, uint32_t r,
-                                          const uint32_t *__restrict__ id_rank, int lane) {
-    bool mine_better = my_s > s;
-    if (my_s == s) mine_better = na_tie_key(my_r, id_rank) < na_tie_key(r, id_rank);
-    const int pos = __popc(__ballot_sync(FCB_FULL, mine_better));
-    const float up_s = __shfl_up_sync(FCB_FULL, my_s, 1);
-    const uint32_t up_r = __shfl_up_sync(FCB_FULL, my_r, 1);
-    if (lane == pos) { my_s = s; my_r = r; }
-    else if (lane > pos) { my_s = up_s; my_r = up_r; }
-}
-
-__device__ __forceinline__ void na_merge_list(float &my_s, uint32_t &my_r, FcbCand e,
-                                              const uint32_t *__restrict__ id_rank, int lane) {
-    float thr = __shfl_sync(FCB_FULL, my_s, 31);
-    for (int i = 0; i < FCB_FUSED_CAND; ++i) {
-        const float s = __shfl_sync(FCB_FULL, e.score, i);
-        const uint32_t r = __shfl_sync(FCB_FULL, e.row, i);
-        if (r == FCB_NO_ROW || !(s >= thr)) break;
-        na_insert(my_s, my_r, s, r, id_rank, lane);
-        thr = __shfl_sync(FCB_FULL, my_s, 31);
+// Exact answer by ONE CTA, used only when the certificate below fails (more rows within float32 rounding of the k-th
+// score than the 32-candidate margin: duplicated rows, a degenerate query). The engine route hands such a query to a
+// grid-wide float64 kernel with an 8-byte-per-row key buffer; this entry point may not allocate one, so the last CTA
+// walks the segment again on its own: canonical float64 score of every passing row, each warp keeping its 32 best by
+// (score desc, id asc) in registers, the 8 lists merged through shared memory. Slow for a large segment (one SM), but
+// allocation-free, and only ever run for the queries the fast pass cannot prove.
+template <typename T>
+__device__ __noinline__ void na_exact_rescan(const NoallocParams &p, int64_t lo, int64_t hi, bool has_date, bool has_cat) {
+    __shared__ double x_s[FCB_SCAN_WARPS][32];
+    __shared__ uint32_t x_t[FCB_SCAN_WARPS][32], x_r[FCB_SCAN_WARPS][32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const T *__restrict__ vec = reinterpret_cast<const T *>(p.vectors);
+    const fcb_filter f = p.filter;
+    double bs = -INFINITY;
+    uint32_t bt = 0xffffffffu, br = FCB_NO_ROW;
+    auto insert = [&](double sc, uint32_t tie, uint32_t row) {            // warp-uniform arguments
+        const bool mine_better = br != FCB_NO_ROW && (bs > sc || (bs == sc && bt < tie));
+        const int pos = __popc(__ballot_sync(FCB_FULL, mine_better));     // better entries form a prefix
+        const double us = __shfl_up_sync(FCB_FULL, bs, 1);
+        const uint32_t ut = __shfl_up_sync(FCB_FULL, bt, 1), ur = __shfl_up_sync(FCB_FULL, br, 1);
+        if (lane == pos) { bs = sc; bt = tie; br = row; }
+        else if (lane > pos) { bs = us; bt = ut; br = ur; }
+    };
+    for (int64_t row = lo + warp; row < hi; row += FCB_SCAN_WARPS) {
+        bool pass = true;
+        if (has_date) { const int64_t d = p.dates[row]; pass = d >= f.date_lo && d <= f.date_hi; }
+        if (pass && has_cat) { const unsigned c = p.cats[row]; pass = c < 64 && ((f.category_mask >> c) & 1ull); }
+        if (!pass) continue;
+        const double sc = fcb_canon_score_warp<T>(vec + row * (int64_t)p.dim, p.query, p.dim, lane);
+        insert(sc, fcb_tie_key((uint32_t)row, p.id_rank), (uint32_t)row);
     }
+    x_s[warp][lane] = bs; x_t[warp][lane] = bt; x_r[warp][lane] = br;
+    __syncthreads();
+    if (warp != 0) return;
+    for (int w = 1; w < FCB_SCAN_WARPS; ++w)
+        for (int i = 0; i < 32; ++i) {
+            if (x_r[w][i] == FCB_NO_ROW) break;
+            insert(x_s[w][i], x_t[w][i], x_r[w][i]);
+        }
+    const int nvalid = __popc(__ballot_sync(FCB_FULL, br != FCB_NO_ROW));
+    const int count = nvalid < p.k ? nvalid : p.k;
+    if (lane < p.k) {
+        const bool ok = lane < count;
+        p.out_ids[lane] = ok ? (p.ids ? p.ids[br] : (uint64_t)(p.row_base + br)) : UINT64_MAX;
+        p.out_scores[lane] = ok ? bs : -INFINITY;
+    }
+    if (lane == 0) *p.out_count = count;
 }
 
-// dot and sum of squares of one 16-byte piece; the sum of squares follows the accumulation order
-// of inv_norm_kernel (fcb_engine.cu) so both routes rank rows from identical float32 scores
+// dot and sum of squares of one 16-byte piece. The sum of squares uses the same per-lane order as inv_norm_kernel
+// (fcb_engine.cu): lane l accumulates the 16-byte pieces l, l+32, ... with fmaf, then the same xor butterfly — which is
+// the only reason the in-scan rsqrtf(ss) equals the precomputed inverse norm bit for bit. The first-pass float32 scores
+// only pick the 32 candidates; what is returned is always the canonical float64 re-score.
 template <typename T> struct NaPiece;
 template <> struct NaPiece<float> {
     static constexpr int VEC = 4;
@@ -152,6 +177,7 @@ scan_topk_noalloc_kernel(const __grid_constant__ NoallocParams p) {
 
     float my_s = -INFINITY, thr = -INFINITY;
     uint32_t my_r = FCB_NO_ROW;
+    bool ood = false;
 
     const int64_t stride = (int64_t)gridDim.x * FCB_SCAN_WARPS;
     for (int64_t g = (int64_t)blockIdx.x * FCB_SCAN_WARPS + warp; g < ngroups; g += stride) {
@@ -186,20 +212,21 @@ scan_topk_noalloc_kernel(const __grid_constant__ NoallocParams p) {
 #pragma unroll
         for (int r = 0; r < R; ++r) {
             const float inv = ss[r] > 0.f ? rsqrtf(ss[r]) : 0.f;
+            // a passing row whose sum of squares left float32's safe range (or is zero): the first pass has no error
+            // bound for it, so the last CTA must answer exactly (the engine route checks this once, at fcb_load_shard)
+            if (((pm >> r) & 1u) && !(ss[r] >= 7.8886091e-31f && ss[r] <= 1.2676506e30f)) ood = true;
             const float s = dot[r] * inv;
             if (((pm >> r) & 1u) && s >= thr) {
-                na_insert(my_s, my_r, s, (uint32_t)(r0 + r), id_rank, lane);
+                fcb_warp_insert(my_s, my_r, s, (uint32_t)(r0 + r), id_rank, lane);
                 thr = __shfl_sync(FCB_FULL, my_s, 31);
             }
         }
     }
 
-    m_s[warp][lane] = FcbCand{my_s, my_r};
+    fcb_cta_merge_tree(my_s, my_r, m_s, id_rank, warp, lane);
+    if (warp == 0) lists[(size_t)blockIdx.x * FCB_FUSED_CAND + lane] = FcbCand{my_s, my_r};
     __syncthreads();
-    if (warp == 0) {
-        for (int w = 1; w < FCB_SCAN_WARPS; ++w) na_merge_list(my_s, my_r, m_s[w][lane], id_rank, lane);
-        lists[(size_t)blockIdx.x * FCB_FUSED_CAND + lane] = FcbCand{my_s, my_r};
-    }
+    if (ood && lane == 0) atomicOr(counter + 1, 1u);               // header word 1: "a row outside the float32 range passed"
     __syncthreads();
     if (tid == 0) {
         __threadfence();
@@ -212,16 +239,10 @@ scan_topk_noalloc_kernel(const __grid_constant__ NoallocParams p) {
     my_s = -INFINITY; my_r = FCB_NO_ROW;
     for (unsigned L = warp; L < gridDim.x; L += FCB_SCAN_WARPS) {
         const uint2 raw = __ldcg(reinterpret_cast<const uint2 *>(lists + (size_t)L * FCB_FUSED_CAND + lane));
-        na_merge_list(my_s, my_r, FcbCand{__uint_as_float(raw.x), raw.y}, id_rank, lane);
+        fcb_warp_merge_list(my_s, my_r, FcbCand{__uint_as_float(raw.x), raw.y}, id_rank, lane);
     }
     __syncthreads();
-    m_s[warp][lane] = FcbCand{my_s, my_r};
-    __syncthreads();
-    if (warp == 0) {
-        for (int w = 1; w < FCB_SCAN_WARPS; ++w) na_merge_list(my_s, my_r, m_s[w][lane], id_rank, lane);
-        m_s[0][lane] = FcbCand{my_s, my_r};
-    }
-    __syncthreads();
+    fcb_cta_merge_tree(my_s, my_r, m_s, id_rank, warp, lane);
     for (int c = warp; c < FCB_FUSED_CAND; c += FCB_SCAN_WARPS) {
         const uint32_t row = m_s[0][c].row;
         double sc = -INFINITY;
@@ -234,18 +255,23 @@ scan_topk_noalloc_kernel(const __grid_constant__ NoallocParams p) {
     }
     __syncthreads();
     if (warp == 0) {
-        const bool valid = m_s[0][lane].row != FCB_NO_ROW;
-        const int nvalid = __popc(__ballot_sync(FCB_FULL, valid));
-        const double ms = f_score[lane];
-        const uint64_t mi = f_id[lane];
-        int rank = 0;
-        for (int j = 0; j < FCB_FUSED_CAND; ++j)
-            rank += (m_s[0][j].row != FCB_NO_ROW) && fcb_better64(f_score[j], f_id[j], ms, mi);
-        const int count = nvalid < p.k ? nvalid : p.k;
-        if (valid && rank < p.k) { p.out_ids[rank] = mi; p.out_scores[rank] = ms; }
-        if (lane >= count && lane < p.k) { p.out_ids[lane] = UINT64_MAX; p.out_scores[lane] = -INFINITY; }
-        if (lane == 0) *p.out_count = count;
+        double kth;
+        int nvalid;
+        fcb_rank_and_write(m_s[0], f_score, f_id, p.k, lane, p.out_ids, p.out_scores, p.out_count, kth, nvalid);
+        // the same certificate as the engine route (fcb_search.cu, scan_tail): a dropped row's canonical score is at most
+        // worst kept first-pass score / |q| + eps
+        int flag = 0;
+        if (nvalid == FCB_FUSED_CAND) {
+            const double nq = __dsqrt_rn(fcb_canon_qq_warp(qd, p.dim, lane));
+            const float worst = m_s[0][FCB_FUSED_CAND - 1].score;
+            const bool domain = nq > 8.9e-16 && nq < 1.1e15 && isfinite(worst);
+            flag = !(domain && kth > (double)worst / nq + fcb_first_pass_eps(p.dim));
+        }
+        if (__ldcg(counter + 1) != 0) flag = 1;
+        if (lane == 0) s_last = flag;                                  // reuse: 1 = not certified
     }
+    __syncthreads();
+    if (s_last) na_exact_rescan<T>(p, lo, hi, has_date, has_cat);
 }
 
 // ---- per-device set-up state: plain static storage, nothing allocated

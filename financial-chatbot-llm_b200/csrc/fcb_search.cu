@@ -16,6 +16,7 @@
 #include <string.h>
 
 #include "fcb_internal.cuh"
+#include "fcb_topk.cuh"
 
 struct ScanParams {
     const void *vectors;
@@ -31,6 +32,8 @@ struct ScanParams {
     const int32_t *redo_list;              // optional: device list of query indices to run (re-run of uncertified
     const int32_t *redo_count;             //   queries of the dense path); grid.y rows then stride over that list
     unsigned long long *timing;            // diagnostic: %globaltimer at phase boundaries (NULL in production)
+    int32_t *cert_flags;                   // [batch]: 1 = the float32 first pass could not certify this query (fcb_exact.cu re-runs it)
+    double cert_eps;                       // fcb_first_pass_eps(dim)
     int64_t n_rows, row_base;
     int dim, k;
     FcbCand *cand;
@@ -45,88 +48,6 @@ __device__ __forceinline__ void stamp(const ScanParams &p, int slot) {
         unsigned long long t;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
         p.timing[slot] = t;
-    }
-}
-
-__device__ __forceinline__ uint32_t tie_key(uint32_t row, const uint32_t *__restrict__ id_rank) {
-    return (row == FCB_NO_ROW || id_rank == nullptr) ? row : id_rank[row];
-}
-
-// Insert (s, r) into the warp's sorted list (lane i holds the i-th best). Warp-uniform inputs.
-__device__ __forceinline__ void warp_insert(float &my_s, uint32_t &my_r, float s, uint32_t r,
-                                            const uint32_t *__restrict__ id_rank, int lane) {
-    bool mine_better = my_s > s;
-    if (my_s == s) mine_better = tie_key(my_r, id_rank) < tie_key(r, id_rank);
-    const int pos = __popc(__ballot_sync(FCB_FULL, mine_better));   // better entries form a prefix
-    const float up_s = __shfl_up_sync(FCB_FULL, my_s, 1);
-    const uint32_t up_r = __shfl_up_sync(FCB_FULL, my_r, 1);
-    if (lane == pos) { my_s = s; my_r = r; }
-    else if (lane > pos) { my_s = up_s; my_r = up_r; }
-}
-
-__device__ __forceinline__ bool cand_better(float s1, uint32_t r1, float s2, uint32_t r2,
-                                            const uint32_t *__restrict__ id_rank) {
-    if (s1 != s2) return s1 > s2;
-    return tie_key(r1, id_rank) < tie_key(r2, id_rank);
-}
-
-// Merge a sorted 32-entry list (entry i in lane i of `e`) into the warp's sorted list: lane i keeps the
-// better of mine[i] and other[31 - i] (a bitonic sequence holding the 32 best of the union), then a
-// 5-step bitonic merge restores best-first order. ~50 instructions instead of up to 32 insertions.
-__device__ __forceinline__ void warp_merge_list(float &my_s, uint32_t &my_r, FcbCand e,
-                                                const uint32_t *__restrict__ id_rank, int lane) {
-    const float thr = __shfl_sync(FCB_FULL, my_s, 31);
-    const float top = __shfl_sync(FCB_FULL, e.score, 0);
-    const uint32_t top_r = __shfl_sync(FCB_FULL, e.row, 0);
-    if (top_r == FCB_NO_ROW || !(top >= thr)) return;          // nothing in `e` can enter
-    const int n_valid = __popc(__ballot_sync(FCB_FULL, e.row != FCB_NO_ROW));
-    if (n_valid <= 3) {                                        // short list (small segments): plain insertions
-        for (int i = 0; i < n_valid; ++i)
-            warp_insert(my_s, my_r, __shfl_sync(FCB_FULL, e.score, i), __shfl_sync(FCB_FULL, e.row, i), id_rank, lane);
-        return;
-    }
-    const float os = __shfl_sync(FCB_FULL, e.score, 31 - lane);
-    const uint32_t orow = __shfl_sync(FCB_FULL, e.row, 31 - lane);
-    if (cand_better(os, orow, my_s, my_r, id_rank)) { my_s = os; my_r = orow; }
-#pragma unroll
-    for (int d = 16; d >= 1; d >>= 1) {
-        const float ps = __shfl_xor_sync(FCB_FULL, my_s, d);
-        const uint32_t pr = __shfl_xor_sync(FCB_FULL, my_r, d);
-        const bool want_better = (lane & d) == 0;              // lower lane of the pair keeps the better entry
-        if (cand_better(ps, pr, my_s, my_r, id_rank) == want_better && (ps != my_s || pr != my_r)) { my_s = ps; my_r = pr; }
-    }
-}
-
-// Two independent merges in one instruction stream (no early exits, so the two shuffle chains
-// interleave): used by the last CTA, which has up to 2 * SMs lists to fold.
-__device__ __forceinline__ void warp_merge_list2(float &s0, uint32_t &r0, FcbCand e0, float &s1, uint32_t &r1, FcbCand e1,
-                                                 const uint32_t *__restrict__ id_rank, int lane) {
-    const float o0 = __shfl_sync(FCB_FULL, e0.score, 31 - lane), o1 = __shfl_sync(FCB_FULL, e1.score, 31 - lane);
-    const uint32_t q0 = __shfl_sync(FCB_FULL, e0.row, 31 - lane), q1 = __shfl_sync(FCB_FULL, e1.row, 31 - lane);
-    if (cand_better(o0, q0, s0, r0, id_rank)) { s0 = o0; r0 = q0; }
-    if (cand_better(o1, q1, s1, r1, id_rank)) { s1 = o1; r1 = q1; }
-#pragma unroll
-    for (int d = 16; d >= 1; d >>= 1) {
-        const float p0 = __shfl_xor_sync(FCB_FULL, s0, d), p1 = __shfl_xor_sync(FCB_FULL, s1, d);
-        const uint32_t t0 = __shfl_xor_sync(FCB_FULL, r0, d), t1 = __shfl_xor_sync(FCB_FULL, r1, d);
-        const bool want_better = (lane & d) == 0;
-        if (cand_better(p0, t0, s0, r0, id_rank) == want_better && (p0 != s0 || t0 != r0)) { s0 = p0; r0 = t0; }
-        if (cand_better(p1, t1, s1, r1, id_rank) == want_better && (p1 != s1 || t1 != r1)) { s1 = p1; r1 = t1; }
-    }
-}
-
-// 8 warp lists -> warp 0 through shared memory, as a 3-level tree (3 merges deep instead of 7).
-__device__ __forceinline__ void cta_merge_tree(float &my_s, uint32_t &my_r, FcbCand (*m_s)[FCB_FUSED_CAND],
-                                               const uint32_t *__restrict__ id_rank, int warp, int lane) {
-    m_s[warp][lane] = FcbCand{my_s, my_r};
-    __syncthreads();
-#pragma unroll
-    for (int stride = 1; stride < FCB_SCAN_WARPS; stride <<= 1) {
-        if ((warp & (2 * stride - 1)) == 0) {
-            warp_merge_list(my_s, my_r, m_s[warp + stride][lane], id_rank, lane);
-            m_s[warp][lane] = FcbCand{my_s, my_r};
-        }
-        __syncthreads();
     }
 }
 
@@ -171,17 +92,17 @@ __device__ __noinline__ void scan_tail(const ScanParams &p, int b, unsigned char
         for (; L + FCB_SCAN_WARPS < gridDim.x; L += 2 * FCB_SCAN_WARPS) {       // two lists per step
             const uint2 a = __ldcg(reinterpret_cast<const uint2 *>(lists + (size_t)L * FCB_FUSED_CAND + lane));
             const uint2 c = __ldcg(reinterpret_cast<const uint2 *>(lists + (size_t)(L + FCB_SCAN_WARPS) * FCB_FUSED_CAND + lane));
-            warp_merge_list2(my_s, my_r, FcbCand{__uint_as_float(a.x), a.y}, s1, r1, FcbCand{__uint_as_float(c.x), c.y},
+            fcb_warp_merge_list2(my_s, my_r, FcbCand{__uint_as_float(a.x), a.y}, s1, r1, FcbCand{__uint_as_float(c.x), c.y},
                              id_rank, lane);
         }
         if (L < gridDim.x) {
             const uint2 a = __ldcg(reinterpret_cast<const uint2 *>(lists + (size_t)L * FCB_FUSED_CAND + lane));
-            warp_merge_list(my_s, my_r, FcbCand{__uint_as_float(a.x), a.y}, id_rank, lane);
+            fcb_warp_merge_list(my_s, my_r, FcbCand{__uint_as_float(a.x), a.y}, id_rank, lane);
         }
-        warp_merge_list(my_s, my_r, FcbCand{s1, r1}, id_rank, lane);
+        fcb_warp_merge_list(my_s, my_r, FcbCand{s1, r1}, id_rank, lane);
     }
     __syncthreads();                       // m_s reuse: every warp finished reading it above
-    cta_merge_tree(my_s, my_r, m_s, id_rank, warp, lane);
+    fcb_cta_merge_tree(my_s, my_r, m_s, id_rank, warp, lane);
     stamp(p, 5);
 
     // ---- canonical float64 re-score of the 32 survivors: the float64 query goes to shared memory,
@@ -189,8 +110,8 @@ __device__ __noinline__ void scan_tail(const ScanParams &p, int b, unsigned char
     double *qd_s = reinterpret_cast<double *>(smem_raw + (((size_t)p.dim * sizeof(float) + 15) & ~(size_t)15));
     for (int i = tid; i < p.dim; i += FCB_SCAN_THREADS) qd_s[i] = qd[i];
     __syncthreads();
+    const double qq = fcb_canon_qq_warp(qd_s, p.dim, lane);
     {
-        const double qq = fcb_canon_qq_warp(qd_s, p.dim, lane);
         const T *rows4[4];
         uint32_t rr[4];
 #pragma unroll
@@ -214,26 +135,25 @@ __device__ __noinline__ void scan_tail(const ScanParams &p, int b, unsigned char
     }
     __syncthreads();
     if (warp == 0) {
-        const bool valid = m_s[0][lane].row != FCB_NO_ROW;
-        const int nvalid = __popc(__ballot_sync(FCB_FULL, valid));
-        const double ms = f_score[lane];
-        const uint64_t mi = f_id[lane];
-        int rank = 0;
-#pragma unroll 8
-        for (int j = 0; j < FCB_FUSED_CAND; ++j)
-            rank += (m_s[0][j].row != FCB_NO_ROW) && fcb_better64(f_score[j], f_id[j], ms, mi);
-        const int count = nvalid < p.k ? nvalid : p.k;
-        if (valid && rank < p.k) {
-            p.out_ids[(size_t)b * p.k + rank] = mi;
-            p.out_scores[(size_t)b * p.k + rank] = ms;
-        }
-        if (lane >= count && lane < p.k) {
-            p.out_ids[(size_t)b * p.k + lane] = UINT64_MAX;
-            p.out_scores[(size_t)b * p.k + lane] = -INFINITY;
-        }
+        double kth;
+        int nvalid;
+        fcb_rank_and_write(m_s[0], f_score, f_id, p.k, lane, p.out_ids + (size_t)b * p.k, p.out_scores + (size_t)b * p.k,
+                           p.out_counts + b, kth, nvalid);
         if (lane == 0) {
-            p.out_counts[b] = count;
             p.counters[b] = 0;             // ready for the next call
+            // Certificate. Rows that are NOT among the 32 survivors have a first-pass score <= the worst kept one, so
+            // their canonical score is at most worst / |q| + eps: if the exact k-th score clears that, no such row can
+            // belong to the top k (or tie with its last entry). Fewer than 32 survivors: every passing row was kept.
+            if (p.cert_flags != nullptr) {
+                int flag = 0;
+                if (nvalid == FCB_FUSED_CAND) {
+                    const double nq = __dsqrt_rn(qq);
+                    const float worst = m_s[0][FCB_FUSED_CAND - 1].score;
+                    const bool domain = nq > 8.9e-16 && nq < 1.1e15 && isfinite(worst);   // 2^-50 .. 2^50
+                    flag = !(domain && kth > (double)worst / nq + p.cert_eps);
+                }
+                p.cert_flags[b] = flag;
+            }
         }
     }
     stamp(p, 8);
@@ -321,7 +241,7 @@ __device__ __forceinline__ void scan_one_query(const ScanParams &p, const int b,
             for (int r = 0; r < R; ++r) {
                 const float s = acc[r] * __shfl_sync(FCB_FULL, inv, r);
                 if (((pm >> r) & 1u) && s >= thr) {
-                    warp_insert(my_s, my_r, s, (uint32_t)(r0 + r), id_rank, lane);
+                    fcb_warp_insert(my_s, my_r, s, (uint32_t)(r0 + r), id_rank, lane);
                     thr = __shfl_sync(FCB_FULL, my_s, 31);
                 }
             }
@@ -330,7 +250,7 @@ __device__ __forceinline__ void scan_one_query(const ScanParams &p, const int b,
     }
 
     // ---- CTA merge: 8 warp lists -> warp 0 (tree through shared memory)
-    cta_merge_tree(my_s, my_r, m_s, id_rank, warp, lane);
+    fcb_cta_merge_tree(my_s, my_r, m_s, id_rank, warp, lane);
     if (blockIdx.x == 0) stamp(p, 2);
     if (warp == 0) p.cand[((size_t)b * gridDim.x + blockIdx.x) * FCB_FUSED_CAND + lane] = FcbCand{my_s, my_r};
     __syncthreads();
@@ -458,48 +378,87 @@ extern "C" int32_t fcb_debug_scan_timing(uint64_t *buf) {
     return FCB_OK;
 }
 
+// The host-side view of one call's filters: clipped to what the shard can answer (a predicate on an absent column or an
+// empty date range matches nothing), the largest segment, and where the kernels find them — passed by value for small
+// batches, else (or when `need_device`) in a slot of the pinned -> device ring.
+struct StagedFilters {
+    fcb_filter inl[FCB_INLINE_FILTERS];
+    const fcb_filter *d_filters = nullptr;
+    const fcb_filter *h_stage = nullptr;   // the pinned copy behind d_filters
+    int use_inline = 0;
+    int64_t max_rows = 0;
+    bool same = true;                      // every filter equals the first
+};
+
+static int32_t stage_filters(fcb_engine *e, const fcb_filter *h_filters, int32_t batch, bool need_device, cudaStream_t st,
+                             StagedFilters &sf) {
+    const fcb_shard &s = e->shard;
+    sf.use_inline = batch <= FCB_INLINE_FILTERS;
+    const bool to_device = need_device || !sf.use_inline;
+    fcb_filter *stage = nullptr;
+    int slot = 0;
+    if (to_device) {
+        slot = e->filter_slot;
+        e->filter_slot = (slot + 1) % FCB_FILTER_SLOTS;
+        FCB_CUDA(e, cudaEventSynchronize(e->filter_ev[slot]));      // slot's previous copy has drained
+        stage = e->h_filters + (size_t)slot * e->max_batch;
+        sf.d_filters = e->d_filters + (size_t)slot * e->max_batch;
+        sf.h_stage = stage;
+    }
+    for (int b = 0; b < batch; ++b) {
+        fcb_filter f = h_filters[b];
+        const bool has_date = f.date_lo != FCB_DATE_MIN || f.date_hi != FCB_DATE_MAX;
+        const bool has_cat = f.category_mask != FCB_ALL_CATEGORIES;
+        if ((has_date && !s.dates) || (has_cat && !s.categories) || f.date_lo > f.date_hi) f.row_end = f.row_begin;
+        int64_t lo = f.row_begin - s.row_base, hi = f.row_end - s.row_base;
+        if (lo < 0) lo = 0;
+        if (hi > s.n_rows) hi = s.n_rows;
+        if (hi - lo > sf.max_rows) sf.max_rows = hi - lo;
+        if (b > 0 && memcmp(&h_filters[b], &h_filters[0], sizeof(fcb_filter)) != 0) sf.same = false;
+        if (sf.use_inline) sf.inl[b] = f;
+        if (to_device) stage[b] = f;
+    }
+    if (to_device) {
+        FCB_CUDA(e, cudaMemcpyAsync(const_cast<fcb_filter *>(sf.d_filters), stage, (size_t)batch * sizeof(fcb_filter),
+                                    cudaMemcpyHostToDevice, st));
+        FCB_CUDA(e, cudaEventRecord(e->filter_ev[slot], st));
+    }
+    return FCB_OK;
+}
+
+// `d_flags` ([batch] device int32) receives the certificate flags; NULL = the engine's own array. With `defer_fallback`
+// (the synchronous host entry point, which sees the flags anyway) the exact fallback of the fused path is NOT enqueued:
+// *fallback_pending tells the caller to look at the flags and call fcb_exact_enqueue itself if one is set.
 static int32_t search_device(fcb_engine *e, const double *d_queries, const fcb_filter *h_filters, int32_t batch,
                              int32_t k, uint64_t *d_out_ids, double *d_out_scores, int32_t *d_out_counts,
-                             cudaStream_t st) {
+                             cudaStream_t st, int32_t *d_flags, bool defer_fallback, bool *fallback_pending,
+                             StagedFilters *sf_out) {
     const fcb_shard &s = e->shard;
     e->last_launches = 0;
+    if (fallback_pending) *fallback_pending = false;
+    if (!d_flags) d_flags = fcb_exact_flags(e);
+    StagedFilters sf_local;
+    StagedFilters &sf = sf_out ? *sf_out : sf_local;
+    {
+        const int32_t rc = stage_filters(e, h_filters, batch, k > FCB_FUSED_MAX_K && batch > 1, st, sf);
+        if (rc != FCB_OK) return rc;
+    }
+    if (e->rows_out_of_domain > 0) {
+        // rows with norms outside the float32 first pass's range: no error bound, so every query is answered exactly
+        FCB_CUDA(e, cudaMemsetAsync(d_flags, 1, (size_t)batch * sizeof(int32_t), st));
+        return fcb_exact_enqueue(e, d_queries, sf.d_filters, sf.inl, sf.use_inline ? 1 : 0, batch, k, d_flags, d_out_ids,
+                                 d_out_scores, d_out_counts, st);
+    }
     if (k > FCB_FUSED_MAX_K) {
-        // a batch of small segments (every one fits one sorted chunk): ONE launch for all of them
-        if (batch > 1 && e->d_bsel) {
-            int64_t max_rows = 0;
-            for (int b = 0; b < batch; ++b) {
-                int64_t lo = h_filters[b].row_begin - s.row_base, hi = h_filters[b].row_end - s.row_base;
-                if (lo < 0) lo = 0;
-                if (hi > s.n_rows) hi = s.n_rows;
-                if (hi - lo > max_rows) max_rows = hi - lo;
-            }
-            if (max_rows <= 1024) {
-                const int slot = e->filter_slot;
-                e->filter_slot = (slot + 1) % FCB_FILTER_SLOTS;
-                FCB_CUDA(e, cudaEventSynchronize(e->filter_ev[slot]));      // slot's previous copy has drained
-                fcb_filter *stage = e->h_filters + (size_t)slot * e->max_batch;
-                fcb_filter *d_f = e->d_filters + (size_t)slot * e->max_batch;
-                for (int b = 0; b < batch; ++b) {
-                    fcb_filter f = h_filters[b];
-                    const bool has_date = f.date_lo != FCB_DATE_MIN || f.date_hi != FCB_DATE_MAX;
-                    const bool has_cat = f.category_mask != FCB_ALL_CATEGORIES;
-                    if ((has_date && !s.dates) || (has_cat && !s.categories) || f.date_lo > f.date_hi) f.row_end = f.row_begin;
-                    stage[b] = f;
-                }
-                FCB_CUDA(e, cudaMemcpyAsync(d_f, stage, (size_t)batch * sizeof(fcb_filter), cudaMemcpyHostToDevice, st));
-                FCB_CUDA(e, cudaEventRecord(e->filter_ev[slot], st));
-                return fcb_search_general_small_batch(e, d_queries, d_f, batch, k, max_rows, d_out_ids, d_out_scores,
-                                                      d_out_counts, st);
-            }
-        }
-        // general-k path: one query at a time, stream-ordered (fcb_select.cu)
+        // a batch of small segments (every one fits one sorted chunk): ONE launch for all of them, exact by construction
+        if (batch > 1 && e->d_bsel && sf.max_rows <= 1024)
+            return fcb_search_general_small_batch(e, d_queries, sf.d_filters, batch, k, sf.max_rows, d_out_ids, d_out_scores,
+                                                  d_out_counts, st);
+        // general-k path: one query at a time, stream-ordered (fcb_select.cu); certificate + exact fallback per query
         for (int b = 0; b < batch; ++b) {
-            fcb_filter f = h_filters[b];
-            const bool has_date = f.date_lo != FCB_DATE_MIN || f.date_hi != FCB_DATE_MAX;
-            const bool has_cat = f.category_mask != FCB_ALL_CATEGORIES;
-            if ((has_date && !s.dates) || (has_cat && !s.categories) || f.date_lo > f.date_hi) f.row_end = f.row_begin;
+            const fcb_filter &f = sf.use_inline ? sf.inl[b] : sf.h_stage[b];
             const int32_t rc = fcb_search_general(e, d_queries + (size_t)b * s.dim, f, k, d_out_ids + (size_t)b * k,
-                                                  d_out_scores + (size_t)b * k, d_out_counts + b, st);
+                                                  d_out_scores + (size_t)b * k, d_out_counts + b, d_flags + b, st);
             if (rc != FCB_OK) return rc;
         }
         return FCB_OK;
@@ -511,56 +470,37 @@ static int32_t search_device(fcb_engine *e, const double *d_queries, const fcb_f
     p.cand = e->d_cand; p.counters = e->d_counters;
     p.out_ids = d_out_ids; p.out_scores = d_out_scores; p.out_counts = d_out_counts;
     p.timing = g_scan_timing;
+    p.cert_flags = d_flags; p.cert_eps = fcb_first_pass_eps(s.dim);
 
     // batched dense path: bf16 shard, a large batch whose filters are all the same, a segment big
     // enough to amortise the tensor-core pipeline. Uncertified queries are re-run by the exact scan below.
-    if (e->dense && batch >= FCB_DENSE_MIN_BATCH && batch <= 256) {
-        bool same = true;
-        for (int b = 1; b < batch && same; ++b) same = memcmp(&h_filters[b], &h_filters[0], sizeof(fcb_filter)) == 0;
+    bool dense_ran = false;
+    if (e->dense && batch >= FCB_DENSE_MIN_BATCH && batch <= 256 && sf.same && sf.max_rows >= 65536) {
         fcb_filter f0 = h_filters[0];
         const bool has_date = f0.date_lo != FCB_DATE_MIN || f0.date_hi != FCB_DATE_MAX;
         const bool has_cat = f0.category_mask != FCB_ALL_CATEGORIES;
         if ((has_date && !s.dates) || (has_cat && !s.categories) || f0.date_lo > f0.date_hi) f0.row_end = f0.row_begin;
-        int64_t lo = f0.row_begin - s.row_base, hi = f0.row_end - s.row_base;
-        if (lo < 0) lo = 0;
-        if (hi > s.n_rows) hi = s.n_rows;
-        if (same && hi - lo >= 65536) {
-            const int32_t rc = fcb_search_dense(e, d_queries, f0, batch, k, d_out_ids, d_out_scores, d_out_counts, st,
-                                                &p.redo_list, &p.redo_count);
-            if (rc != FCB_OK) return rc;
-        }
+        // the re-run scan writes the flags of the queries it runs only: the certified ones must read 0
+        FCB_CUDA(e, cudaMemsetAsync(d_flags, 0, (size_t)batch * sizeof(int32_t), st));
+        const int32_t rc = fcb_search_dense(e, d_queries, f0, batch, k, d_out_ids, d_out_scores, d_out_counts, st,
+                                            &p.redo_list, &p.redo_count);
+        if (rc != FCB_OK) return rc;
+        dense_ran = true;
     }
 
-    // resolve filters on the host: clip to the shard, reject predicates on absent columns
-    fcb_filter *stage = nullptr;
-    p.use_inline = batch <= FCB_INLINE_FILTERS;
-    if (!p.use_inline) {
-        const int slot = e->filter_slot;
-        e->filter_slot = (slot + 1) % FCB_FILTER_SLOTS;
-        FCB_CUDA(e, cudaEventSynchronize(e->filter_ev[slot]));      // slot's previous copy has drained
-        stage = e->h_filters + (size_t)slot * e->max_batch;
-        p.filters = e->d_filters + (size_t)slot * e->max_batch;
+    p.use_inline = sf.use_inline;
+    p.filters = sf.d_filters;
+    if (sf.use_inline) for (int b = 0; b < batch; ++b) p.inl[b] = sf.inl[b];
+    int32_t rc = s.dtype == FCB_DTYPE_F32 ? launch_fused<float>(e, p, batch, sf.max_rows, st)
+                                          : launch_fused<__nv_bfloat16>(e, p, batch, sf.max_rows, st);
+    if (rc != FCB_OK) return rc;
+    if (sf.max_rows < FCB_FUSED_CAND) return FCB_OK;           // every passing row is a survivor: certified by construction
+    if (defer_fallback && !dense_ran) {
+        if (fallback_pending) *fallback_pending = true;
+        return FCB_OK;
     }
-    int64_t max_rows = 0;
-    for (int b = 0; b < batch; ++b) {
-        fcb_filter f = h_filters[b];
-        const bool has_date = f.date_lo != FCB_DATE_MIN || f.date_hi != FCB_DATE_MAX;
-        const bool has_cat = f.category_mask != FCB_ALL_CATEGORIES;
-        if ((has_date && !s.dates) || (has_cat && !s.categories) || f.date_lo > f.date_hi) f.row_end = f.row_begin;
-        int64_t lo = f.row_begin - s.row_base, hi = f.row_end - s.row_base;
-        if (lo < 0) lo = 0;
-        if (hi > s.n_rows) hi = s.n_rows;
-        if (hi - lo > max_rows) max_rows = hi - lo;
-        if (p.use_inline) p.inl[b] = f; else stage[b] = f;
-    }
-    if (!p.use_inline) {
-        const int slot = (e->filter_slot + FCB_FILTER_SLOTS - 1) % FCB_FILTER_SLOTS;
-        FCB_CUDA(e, cudaMemcpyAsync(const_cast<fcb_filter *>(p.filters), stage, (size_t)batch * sizeof(fcb_filter),
-                                    cudaMemcpyHostToDevice, st));
-        FCB_CUDA(e, cudaEventRecord(e->filter_ev[slot], st));
-    }
-    if (s.dtype == FCB_DTYPE_F32) return launch_fused<float>(e, p, batch, max_rows, st);
-    return launch_fused<__nv_bfloat16>(e, p, batch, max_rows, st);
+    return fcb_exact_enqueue(e, d_queries, sf.d_filters, sf.inl, sf.use_inline ? 1 : 0, batch, k, d_flags, d_out_ids,
+                             d_out_scores, d_out_counts, st);
 }
 
 // Called by fcb_load_shard: time every (R, U) candidate on a full-shard scan with a pseudo-random query (results discarded)
@@ -642,7 +582,8 @@ extern "C" int32_t fcb_search(fcb_engine *e, const double *queries, const fcb_fi
     if (rc != FCB_OK) return rc;
     FcbDeviceGuard g(e->device);
     if (!g.ok) return fcb_fail(e, FCB_ERR_CUDA, "fcb_search: cannot select device %d", e->device);
-    return search_device(e, queries, filters, batch, k, out_ids, out_scores, out_counts, (cudaStream_t)stream);
+    return search_device(e, queries, filters, batch, k, out_ids, out_scores, out_counts, (cudaStream_t)stream, nullptr, false,
+                         nullptr, nullptr);
 }
 
 extern "C" int32_t fcb_search_host(fcb_engine *e, const double *queries, const fcb_filter *filters, int32_t batch,
@@ -657,15 +598,32 @@ extern "C" int32_t fcb_search_host(fcb_engine *e, const double *queries, const f
     cudaStream_t st = e->stream;
     FCB_CUDA(e, cudaMemcpyAsync(e->d_q, e->h_q, qn * sizeof(double), cudaMemcpyHostToDevice, st));
     FCB_CUDA(e, cudaEventRecord(e->ev0, st));
-    // results are laid out for THIS call's (batch, k) inside the one staging block: ids | scores | counts
+    // results are laid out for THIS call's (batch, k) inside the one staging block: ids | scores | counts | certificate flags
     uint64_t *d_ids = e->d_ids, *h_ids = e->h_ids;
     double *d_scores = reinterpret_cast<double *>(d_ids + rn), *h_scores = reinterpret_cast<double *>(h_ids + rn);
     int32_t *d_counts = reinterpret_cast<int32_t *>(d_scores + rn), *h_counts = reinterpret_cast<int32_t *>(h_scores + rn);
-    rc = search_device(e, e->d_q, filters, batch, k, d_ids, d_scores, d_counts, st);
+    int32_t *d_flags = d_counts + batch, *h_flags = h_counts + batch;
+    bool pending = false;
+    StagedFilters sf;
+    rc = search_device(e, e->d_q, filters, batch, k, d_ids, d_scores, d_counts, st, d_flags, true, &pending, &sf);
     if (rc != FCB_OK) return rc;
     FCB_CUDA(e, cudaEventRecord(e->ev1, st));
-    FCB_CUDA(e, cudaMemcpyAsync(h_ids, d_ids, rn * 16 + (size_t)batch * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    const size_t res_bytes = rn * 16 + (size_t)batch * sizeof(int32_t) * (pending ? 2 : 1);
+    FCB_CUDA(e, cudaMemcpyAsync(h_ids, d_ids, res_bytes, cudaMemcpyDeviceToHost, st));
     FCB_CUDA(e, cudaStreamSynchronize(st));
+    if (pending) {
+        // the fused scan could not certify some query (the flags came back with the results): answer those exactly
+        bool any = false;
+        for (int b = 0; b < batch; ++b) any = any || h_flags[b] != 0;
+        if (any) {
+            rc = fcb_exact_enqueue(e, e->d_q, sf.d_filters, sf.inl, sf.use_inline ? 1 : 0, batch, k, d_flags, d_ids, d_scores,
+                                   d_counts, st);
+            if (rc != FCB_OK) return rc;
+            FCB_CUDA(e, cudaEventRecord(e->ev1, st));
+            FCB_CUDA(e, cudaMemcpyAsync(h_ids, d_ids, rn * 16 + (size_t)batch * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+            FCB_CUDA(e, cudaStreamSynchronize(st));
+        }
+    }
     memcpy(out_ids, h_ids, rn * sizeof(uint64_t));
     memcpy(out_scores, h_scores, rn * sizeof(double));
     memcpy(out_counts, h_counts, (size_t)batch * sizeof(int32_t));

@@ -17,6 +17,7 @@
 // Segments that fit the candidate buffer whole (an ordinary tenant asked for "everything", the tool's
 // default call) skip steps 1-4: direct_rescore_kernel scores every passing row in float64 right away.
 #include "fcb_internal.cuh"
+#include "fcb_topk.cuh"
 
 #define SEL_THREADS 256
 #define SORT_CHUNK 1024                    // candidates sorted per CTA (bitonic, shared memory)
@@ -390,6 +391,39 @@ __global__ void __launch_bounds__(256) rank_merge_kernel(const FcbSelectState *s
     if (rank < (unsigned)k) { out_ids[rank] = mi; out_scores[rank] = ms; }
 }
 
+// Certificate of the select path (after the results are written): the K' selected rows are the K' best by float32 key,
+// so a row that was NOT selected has a first-pass score <= the selection threshold's; its canonical score is therefore at
+// most thr / |q| + eps (fcb_first_pass_eps). If the exact k-th score clears that, no dropped row belongs to the top k.
+// Otherwise the flag is set and the exact float64 path (fcb_exact.cu), enqueued right behind, answers the query again.
+__global__ void __launch_bounds__(SEL_THREADS) general_cert_kernel(const FcbSelectState *st, unsigned kprime, const double *__restrict__ q,
+                                                                   int dim, double eps, const double *__restrict__ out_scores,
+                                                                   const int32_t *__restrict__ out_count, int32_t *__restrict__ flag) {
+    __shared__ unsigned s_scan[256], s_out[3];
+    __shared__ double s_qq;
+    uint64_t thr;
+    unsigned remaining;
+    bool settled;
+    resolve_state(st, 8, kprime, thr, remaining, settled, s_scan, s_out);
+    if (threadIdx.x < 32) {
+        const double qq = fcb_canon_qq_warp(q, dim, threadIdx.x);
+        if (threadIdx.x == 0) s_qq = qq;
+    }
+    __syncthreads();
+    if (threadIdx.x != 0) return;
+    int f = 0;
+    if (st->n_pass > kprime) {                                     // rows were dropped
+        uint32_t u = (uint32_t)(thr >> 32);                        // float32 score of the worst selected row (make_key's inverse)
+        u ^= (u >> 31) ? 0x80000000u : 0xffffffffu;
+        const float worst = __uint_as_float(u);
+        const double nq = __dsqrt_rn(s_qq);
+        const int cnt = *out_count;
+        const double kth = cnt > 0 ? out_scores[cnt - 1] : -INFINITY;
+        const bool domain = nq > 8.9e-16 && nq < 1.1e15 && isfinite(worst);
+        f = !(domain && kth > (double)worst / nq + eps);
+    }
+    *flag = f;
+}
+
 // A segment that fits the candidate buffer whole: predicate + canonical float64 score for every row, one warp each.
 // `fused` (at most 1024 rows): the CTA that finishes last also sorts the candidates, writes the results and leaves the
 // selection state zeroed — the whole query is this one launch.
@@ -504,7 +538,7 @@ int32_t fcb_search_general_small_batch(fcb_engine *e, const double *d_queries, c
 
 template <typename T>
 static int32_t general_impl(fcb_engine *e, const double *d_query, const fcb_filter &f, int32_t k, uint64_t *d_out_ids,
-                            double *d_out_scores, int32_t *d_out_count, cudaStream_t st) {
+                            double *d_out_scores, int32_t *d_out_count, int32_t *d_flag, cudaStream_t st) {
     const fcb_shard &s = e->shard;
     const unsigned kprime = (unsigned)kprime_for(k);
     int64_t lo = f.row_begin - s.row_base, hi = f.row_end - s.row_base;
@@ -569,13 +603,21 @@ static int32_t general_impl(fcb_engine *e, const double *d_query, const fcb_filt
         e->last_launches += 1;
     }
     FCB_CUDA(e, cudaGetLastError());
+    if (!direct && n > 0) {
+        // the select path ranked rows by float32 keys: certify, and let the exact path answer what cannot be certified
+        general_cert_kernel<<<1, SEL_THREADS, 0, st>>>(e->d_sel, kprime, d_query, s.dim, fcb_first_pass_eps(s.dim), d_out_scores,
+                                                       d_out_count, d_flag);
+        FCB_CUDA(e, cudaGetLastError());
+        e->last_launches += 1;
+        return fcb_exact_enqueue(e, d_query, nullptr, &f, 1, 1, k, d_flag, d_out_ids, d_out_scores, d_out_count, st);
+    }
     return FCB_OK;
 }
 
 int32_t fcb_search_general(fcb_engine *e, const double *d_query, const fcb_filter &f, int32_t k, uint64_t *d_out_ids,
-                           double *d_out_scores, int32_t *d_out_count, cudaStream_t st) {
+                           double *d_out_scores, int32_t *d_out_count, int32_t *d_flag, cudaStream_t st) {
     if (!e->d_keys) return fcb_fail(e, FCB_ERR_STATE, "fcb_search: general-k scratch missing (max_k <= %d at fcb_open?)", FCB_FUSED_MAX_K);
     if (e->shard.dtype == FCB_DTYPE_F32)
-        return general_impl<float>(e, d_query, f, k, d_out_ids, d_out_scores, d_out_count, st);
-    return general_impl<__nv_bfloat16>(e, d_query, f, k, d_out_ids, d_out_scores, d_out_count, st);
+        return general_impl<float>(e, d_query, f, k, d_out_ids, d_out_scores, d_out_count, d_flag, st);
+    return general_impl<__nv_bfloat16>(e, d_query, f, k, d_out_ids, d_out_scores, d_out_count, d_flag, st);
 }

@@ -173,6 +173,11 @@ class Engine:
         return int(self._lib.fcb_last_dense_redo(self._h, batch))
 
     @property
+    def exact_reruns(self) -> int:
+        """Queries since load_shard that a fast path could not certify and the exact float64 kernel answered."""
+        return int(self._lib.fcb_exact_reruns(self._h))
+
+    @property
     def last_search_launches(self) -> int:
         return int(self._lib.fcb_last_search_launches(self._h))
 

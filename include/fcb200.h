@@ -113,7 +113,12 @@ int32_t fcb_load_shard(fcb_engine *e, const fcb_shard *shard);
  *   out_counts   device [batch]      number of valid results (<= k)
  * Exact (every filtered-in row is scored); search_params (hnsw_ef / exact, :98-101) have no
  * counterpart because nothing is approximate. Order: score descending, ties by ascending id.
- * Asynchronous on `stream`. */
+ * Exact BY CONSTRUCTION: the fast kernels rank rows by a float32 (or tensor-core) first pass, re-score a bounded
+ * number of candidates in float64 and then CERTIFY the answer — the exact k-th score must clear the best score any
+ * dropped row could have, worst-case first-pass error included. A query that cannot be certified (more near-ties at
+ * the k-th score than the candidate margin holds, e.g. many duplicated transactions) is answered again, on the same
+ * stream and without a host round trip, by an all-float64 kernel (score every passing row canonically, radix-select
+ * the k-th, resolve ties by id). fcb_exact_reruns() counts those. Asynchronous on `stream`. */
 int32_t fcb_search(fcb_engine *e, const double *queries, const fcb_filter *filters, int32_t batch,
                    int32_t k, uint64_t *out_ids, double *out_scores, int32_t *out_counts,
                    void *stream);
@@ -173,6 +178,11 @@ int32_t fcb_debug_scan_timing(uint64_t *buf);
  * shape computes bit-identical results). Both 0: not measured (small shard, FCB_SCAN_TUNE=0 or FCB_SCAN_CFG set) — the
  * built-in table decides per call. Measurement aid; no counterpart in the reference. */
 int32_t fcb_scan_config(const fcb_engine *e, int32_t *r, int32_t *u);
+
+/* How many queries since fcb_load_shard the certificate of a fast path refused and the exact float64 kernel
+ * answered instead (see fcb_search); -1 without a shard. Synchronises the device. Measurement aid; no counterpart in
+ * the reference, whose local mode is brute force in float64 throughout. */
+int64_t fcb_exact_reruns(fcb_engine *e);
 
 /* Number of kernels the last fcb_search / fcb_search_host call launched. Measurement aid. */
 int32_t fcb_last_search_launches(const fcb_engine *e);

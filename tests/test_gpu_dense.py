@@ -1,6 +1,8 @@
 """Batched tensor-core path (tcgen05/TMEM/TMA; BASELINE config 3): many queries sharing one segment of a
-bf16 shard. First pass in bf16 on the tensor cores, canonical float64 rescore, certificate + exact
-re-run; results must equal the C oracle bit for bit (ids, float64 scores, counts)."""
+bf16 shard. First pass on the tensor cores (bf16 corpus x float16 query tile), canonical float64 rescore, a worst-case
+certificate + exact re-run; results must equal the C oracle bit for bit (ids, float64 scores, counts)."""
+import os
+
 import numpy as np
 import pytest
 
@@ -23,7 +25,7 @@ def run_case(spec, whale_rows, batches, k=10, date_frac=None, mutate=None, expec
     for B in batches:
         qs = np.stack([synth.query_vector(spec, 1000 + i) for i in range(B)])
         ids, sc, cnt = eng.search_host(qs, [make_filter(rb, re_, dlo, None)] * B, k)
-        assert eng.last_search_launches == 4          # pack + tcgen05 pass + finalize + (flag-gated) exact re-run
+        assert eng.last_search_launches == 5          # pack + tcgen05 pass + finalize + (flag-gated) scan re-run + (flag-gated) float64 path
         redo = eng.last_dense_redo(B)                 # queries the tensor-core pass could not certify
         assert (redo > 0) if expect_redo else (redo == 0), redo
         for b in range(B):
@@ -47,8 +49,8 @@ def test_dense_dim1536_with_shared_date_filter(built):
 
 
 def test_dense_uncertified_queries_fall_back_to_exact_scan(built):
-    """~200 rows within 1e-4 of the best score: the bf16-query first pass cannot certify the top-10,
-    so the flag-gated exact scan must produce the answer (and ties by id must hold)."""
+    """~200 copies of the best row (half of them one low bit away): neither the tensor-core pass nor the float32 scan
+    behind it can certify the top-10, so the flag-gated float64 kernel must produce the answer (ties by id must hold)."""
     from financial_chatbot_llm_b200 import synth
     from oracle import canon
     spec = synth.SynthSpec(n_rows=70000, dim=256, n_users=2, seed=53, whale_rows=69000)
@@ -81,3 +83,56 @@ def test_mixed_filters_use_the_grouped_scan(built):
         oi, os_ = canon.search(hc.bf16_bits, qs[b], 10, row_begin=int(hc.offsets[u]), row_end=int(hc.offsets[u + 1]))
         assert ids[b, :cnt[b]].tolist() == oi.tolist() and sc[b, :cnt[b]].tolist() == os_.tolist()
     eng.close()
+
+
+@pytest.mark.parametrize("qfmt", ["f16", "bf16"])
+def test_accumulator_error_is_inside_the_certificate_model(built, qfmt, monkeypatch):
+    """The certificate's worst-case margin rests on a MODEL of the tensor-core accumulation (csrc/fcb_dense.cu,
+    dense_finalize_kernel: eps_acc = (dim / 16) * 17 * 2^-23 relative to |x||h|). Dump the raw accumulators of the first
+    1024 rows and compare them with the exact float64 dot products of the same operands (the bf16 rows and the 16-bit
+    query tile, emulated bit for bit on the host): the measured error must sit inside the model, with room to spare.
+    Also proves that kind::f16 accepts a bf16 A operand with a float16 B operand."""
+    import torch
+    from financial_chatbot_llm_b200 import _lib, loader, synth
+    from financial_chatbot_llm_b200.engine import Engine, make_filter
+    monkeypatch.setenv("FCB_DENSE_QFMT", qfmt)
+    dim, B, R = 1536, 64, 1024
+    spec = synth.SynthSpec(n_rows=66600, dim=dim, n_users=3, seed=57, whale_rows=66000)
+    hc = synth.make_host_corpus(spec, bf16=True)
+    eng = Engine(device=0, max_batch=256, max_k=16)
+    loader.collection_from_host(hc, eng, bf16=True)
+    qs = np.stack([synth.query_vector(spec, 3000 + i) for i in range(B)])
+    dbg = torch.zeros((R, 256), dtype=torch.float32, device="cuda")
+    lib = _lib.load()
+    lib.fcb_debug_dense_dump(dbg.data_ptr(), R)
+    try:
+        eng.search_host(qs, [make_filter(0, 66000)] * B, 10)
+        torch.cuda.synchronize()
+    finally:
+        lib.fcb_debug_dense_dump(None, 0)
+    got = dbg.cpu().numpy()[:, :B].astype(np.float64)
+    if qfmt == "f16":
+        alpha = 256.0 / np.sqrt((qs * qs).sum(axis=1))
+        h = (qs * alpha[:, None]).astype(np.float32).astype(np.float16).astype(np.float64)
+    else:
+        h = synth.bf16_bits_to_f32(synth.f32_to_bf16_bits(qs.astype(np.float32))).reshape(B, dim).astype(np.float64)
+    x = hc.vectors[:R].astype(np.float64)
+    want = x @ h.T
+    scale = np.linalg.norm(x, axis=1)[:, None] * np.linalg.norm(h, axis=1)[None, :]
+    rel = np.abs(got - want) / scale
+    bound = (dim / 16) * 17 * 2.0 ** -23
+    print(f"qfmt={qfmt}: max accumulator error {rel.max():.3e} of |x||h| (model bound {bound:.3e})")
+    assert rel.max() < 0.1 * bound, "the accumulator is far less accurate than the certificate's model allows for"
+    assert eng.last_dense_redo(B) == 0
+    eng.close()
+
+
+def test_worst_case_and_statistical_margins_return_the_same_answer(built, monkeypatch):
+    """The worst-case certificate is the default; FCB_DENSE_RIGOROUS=0 keeps round 1's 8-sigma margin for A/B runs. Both
+    must return the oracle's answer on the same corpus (the margin only decides WHO computes it), and on this ordinary
+    corpus neither may need a re-run."""
+    from financial_chatbot_llm_b200 import synth
+    spec = synth.SynthSpec(n_rows=72000, dim=512, n_users=4, seed=58, whale_rows=70500)
+    for mode in ("1", "0"):
+        monkeypatch.setenv("FCB_DENSE_RIGOROUS", mode)
+        run_case(spec, 70500, (48,))
