@@ -5,7 +5,7 @@ parses a JSON string with pandas (:29), computes
 ``transactions.groupby(plot_config.group_by)[plot_config.y_axis].sum()`` for ``bar`` (:45) and
 ``pie`` (:52), and draws the result with matplotlib (:32-75). Only the group-by sum is on the hot
 path; the drawing is serial CPU work over a handful of groups and is out of
-scope (matplotlib is not installed here).
+scope: the tool-shaped entries here return the grouped series as a JSON data URI instead of a PNG.
 
 Three entry levels:
   * ``groupby_user_category_month``  — the bulk path: (user, category, UTC month) sums over the
@@ -29,7 +29,7 @@ from typing import Literal, Optional
 import numpy as np
 from pydantic import BaseModel, Field
 
-from .engine import Engine
+from .engine import Engine, aggregate_columns
 
 
 class PlotConfig(BaseModel):
@@ -89,19 +89,16 @@ def grouped_sum_json(transactions_json: str, group_by: str, y_axis: str, device:
     n = int(v.size)
     if n == 0:
         return pd.Series([], index=pd.Index([], name=group_by), name=y_axis, dtype=np.int64)
+    # the key column becomes the CSR segments, the value column the integer units: one engine-less call, no vectors
     dev = torch.device("cuda", device)
-    eng = Engine(device=device, max_batch=1, max_k=1)
-    try:
-        eng.load_shard(torch.zeros((n, 4), dtype=torch.float32, device=dev),
-                       dates=torch.zeros(n, dtype=torch.int32, device=dev),
-                       categories=torch.zeros(n, dtype=torch.uint8, device=dev),
-                       cents=torch.from_numpy(v[order]).to(dev), seg_offsets=torch.from_numpy(offsets).to(dev))
-        sums, present, dropped = eng.aggregate(0, len(uniq), 0, 1, 1)
-        torch.cuda.synchronize(dev)
-        assert int(dropped.item()) == 0 and bool(present.all())
-        out = sums.view(-1).cpu().numpy()
-    finally:
-        eng.close()
+    zeros_i = torch.zeros(n, dtype=torch.int32, device=dev)               # one month, one category: the window is 1 x 1
+    zeros_b = torch.zeros(n, dtype=torch.uint8, device=dev)
+    sums, present, dropped = aggregate_columns(device, zeros_i, zeros_b, torch.from_numpy(v[order]).to(dev),
+                                               torch.from_numpy(offsets).to(dev), 0, len(uniq), 0, 1, 1)
+    torch.cuda.synchronize(dev)
+    if int(dropped.item()) != 0 or not bool(present.all()):
+        raise RuntimeError("fcb_aggregate_columns dropped rows of a 1 x 1 window")
+    out = sums.view(-1).cpu().numpy()
     data = out if scale == 1 else out.astype(np.float64) / scale
     return pd.Series(data, index=pd.Index(uniq, name=group_by), name=y_axis)
 
@@ -154,45 +151,42 @@ def grouped_sum_retrieved(collection, query, query_filter, limit: int, group_by,
     sums, present, stats = sums[0].cpu().numpy(), present[0].cpu().numpy().astype(bool), stats.cpu().numpy()
     if int(stats[0]):
         raise ValueError(f"{int(stats[0])} retrieved rows fall outside the category/month window")
+    # fold the observed (category, month) cells along the key that is not grouped on — exact integer arithmetic in numpy,
+    # observed groups only, keys ascending: what pandas' groupby(...).sum() yields for the retrieved payloads
     code_name = {c: n for n, c in collection.category_codes.items()}
-    rows = []                                                # (key tuple, cents) of the observed cells
-    for c, m in zip(*np.nonzero(present)):
-        rows.append(({"category": code_name.get(int(c), int(c)), "month": month_label(month_lo + int(m))}, int(sums[c, m])))
-    frame = pd.DataFrame([{**kv, y_axis: v} for kv, v in rows], columns=["category", "month", y_axis])
-    frame[y_axis] = frame[y_axis].astype(np.int64)
-    out = frame.groupby(keys if len(keys) > 1 else keys[0])[y_axis].sum()    # folds the cells of the key not grouped on
+    cc, mm = np.nonzero(present)
+    cat_labels = np.array([code_name.get(int(c), int(c)) for c in range(sums.shape[0])], dtype=object)
+    month_labels = np.array([month_label(month_lo + m) for m in range(sums.shape[1])], dtype=object)
+    if len(keys) == 2:
+        tuples = [(cat_labels[c], month_labels[m]) if keys[0] == "category" else (month_labels[m], cat_labels[c]) for c, m in zip(cc, mm)]
+        order = sorted(range(len(tuples)), key=lambda i: tuples[i])
+        index = pd.MultiIndex.from_tuples([tuples[i] for i in order], names=keys)
+        data = np.array([int(sums[cc[i], mm[i]]) for i in order], dtype=np.int64)
+    else:
+        axis = 1 if keys[0] == "category" else 0                          # sum over the OTHER key
+        seen = present.any(axis=axis)
+        labels = (cat_labels if keys[0] == "category" else month_labels)[seen]
+        totals = np.where(present, sums, 0).sum(axis=axis, dtype=np.int64)[seen]
+        order = np.argsort(labels.astype(str), kind="stable")
+        index = pd.Index(labels[order], name=keys[0])
+        data = totals[order]
+    out = pd.Series(data, index=index, name=y_axis, dtype=np.int64)
     return out if y_axis == "amount_cents" else out.astype(np.float64) / 100.0
 
 
 def _render(grouped, plot_config: PlotConfig) -> str:
-    """The drawing half of tools/plot_tool.py:43-75 for an already grouped series (a JSON data URI when
-    matplotlib is not importable)."""
-    try:
-        import matplotlib
-        matplotlib.use("Agg")
-        import matplotlib.pyplot as plt
-    except ImportError:
-        body = json.dumps({"title": plot_config.title, "plot_type": plot_config.plot_type,
-                           "labels": [str(x) for x in grouped.index.tolist()],
-                           "values": [float(x) for x in grouped.tolist()]})
-        return "data:application/json;base64," + base64.b64encode(body.encode()).decode()
-    plt.figure(figsize=(10, 6))
-    if plot_config.plot_type == "bar":
-        grouped.plot(kind="bar")
-    else:
-        plt.pie(grouped, labels=grouped.index.astype(str).tolist(), autopct="%1.1f%%")
-    plt.title(plot_config.title)
-    plt.tight_layout()
-    buf = io.BytesIO()
-    plt.savefig(buf, format="png")
-    plt.close()
-    return "data:image/png;base64," + base64.b64encode(buf.getvalue()).decode("utf-8")
+    """What stands in for the drawing half of tools/plot_tool.py:43-75: the grouped series as a JSON data URI (title,
+    plot type, labels, values). Rendering a figure is out of scope."""
+    body = json.dumps({"title": plot_config.title, "plot_type": plot_config.plot_type,
+                       "labels": [str(x) for x in grouped.index.tolist()],
+                       "values": [float(x) for x in grouped.tolist()]})
+    return "data:application/json;base64," + base64.b64encode(body.encode()).decode()
 
 
 def create_financial_plot(transactions_json: str, plot_config: PlotConfig) -> str:
     """Tool-shaped entry (reference tools/plot_tool.py:16-78) for the aggregating plot types.
-    The group-by runs on the GPU; the figure itself is drawn only when matplotlib is importable,
-    otherwise the grouped series is returned as a JSON data URI. Errors come back as the
+    The group-by runs on the GPU; the grouped series comes back as a JSON data URI (no figure is drawn: out of
+    scope). Errors come back as the
     reference's ``"Error creating plot: ..."`` string (:77-78)."""
     try:
         if plot_config.plot_type in ("bar", "pie") and plot_config.group_by and plot_config.y_axis:

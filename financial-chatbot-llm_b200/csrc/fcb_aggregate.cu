@@ -558,24 +558,24 @@ int32_t fcb_check_dates_sorted(fcb_engine *e) {
     return FCB_OK;
 }
 
-extern "C" int32_t fcb_aggregate(fcb_engine *e, int64_t seg_begin, int64_t seg_end, int32_t month_lo, int32_t n_months,
-                                 int32_t n_categories, int64_t *sums, uint8_t *present, uint64_t *dropped, void *stream) {
-    if (!e) return FCB_ERR_INVALID;
-    if (!e->loaded) return fcb_fail(e, FCB_ERR_STATE, "fcb_aggregate: no shard loaded");
-    const fcb_shard &s = e->shard;
-    if (!s.dates || !s.categories || !s.cents || !s.seg_offsets)
-        return fcb_fail(e, FCB_ERR_STATE, "fcb_aggregate: the shard needs dates, categories, cents and seg_offsets");
+// Validates the window, zeroes the outputs and launches the kernel(s) for one shard's columns. `e` may be NULL (the
+// engine-less entry point): errors then land in the per-thread message fcb_last_error(NULL) returns.
+static int32_t agg_launch(fcb_engine *e, int device, int num_sms, int dates_sorted, const int32_t *dates, const uint8_t *cats,
+                          const int32_t *cents, const int64_t *seg_offsets, int64_t n_rows, int64_t n_segs, int64_t row_base,
+                          int64_t seg_begin, int64_t seg_end, int32_t month_lo, int32_t n_months, int32_t n_categories,
+                          int64_t *sums, uint8_t *present, uint64_t *dropped, cudaStream_t st) {
+    if (!dates || !cats || !cents || !seg_offsets)
+        return fcb_fail(e, FCB_ERR_STATE, "fcb_aggregate: needs the dates, categories, cents and seg_offsets columns");
     if (!sums || !present || !dropped) return fcb_fail(e, FCB_ERR_INVALID, "fcb_aggregate: NULL output");
-    if (seg_begin < 0 || seg_end > s.n_segs || seg_begin > seg_end)
+    if (seg_begin < 0 || seg_end > n_segs || seg_begin > seg_end)
         return fcb_fail(e, FCB_ERR_INVALID, "fcb_aggregate: segment range [%lld, %lld) outside 0..%lld",
-                        (long long)seg_begin, (long long)seg_end, (long long)s.n_segs);
+                        (long long)seg_begin, (long long)seg_end, (long long)n_segs);
     if (n_months < 1 || n_months > AGG_MAX_MONTHS || n_categories < 1 || n_categories > 64 ||
         (int64_t)n_months * n_categories > AGG_MAX_CELLS)
         return fcb_fail(e, FCB_ERR_UNSUPPORTED, "fcb_aggregate: need 1..%d months, 1..64 categories, <= %d cells per user",
                         AGG_MAX_MONTHS, AGG_MAX_CELLS);
-    FcbDeviceGuard g(e->device);
-    if (!g.ok) return fcb_fail(e, FCB_ERR_CUDA, "fcb_aggregate: cannot select device %d", e->device);
-    cudaStream_t st = (cudaStream_t)stream;
+    FcbDeviceGuard g(device);
+    if (!g.ok) return fcb_fail(e, FCB_ERR_CUDA, "fcb_aggregate: cannot select device %d", device);
     const int64_t segs = seg_end - seg_begin;
     const int C = n_months * n_categories;
     FCB_CUDA(e, cudaMemsetAsync(sums, 0, (size_t)segs * C * sizeof(int64_t), st));
@@ -584,8 +584,8 @@ extern "C" int32_t fcb_aggregate(fcb_engine *e, int64_t seg_begin, int64_t seg_e
     if (segs == 0) return FCB_OK;
 
     AggParams p{};
-    p.seg_offsets = s.seg_offsets; p.dates = s.dates; p.cats = s.categories; p.cents = s.cents;
-    p.seg_begin = seg_begin; p.seg_end = seg_end; p.row_base = s.row_base; p.n_rows = s.n_rows;
+    p.seg_offsets = seg_offsets; p.dates = dates; p.cats = cats; p.cents = cents;
+    p.seg_begin = seg_begin; p.seg_end = seg_end; p.row_base = row_base; p.n_rows = n_rows;
     p.month_lo = month_lo; p.n_months = n_months; p.n_categories = n_categories;
     p.day0 = first_day_of_month(month_lo);
     p.n_days = first_day_of_month(month_lo + n_months) - p.day0;
@@ -597,38 +597,62 @@ extern "C" int32_t fcb_aggregate(fcb_engine *e, int64_t seg_begin, int64_t seg_e
         FCB_CUDA(e, cudaFuncSetAttribute(aggregate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const char *force = getenv("FCB_AGG_KERNEL");                   // tuning: "atomic" / "sorted"
     const bool sorted_ok = n_categories <= 32;
-    const bool use_sorted = sorted_ok && (force ? force[0] == 's' : e->dates_sorted != 0);
+    const bool use_sorted = sorted_ok && (force ? force[0] == 's' : dates_sorted != 0);
     // any-order data whose table fits the warp's bin matrix: users below AGS_TABLE_USER rows go to the ordered kernel's
     // warp-table path (order-agnostic, 4-6 ns per 1000 rows; the atomic kernel handles them CTA-wide at 7-12 ns), the rest
     // to the atomic kernel; the two launches touch disjoint users
     const char *split_knob = getenv("FCB_AGG_SPLIT");
     const bool split = !use_sorted && sorted_ok && C * 9 <= n_categories * 32 * 8 && !(split_knob && split_knob[0] == '0') &&
                        !(force && force[0] == 'a');
-    const size_t smem_s_all = (((size_t)p.n_days * 2 + 15) & ~(size_t)15) + (((size_t)(n_months + 1) * 4 + 15) & ~(size_t)15) +
-                              (size_t)(AGG_THREADS / 32) * n_categories * 32 * 8 +
-                              (size_t)(AGG_THREADS / 32) * (AGS_AHEAD + 1) * AGS_SLOT_BYTES;
+    const size_t smem_s = (((size_t)p.n_days * 2 + 15) & ~(size_t)15) + (((size_t)(n_months + 1) * 4 + 15) & ~(size_t)15) +
+                          (size_t)(AGG_THREADS / 32) * n_categories * 32 * 8 +
+                          (size_t)(AGG_THREADS / 32) * (AGS_AHEAD + 1) * AGS_SLOT_BYTES;
+    if ((split || use_sorted) && smem_s > 48 * 1024)
+        FCB_CUDA(e, cudaFuncSetAttribute(aggregate_sorted_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_s));
     if (split) {
-        if (smem_s_all > 48 * 1024)
-            FCB_CUDA(e, cudaFuncSetAttribute(aggregate_sorted_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_s_all));
         p.split = 2;
-        aggregate_sorted_kernel<<<e->num_sms * AGS_CTAS, AGG_THREADS, smem_s_all, st>>>(p);
+        aggregate_sorted_kernel<<<num_sms * AGS_CTAS, AGG_THREADS, smem_s, st>>>(p);
         p.split = 1;
-        aggregate_kernel<<<e->num_sms * 4, AGG_THREADS, smem, st>>>(p);
-        FCB_CUDA(e, cudaGetLastError());
-        return FCB_OK;
-    }
-    if (use_sorted) {
-        const size_t smem_s = (((size_t)p.n_days * 2 + 15) & ~(size_t)15) + (((size_t)(n_months + 1) * 4 + 15) & ~(size_t)15) +
-                              (size_t)(AGG_THREADS / 32) * n_categories * 32 * 8 +
-                              (size_t)(AGG_THREADS / 32) * (AGS_AHEAD + 1) * AGS_SLOT_BYTES;
-        if (smem_s > 48 * 1024)
-            FCB_CUDA(e, cudaFuncSetAttribute(aggregate_sorted_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_s));
-        aggregate_sorted_kernel<<<e->num_sms * AGS_CTAS, AGG_THREADS, smem_s, st>>>(p);
+        aggregate_kernel<<<num_sms * 4, AGG_THREADS, smem, st>>>(p);
+    } else if (use_sorted) {
+        aggregate_sorted_kernel<<<num_sms * AGS_CTAS, AGG_THREADS, smem_s, st>>>(p);
     } else {
-        aggregate_kernel<<<e->num_sms * 4, AGG_THREADS, smem, st>>>(p);
+        aggregate_kernel<<<num_sms * 4, AGG_THREADS, smem, st>>>(p);
     }
     FCB_CUDA(e, cudaGetLastError());
     return FCB_OK;
+}
+
+extern "C" int32_t fcb_aggregate(fcb_engine *e, int64_t seg_begin, int64_t seg_end, int32_t month_lo, int32_t n_months,
+                                 int32_t n_categories, int64_t *sums, uint8_t *present, uint64_t *dropped, void *stream) {
+    if (!e) return FCB_ERR_INVALID;
+    if (!e->loaded) return fcb_fail(e, FCB_ERR_STATE, "fcb_aggregate: no shard loaded");
+    const fcb_shard &s = e->shard;
+    return agg_launch(e, e->device, e->num_sms, e->dates_sorted, s.dates, s.categories, s.cents, s.seg_offsets, s.n_rows, s.n_segs,
+                      s.row_base, seg_begin, seg_end, month_lo, n_months, n_categories, sums, present, dropped, (cudaStream_t)stream);
+}
+
+// The same group-by over caller-owned device columns, without an engine: no vectors, no inverse norms, nothing allocated.
+extern "C" int32_t fcb_aggregate_columns(int32_t device, const int32_t *dates, const uint8_t *categories, const int32_t *cents,
+                                         const int64_t *seg_offsets, int64_t n_rows, int64_t n_segs, int64_t row_base,
+                                         int32_t dates_sorted, int64_t seg_begin, int64_t seg_end, int32_t month_lo,
+                                         int32_t n_months, int32_t n_categories, int64_t *sums, uint8_t *present,
+                                         uint64_t *dropped, void *stream) {
+    if (n_rows < 0 || n_segs < 0 || row_base < 0)
+        return fcb_fail(nullptr, FCB_ERR_INVALID, "fcb_aggregate_columns: negative n_rows / n_segs / row_base");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev)
+        return fcb_fail(nullptr, FCB_ERR_CUDA, "fcb_aggregate_columns: no CUDA device %d (this library has no CPU path)", device);
+    static int sms[64];                                            // SM count per device, looked up once
+    if (device < 64 && sms[device] == 0) {
+        int v = 0;
+        if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, device) != cudaSuccess || v <= 0)
+            return fcb_fail(nullptr, FCB_ERR_CUDA, "fcb_aggregate_columns: cannot query device %d", device);
+        sms[device] = v;
+    }
+    return agg_launch(nullptr, device, device < 64 ? sms[device] : 148, dates_sorted, dates, categories, cents, seg_offsets, n_rows,
+                      n_segs, row_base, seg_begin, seg_end, month_lo, n_months, n_categories, sums, present, dropped,
+                      (cudaStream_t)stream);
 }
 
 // ---- group-by over the points a search just returned ------------------------------

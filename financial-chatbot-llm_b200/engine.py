@@ -182,6 +182,31 @@ class Engine:
         return int(self._lib.fcb_last_search_launches(self._h))
 
 
+def aggregate_columns(device: int, dates, categories, cents, seg_offsets, seg_begin: int, seg_end: int, month_lo: int,
+                      n_months: int, n_categories: int, sums=None, present=None, dropped=None, *, row_base: int = 0,
+                      dates_sorted: bool = False, stream: Optional[int] = None):
+    """fcb_aggregate_columns: the (user, category, month) integer-cents group-by over caller-owned CUDA columns, without an
+    engine (no vectors, nothing allocated inside the library). Returns (sums int64 [S, C, M], present uint8 [S, C, M],
+    dropped int64 [1]); asynchronous on torch's current stream."""
+    import torch
+    lib = _lib.load()
+    dev = torch.device("cuda", device)
+    S = seg_end - seg_begin
+    if sums is None:
+        sums = torch.empty((S, n_categories, n_months), dtype=torch.int64, device=dev)
+    if present is None:
+        present = torch.empty((S, n_categories, n_months), dtype=torch.uint8, device=dev)
+    if dropped is None:
+        dropped = torch.empty(1, dtype=torch.int64, device=dev)
+    if stream is None:
+        stream = torch.cuda.current_stream(device).cuda_stream
+    check(lib.fcb_aggregate_columns(device, dates.data_ptr(), categories.data_ptr(), cents.data_ptr(), seg_offsets.data_ptr(),
+                                    cents.numel(), seg_offsets.numel() - 1, row_base, 1 if dates_sorted else 0, seg_begin, seg_end,
+                                    month_lo, n_months, n_categories, sums.data_ptr(), present.data_ptr(), dropped.data_ptr(),
+                                    C.c_void_p(stream)))
+    return sums, present, dropped
+
+
 def synth_vectors(out, row_lo: int, seed: int, n_clusters: int) -> None:
     """Fill CUDA tensor ``out`` [n, dim] (float32/bfloat16) with rows row_lo.. of the synthetic corpus."""
     import torch

@@ -203,6 +203,19 @@ int32_t fcb_aggregate(fcb_engine *e, int64_t seg_begin, int64_t seg_end, int32_t
                       int32_t n_months, int32_t n_categories, int64_t *sums, uint8_t *present,
                       uint64_t *dropped, void *stream);
 
+/* The same group-by over caller-owned device columns, without an engine (nothing is allocated, no vectors are needed):
+ * what the tool-shaped path uses for the rows of ONE transactions_json (tools/plot_tool.py:29,45,52 — one key column that
+ * becomes the CSR segments, one value column) and what a caller holding only the payload columns uses at scale.
+ *   dates / categories / cents   device [n_rows] as in fcb_shard; seg_offsets device [n_segs + 1] global CSR offsets
+ *   row_base                     global row number of the columns' first row
+ *   dates_sorted                 1 if the dates are non-decreasing within every user (selects the atomic-free kernel;
+ *                                the result is the same either way), else 0
+ * Other arguments and outputs as for fcb_aggregate. Errors: fcb_last_error(NULL). Asynchronous on `stream`. */
+int32_t fcb_aggregate_columns(int32_t device, const int32_t *dates, const uint8_t *categories, const int32_t *cents,
+                              const int64_t *seg_offsets, int64_t n_rows, int64_t n_segs, int64_t row_base,
+                              int32_t dates_sorted, int64_t seg_begin, int64_t seg_end, int32_t month_lo, int32_t n_months,
+                              int32_t n_categories, int64_t *sums, uint8_t *present, uint64_t *dropped, void *stream);
+
 /* Group-by over the points a search just returned: the reference's agent feeds the
  * output of retrieve_transactions (tools/qdrant_tool.py:147-170) back through JSON into
  * transactions.groupby(...)[...].sum() (tools/plot_tool.py:29,45,52); here the ids fcb_search wrote stay on
