@@ -360,8 +360,8 @@ def extra_cfg5(dev, steps):
 
 # ------------------------------------------------------------------------------------------ cfg4 (N > 1)
 def bench_cfg4(dev, world, rank, steps):
-    from financial_chatbot_llm_b200 import cfg4
-    return cfg4.run(dev, world, rank, steps, timed_steps)
+    import bench_cfg4
+    return bench_cfg4.run(dev, world, rank, steps, timed_steps)
 
 
 # ------------------------------------------------------------------------------------------ B200 arm

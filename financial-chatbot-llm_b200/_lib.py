@@ -42,6 +42,14 @@ class FcbFilter(C.Structure):
                 ("category_mask", C.c_uint64)]
 
 
+FCB_MAX_WORLD = 8
+FCB_PEER_HANDLE_BYTES = 64
+
+
+class FcbExchange(C.Structure):
+    _fields_ = [("world", C.c_int32), ("rank", C.c_int32), ("bufs", C.c_void_p * FCB_MAX_WORLD), ("cuts", C.c_void_p)]
+
+
 class FcbError(RuntimeError):
     def __init__(self, code: int, message: str):
         super().__init__(f"fcb200 error {code}: {message}")
@@ -69,7 +77,14 @@ SIGNATURES = {
     "fcb_debug_dense_prof": (C.c_int32, [C.c_void_p]),
     "fcb_debug_dense_dump": (C.c_int32, [C.c_void_p, C.c_int64]),
     "fcb_last_dense_redo": (C.c_int32, [C.c_void_p, C.c_int32]),
+    "fcb_last_dense_widened": (C.c_int32, [C.c_void_p, C.c_int32]),
     "fcb_exact_reruns": (C.c_int64, [C.c_void_p]),
+    "fcb_exchange_bytes": (C.c_int64, [C.c_int32, C.c_int32]),
+    "fcb_peer_alloc": (C.c_int32, [C.c_int32, C.c_int64, C.POINTER(C.c_void_p), C.c_void_p]),
+    "fcb_peer_open": (C.c_int32, [C.c_int32, C.c_void_p, C.POINTER(C.c_void_p)]),
+    "fcb_peer_close": (C.c_int32, [C.c_int32, C.c_void_p, C.c_int32]),
+    "fcb_search_routed": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_uint32,
+                                      C.c_void_p, C.c_void_p]),
     "fcb_aggregate": (C.c_int32, [C.c_void_p, C.c_int64, C.c_int64, C.c_int32, C.c_int32, C.c_int32,
                                   C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "fcb_aggregate_columns": (C.c_int32, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64,

@@ -27,8 +27,6 @@
 #include <cuda.h>
 #include <stdlib.h>
 
-#include <cuda_fp16.h>
-
 #include "fcb_internal.cuh"
 #include "fcb_topk.cuh"
 
@@ -61,7 +59,8 @@ struct DenseParams {
     float *debug_out;                       // diagnostic: raw accumulators [debug_rows, DN_N] (NULL in production)
     int64_t debug_rows;
     long long *prof;                        // diagnostic: per-role cycle counters of CTA 0 (NULL in production)
-    int q_is_bf16;                          // format of the packed query tile: 1 = bfloat16, 0 = float16 (8x finer rounding)
+    const float *slack;                     // [DN_N] how far below the cross-CTA bound a row may lie and still be listed (first-pass units)
+    float *thr_out;                         // [DN_N][gt_stride] final pruning threshold of every CTA and query: no unlisted row scores above it
     int n_stages;                           // cta_group::2 kernel: depth of the shared-memory ring (3 or 4)
     unsigned *gtop;                         // [DN_N][gt_stride] best score of every CTA's list, order-preserving uint (cta_group::2 kernel)
     int gt_stride;
@@ -137,11 +136,11 @@ __device__ __forceinline__ uint64_t make_sw128_desc(uint32_t smem_addr) {
     return (uint64_t)((smem_addr & 0x3FFFF) >> 4) | ((uint64_t)1 << 16) | ((uint64_t)(1024 >> 4) << 32) |
            ((uint64_t)1 << 46) | ((uint64_t)2 << 61);
 }
-// instruction descriptor (cute::UMMA::InstrDescriptor): c_format F32 (1) [4,6), a_format [7,10) = BF16 (1: the corpus),
-// b_format [10,13) = F16 (0) or BF16 (1) for the query tile (kind::f16 takes the two operand formats independently),
-// both K-major, N>>3 [17,23), M>>4 [24,29)
-__device__ __forceinline__ constexpr uint32_t make_idesc(int M, int N, int b_is_bf16) {
-    return (1u << 4) | (1u << 7) | ((uint32_t)(b_is_bf16 ? 1 : 0) << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+// instruction descriptor (cute::UMMA::InstrDescriptor): c_format F32 (1) [4,6), a/b format BF16 (1)
+// [7,10) / [10,13), both K-major, N>>3 [17,23), M>>4 [24,29). (A bf16 A operand with a float16 B operand — 8x finer
+// rounding of the query tile — was tried: kind::f16 traps with "illegal instruction" when the two formats differ.)
+__device__ __forceinline__ constexpr uint32_t make_idesc_bf16(int M, int N) {
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
 
 // order-preserving float <-> uint (larger float = larger uint), for atomicMax on scores of either sign
@@ -222,7 +221,7 @@ dense_topk_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
     } else if (warp == 1) {
         // ================= MMA issuer =================
         if (lane == 0) {
-            const uint32_t idesc = make_idesc(DN_BLOCK_M, p.n_eff, p.q_is_bf16);
+            const uint32_t idesc = make_idesc_bf16(DN_BLOCK_M, p.n_eff);
             int stage = 0;
             uint32_t phase = 0;
             int it = 0;
@@ -318,6 +317,7 @@ dense_topk_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_consta
         }
     }
     __syncthreads();
+    for (int q = tid; q < p.n_queries; q += DN_THREADS) p.thr_out[(size_t)q * p.gt_stride + blockIdx.x] = thr_s[q];
     if (warp == 2) {
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(DN_TMEM_COLS) : "memory");
     }
@@ -457,7 +457,7 @@ dense_topk2_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
     } else if (warp == 1) {
         // ================= MMA issuer (leader CTA only) =================
         if (leader && lane == 0) {
-            const uint32_t idesc = make_idesc(2 * DN_BLOCK_M, p.n_eff, p.q_is_bf16);
+            const uint32_t idesc = make_idesc_bf16(2 * DN_BLOCK_M, p.n_eff);
             int stage = 0;
             uint32_t phase = 0;
             int it = 0;
@@ -525,7 +525,10 @@ dense_topk2_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
                     unsigned v = m[u];
 #pragma unroll
                     for (int off = 16; off >= 1; off >>= 1) v = min(v, __shfl_xor_sync(FCB_FULL, v, off));
-                    if (lane == 0 && q0 + u < p.n_queries && v > dn_ord(-INFINITY)) gb_s[q0 + u] = dn_unord(v - 1);
+                    // ... and lowered by the query's slack (twice the worst-case first-pass error, dense_pack_queries_kernel):
+                    // every row that could still belong to the exact top k then stays listed, and dense_finalize_kernel
+                    // re-scores all of those instead of giving the query up
+                    if (lane == 0 && q0 + u < p.n_queries && v > dn_ord(-INFINITY)) gb_s[q0 + u] = dn_unord(v - 1) - p.slack[q0 + u];
                 }
             }
         }
@@ -684,45 +687,66 @@ dense_topk2_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     for (int i = tid; i < p.n_eff * FCB_FUSED_CAND; i += DN2_THREADS) my_top[i] = top_s[i];   // hand the lists to dense_finalize_kernel
+    for (int q = tid; q < p.n_queries; q += DN2_THREADS) p.thr_out[(size_t)q * p.gt_stride + blockIdx.x] = thr_s[q];   // ... and the final thresholds
     cluster_sync_all();                                                // nobody still targets the peer's barriers / TMEM
     if (warp == 2) {
         asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(DN_TMEM_COLS) : "memory");
     }
 }
 
-// float64 queries -> the 16-bit query tile [DN_N, dim] of the tensor-core pass, rows >= batch zero. One CTA per row.
-// float16 (default): h = fl16(alpha q) with alpha = 256 / |q| — unit-norm components of a 1536-vector sit around
-// 0.025, so alpha puts them near 6: far from float16's subnormals (6e-5) and its maximum (65504); the 11-bit
-// significand rounds 8x finer than bfloat16's 8 bits. bfloat16: h = bf16(q), alpha = 1. The first-pass scores are in
-// "h units" either way (the kernel only compares them with each other); dense_finalize_kernel divides by alpha |q| and
-// measures the rounding error |h / alpha - q| / |q| from the stored tile itself.
+// Worst-case distance, in cosine units, between a first-pass score of the tensor-core pass and the row's canonical float64
+// score. First-pass score of a row x: a = fl32(acc * inv32), acc = the accumulator of x . h, h = bf16(q).
+//   rho      = |h - q| / |q|             rounding of the query tile: |(h - q) . x| / (|x||q|) <= rho for ANY row (Cauchy-Schwarz);
+//                                        measured from the tile itself, ~1.1e-3
+//   eps_acc  = (dim / 16) * 17 * 2^-23   the accumulator: every UMMA K-step adds 16 exact products (8 x 8 significand bits) to it;
+//                                        the model is one truncation to 24 significant bits, relative to the largest addend
+//                                        (itself <= |x||h|), per addend and step: 2.0e-4 at dim 1536.
+//                                        tests/test_gpu_dense.py measures the real error against this bound (~100x smaller).
+//   eps_inv  = (n / 2 + 8) * 2^-24       the float32 inverse norm (sum of squares of n = dim/32 + 8 steps, rsqrtf) and the product
+__host__ __device__ inline double dense_margin(double rho, int dim) {
+    const double n_chain = (double)(dim / 32 + 8);
+    const double eps_acc = (double)(dim / 16) * 17.0 * 1.1920928955078125e-7 * (1.0 + rho);
+    const double eps_inv = (0.5 * n_chain + 8.0) * 5.9604644775390625e-8;
+    return rho * (1.0 + 1e-9) + eps_acc + eps_inv + 1e-12;
+}
+
+// float64 queries -> the bf16 query tile [DN_N, dim] of the tensor-core pass (rows >= batch zero), one CTA per row; plus
+// each query's SLACK in first-pass units (cosine x |q|): twice the worst-case first-pass error. The kernel lists every row
+// whose first-pass score is within the slack of its cross-CTA pruning bound, so that dense_finalize_kernel finds every row
+// that could still belong to the exact top k among the listed ones.
 __global__ void __launch_bounds__(256) dense_pack_queries_kernel(const double *__restrict__ q, int batch, int dim,
-                                                                 uint16_t *__restrict__ out, double *__restrict__ alpha_out,
-                                                                 int q_is_bf16) {
-    __shared__ double s_part[8];
+                                                                 __nv_bfloat16 *__restrict__ out, float *__restrict__ slack) {
+    __shared__ double s_qq[8], s_ee[8];
     const int b = blockIdx.x, tid = threadIdx.x;
-    uint16_t *row = out + (size_t)b * dim;
+    __nv_bfloat16 *row = out + (size_t)b * dim;
     if (b >= batch) {
-        for (int j = tid; j < dim; j += 256) row[j] = 0;
+        for (int j = tid; j < dim; j += 256) row[j] = __float2bfloat16_rn(0.f);
+        if (tid == 0) slack[b] = 0.f;
         return;
     }
     const double *qb = q + (size_t)b * dim;
-    double alpha = 1.0;
-    if (!q_is_bf16) {
-        double ss = 0.0;
-        for (int j = tid; j < dim; j += 256) ss = fma(qb[j], qb[j], ss);
-#pragma unroll
-        for (int off = 16; off >= 1; off >>= 1) ss += __shfl_xor_sync(FCB_FULL, ss, off);
-        if ((tid & 31) == 0) s_part[tid >> 5] = ss;
-        __syncthreads();
-        double tot = 0.0;
-        for (int w = 0; w < 8; ++w) tot += s_part[w];
-        alpha = tot > 0.0 ? 256.0 / sqrt(tot) : 0.0;
-    }
-    if (tid == 0) alpha_out[b] = alpha;
+    double qq = 0.0, ee = 0.0;
     for (int j = tid; j < dim; j += 256) {
-        const float v = (float)(qb[j] * alpha);
-        row[j] = q_is_bf16 ? __bfloat16_as_ushort(__float2bfloat16_rn(v)) : __half_as_ushort(__float2half_rn(v));
+        const double qv = qb[j];
+        const __nv_bfloat16 h = __float2bfloat16_rn((float)qv);
+        row[j] = h;
+        const double er = (double)__bfloat162float(h) - qv;
+        qq = fma(qv, qv, qq);
+        ee = fma(er, er, ee);
+    }
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) {
+        qq += __shfl_xor_sync(FCB_FULL, qq, off);
+        ee += __shfl_xor_sync(FCB_FULL, ee, off);
+    }
+    if ((tid & 31) == 0) { s_qq[tid >> 5] = qq; s_ee[tid >> 5] = ee; }
+    __syncthreads();
+    if (tid == 0) {
+        double tq = 0.0, te = 0.0;
+        for (int w = 0; w < 8; ++w) { tq += s_qq[w]; te += s_ee[w]; }
+        const double nq = sqrt(tq);
+        const double rho = nq > 0.0 ? sqrt(te) / nq : 0.0;
+        slack[b] = __double2float_ru(2.0 * dense_margin(rho, dim) * nq * 1.001);
     }
 }
 
@@ -732,24 +756,44 @@ struct DenseFinalParams {
     const uint32_t *id_rank;
     const double *queries;
     const FcbCand *cta_top;
+    const float *thr_out;                   // [DN_N][gt_stride] final pruning thresholds of the CTAs
+    int gt_stride;
     int n_lists;
     int64_t row_base;
     int dim, k;
     uint64_t *out_ids;
     double *out_scores;
     int32_t *out_counts;
-    int32_t *redo;                          // [batch]: 1 = not certified, re-run exactly
+    int32_t *redo;                          // [batch]: 1 = could not be answered exactly from the lists: re-run by the exact scan
     int32_t *redo_list, *redo_count;        // compact list of those queries for the re-run launch
+    int32_t *widened;                       // [batch]: 1 = answered by re-scoring more than the 32 best listed rows (measurement aid)
     int rigorous;                           // 1 (default): worst-case margin, 0: 8-sigma margin of the rounding model (A/B only)
-    const uint16_t *q_packed;               // the query tile the tensor-core pass used
-    const double *alpha;                    // [batch] its scale
-    int q_is_bf16;
 };
 
+#define DN_EXTRA_CAP 512                    // listed rows beyond the best 32 that one query may have re-scored
+
+// One CTA per query. EXACT BY CONSTRUCTION, with m = dense_margin (the worst-case first-pass error):
+//   1. the 32 best listed rows by first-pass score are re-scored canonically; E = the k-th best exact score among them.
+//      No row outside the true top k... rather: every row of the true top k scores >= E exactly, hence >= E - m in the
+//      first pass. Let W = E - m.
+//   2. If the worst of the 32 lies below W, the 32 hold every such row: done (the common case).
+//   3. Otherwise the candidates are ALL rows with a first-pass score >= W. A row that is not in any CTA's list was pruned
+//      by a threshold that CTA exported (thr_out): its first-pass score is <= U = the largest of them. If U < W, every
+//      candidate IS listed: re-score those beyond the first 32 too, rank all of them, write the k best. (The kernel keeps
+//      its cross-CTA bound 2 m below the 32nd best score it can prove, so U < W holds unless some CTA's own 32-deep list
+//      overflowed inside the window.)
+//   4. Else (or with more than DN_EXTRA_CAP candidates): the flag is set and the exact float32-query scan, itself certified
+//      and backed by the float64 kernel, answers the query.
 __global__ void __launch_bounds__(256) dense_finalize_kernel(const __grid_constant__ DenseFinalParams p) {
     __shared__ FcbCand m_s[8][FCB_FUSED_CAND];
     __shared__ double f_score[FCB_FUSED_CAND];
     __shared__ uint64_t f_id[FCB_FUSED_CAND];
+    __shared__ double x_score[DN_EXTRA_CAP];
+    __shared__ uint64_t x_id[DN_EXTRA_CAP];
+    __shared__ int s_mode;                  // 0: done, 1: widen (re-score every listed row >= s_window)
+    __shared__ float s_window;
+    __shared__ FcbCand s_worst;             // the worst of the 32 first-pass survivors
+    __shared__ unsigned s_extra;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int b = blockIdx.x;
     const __nv_bfloat16 *vec = reinterpret_cast<const __nv_bfloat16 *>(p.vectors);
@@ -769,33 +813,17 @@ __global__ void __launch_bounds__(256) dense_finalize_kernel(const __grid_consta
         }
         if (lane == 0) { f_score[c] = sc; f_id[c] = id; }
     }
+    if (tid == 0) { s_mode = 0; s_extra = 0; }
     __syncthreads();
     if (warp == 0) {
         double kth;
         int nvalid;
         fcb_rank_and_write(m_s[0], f_score, f_id, p.k, lane, p.out_ids + (size_t)b * p.k, p.out_scores + (size_t)b * p.k,
                            p.out_counts + b, kth, nvalid);
-        // Certificate. First-pass score of a row: a = fl32(acc * inv32) with acc the tensor-core accumulator of x . h
-        // (h = the 16-bit query tile, ~ alpha q). In cosine units, a / (alpha |q|) differs from the row's cosine by at most
-        //   rho      = |h / alpha - q| / |q|       rounding of the query tile, for ANY row (Cauchy-Schwarz); measured here
-        //                                          from the tile itself: ~1.4e-4 for float16, ~1.1e-3 for bfloat16
-        //   eps_acc  = (dim / 16) * 17 * 2^-23     the accumulator: every UMMA K-step adds 16 exact products to it; the
-        //                                          model is one truncation to 24 significant bits (relative to the largest
-        //                                          addend, itself <= |x||h|) per addend and step — 2.0e-4 at dim 1536.
-        //                                          tests/test_gpu_dense.py measures the real error against this bound.
-        //   eps_inv  = (n / 2 + 8) * 2^-24         inverse norm (float32 sum of squares, rsqrtf) and the final product
-        // A row that is not among the 32 survivors has a <= the worst kept one, so the answer is certified when the exact
-        // k-th score clears worst + margin (or fewer than 32 rows qualified). The legacy margin (FCB_DENSE_RIGOROUS=0, for
-        // A/B runs only) is 8 standard deviations of a statistical model of rho.
         double qq = 0.0, ee = 0.0;
-        const double alpha = p.alpha[b];
-        const double ialpha = alpha > 0.0 ? 1.0 / alpha : 0.0;
-        const uint16_t *hq = p.q_packed + (size_t)b * p.dim;
         for (int j = lane; j < p.dim; j += 32) {
             const double qv = qd[j];
-            const double hv = p.q_is_bf16 ? (double)__bfloat162float(__ushort_as_bfloat16(hq[j]))
-                                          : (double)__half2float(__ushort_as_half(hq[j]));
-            const double er = hv * ialpha - qv;
+            const double er = (double)__bfloat162float(__float2bfloat16_rn((float)qv)) - qv;
             qq = __fma_rn(qv, qv, qq);
             ee = __fma_rn(er, er, ee);
         }
@@ -806,19 +834,64 @@ __global__ void __launch_bounds__(256) dense_finalize_kernel(const __grid_consta
         }
         const double nq = sqrt(qq);
         const double rho = nq > 0.0 ? sqrt(ee) / nq : 1.0;
-        const double n_chain = (double)(p.dim / 32 + 8);
-        const double eps_acc = (double)(p.dim / 16) * 17.0 * 1.1920928955078125e-7 * (1.0 + rho);
-        const double eps_inv = (0.5 * n_chain + 8.0) * 5.9604644775390625e-8;
-        const double margin = p.rigorous ? rho * (1.0 + 1e-9) + eps_acc + eps_inv + 1e-12
-                                         : 8.0 * rho * sqrt(3.0 / (double)p.dim) + 1e-6;
-        const float worst32 = __shfl_sync(FCB_FULL, my_s, 31);
-        const bool domain = alpha > 0.0 && nq > 8.9e-16 && nq < 1.1e15 && isfinite(worst32);
-        const double worst = domain ? (double)worst32 * ialpha / nq : 0.0;
+        const double margin = p.rigorous ? dense_margin(rho, p.dim) : 8.0 * rho * sqrt(3.0 / (double)p.dim) + 1e-6;
+        const float worst32 = m_s[0][FCB_FUSED_CAND - 1].score;
+        // the largest first-pass score an UNLISTED row can have
+        float U = -INFINITY;
+        for (int c = lane; c < p.n_lists; c += 32) U = fmaxf(U, p.thr_out[(size_t)b * p.gt_stride + c]);
+#pragma unroll
+        for (int off = 16; off >= 1; off >>= 1) U = fmaxf(U, __shfl_xor_sync(FCB_FULL, U, off));
         if (lane == 0) {
-            const int flag = (nvalid == FCB_FUSED_CAND && !(domain && worst + margin < kth)) ? 1 : 0;
+            int flag = 0, widened = 0;
+            if (nvalid == FCB_FUSED_CAND) {
+                const bool domain = nq > 8.9e-16 && nq < 1.1e15 && isfinite(worst32) && isfinite(kth);
+                const float window = domain ? __double2float_rd((kth - margin) * nq) : 0.f;   // W in first-pass units, rounded down
+                if (!domain) flag = 1;
+                else if (worst32 < window) flag = 0;                  // the 32 hold every row that could matter
+                else if (!p.rigorous || !(U < window)) flag = 1;      // an unlisted row could matter
+                else { s_mode = 1; s_window = window; s_worst = m_s[0][FCB_FUSED_CAND - 1]; widened = 1; }
+            }
             p.redo[b] = flag;
+            p.widened[b] = widened;
             if (flag) p.redo_list[atomicAdd(p.redo_count, 1)] = b;
         }
+    }
+    __syncthreads();
+    if (!s_mode) return;
+
+    // ---- widen: every listed row with a first-pass score >= the window that is not one of the 32 already re-scored
+    const float window = s_window;
+    const FcbCand worst = s_worst;
+    for (int L = warp; L < p.n_lists; L += 8) {
+        const FcbCand e = p.cta_top[((size_t)L * DN_N + b) * FCB_FUSED_CAND + lane];
+        const bool want = e.row != FCB_NO_ROW && e.score >= window && fcb_cand_better(worst.score, worst.row, e.score, e.row, p.id_rank);
+        unsigned todo = __ballot_sync(FCB_FULL, want);
+        while (todo) {
+            const int src = __ffs(todo) - 1;
+            todo &= todo - 1;
+            const uint32_t row = __shfl_sync(FCB_FULL, e.row, src);
+            const double sc = fcb_canon_score_warp<__nv_bfloat16>(vec + (int64_t)row * p.dim, qd, p.dim, lane);
+            if (lane == 0) {
+                const unsigned slot = atomicAdd(&s_extra, 1u);
+                if (slot < DN_EXTRA_CAP) { x_score[slot] = sc; x_id[slot] = p.ids ? p.ids[row] : (uint64_t)(p.row_base + row); }
+            }
+        }
+    }
+    __syncthreads();
+    const unsigned n_extra = s_extra;
+    if (n_extra > DN_EXTRA_CAP) {                                       // too many near-ties for this kernel: the exact scan answers
+        if (tid == 0) { p.redo[b] = 1; p.widened[b] = 0; p.redo_list[atomicAdd(p.redo_count, 1)] = b; }
+        return;
+    }
+    // rank the 32 + n_extra candidates by (score desc, id asc); ids are unique, so the ranks are distinct
+    const unsigned n = FCB_FUSED_CAND + n_extra;
+    for (unsigned e = tid; e < n; e += 256) {
+        const double ms = e < FCB_FUSED_CAND ? f_score[e] : x_score[e - FCB_FUSED_CAND];
+        const uint64_t mi = e < FCB_FUSED_CAND ? f_id[e] : x_id[e - FCB_FUSED_CAND];
+        int rank = 0;
+        for (unsigned j = 0; j < FCB_FUSED_CAND; ++j) rank += fcb_better64(f_score[j], f_id[j], ms, mi);
+        for (unsigned j = 0; j < n_extra; ++j) rank += fcb_better64(x_score[j], x_id[j], ms, mi);
+        if (rank < p.k) { p.out_ids[(size_t)b * p.k + rank] = mi; p.out_scores[(size_t)b * p.k + rank] = ms; }
     }
 }
 
@@ -853,9 +926,10 @@ struct FcbDense {
     CUtensorMap map_qh[DN_N / 32];          // ... box rows = N / 2 for the cta_group::2 kernel
     int rigorous = 0;
     int two_cta = 1;
-    uint16_t *q_bf16 = nullptr;             // [DN_N, dim] the 16-bit query tile (float16 or bfloat16)
-    double *alpha = nullptr;                // [DN_N] its per-query scale
-    int q_is_bf16 = 0;
+    __nv_bfloat16 *q_bf16 = nullptr;        // [DN_N, dim]
+    float *slack = nullptr;                 // [DN_N] per-query slack of the cross-CTA pruning bound (first-pass units)
+    float *thr_out = nullptr;               // [DN_N][gt_stride] final pruning thresholds
+    int32_t *widened = nullptr;             // [DN_N]
     FcbCand *cta_top = nullptr, *pend = nullptr;
     unsigned *gtop = nullptr;               // [DN_N][gt_stride] per-CTA best scores of the cta_group::2 kernel
     int gt_stride = 0;
@@ -867,7 +941,7 @@ struct FcbDense {
 void fcb_dense_free(fcb_engine *e) {
     FcbDense *d = reinterpret_cast<FcbDense *>(e->dense);
     if (!d) return;
-    cudaFree(d->q_bf16); cudaFree(d->alpha); cudaFree(d->cta_top); cudaFree(d->pend); cudaFree(d->redo); cudaFree(d->error_flag); cudaFree(d->gtop);
+    cudaFree(d->q_bf16); cudaFree(d->slack); cudaFree(d->thr_out); cudaFree(d->widened); cudaFree(d->cta_top); cudaFree(d->pend); cudaFree(d->redo); cudaFree(d->error_flag); cudaFree(d->gtop);
     delete d;
     e->dense = nullptr;
 }
@@ -886,7 +960,9 @@ int32_t fcb_dense_alloc(fcb_engine *e) {
     d->gt_stride = ((d->grid + 31) / 32) * 32;
     const size_t lists = (size_t)d->grid * DN_N;
     if (cudaMalloc(&d->q_bf16, (size_t)DN_N * s.dim * 2) != cudaSuccess ||
-        cudaMalloc(&d->alpha, (size_t)DN_N * sizeof(double)) != cudaSuccess ||
+        cudaMalloc(&d->slack, (size_t)DN_N * sizeof(float)) != cudaSuccess ||
+        cudaMalloc(&d->thr_out, (size_t)DN_N * d->gt_stride * sizeof(float)) != cudaSuccess ||
+        cudaMalloc(&d->widened, (size_t)DN_N * sizeof(int32_t)) != cudaSuccess ||
         cudaMalloc(&d->cta_top, lists * FCB_FUSED_CAND * sizeof(FcbCand)) != cudaSuccess ||
         cudaMalloc(&d->pend, lists * DN_PEND_CAP * sizeof(FcbCand)) != cudaSuccess ||
         cudaMalloc(&d->redo, (size_t)(2 * DN_N + 1) * sizeof(int32_t)) != cudaSuccess ||
@@ -904,8 +980,6 @@ int32_t fcb_dense_alloc(fcb_engine *e) {
         rc = encode_map(e, &d->map_qh[i], d->q_bf16, DN_N, (uint64_t)s.dim, 16 * (i + 1));
     const char *rig = getenv("FCB_DENSE_RIGOROUS");                 // "0": the statistical margin of round 1 (A/B runs only)
     d->rigorous = !(rig && rig[0] == '0');
-    const char *qf = getenv("FCB_DENSE_QFMT");                      // "bf16": bfloat16 query tile instead of float16
-    d->q_is_bf16 = qf && qf[0] == 'b';
     const char *one = getenv("FCB_DENSE_1CTA");                     // tuning / fallback switch
     d->two_cta = !(one && one[0] == '1') && (d->grid % 2 == 0);
     if (rc != FCB_OK) { fcb_dense_free(e); return rc; }
@@ -944,14 +1018,14 @@ int32_t fcb_search_dense(fcb_engine *e, const double *d_queries, const fcb_filte
     FcbDense *d = reinterpret_cast<FcbDense *>(e->dense);
     const fcb_shard &s = e->shard;
     if (!d) return fcb_fail(e, FCB_ERR_STATE, "fcb_search: batched path not initialised");
-    dense_pack_queries_kernel<<<DN_N, 256, 0, st>>>(d_queries, batch, s.dim, d->q_bf16, d->alpha, d->q_is_bf16);
+    dense_pack_queries_kernel<<<DN_N, 256, 0, st>>>(d_queries, batch, s.dim, d->q_bf16, d->slack);
     DenseParams p{};
     p.inv_norm = e->inv_norm; p.id_rank = s.id_rank; p.dates = s.dates; p.cats = s.categories; p.filter = f;
     p.n_rows = s.n_rows; p.row_base = s.row_base; p.dim = s.dim;
     p.n_queries = batch; p.n_eff = ((batch + 31) / 32) * 32;
     p.cta_top = d->cta_top; p.pend = d->pend; p.error_flag = d->error_flag;
     p.debug_out = g_debug_out; p.debug_rows = g_debug_rows; p.prof = g_dense_prof;
-    p.gtop = d->gtop; p.gt_stride = d->gt_stride; p.q_is_bf16 = d->q_is_bf16;
+    p.gtop = d->gtop; p.gt_stride = d->gt_stride; p.slack = d->slack; p.thr_out = d->thr_out;
     FCB_CUDA(e, cudaMemsetAsync(d->gtop, 0, (size_t)DN_N * d->gt_stride * sizeof(unsigned), st));   // 0 orders below every float
     p.n_stages = p.n_eff <= 96 ? 4 : 3;                              // stages + 4 KB + lists (n_eff x 256 B) must fit 227 KB
     const size_t smem = (size_t)DN_STAGES * DN_STAGE_BYTES + 4096;
@@ -966,7 +1040,7 @@ int32_t fcb_search_dense(fcb_engine *e, const double *d_queries, const fcb_filte
     fp.vectors = s.vectors; fp.ids = s.ids; fp.id_rank = s.id_rank; fp.queries = d_queries; fp.cta_top = d->cta_top;
     fp.n_lists = d->grid; fp.row_base = s.row_base; fp.dim = s.dim; fp.k = k;
     fp.out_ids = d_out_ids; fp.out_scores = d_out_scores; fp.out_counts = d_out_counts; fp.redo = d->redo;
-    fp.rigorous = d->rigorous; fp.q_packed = d->q_bf16; fp.alpha = d->alpha; fp.q_is_bf16 = d->q_is_bf16;
+    fp.rigorous = d->rigorous; fp.thr_out = d->thr_out; fp.gt_stride = d->gt_stride; fp.widened = d->widened;
     fp.redo_list = d->redo + DN_N; fp.redo_count = d->redo + 2 * DN_N;
     FCB_CUDA(e, cudaMemsetAsync(fp.redo_count, 0, sizeof(int32_t), st));
     dense_finalize_kernel<<<batch, 256, 0, st>>>(fp);
@@ -977,16 +1051,25 @@ int32_t fcb_search_dense(fcb_engine *e, const double *d_queries, const fcb_filte
     return FCB_OK;
 }
 
-// Measurement aid: how many queries of the last batched-path call were NOT certified by the
-// tensor-core pass and were therefore answered by the exact scan. Synchronises the device.
-extern "C" int32_t fcb_last_dense_redo(fcb_engine *e, int32_t batch) {
+static int32_t count_flags(fcb_engine *e, const int32_t *d_flags, int32_t batch) {
     if (!e || !e->dense || batch < 1 || batch > DN_N) return -1;
     FcbDeviceGuard g(e->device);
-    FcbDense *d = reinterpret_cast<FcbDense *>(e->dense);
     int32_t h[DN_N];
     if (cudaDeviceSynchronize() != cudaSuccess) return -1;
-    if (cudaMemcpy(h, d->redo, (size_t)batch * sizeof(int32_t), cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
+    if (cudaMemcpy(h, d_flags, (size_t)batch * sizeof(int32_t), cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
     int32_t n = 0;
     for (int i = 0; i < batch; ++i) n += h[i] != 0;
     return n;
+}
+
+// Measurement aid: how many queries of the last batched-path call could NOT be answered exactly from the tensor-core
+// pass's lists and were therefore answered by the exact scan. Synchronises the device.
+extern "C" int32_t fcb_last_dense_redo(fcb_engine *e, int32_t batch) {
+    return e && e->dense ? count_flags(e, reinterpret_cast<FcbDense *>(e->dense)->redo, batch) : -1;
+}
+
+// Measurement aid: how many queries of the last batched-path call were answered by re-scoring MORE than the 32 best
+// listed rows (every listed row inside the worst-case error window). Synchronises the device.
+extern "C" int32_t fcb_last_dense_widened(fcb_engine *e, int32_t batch) {
+    return e && e->dense ? count_flags(e, reinterpret_cast<FcbDense *>(e->dense)->widened, batch) : -1;
 }

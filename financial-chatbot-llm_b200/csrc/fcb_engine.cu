@@ -46,7 +46,10 @@ extern "C" int32_t fcb_close(fcb_engine *e) {
         cudaFree(e->d_cand);
         cudaFree(e->d_counters);
         cudaFreeHost(e->h_filters);
+        cudaFree(e->d_route);
+        cudaFreeHost(e->h_route);
         for (auto &ev : e->filter_ev) if (ev) cudaEventDestroy(ev);
+        for (auto &ev : e->route_ev) if (ev) cudaEventDestroy(ev);
         if (e->ev0) cudaEventDestroy(e->ev0);
         if (e->ev1) cudaEventDestroy(e->ev1);
         if (e->stream) cudaStreamDestroy(e->stream);
@@ -70,6 +73,10 @@ static int32_t open_impl(fcb_engine *e, const fcb_config *cfg) {
     FCB_CUDA(e, cudaEventCreate(&e->ev0));
     FCB_CUDA(e, cudaEventCreate(&e->ev1));
     for (auto &ev : e->filter_ev) FCB_CUDA(e, cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    for (auto &ev : e->route_ev) FCB_CUDA(e, cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    const size_t nr = (size_t)FCB_FILTER_SLOTS * (2 * (size_t)e->max_batch + 1);
+    FCB_CUDA(e, cudaMalloc(&e->d_route, nr * sizeof(int32_t)));
+    FCB_CUDA(e, cudaMallocHost(&e->h_route, nr * sizeof(int32_t)));
 
     const size_t nf = (size_t)FCB_FILTER_SLOTS * e->max_batch;
     FCB_CUDA(e, cudaMalloc(&e->d_filters, nf * sizeof(fcb_filter)));

@@ -18,6 +18,7 @@
 #define FCB_INLINE_FILTERS 4               // filters passed by value in the kernel parameters
 #define FCB_FILTER_SLOTS 8                 // ring of pinned filter staging slots (batch > inline)
 #define FCB_DENSE_MIN_BATCH 32             // batches at least this large may take the tensor-core path
+#define FCB_MAX_WORLD 8                    // ranks of one routed exchange (the GPUs of one box)
 #define FCB_NO_ROW 0xffffffffu
 #define FCB_COS_EPS 1.1920929e-7           // zero-norm guard (float32 eps), as in the oracle
 
@@ -48,6 +49,11 @@ struct fcb_engine {
     fcb_filter *h_filters = nullptr;       // [FCB_FILTER_SLOTS][max_batch]
     cudaEvent_t filter_ev[FCB_FILTER_SLOTS] = {};
     int filter_slot = 0;
+    // routed search (fcb_search_routed): per call, owner[max_batch] | subset[max_batch] | count, staged through the same kind of ring
+    int32_t *h_route = nullptr, *d_route = nullptr;
+    cudaEvent_t route_ev[FCB_FILTER_SLOTS] = {};
+    int route_slot = 0;
+    int list_rows = 0;                     // grid rows of a scan launch that strides over a device list (0: the re-run default of 8)
 
     // staging for fcb_search_host (sized at load: needs dim)
     double *h_q = nullptr, *d_q = nullptr;
@@ -114,6 +120,12 @@ int32_t *fcb_exact_flags(fcb_engine *e);   // device [max_batch]
 int32_t fcb_exact_enqueue(fcb_engine *e, const double *d_queries, const fcb_filter *d_filters, const fcb_filter *inl,
                           int filters_mode, int32_t batch, int32_t k, const int32_t *d_flags, uint64_t *d_out_ids,
                           double *d_out_scores, int32_t *d_out_counts, cudaStream_t st);
+
+// owner-computes exchange over peer memory (fcb_exchange.cu)
+__host__ __device__ inline size_t fcb_exchange_parity_bytes(int slots, int k) { return (size_t)slots * k * 16 + (size_t)slots * 8; }
+int32_t fcb_exchange_launch(fcb_engine *e, const fcb_exchange *x, int32_t slots, int32_t k, uint32_t seq, const int32_t *d_owner,
+                            const uint64_t *d_ids, const double *d_scores, const int32_t *d_counts, int32_t *d_status,
+                            cudaStream_t st);
 
 // error plumbing (fcb_engine.cu)
 int32_t fcb_fail(fcb_engine *e, int32_t code, const char *fmt, ...);

@@ -305,7 +305,9 @@ static int32_t check_search_args(fcb_engine *e, const void *queries, const fcb_f
 
 template <typename T, int R, int U>
 static int32_t launch_fused_cfg(fcb_engine *e, ScanParams &p, int batch, int64_t max_rows, cudaStream_t st) {
-    const int grid_y = p.redo_list != nullptr && batch > 8 ? 8 : batch;   // re-run launch: 8 rows stride over the list
+    // a launch over a device list of query indices: the dense path's re-run takes 8 rows (the list is usually empty),
+    // the routed search one row per listed query
+    const int grid_y = p.redo_list != nullptr ? (e->list_rows > 0 ? e->list_rows : (batch > 8 ? 8 : batch)) : batch;
     const int64_t groups = (max_rows + R - 1) / R;
     // >= 2 groups per warp when the segment allows; never more CTAs than the scratch holds
     int64_t ctas = (groups + 2 * FCB_SCAN_WARPS - 1) / (2 * FCB_SCAN_WARPS);
@@ -501,6 +503,90 @@ static int32_t search_device(fcb_engine *e, const double *d_queries, const fcb_f
     }
     return fcb_exact_enqueue(e, d_queries, sf.d_filters, sf.inl, sf.use_inline ? 1 : 0, batch, k, d_flags, d_out_ids,
                              d_out_scores, d_out_counts, st);
+}
+
+// Routed search + owner-computes exchange (include/fcb200.h, csrc/fcb_exchange.cu): scan only the queries whose row range
+// lies in THIS rank's shard, then push their results to every rank and wait for everybody else's.
+extern "C" int32_t fcb_search_routed(fcb_engine *e, const fcb_exchange *x, const double *queries, const fcb_filter *filters,
+                                     int32_t batch, int32_t k, uint32_t seq, int32_t *status, void *stream) {
+    if (!e) return FCB_ERR_INVALID;
+    if (!x || !x->cuts || !status) return fcb_fail(e, FCB_ERR_INVALID, "fcb_search_routed: NULL argument");
+    if (x->world < 1 || x->world > FCB_MAX_WORLD || x->rank < 0 || x->rank >= x->world)
+        return fcb_fail(e, FCB_ERR_INVALID, "fcb_search_routed: world %d / rank %d outside 1..%d", x->world, x->rank, FCB_MAX_WORLD);
+    for (int g = 0; g < x->world; ++g)
+        if (!x->bufs[g]) return fcb_fail(e, FCB_ERR_INVALID, "fcb_search_routed: exchange buffer of rank %d is NULL", g);
+    if (seq == 0) return fcb_fail(e, FCB_ERR_INVALID, "fcb_search_routed: sequence numbers start at 1");
+    int32_t rc = check_search_args(e, queries, filters, batch, k, status, status, status);
+    if (rc != FCB_OK) return rc;
+    if (k > FCB_FUSED_MAX_K)
+        return fcb_fail(e, FCB_ERR_UNSUPPORTED, "fcb_search_routed: k %d > %d (use fcb_search + all-gather + fcb_merge_topk)", k, FCB_FUSED_MAX_K);
+    if (e->rows_out_of_domain > 0)
+        return fcb_fail(e, FCB_ERR_UNSUPPORTED, "fcb_search_routed: the shard holds rows outside the float32 range (use fcb_search)");
+    FcbDeviceGuard g(e->device);
+    if (!g.ok) return fcb_fail(e, FCB_ERR_CUDA, "fcb_search_routed: cannot select device %d", e->device);
+    cudaStream_t st = (cudaStream_t)stream;
+    const fcb_shard &s = e->shard;
+    e->last_launches = 0;
+
+    // ---- who owns what: the shard holding the first row of the range; a range spanning two shards needs a merge
+    const int rslot = e->route_slot;
+    e->route_slot = (rslot + 1) % FCB_FILTER_SLOTS;
+    FCB_CUDA(e, cudaEventSynchronize(e->route_ev[rslot]));
+    const size_t rstride = 2 * (size_t)e->max_batch + 1;
+    int32_t *h_owner = e->h_route + (size_t)rslot * rstride, *h_subset = h_owner + e->max_batch, *h_count = h_subset + e->max_batch;
+    int32_t *d_owner = e->d_route + (size_t)rslot * rstride, *d_subset = d_owner + e->max_batch, *d_count = d_subset + e->max_batch;
+    int n_mine = 0;
+    for (int b = 0; b < batch; ++b) {
+        const fcb_filter &f = filters[b];
+        int owner = 0;
+        if (f.row_begin < f.row_end) {
+            int lo = 0, hi = x->world - 1;                         // last shard whose first row is <= row_begin
+            while (lo < hi) { const int mid = (lo + hi + 1) >> 1; if (x->cuts[mid] <= f.row_begin) lo = mid; else hi = mid - 1; }
+            owner = lo;
+            if (f.row_end > x->cuts[owner + 1] || f.row_begin < x->cuts[0])
+                return fcb_fail(e, FCB_ERR_UNSUPPORTED, "fcb_search_routed: query %d spans rows [%lld, %lld) of more than one shard "
+                                "(answer it with fcb_search + all-gather + fcb_merge_topk)", b, (long long)f.row_begin, (long long)f.row_end);
+        }
+        h_owner[b] = owner;
+        if (owner == x->rank) h_subset[n_mine++] = b;
+    }
+    *h_count = n_mine;
+    FCB_CUDA(e, cudaMemcpyAsync(d_owner, h_owner, rstride * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+    FCB_CUDA(e, cudaEventRecord(e->route_ev[rslot], st));
+
+    // local results: the engine's result staging block (ids | scores | counts | flags), sized for max_batch x max_k
+    const size_t rn = (size_t)batch * k;
+    uint64_t *d_ids = e->d_ids;
+    double *d_scores = reinterpret_cast<double *>(d_ids + rn);
+    int32_t *d_counts = reinterpret_cast<int32_t *>(d_scores + rn), *d_flags = d_counts + batch;
+    if (n_mine > 0) {
+        StagedFilters sf;
+        rc = stage_filters(e, filters, batch, true, st, sf);
+        if (rc != FCB_OK) return rc;
+        FCB_CUDA(e, cudaMemsetAsync(d_flags, 0, (size_t)batch * sizeof(int32_t), st));   // only the listed queries write theirs
+        ScanParams p{};
+        p.vectors = s.vectors; p.inv_norm = e->inv_norm; p.ids = s.ids; p.id_rank = s.id_rank;
+        p.dates = s.dates; p.cats = s.categories; p.queries = queries;
+        p.n_rows = s.n_rows; p.row_base = s.row_base; p.dim = s.dim; p.k = k;
+        p.cand = e->d_cand; p.counters = e->d_counters;
+        p.out_ids = d_ids; p.out_scores = d_scores; p.out_counts = d_counts;
+        p.cert_flags = d_flags; p.cert_eps = fcb_first_pass_eps(s.dim);
+        p.use_inline = 0; p.filters = sf.d_filters;
+        p.redo_list = d_subset; p.redo_count = d_count;
+        e->list_rows = n_mine;
+        rc = s.dtype == FCB_DTYPE_F32 ? launch_fused<float>(e, p, batch, sf.max_rows, st)
+                                      : launch_fused<__nv_bfloat16>(e, p, batch, sf.max_rows, st);
+        e->list_rows = 0;
+        if (rc != FCB_OK) return rc;
+        if (sf.max_rows >= FCB_FUSED_CAND) {
+            rc = fcb_exact_enqueue(e, queries, sf.d_filters, sf.inl, 0, batch, k, d_flags, d_ids, d_scores, d_counts, st);
+            if (rc != FCB_OK) return rc;
+        }
+    }
+    rc = fcb_exchange_launch(e, x, batch, k, seq, d_owner, d_ids, d_scores, d_counts, status, st);
+    if (rc != FCB_OK) return rc;
+    e->last_launches += 1;
+    return FCB_OK;
 }
 
 // Called by fcb_load_shard: time every (R, U) candidate on a full-shard scan with a pseudo-random query (results discarded)

@@ -172,6 +172,10 @@ class Engine:
         """Queries of the last batched tensor-core call answered by the exact re-run (-1: path inactive)."""
         return int(self._lib.fcb_last_dense_redo(self._h, batch))
 
+    def last_dense_widened(self, batch: int) -> int:
+        """Queries of the last batched tensor-core call answered by re-scoring more than the 32 best listed rows."""
+        return int(self._lib.fcb_last_dense_widened(self._h, batch))
+
     @property
     def exact_reruns(self) -> int:
         """Queries since load_shard that a fast path could not certify and the exact float64 kernel answered."""

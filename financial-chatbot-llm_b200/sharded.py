@@ -177,3 +177,122 @@ class ShardedB200Client(B200QdrantClient):
             pts.append(ScoredPoint(id=col.point_id_fn(row) if col.point_id_fn else pid, version=0, score=s, vector=None,
                                    payload=col.payload_fn(row) if with_payload else None))
         return QueryResponse(points=pts)
+
+
+# ---- owner-computes routing over NVLink peer memory (fcb_search_routed, csrc/fcb_exchange.cu) ------------------------
+
+FILTER_DTYPE = np.dtype([("row_begin", "<i8"), ("row_end", "<i8"), ("date_lo", "<i8"), ("date_hi", "<i8"),
+                         ("category_mask", "<u8")])             # = fcb_filter: batches of filters without a Python loop per call
+
+
+def filters_array(row_begin, row_end, date_lo=None, date_hi=None, category_mask=None) -> np.ndarray:
+    """A batch of fcb_filter as ONE numpy structured array (row ranges as arrays; bounds default to 'no filter')."""
+    rb = np.asarray(row_begin, dtype=np.int64)
+    out = np.empty(rb.shape[0], dtype=FILTER_DTYPE)
+    out["row_begin"], out["row_end"] = rb, np.asarray(row_end, dtype=np.int64)
+    out["date_lo"] = _lib.FCB_DATE_MIN if date_lo is None else date_lo
+    out["date_hi"] = _lib.FCB_DATE_MAX if date_hi is None else date_hi
+    out["category_mask"] = _lib.FCB_ALL_CATEGORIES if category_mask is None else category_mask
+    return out
+
+
+class _DevicePointer:
+    """A raw device allocation dressed for torch.as_tensor (zero copy)."""
+    def __init__(self, ptr: int, shape, typestr: str):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (int(ptr), False), "version": 2}
+
+
+class PeerExchange:
+    """The exchange buffers of one (slots, k) shape: this rank's allocation plus every peer's, opened through CUDA IPC
+    (the 64-byte handles travel by all_gather_object; after that no collective is involved). `cuts[g] .. cuts[g + 1]` are
+    rank g's global rows. One routed search in flight at a time; consume `results()` on the stream of the call before
+    the next call."""
+
+    def __init__(self, device: int, world: int, rank: int, slots: int, k: int, cuts: Sequence[int], group: Any = None):
+        import torch
+        import torch.distributed as dist
+        if world > _lib.FCB_MAX_WORLD:
+            raise ValueError(f"at most {_lib.FCB_MAX_WORLD} ranks")
+        self._lib = _lib.load()
+        self.device, self.world, self.rank, self.slots, self.k = device, world, rank, slots, k
+        self.bytes = int(self._lib.fcb_exchange_bytes(slots, k))
+        own = C.c_void_p()
+        handle = (C.c_ubyte * _lib.FCB_PEER_HANDLE_BYTES)()
+        _lib.check(self._lib.fcb_peer_alloc(device, self.bytes, C.byref(own), handle))
+        handles: List[Any] = [None] * world
+        if world > 1:
+            dist.all_gather_object(handles, bytes(handle), group=group)
+        else:
+            handles[0] = bytes(handle)
+        self._ptrs: List[int] = []
+        for g in range(world):
+            if g == rank:
+                self._ptrs.append(int(own.value))
+                continue
+            p = C.c_void_p()
+            h = (C.c_ubyte * _lib.FCB_PEER_HANDLE_BYTES).from_buffer_copy(handles[g])
+            _lib.check(self._lib.fcb_peer_open(device, h, C.byref(p)))
+            self._ptrs.append(int(p.value))
+        self._cuts = np.ascontiguousarray(cuts, dtype=np.int64)
+        assert self._cuts.shape[0] == world + 1
+        bufs = (C.c_void_p * _lib.FCB_MAX_WORLD)(*([C.c_void_p(p) for p in self._ptrs] + [None] * (_lib.FCB_MAX_WORLD - world)))
+        self.x = _lib.FcbExchange(world, rank, bufs, self._cuts.ctypes.data)
+        self.seq = 0
+        self.status = torch.zeros(1, dtype=torch.int32, device=torch.device("cuda", device))
+        if world > 1:
+            dist.barrier(group=group)                  # everybody has opened everybody's buffer before the first push
+
+    def results(self, seq: Optional[int] = None):
+        """(ids int64 [slots, k], scores float64 [slots, k], counts int32 [slots]) of exchange `seq` (default: the last
+        one) as zero-copy CUDA tensors over this rank's buffer."""
+        import torch
+        seq = self.seq if seq is None else seq
+        base = self._ptrs[self.rank] + (seq & 1) * (self.bytes // 2)
+        n = self.slots * self.k
+        dev = torch.device("cuda", self.device)
+        ids = torch.as_tensor(_DevicePointer(base, (self.slots, self.k), "<i8"), device=dev)
+        scores = torch.as_tensor(_DevicePointer(base + 8 * n, (self.slots, self.k), "<f8"), device=dev)
+        counts = torch.as_tensor(_DevicePointer(base + 16 * n, (self.slots,), "<i4"), device=dev)
+        return ids, scores, counts
+
+    def close(self) -> None:
+        for g, p in enumerate(self._ptrs):
+            self._lib.fcb_peer_close(self.device, C.c_void_p(p), 1 if g == self.rank else 0)
+        self._ptrs = []
+
+
+class RoutedSearcher:
+    """Collective search where every tenant lives on ONE shard (cuts on user boundaries): the owner computes the final
+    top-k of its queries and writes it into every rank's exchange buffer; no all-gather, no merge. Call on every rank
+    with the same queries (resident on every rank's GPU), the same filters and the same k."""
+
+    def __init__(self, collection: Collection, exchange: PeerExchange):
+        self.col, self.xch = collection, exchange
+        self._lib = _lib.load()
+
+    def search_device(self, d_queries, filters: np.ndarray, k: int, stream: Optional[int] = None) -> int:
+        """Asynchronous. `filters`: structured array (FILTER_DTYPE), one per exchange slot. Returns the sequence number;
+        `exchange.results(seq)` holds the answers once the stream has run the call."""
+        import torch
+        xch = self.xch
+        if filters.dtype != FILTER_DTYPE or filters.shape[0] != xch.slots or k != xch.k:
+            raise ValueError("filters must be a FILTER_DTYPE array with one entry per exchange slot, k the exchange's k")
+        if stream is None:
+            stream = torch.cuda.current_stream(xch.device).cuda_stream
+        xch.seq += 1
+        eng = self.col.engine
+        _lib.check(self._lib.fcb_search_routed(eng._h, C.byref(xch.x), d_queries.data_ptr(), filters.ctypes.data, xch.slots, k,
+                                               xch.seq, xch.status.data_ptr(), C.c_void_p(stream)), eng._h)
+        return xch.seq
+
+    def search(self, queries: np.ndarray, filters: np.ndarray, k: int):
+        """Host arrays in, host arrays out (ids uint64, scores, counts); synchronous."""
+        import torch
+        dev = torch.device("cuda", self.xch.device)
+        dq = torch.from_numpy(np.ascontiguousarray(queries, dtype=np.float64)).to(dev)
+        seq = self.search_device(dq, filters, k)
+        ids, scores, counts = self.xch.results(seq)
+        out = ids.cpu().numpy().view(np.uint64), scores.cpu().numpy(), counts.cpu().numpy()
+        if int(self.xch.status.item()) != 0:
+            raise _lib.FcbError(_lib.FCB_ERR_STATE, "routed search: a peer never delivered its results (exchange timed out)")
+        return out

@@ -152,9 +152,13 @@ int32_t fcb_search_noalloc(int32_t device, const fcb_shard *shard, const double 
 float fcb_last_search_ms(const fcb_engine *e);
 
 /* Batched tensor-core path only (bf16 shard, batch >= 32, identical filters): number of queries of
- * the last call that the bf16 first pass could not certify and the exact scan answered instead;
- * -1 if the path is not active. Synchronises the device. Measurement aid. */
+ * the last call that could not be answered exactly from the first pass's candidate lists and that the exact scan
+ * answered instead; -1 if the path is not active. Synchronises the device. Measurement aid. */
 int32_t fcb_last_dense_redo(fcb_engine *e, int32_t batch);
+
+/* Same path: number of queries of the last call that were answered by re-scoring more than the 32 best listed rows —
+ * every listed row inside the worst-case error window of the bf16 first pass (csrc/fcb_dense.cu). Measurement aid. */
+int32_t fcb_last_dense_widened(fcb_engine *e, int32_t batch);
 
 /* Diagnostic for the batched tensor-core path: the next calls also dump the raw accumulators
  * (un-normalised bf16 dot products) of the first `rows` rows of the segment into `out`
@@ -244,6 +248,40 @@ int32_t fcb_merge_topk(int32_t device, const uint64_t *cand_ids, const double *c
                        const int32_t *cand_counts, int64_t shard_stride_bytes, int32_t n_shards,
                        int32_t batch, int32_t k, uint64_t *out_ids, double *out_scores,
                        int32_t *out_counts, void *stream);
+
+/* ---- Owner-computes exchange of the sharded search (north_star's sharded corpus; no counterpart in the reference, whose
+ * Qdrant server routes and merges internally). With the shard cuts on user boundaries a tenant lives on ONE GPU, so its
+ * query needs no merge: the owner computes the final top-k and hands it to every other rank. fcb_search_routed does both in
+ * one call per rank and batch: the fused scan over the queries THIS rank owns, then one kernel that writes their results
+ * straight into the exchange buffer of every rank over NVLink peer mappings (plain stores + a stamp) and waits until its
+ * own buffer holds every query's answer. No NCCL call, no merge launch, no host round trip on the data path.
+ *
+ * Exchange buffers: every rank allocates one with fcb_peer_alloc (fcb_exchange_bytes(slots, k) bytes), the 64-byte
+ * handles travel by any side channel (torch.distributed all_gather_object in sharded.py), and every rank opens the
+ * others' with fcb_peer_open. Layout of one buffer, two parities p = seq & 1 at byte p * fcb_exchange_bytes / 2:
+ *   ids uint64 [slots][k] | scores float64 [slots][k] | counts int32 [slots] | stamps uint32 [slots]. */
+#define FCB_MAX_WORLD 8
+#define FCB_PEER_HANDLE_BYTES 64
+typedef struct fcb_exchange {
+    int32_t world, rank;                /* ranks of the box (<= FCB_MAX_WORLD) and this process's                     */
+    void *bufs[FCB_MAX_WORLD];          /* bufs[g]: rank g's exchange buffer as mapped in THIS process (device pointer) */
+    const int64_t *cuts;                /* HOST [world + 1]: rank g holds global rows [cuts[g], cuts[g + 1])           */
+} fcb_exchange;
+
+int64_t fcb_exchange_bytes(int32_t slots, int32_t k);
+int32_t fcb_peer_alloc(int32_t device, int64_t bytes, void **ptr, uint8_t *handle /* [FCB_PEER_HANDLE_BYTES] */);
+int32_t fcb_peer_open(int32_t device, const uint8_t *handle, void **ptr);
+int32_t fcb_peer_close(int32_t device, void *ptr, int32_t owned /* 1: from fcb_peer_alloc, 0: from fcb_peer_open */);
+
+/* The same call on every rank, with the same queries (device [batch, dim] float64, resident on every rank), filters (HOST
+ * [batch]), k (<= 16) and sequence number `seq` (1, 2, 3, ... per exchange; it selects the parity and is the stamp). A query
+ * whose row range lies in rank g's shard is scanned by rank g only; a range that spans two shards is refused with
+ * FCB_ERR_UNSUPPORTED (answer those with fcb_search + all-gather + fcb_merge_topk). When the work enqueued by this call has
+ * finished on `stream`, parity seq & 1 of bufs[rank] holds all `batch` answers; *status (device int32, zeroed by the caller)
+ * reads 1 if a peer never delivered (the wait is bounded: a few seconds). Consume the results on the same stream before the
+ * next call (that is what keeps a fast peer from overwriting them, see csrc/fcb_exchange.cu). Asynchronous on `stream`. */
+int32_t fcb_search_routed(fcb_engine *e, const fcb_exchange *x, const double *queries, const fcb_filter *filters,
+                          int32_t batch, int32_t k, uint32_t seq, int32_t *status, void *stream);
 
 /* 1 if fcb_load_shard found metadata.date non-decreasing within every user segment (a time-ordered
  * transaction log), 0 if not, -1 without a shard. fcb_aggregate then uses its atomic-free kernel; the

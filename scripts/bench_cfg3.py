@@ -37,5 +37,5 @@ for B in batches:
     ms = e0.elapsed_time(e1) / steps
     print(json.dumps({"lib": os.environ.get("FCB_LIB_PATH", "in-tree"), "batch": B, "ms": round(ms, 4),
                       "tensor_TFLOPs": round(2.0 * rows * dim * (((B + 31) // 32) * 32) / ms / 1e9, 1),
-                      "redo": eng.last_dense_redo(B), "ids_checksum": int(oi[:B].sum().item())}), flush=True)
+                      "redo": eng.last_dense_redo(B), "widened": eng.last_dense_widened(B), "exact_reruns": eng.exact_reruns, "ids_checksum": int(oi[:B].sum().item())}), flush=True)
 eng.close()

@@ -148,3 +148,18 @@ def test_row_of_id_global_map_and_miss():
     assert plain.row_of_id(2999) == 2999
     with pytest.raises(KeyError):
         plain.row_of_id(3000)
+
+
+def test_filters_array_has_the_layout_of_fcb_filter():
+    """Batches of filters travel to fcb_search_routed as ONE numpy structured array: same bytes as an FcbFilter array."""
+    import ctypes as C
+    from financial_chatbot_llm_b200 import _lib, sharded
+    from financial_chatbot_llm_b200.engine import make_filter
+    rb, re_ = np.array([0, 10, 500]), np.array([10, 25, 500])
+    arr = sharded.filters_array(rb, re_)
+    assert arr.dtype.itemsize == C.sizeof(_lib.FcbFilter) == 40
+    want = (_lib.FcbFilter * 3)(*[make_filter(int(a), int(b)) for a, b in zip(rb, re_)])
+    assert arr.tobytes() == bytes(want)
+    arr = sharded.filters_array(rb, re_, date_lo=5, date_hi=9, category_mask=3)
+    want = (_lib.FcbFilter * 3)(*[make_filter(int(a), int(b), 5, 9, 3) for a, b in zip(rb, re_)])
+    assert arr.tobytes() == bytes(want)
