@@ -12,19 +12,22 @@
 //   3. when a tie straddles the cut: radix select of the wanted number of SMALLEST tie keys (row, or id rank) among the
 //      rows whose key equals the k-th — so ties at the k-th score resolve by ascending id, like everywhere else,
 //   4. compaction of exactly min(k, passing rows) rows, ranking by (score desc, id asc), results written.
-// It is ONE cooperative launch (grid = what is co-resident, grid-wide barriers between the phases) that leaves at once
-// when no flag is set — the cost on the common path is that empty launch. No host round trip, no CPU path.
+// It is ONE ordinary launch of two CTAs per SM that leaves at once when no flag is set — the cost on the common path is that
+// empty launch. Only a flagged query makes the CTAs meet at grid-wide barriers between the phases (a ticket counter in
+// global memory; two small CTAs per SM are co-resident on an otherwise idle GPU and squeeze in beside anything that does not
+// fill an SM; the waits are BOUNDED — a grid that cannot assemble gives up, raises the error word and fcb_exact_reruns
+// reports it — so nothing can hang). A cooperative launch would give the co-residency guarantee for free, but the driver
+// runs a cooperative grid only on an idle device: every search would then serialise against whatever else the GPU is doing.
+// No host round trip, no CPU path.
 // The keys ARE the canonical scores (order-preserving bit transform), so the scores written are bit-identical to a
 // re-score. Replaces nothing in the reference: qdrant's local mode is exact by being brute force in float64.
-#include <cooperative_groups.h>
-
 #include "fcb_internal.cuh"
 #include "fcb_topk.cuh"
 
-namespace cg = cooperative_groups;
-
 #define EX_THREADS 256
 #define EX_WARPS (EX_THREADS / 32)
+
+#define EX_BARRIER_SPINS (1u << 26)        // x ~0.1 us of back-off: a grid that cannot assemble gives up after several seconds
 
 struct FcbExactState {
     unsigned hist[8][256];                 // digit histograms of the score-key passes
@@ -33,10 +36,42 @@ struct FcbExactState {
     unsigned n_sel;                        // compaction cursor
 };
 
+struct FcbExactBarrier {                   // survives the per-query clearing of the state
+    unsigned count;                        // CTAs that have arrived at the current barrier
+    unsigned generation;                   // bumped by the last arrival
+    unsigned error;                        // 1: a barrier timed out (the answers of that launch are not valid)
+};
+
+// Grid-wide barrier for a grid whose CTAs are all resident (see the header). Bounded: on a timeout the error word is raised
+// and every later wait returns at once.
+__device__ __forceinline__ void ex_grid_barrier(FcbExactBarrier *bar) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        volatile unsigned *gen = &bar->generation;
+        volatile unsigned *err = &bar->error;
+        const unsigned g = *gen;
+        __threadfence();
+        if (atomicAdd(&bar->count, 1u) == gridDim.x - 1) {
+            bar->count = 0;
+            __threadfence();
+            atomicAdd(&bar->generation, 1u);
+        } else {
+            unsigned spins = 0;
+            while (*gen == g && *err == 0) {
+                if (++spins > EX_BARRIER_SPINS) { *err = 1; break; }
+                __nanosleep(100);
+            }
+        }
+        __threadfence();
+    }
+    __syncthreads();
+}
+
 struct FcbExact {                          // engine-owned scratch (fcb_load_shard)
     uint64_t *keys = nullptr;              // [n_rows]; the general-k path's key buffer when that exists
     bool own_keys = false;
     FcbExactState *state = nullptr;
+    FcbExactBarrier *barrier = nullptr;
     uint64_t *sel_keys = nullptr;          // [max_k]
     uint32_t *sel_rows = nullptr, *sel_ties = nullptr;
     int32_t *flags = nullptr;              // [max_batch] certificate flags of device-API calls
@@ -59,6 +94,7 @@ struct ExactParams {
     const int32_t *flags;
     uint64_t *keys;
     FcbExactState *st;
+    FcbExactBarrier *bar;
     uint64_t *sel_keys;
     uint32_t *sel_rows, *sel_ties;
     uint64_t *out_ids;
@@ -104,7 +140,6 @@ __global__ void __launch_bounds__(EX_THREADS) exact_fallback_kernel(const __grid
     double *q_s = reinterpret_cast<double *>(ex_smem);                     // [dim] float64 query
     __shared__ unsigned s_hist[256], s_scan[256], s_out[3];
     __shared__ int s_any;
-    cg::grid_group grid = cg::this_grid();
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int64_t gtid = (int64_t)blockIdx.x * EX_THREADS + tid, gthreads = (int64_t)gridDim.x * EX_THREADS;
     const T *__restrict__ vec = reinterpret_cast<const T *>(p.vectors);
@@ -136,7 +171,7 @@ __global__ void __launch_bounds__(EX_THREADS) exact_fallback_kernel(const __grid
         for (int i = tid; i < p.dim; i += EX_THREADS) q_s[i] = qd[i];
         s_hist[tid] = 0;
         __syncthreads();
-        grid.sync();
+        ex_grid_barrier(p.bar);
 
         // ---- phase 1: canonical float64 score of every passing row -> key; histogram of the top byte
         {
@@ -174,7 +209,7 @@ __global__ void __launch_bounds__(EX_THREADS) exact_fallback_kernel(const __grid
             __syncthreads();
             if (s_hist[tid]) atomicAdd(&p.st->hist[0][tid], s_hist[tid]);
         }
-        grid.sync();
+        ex_grid_barrier(p.bar);
 
         const unsigned n_pass = __ldcg(&p.st->n_pass);
         const unsigned want = n_pass < (unsigned)p.k ? n_pass : (unsigned)p.k;
@@ -183,7 +218,7 @@ __global__ void __launch_bounds__(EX_THREADS) exact_fallback_kernel(const __grid
                 for (int t = tid; t < p.k; t += EX_THREADS) { out_ids[t] = UINT64_MAX; out_scores[t] = -INFINITY; }
                 if (tid == 0) { p.out_counts[b] = 0; atomicAdd(p.reruns, 1ull); }
             }
-            grid.sync();
+            ex_grid_barrier(p.bar);
             continue;
         }
 
@@ -209,7 +244,7 @@ __global__ void __launch_bounds__(EX_THREADS) exact_fallback_kernel(const __grid
             }
             __syncthreads();
             if (s_hist[tid]) atomicAdd(&p.st->hist[pass + 1][tid], s_hist[tid]);
-            grid.sync();
+            ex_grid_barrier(p.bar);
         }
         // keys strictly above the cut are all wanted; of the keys equal to it (whole_bucket: sharing its prefix) `rem`
         const uint64_t cut_mask = passes_done == 8 ? ~0ull : ~0ull << (64 - 8 * passes_done);
@@ -232,7 +267,7 @@ __global__ void __launch_bounds__(EX_THREADS) exact_fallback_kernel(const __grid
                 }
                 __syncthreads();
                 if (s_hist[tid]) atomicAdd(&p.st->thist[pass][tid], s_hist[tid]);
-                grid.sync();
+                ex_grid_barrier(p.bar);
                 unsigned digit;
                 ex_pick_digit(p.st->thist[pass], trem, false, s_scan, s_out, digit, trem, tb);
                 tprefix |= digit << shift;
@@ -256,7 +291,7 @@ __global__ void __launch_bounds__(EX_THREADS) exact_fallback_kernel(const __grid
                 }
             }
         }
-        grid.sync();
+        ex_grid_barrier(p.bar);
 
         // ---- phase 5: rank by (score desc, id asc) and write
         for (int64_t e = gtid; e < (int64_t)want; e += gthreads) {
@@ -275,7 +310,7 @@ __global__ void __launch_bounds__(EX_THREADS) exact_fallback_kernel(const __grid
             for (int t = (int)want + tid; t < p.k; t += EX_THREADS) { out_ids[t] = UINT64_MAX; out_scores[t] = -INFINITY; }
             if (tid == 0) { p.out_counts[b] = (int32_t)want; atomicAdd(p.reruns, 1ull); }
         }
-        grid.sync();                                                       // state, keys and selection are reused by the next query
+        ex_grid_barrier(p.bar);                                                       // state, keys and selection are reused by the next query
     }
 }
 
@@ -285,6 +320,7 @@ void fcb_exact_free(fcb_engine *e) {
     FcbExact *x = reinterpret_cast<FcbExact *>(e->exact);
     if (!x) return;
     if (x->own_keys) cudaFree(x->keys);
+    cudaFree(x->barrier);
     cudaFree(x->state); cudaFree(x->sel_keys); cudaFree(x->sel_rows); cudaFree(x->sel_ties); cudaFree(x->flags); cudaFree(x->reruns);
     delete x;
     e->exact = nullptr;
@@ -297,7 +333,7 @@ static int32_t exact_grid(fcb_engine *e, size_t smem, int *grid) {
     int per_sm = 0;
     FCB_CUDA(e, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, EX_THREADS, smem));
     if (per_sm < 1) return fcb_fail(e, FCB_ERR_CUDA, "fcb_load_shard: the exact fallback kernel does not fit an SM");
-    if (per_sm > 4) per_sm = 4;
+    if (per_sm > 2) per_sm = 2;                                     // leave room on every SM: the grid must be co-resident
     *grid = per_sm * e->num_sms;
     return FCB_OK;
 }
@@ -317,7 +353,8 @@ int32_t fcb_exact_alloc(fcb_engine *e) {
         }
         x->own_keys = true;
     }
-    if (cudaMalloc(&x->state, sizeof(FcbExactState)) != cudaSuccess || cudaMalloc(&x->sel_keys, kmax * sizeof(uint64_t)) != cudaSuccess ||
+    if (cudaMalloc(&x->state, sizeof(FcbExactState)) != cudaSuccess || cudaMalloc(&x->barrier, sizeof(FcbExactBarrier)) != cudaSuccess ||
+        cudaMalloc(&x->sel_keys, kmax * sizeof(uint64_t)) != cudaSuccess ||
         cudaMalloc(&x->sel_rows, kmax * sizeof(uint32_t)) != cudaSuccess || cudaMalloc(&x->sel_ties, kmax * sizeof(uint32_t)) != cudaSuccess ||
         cudaMalloc(&x->flags, B * sizeof(int32_t)) != cudaSuccess || cudaMalloc(&x->reruns, sizeof(unsigned long long)) != cudaSuccess) {
         cudaGetLastError();
@@ -326,6 +363,7 @@ int32_t fcb_exact_alloc(fcb_engine *e) {
     }
     FCB_CUDA(e, cudaMemsetAsync(x->flags, 0, B * sizeof(int32_t), e->stream));
     FCB_CUDA(e, cudaMemsetAsync(x->reruns, 0, sizeof(unsigned long long), e->stream));
+    FCB_CUDA(e, cudaMemsetAsync(x->barrier, 0, sizeof(FcbExactBarrier), e->stream));
     const size_t smem = (size_t)e->shard.dim * sizeof(double);
     int32_t rc = e->shard.dtype == FCB_DTYPE_F32 ? exact_grid<float>(e, smem, &x->grid_f32)
                                                  : exact_grid<__nv_bfloat16>(e, smem, &x->grid_bf16);
@@ -351,15 +389,13 @@ int32_t fcb_exact_enqueue(fcb_engine *e, const double *d_queries, const fcb_filt
     if (filters_mode == 1) for (int b = 0; b < batch && b < FCB_INLINE_FILTERS; ++b) p.inl[b] = inl[b];
     if (filters_mode == 2) p.inl[0] = inl[0];
     p.n_rows = s.n_rows; p.row_base = s.row_base; p.dim = s.dim; p.k = k; p.batch = batch;
-    p.flags = d_flags; p.keys = x->keys; p.st = x->state;
+    p.flags = d_flags; p.keys = x->keys; p.st = x->state; p.bar = x->barrier;
     p.sel_keys = x->sel_keys; p.sel_rows = x->sel_rows; p.sel_ties = x->sel_ties;
     p.out_ids = d_out_ids; p.out_scores = d_out_scores; p.out_counts = d_out_counts; p.reruns = x->reruns;
-    void *args[] = {&p};
     const size_t smem = (size_t)s.dim * sizeof(double);
-    if (s.dtype == FCB_DTYPE_F32)
-        FCB_CUDA(e, cudaLaunchCooperativeKernel((const void *)exact_fallback_kernel<float>, dim3(x->grid_f32), dim3(EX_THREADS), args, smem, st));
-    else
-        FCB_CUDA(e, cudaLaunchCooperativeKernel((const void *)exact_fallback_kernel<__nv_bfloat16>, dim3(x->grid_bf16), dim3(EX_THREADS), args, smem, st));
+    if (s.dtype == FCB_DTYPE_F32) exact_fallback_kernel<float><<<x->grid_f32, EX_THREADS, smem, st>>>(p);
+    else exact_fallback_kernel<__nv_bfloat16><<<x->grid_bf16, EX_THREADS, smem, st>>>(p);
+    FCB_CUDA(e, cudaGetLastError());
     e->last_launches += 1;
     return FCB_OK;
 }
@@ -369,7 +405,15 @@ extern "C" int64_t fcb_exact_reruns(fcb_engine *e) {
     FcbDeviceGuard g(e->device);
     FcbExact *x = reinterpret_cast<FcbExact *>(e->exact);
     unsigned long long h = 0;
+    FcbExactBarrier hb{};
     if (!g.ok || cudaDeviceSynchronize() != cudaSuccess ||
-        cudaMemcpy(&h, x->reruns, sizeof h, cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
+        cudaMemcpy(&h, x->reruns, sizeof h, cudaMemcpyDeviceToHost) != cudaSuccess ||
+        cudaMemcpy(&hb, x->barrier, sizeof hb, cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
+    if (hb.error) {
+        cudaMemset(x->barrier, 0, sizeof(FcbExactBarrier));           // usable again
+        fcb_fail(e, FCB_ERR_STATE, "the exact float64 kernel could not assemble its grid (a barrier timed out): the GPU was "
+                 "saturated by other work; the answers of that call are not valid");
+        return -2;
+    }
     return (int64_t)h;
 }

@@ -8,21 +8,91 @@ socket with ``EngineClient``, which duck-types ``QdrantClient.query_points``; th
 requests that arrive within a short window into one grouped ``fcb_search`` launch (the path that does
 270k q/s at 64 tenants per call instead of 36k q/s one by one) and returns scored points with payloads.
 
-Transport: ``multiprocessing.connection`` (length-prefixed pickles over AF_UNIX) — local, same-user only.
+Transport: length-prefixed frames over an AF_UNIX stream socket. A request is a FIXED BINARY header (struct, below) +
+the collection name + the qdrant filter as JSON + the query vector as raw float64; a reply is JSON (scored points with
+their payload dicts; Python's float repr round-trips float64 scores bit for bit). Nothing is unpickled on either side,
+so a peer can at worst send a malformed request, which is answered with an error frame. The socket file is created with
+mode 0600: the trust boundary is "processes of the same user on this host" (INTEGRATION.md §3).
 """
 from __future__ import annotations
 
+import json
+import math
 import os
 import queue
+import socket
+import struct
 import threading
 import time
-from multiprocessing.connection import Client, Listener
 from typing import Any, Dict, List, Optional
 
 import numpy as np
 
 from .client import Collection, merge_conjunct_lists
-from .qdrant_models import QueryResponse, ScoredPoint
+from .qdrant_models import Filter, QueryResponse, ScoredPoint
+
+# request header: magic, version, flags (bit 0: with_payload), limit, offset, dim, len(collection name), len(filter JSON),
+# score_threshold (NaN: none). Then: name (utf-8), filter JSON (utf-8, may be empty), dim x float64 (little endian).
+_REQ = struct.Struct("<4sHHiiIIId")
+_MAGIC = b"FCB1"
+_LEN = struct.Struct("<I")
+_MAX_FRAME = 64 << 20                  # a request is ~12 KB, a reply with 10 000 payloads a few MB
+
+
+def _recv_exact(sock: socket.socket, n: int) -> bytes:
+    buf = bytearray(n)
+    view, got = memoryview(buf), 0
+    while got < n:
+        r = sock.recv_into(view[got:], n - got)
+        if r == 0:
+            raise EOFError("peer closed the connection")
+        got += r
+    return bytes(buf)
+
+
+def _send_frame(sock: socket.socket, body: bytes) -> None:
+    sock.sendall(_LEN.pack(len(body)) + body)
+
+
+def _recv_frame(sock: socket.socket) -> bytes:
+    (n,) = _LEN.unpack(_recv_exact(sock, _LEN.size))
+    if n > _MAX_FRAME:
+        raise ValueError(f"frame of {n} bytes refused")
+    return _recv_exact(sock, n)
+
+
+def filter_to_json(flt: Any) -> str:
+    """A qdrant filter (our models or qdrant-client's: both pydantic) as JSON; '' for no filter."""
+    if flt is None:
+        return ""
+    if hasattr(flt, "model_dump"):
+        return json.dumps(flt.model_dump(exclude_none=True))
+    raise NotImplementedError(f"cannot serialise a filter of type {type(flt).__name__}")
+
+
+def encode_request(collection_name: str, query, query_filter: Any, limit: int, offset: Optional[int], with_payload: bool,
+                   score_threshold: Optional[float]) -> bytes:
+    q = np.ascontiguousarray(query, dtype="<f8").reshape(-1)
+    name, fj = collection_name.encode("utf-8"), filter_to_json(query_filter).encode("utf-8")
+    head = _REQ.pack(_MAGIC, 1, 1 if with_payload else 0, int(limit), int(offset or 0), q.shape[0], len(name), len(fj),
+                     math.nan if score_threshold is None else float(score_threshold))
+    return head + name + fj + q.tobytes()
+
+
+def decode_request(body: bytes) -> Dict[str, Any]:
+    if len(body) < _REQ.size:
+        raise ValueError("short request")
+    magic, ver, flags, limit, offset, dim, n_name, n_flt, thr = _REQ.unpack_from(body, 0)
+    if magic != _MAGIC or ver != 1:
+        raise ValueError("not an fcb200 request frame")
+    if len(body) != _REQ.size + n_name + n_flt + 8 * dim:
+        raise ValueError("request length does not match its header")
+    at = _REQ.size
+    name = body[at:at + n_name].decode("utf-8"); at += n_name
+    fj = body[at:at + n_flt].decode("utf-8"); at += n_flt
+    return {"collection_name": name, "query": np.frombuffer(body, dtype="<f8", count=dim, offset=at),
+            "query_filter": Filter.model_validate(json.loads(fj)) if fj else None, "limit": limit, "offset": offset,
+            "with_payload": bool(flags & 1), "score_threshold": None if math.isnan(thr) else thr}
 
 
 class _Request:
@@ -44,10 +114,17 @@ class EngineServer:
         self._q: "queue.Queue[_Request]" = queue.Queue()
         self._stop = threading.Event()
         self._threads: List[threading.Thread] = []
-        self.stats = {"requests": 0, "launches": 0, "max_batch": 0}
+        self.stats = {"requests": 0, "launches": 0, "max_batch": 0, "batch_hist": {}}
         if os.path.exists(address):
             os.unlink(address)
-        self._listener = Listener(address, family="AF_UNIX")
+        self._listener = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+        old_umask = os.umask(0o177)                     # the socket file is born 0600: same-user processes only
+        try:
+            self._listener.bind(address)
+        finally:
+            os.umask(old_umask)
+        os.chmod(address, 0o600)
+        self._listener.listen(64)
 
     # ---- lifecycle
     def start(self) -> "EngineServer":
@@ -60,7 +137,9 @@ class EngineServer:
     def stop(self) -> None:
         self._stop.set()
         try:
-            Client(self.address, family="AF_UNIX").close()          # unblock accept()
+            c = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)    # unblock accept()
+            c.connect(self.address)
+            c.close()
         except OSError:
             pass
         self._listener.close()
@@ -73,7 +152,7 @@ class EngineServer:
     def _accept_loop(self) -> None:
         while not self._stop.is_set():
             try:
-                conn = self._listener.accept()
+                conn, _ = self._listener.accept()
             except OSError:
                 return
             if self._stop.is_set():
@@ -82,34 +161,37 @@ class EngineServer:
             t = threading.Thread(target=self._reader, args=(conn,), daemon=True)
             t.start()
 
+    @staticmethod
+    def _reply(conn, lock, obj) -> None:
+        with lock:
+            _send_frame(conn, json.dumps(obj, separators=(",", ":")).encode("utf-8"))
+
     def _reader(self, conn) -> None:
         lock = threading.Lock()
         try:
             while not self._stop.is_set():
-                msg = conn.recv()
+                body = _recv_frame(conn)
                 try:
+                    msg = decode_request(body)
                     if msg["collection_name"] != self.col.name:
                         raise ValueError(f"Collection {msg['collection_name']} not found")
-                    q = np.asarray(msg["query"], dtype=np.float64)
+                    q = msg["query"]
                     if q.shape != (self.col.engine.dim,):
                         raise ValueError(f"query must be a vector of length {self.col.engine.dim}")
                     skip = int(msg.get("offset") or 0)
                     k = int(msg["limit"]) + skip
                     if k < 1:
-                        with lock:
-                            conn.send({"points": []})
+                        self._reply(conn, lock, {"points": []})
                         continue
                     filts = self.col.resolve_dnf(msg.get("query_filter"))   # should / must_not: several conjuncts
                     if not filts:                                            # nothing can match
-                        with lock:
-                            conn.send({"points": []})
+                        self._reply(conn, lock, {"points": []})
                         continue
                     self._q.put(_Request(conn, lock, q, filts, k, skip, bool(msg.get("with_payload", True)),
                                          msg.get("score_threshold")))
                 except Exception as e:                             # the caller's blanket except turns it into []
-                    with lock:
-                        conn.send({"error": f"{type(e).__name__}: {e}"})
-        except (EOFError, OSError):
+                    self._reply(conn, lock, {"error": f"{type(e).__name__}: {e}"})
+        except (EOFError, OSError, ValueError):
             pass
         finally:
             conn.close()
@@ -146,8 +228,10 @@ class EngineServer:
             for lo in range(0, len(rows_f), self.max_batch):
                 parts.append(self.col.engine.search_host(np.stack(rows_q[lo:lo + self.max_batch]),
                                                          rows_f[lo:lo + self.max_batch], k))
+                nb = len(rows_f[lo:lo + self.max_batch])
                 self.stats["launches"] += 1
-                self.stats["max_batch"] = max(self.stats["max_batch"], len(rows_f[lo:lo + self.max_batch]))
+                self.stats["max_batch"] = max(self.stats["max_batch"], nb)
+                self.stats["batch_hist"][nb] = self.stats["batch_hist"].get(nb, 0) + 1
             ids = np.concatenate([p[0] for p in parts]); scores = np.concatenate([p[1] for p in parts])
             counts = np.concatenate([p[2] for p in parts])
             self.stats["requests"] += len(reqs)
@@ -168,13 +252,11 @@ class EngineServer:
                     row = self.col.row_of_id(pid)
                     pts.append({"id": self.col.point_id_fn(row) if self.col.point_id_fn else pid, "version": 0, "score": s,
                                 "payload": self.col.payload_fn(row) if r.with_payload else None, "vector": None})
-                with r.lock:
-                    r.conn.send({"points": pts})
+                self._reply(r.conn, r.lock, {"points": pts})
         except Exception as e:
             for r in reqs:
                 try:
-                    with r.lock:
-                        r.conn.send({"error": f"{type(e).__name__}: {e}"})
+                    self._reply(r.conn, r.lock, {"error": f"{type(e).__name__}: {e}"})
                 except OSError:
                     pass
 
@@ -194,7 +276,9 @@ class EngineClient:
 
     def _connection(self):
         if self._conn is None:
-            self._conn = Client(self.address, family="AF_UNIX")
+            c = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+            c.connect(self.address)
+            self._conn = c
         return self._conn
 
     def close(self) -> None:
@@ -208,12 +292,11 @@ class EngineClient:
                      **kwargs: Any) -> QueryResponse:
         if prefetch is not None or using is not None or with_vectors or query is None:
             raise NotImplementedError("unsupported query_points arguments")
-        msg = {"collection_name": collection_name, "query": list(query), "query_filter": query_filter, "limit": int(limit),
-               "offset": offset, "with_payload": bool(with_payload), "score_threshold": score_threshold}
+        frame = encode_request(collection_name, query, query_filter, limit, offset, bool(with_payload), score_threshold)
         with self._lock:
             conn = self._connection()
-            conn.send(msg)
-            reply = conn.recv()
+            _send_frame(conn, frame)
+            reply = json.loads(_recv_frame(conn))
         if "error" in reply:
             raise RuntimeError(reply["error"])
         return QueryResponse(points=[ScoredPoint(**p) for p in reply["points"]])

@@ -184,7 +184,9 @@ int32_t fcb_debug_scan_timing(uint64_t *buf);
 int32_t fcb_scan_config(const fcb_engine *e, int32_t *r, int32_t *u);
 
 /* How many queries since fcb_load_shard the certificate of a fast path refused and the exact float64 kernel
- * answered instead (see fcb_search); -1 without a shard. Synchronises the device. Measurement aid; no counterpart in
+ * answered instead (see fcb_search); -1 without a shard; -2 (and fcb_last_error) if that kernel ever failed to assemble its
+ * grid because other work saturated the GPU — its waits are bounded, the answers of that call are then not valid.
+ * Synchronises the device. Measurement aid; no counterpart in
  * the reference, whose local mode is brute force in float64 throughout. */
 int64_t fcb_exact_reruns(fcb_engine *e);
 

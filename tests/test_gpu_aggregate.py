@@ -242,3 +242,51 @@ def test_group_by_over_retrieved_points_equals_pandas_on_their_payloads(built, i
     none = m.Filter(must=[m.FieldCondition(key="metadata.user_id", match=m.MatchValue(value="nobody"))])
     assert len(aggregate.grouped_sum_retrieved(col, q, none, 10, "category")) == 0
     eng.close()
+
+
+def test_bucket_kernel_equals_atomic_kernel_and_pandas_on_awkward_shapes(built, monkeypatch):
+    """Users of at least 8192 rows take the atomic-free bucket kernel (rows bucketed by category through shared memory,
+    lane-private month bins). Awkward shapes: user starts that are not multiples of 4 (ragged quads), sizes around the
+    8192-row threshold and around the 4092-row pass length, a user spanning several 64k-row blocks, rows outside the
+    category / month window (must be counted as dropped, identically), full-range int32 values. The dense outputs must be
+    identical to the shared-atomic kernel's (FCB_AGG_LARGE=atomic) and equal pandas."""
+    import torch
+    from financial_chatbot_llm_b200 import synth
+    from financial_chatbot_llm_b200.engine import aggregate_columns
+    from oracle import groupby
+    rng = np.random.default_rng(11)
+    sizes = np.array([3, 8191, 8192, 8193, 1, 4092 * 2 + 1, 200_001, 17, 8192 + 4093, 70_000, 5, 12_345], dtype=np.int64)
+    off = np.zeros(len(sizes) + 1, dtype=np.int64)
+    np.cumsum(sizes, out=off[1:])
+    n = int(off[-1])
+    v = rng.integers(-(2 ** 31), 2 ** 31, size=n, dtype=np.int64).astype(np.int32)
+    v[::5] = rng.integers(-5000, 5000, size=v[::5].size)
+    d = (synth.DATE_BASE + rng.integers(0, 730 * 86400, size=n)).astype(np.int32)
+    c = rng.integers(0, 16, size=n).astype(np.uint8)
+    c[rng.integers(0, n, size=300)] = 200                       # unknown category -> dropped
+    d[rng.integers(0, n, size=300)] = synth.DATE_BASE - 86400   # before the window -> dropped
+    dev = torch.device("cuda", 0)
+    dd, cc, vv, oo = (torch.from_numpy(a).to(dev) for a in (d, c, v, off))
+    mlo = int(groupby.month_index(np.array([synth.DATE_BASE]))[0])
+    res = {}
+    for mode in ("bucket", "atomic"):
+        if mode == "atomic":
+            monkeypatch.setenv("FCB_AGG_LARGE", "atomic")
+        sums, present, dropped = aggregate_columns(0, dd, cc, vv, oo, 0, len(sizes), mlo, 24, 16)
+        torch.cuda.synchronize()
+        res[mode] = (sums.cpu().numpy(), present.cpu().numpy(), int(dropped.item()))
+    assert np.array_equal(res["bucket"][0], res["atomic"][0]) and np.array_equal(res["bucket"][1], res["atomic"][1])
+    keep = (c < 16) & (d >= synth.DATE_BASE)
+    assert res["bucket"][2] == res["atomic"][2] == int((~keep).sum())
+    ser = groupby.groupby_user_category_month(synth.row_users(off, np.arange(n))[keep], c[keep], d[keep], v[keep])
+    idx = ser.index.to_frame(index=False)
+    sums, present, _ = res["bucket"]
+    assert int(present.sum()) == len(ser)
+    assert sums[idx["user"].to_numpy(), idx["category"].to_numpy(), idx["month"].to_numpy() - mlo].tolist() == ser.tolist()
+    # a sub-range of users and a shard that starts in the middle of the columns (row_base > 0)
+    lo_u, hi_u = 5, 10
+    a, b = int(off[lo_u]), int(off[hi_u])
+    s2, p2, d2 = aggregate_columns(0, dd[a:b].contiguous(), cc[a:b].contiguous(), vv[a:b].contiguous(), oo, lo_u, hi_u, mlo, 24, 16,
+                                   row_base=a)
+    torch.cuda.synchronize()
+    assert np.array_equal(s2.cpu().numpy(), sums[lo_u:hi_u]) and np.array_equal(p2.cpu().numpy(), present[lo_u:hi_u])

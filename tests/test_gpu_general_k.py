@@ -41,7 +41,8 @@ def test_k_sweep_on_whale_segment(env):
     hc, eng, _ = env
     for k in (17, 64, 100, 1000, 10000):
         assert check(eng, hc, k, k, 0) == k
-    assert eng.last_search_launches == 13               # key scan, 8 radix passes, compact, re-score, chunk sort, rank merge
+    assert eng.last_search_launches == 15               # key scan, 8 radix passes, compact, re-score, chunk sort, rank merge,
+                                                        # certificate, flag-gated float64 path
 
 
 def test_k_larger_than_segment_and_filters(env):
