@@ -526,6 +526,158 @@ __global__ void __launch_bounds__(AGG_THREADS, AGS_CTAS) aggregate_sorted_kernel
     if (dropped) atomicAdd(p.dropped, (unsigned long long)dropped);
 }
 
+// ---- any row order without shared atomics: warp-private tables + a claim round --------------------------------------
+// The shared-memory atomic unit retires about one lane per clock and SM: one ATOMS per row caps aggregate_kernel at ~3.5 ms
+// per 1B rows (0.38 of the HBM rate) however the cells are laid out. Plain loads and stores run at 32 lanes per clock — what
+// they lack is protection against two lanes of ONE instruction hitting the same cell (with 384 cells that happens to ~1.3
+// pairs of lanes per 32 rows). So every warp gets a PRIVATE [category, month] table (no other warp ever touches it), and a
+// step of 32 rows goes through claim rounds: every pending lane stores its lane number into claim[cell], the warp
+// synchronises, and the lane that reads its own number back has won the cell for this round — it adds its value with a plain
+// load / add / store; the losers (same cell, other lane) go round again. ~1.8 rounds per step on random cells, most of the
+// second round's lanes idle. 32-bit cells with the lo/hi split of aggregate_kernel: a warp sees 512 rows of a tile, so
+// nothing overflows. At the end of a piece the 8 warp tables are summed per cell by the CTA and leave as one 64-bit global
+// reduction per observed cell, exactly like aggregate_kernel's shared cells.
+__device__ __forceinline__ void agg_claim_add(bool valid, int cell, int32_t v, int32_t *w_lo, int32_t *w_hi, uint8_t *w_claim,
+                                              uint8_t *w_present, int lane) {
+    bool mine = valid;
+    unsigned pend = __ballot_sync(FCB_FULL, mine);
+    while (pend) {
+        if (mine) w_claim[cell] = (uint8_t)lane;
+        __syncwarp();
+        const bool win = mine && w_claim[cell] == (uint8_t)lane;
+        __syncwarp();                                          // every read of this round's claims before the next round's writes
+        if (win) {
+            if (v > -(1 << 18) && v < (1 << 18)) {
+                w_lo[cell] += v;
+            } else {
+                const int32_t lo16 = (int32_t)(int16_t)(v & 0xffff);
+                w_lo[cell] += lo16;
+                w_hi[cell] += (int32_t)(((int64_t)v - lo16) >> 16);
+            }
+            w_present[cell] = 1;
+            mine = false;
+        }
+        __syncwarp();                                          // the winner's store before a loser's load of the same cell
+        pend = __ballot_sync(FCB_FULL, mine);
+    }
+}
+
+__global__ void __launch_bounds__(AGG_THREADS, 4) aggregate_claim_kernel(const __grid_constant__ AggParams p) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int C = p.n_categories * p.n_months;
+    const int Cp = (C + 3) & ~3;                                       // per-warp table stride (cells), 16-byte friendly
+    constexpr int W = AGG_THREADS / 32;
+    int32_t *t_lo = reinterpret_cast<int32_t *>(smem_raw);             // [W][Cp]
+    int32_t *t_hi = t_lo + W * Cp;                                     // [W][Cp]
+    uint16_t *month_tab = reinterpret_cast<uint16_t *>(t_hi + W * Cp); // [n_days]
+    uint8_t *t_claim = reinterpret_cast<uint8_t *>(month_tab + ((p.n_days + 1) & ~1));   // [W][Cp]
+    uint8_t *t_present = t_claim + W * Cp;                             // [W][Cp]
+    __shared__ int64_t s_piece[2];
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    int32_t *w_lo = t_lo + warp * Cp, *w_hi = t_hi + warp * Cp;
+    uint8_t *w_claim = t_claim + warp * Cp, *w_present = t_present + warp * Cp;
+    for (int i = tid; i < p.n_days; i += AGG_THREADS) month_tab[i] = (uint16_t)(month_of_day(p.day0 + i) - p.month_lo);
+    for (int i = tid; i < W * Cp; i += AGG_THREADS) { t_lo[i] = 0; t_hi[i] = 0; t_present[i] = 0; t_claim[i] = 0xff; }
+    __syncthreads();
+
+    int64_t R0 = p.seg_offsets[p.seg_begin], R1 = p.seg_offsets[p.seg_end];
+    if (R0 < p.row_base) R0 = p.row_base;
+    if (R1 > p.row_base + p.n_rows) R1 = p.row_base + p.n_rows;
+    const int64_t n_tiles = R1 > R0 ? (R1 - R0 + AGG_TILE - 1) / AGG_TILE : 0;
+    unsigned dropped = 0;
+    const int4 *cents4 = reinterpret_cast<const int4 *>(p.cents);
+    const int4 *dates4 = reinterpret_cast<const int4 *>(p.dates);
+    const uchar4 *cats4 = reinterpret_cast<const uchar4 *>(p.cats);
+
+    for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+        const int64_t a = R0 + t * AGG_TILE;
+        const int64_t b = a + AGG_TILE < R1 ? a + AGG_TILE : R1;
+        if (tid == 0) {                                    // first user whose segment ends after a
+            int64_t lo = p.seg_begin, hi = p.seg_end - 1;
+            while (lo < hi) {
+                const int64_t mid = (lo + hi) >> 1;
+                if (p.seg_offsets[mid + 1] > a) hi = mid; else lo = mid + 1;
+            }
+            s_piece[0] = lo;
+        }
+        __syncthreads();
+        int64_t u = s_piece[0];
+        __syncthreads();
+        int64_t pa = a;
+        while (pa < b) {
+            int64_t uend = p.seg_offsets[u + 1];
+            while (uend <= pa) { ++u; uend = p.seg_offsets[u + 1]; }   // skip empty users
+            const int64_t pb = uend < b ? uend : b;
+            if (p.split == 1 && uend - p.seg_offsets[u] < AGS_TABLE_USER) { pa = pb; continue; }   // the other launch's user
+            int64_t *out_s = p.sums + (u - p.seg_begin) * (int64_t)C;
+            uint8_t *out_p = p.present + (u - p.seg_begin) * (int64_t)C;
+            const bool small = pb - pa < p.small_piece;
+            const int64_t la = pa - p.row_base, lb = pb - p.row_base;
+            const int64_t q0 = la >> 2, q1 = (lb + 3) >> 2;            // quads [q0, q1) cover [la, lb)
+            for (int64_t qb = q0; qb < q1; qb += AGG_THREADS) {       // warp-uniform trip count: the claim rounds are warp-wide
+                const int64_t q = qb + tid, r = q << 2;
+                int v[4] = {0, 0, 0, 0}, d[4] = {0, 0, 0, 0};
+                unsigned c[4] = {0, 0, 0, 0};
+                unsigned in = 0;
+                if (q < q1) {
+                    if (r >= la && r + 4 <= lb) {                       // interior quad: three vector loads
+                        const int4 vv = __ldg(cents4 + q), dd = __ldg(dates4 + q);
+                        const uchar4 cc = __ldg(cats4 + q);
+                        v[0] = vv.x; v[1] = vv.y; v[2] = vv.z; v[3] = vv.w;
+                        d[0] = dd.x; d[1] = dd.y; d[2] = dd.z; d[3] = dd.w;
+                        c[0] = cc.x; c[1] = cc.y; c[2] = cc.z; c[3] = cc.w;
+                        in = 0xfu;
+                    } else {                                            // ragged head / tail of the piece
+#pragma unroll
+                        for (int i = 0; i < 4; ++i)
+                            if (r + i >= la && r + i < lb) { v[i] = p.cents[r + i]; d[i] = p.dates[r + i]; c[i] = p.cats[r + i]; in |= 1u << i; }
+                    }
+                }
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    bool valid = (in >> i) & 1u;
+                    int cell = 0;
+                    if (valid) {
+                        const int32_t di = floor_day(d[i]) - p.day0;
+                        const unsigned mo = (unsigned)di < (unsigned)p.n_days ? month_tab[di] : 0xffffu;
+                        if (c[i] >= (unsigned)p.n_categories || mo >= (unsigned)p.n_months) { ++dropped; valid = false; }
+                        else cell = c[i] * p.n_months + mo;
+                    }
+                    if (small) {                                        // tiny piece: straight to the global cells
+                        if (valid) {
+                            atomicAdd(reinterpret_cast<unsigned long long *>(out_s + cell), (unsigned long long)(long long)v[i]);
+                            out_p[cell] = 1;
+                        }
+                    } else {
+                        agg_claim_add(valid, cell, v[i], w_lo, w_hi, w_claim, w_present, lane);
+                    }
+                }
+            }
+            if (!small) {
+                __syncthreads();
+                for (int cidx = tid; cidx < C; cidx += AGG_THREADS) {   // the 8 warp tables of a cell -> one global reduction
+                    long long lo = 0, hi = 0;
+                    unsigned seen = 0;
+#pragma unroll
+                    for (int w = 0; w < W; ++w) {
+                        seen |= t_present[w * Cp + cidx];
+                        lo += t_lo[w * Cp + cidx]; hi += t_hi[w * Cp + cidx];
+                        t_lo[w * Cp + cidx] = 0; t_hi[w * Cp + cidx] = 0; t_present[w * Cp + cidx] = 0;
+                    }
+                    if (seen) {
+                        atomicAdd(reinterpret_cast<unsigned long long *>(out_s + cidx), (unsigned long long)(hi * 65536 + lo));
+                        out_p[cidx] = 1;
+                    }
+                }
+                __syncthreads();
+            }
+            pa = pb;
+        }
+    }
+    if (dropped) atomicAdd(p.dropped, (unsigned long long)dropped);
+}
+
 // ---- any row order, large users: no atomics on the hot path either ------------------------------------------------
 // The shared-memory atomic unit retires about one lane per clock and SM, which caps aggregate_kernel at ~3.5 ms per 1B rows
 // (0.38 of the HBM rate) however the cells are laid out. This kernel spends plain loads and stores instead:
@@ -861,10 +1013,17 @@ static int32_t agg_launch(fcb_engine *e, int device, int num_sms, int dates_sort
         // months, 256 B per cell), else the shared-atomic kernel. FCB_AGG_LARGE=atomic forces the latter (A/B runs).
         const size_t smem_b = (size_t)C * 32 * 8 + (size_t)4096 * 8 + (size_t)((p.n_days + 3) & ~3) * 2 +
                               (size_t)(2 * AGB_WARPS * 16 + 17) * 4 + 16;
-        const char *large = getenv("FCB_AGG_LARGE");
-        if (n_categories <= 16 && n_months <= 32 && smem_b <= 200 * 1024 && !(large && large[0] == 'a')) {
+        const int Cp = (C + 3) & ~3;
+        const size_t smem_c = (size_t)(AGG_THREADS / 32) * Cp * 10 + (size_t)((p.n_days + 1) & ~1) * 2 + 16;
+        const char *large = getenv("FCB_AGG_LARGE");                // "atomic" / "bucket" / "claim" (A/B runs)
+        const char mode = large ? large[0] : 'c';
+        if (mode == 'b' && n_categories <= 16 && n_months <= 32 && smem_b <= 200 * 1024) {
             FCB_CUDA(e, cudaFuncSetAttribute(aggregate_bucket_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_b));
             aggregate_bucket_kernel<<<num_sms, AGB_THREADS, smem_b, st>>>(p);
+        } else if (mode == 'c' && smem_c <= 56 * 1024) {
+            if (smem_c > 48 * 1024)
+                FCB_CUDA(e, cudaFuncSetAttribute(aggregate_claim_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_c));
+            aggregate_claim_kernel<<<num_sms * 4, AGG_THREADS, smem_c, st>>>(p);
         } else {
             aggregate_kernel<<<num_sms * 4, AGG_THREADS, smem, st>>>(p);
         }

@@ -244,12 +244,12 @@ def test_group_by_over_retrieved_points_equals_pandas_on_their_payloads(built, i
     eng.close()
 
 
-def test_bucket_kernel_equals_atomic_kernel_and_pandas_on_awkward_shapes(built, monkeypatch):
-    """Users of at least 8192 rows take the atomic-free bucket kernel (rows bucketed by category through shared memory,
-    lane-private month bins). Awkward shapes: user starts that are not multiples of 4 (ragged quads), sizes around the
+def test_atomic_free_any_order_kernels_equal_atomic_kernel_and_pandas_on_awkward_shapes(built, monkeypatch):
+    """Users of at least 8192 rows take an atomic-free kernel: by default warp-private tables with claim rounds
+    (aggregate_claim_kernel); FCB_AGG_LARGE=bucket selects the category-bucket kernel. Awkward shapes: user starts that are not multiples of 4 (ragged quads), sizes around the
     8192-row threshold and around the 4092-row pass length, a user spanning several 64k-row blocks, rows outside the
-    category / month window (must be counted as dropped, identically), full-range int32 values. The dense outputs must be
-    identical to the shared-atomic kernel's (FCB_AGG_LARGE=atomic) and equal pandas."""
+    category / month window (must be counted as dropped, identically), full-range int32 values. The dense outputs of all
+    three must be identical (FCB_AGG_LARGE=atomic is the shared-atomic kernel) and equal pandas."""
     import torch
     from financial_chatbot_llm_b200 import synth
     from financial_chatbot_llm_b200.engine import aggregate_columns
@@ -269,18 +269,19 @@ def test_bucket_kernel_equals_atomic_kernel_and_pandas_on_awkward_shapes(built, 
     dd, cc, vv, oo = (torch.from_numpy(a).to(dev) for a in (d, c, v, off))
     mlo = int(groupby.month_index(np.array([synth.DATE_BASE]))[0])
     res = {}
-    for mode in ("bucket", "atomic"):
-        if mode == "atomic":
-            monkeypatch.setenv("FCB_AGG_LARGE", "atomic")
+    for mode in ("claim", "bucket", "atomic"):
+        monkeypatch.setenv("FCB_AGG_LARGE", mode)
         sums, present, dropped = aggregate_columns(0, dd, cc, vv, oo, 0, len(sizes), mlo, 24, 16)
         torch.cuda.synchronize()
         res[mode] = (sums.cpu().numpy(), present.cpu().numpy(), int(dropped.item()))
-    assert np.array_equal(res["bucket"][0], res["atomic"][0]) and np.array_equal(res["bucket"][1], res["atomic"][1])
+    for mode in ("claim", "bucket"):
+        assert np.array_equal(res[mode][0], res["atomic"][0]) and np.array_equal(res[mode][1], res["atomic"][1]), mode
     keep = (c < 16) & (d >= synth.DATE_BASE)
-    assert res["bucket"][2] == res["atomic"][2] == int((~keep).sum())
+    assert res["claim"][2] == res["bucket"][2] == res["atomic"][2] == int((~keep).sum())
     ser = groupby.groupby_user_category_month(synth.row_users(off, np.arange(n))[keep], c[keep], d[keep], v[keep])
     idx = ser.index.to_frame(index=False)
-    sums, present, _ = res["bucket"]
+    monkeypatch.delenv("FCB_AGG_LARGE")
+    sums, present, _ = res["claim"]
     assert int(present.sum()) == len(ser)
     assert sums[idx["user"].to_numpy(), idx["category"].to_numpy(), idx["month"].to_numpy() - mlo].tolist() == ser.tolist()
     # a sub-range of users and a shard that starts in the middle of the columns (row_base > 0)

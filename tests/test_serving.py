@@ -128,3 +128,42 @@ def test_server_with_real_engine_matches_oracle(tmp_path, built):
     srv.stop()
     eng.close()
     assert not bad and srv.stats["requests"] == 180 and srv.stats["max_batch"] >= 2
+
+
+def test_frames_carry_no_pickle_and_the_socket_is_private(tmp_path):
+    """The wire format is a fixed binary header + JSON + raw float64: requests round-trip exactly, a malformed frame is
+    answered with an error (never executed), and the socket file is mode 0600 (same-user trust boundary)."""
+    import inspect
+    import socket
+    import stat
+    src = inspect.getsource(serving)
+    assert "import pickle" not in src and "multiprocessing.connection" not in src.split('"""', 2)[2]
+    flt = m.Filter(must=[m.FieldCondition(key="metadata.user_id", match=m.MatchValue(value="bob")),
+                         m.FieldCondition(key="metadata.date", range=m.Range(gte=1700000000))],
+                   must_not=[m.FieldCondition(key="metadata.category", match=m.MatchAny(any=["Rent", "Fuel"]))])
+    q = np.array([0.1, -2.5e-7, 3.0, 1e300])
+    msg = serving.decode_request(serving.encode_request("transactions", q.tolist(), flt, 7, 2, False, 0.25))
+    assert msg["collection_name"] == "transactions" and msg["limit"] == 7 and msg["offset"] == 2
+    assert msg["with_payload"] is False and msg["score_threshold"] == 0.25 and msg["query"].tolist() == q.tolist()
+    assert msg["query_filter"] == flt
+    assert serving.decode_request(serving.encode_request("t", q, None, 1, None, True, None))["query_filter"] is None
+    with pytest.raises(ValueError):
+        serving.decode_request(b"not a frame at all, but long enough to hold a header ...............")
+
+    eng = FakeEngine()
+    col = client.Collection("transactions", eng, ["alice"], np.array([0, 3]), lambda row: {"page_content": "x", "metadata": {"user_id": "alice"}})
+    addr = str(tmp_path / "p.sock")
+    srv = serving.EngineServer(col, addr).start()
+    try:
+        assert stat.S_IMODE(os.stat(addr).st_mode) == 0o600
+        raw = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+        raw.connect(addr)
+        serving._send_frame(raw, b"\\x80\\x04garbage that a pickle-based server would have tried to load")
+        import json as _json
+        assert "error" in _json.loads(serving._recv_frame(raw))
+        raw.close()
+        cl = serving.EngineClient(address=addr)                       # the server is still serving
+        assert [p.id for p in cl.query_points("transactions", query=[1.0, 0, 0, 0], limit=2, query_filter=user_filter("alice")).points] == [0, 1]
+        cl.close()
+    finally:
+        srv.stop()
