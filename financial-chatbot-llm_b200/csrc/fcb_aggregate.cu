@@ -526,402 +526,6 @@ __global__ void __launch_bounds__(AGG_THREADS, AGS_CTAS) aggregate_sorted_kernel
     if (dropped) atomicAdd(p.dropped, (unsigned long long)dropped);
 }
 
-// ---- any row order without shared atomics: warp-private tables + a claim round --------------------------------------
-// The shared-memory atomic unit retires about one lane per clock and SM: one ATOMS per row caps aggregate_kernel at ~3.5 ms
-// per 1B rows (0.38 of the HBM rate) however the cells are laid out. Plain loads and stores run at 32 lanes per clock — what
-// they lack is protection against two lanes of ONE instruction hitting the same cell (with 384 cells that happens to ~1.3
-// pairs of lanes per 32 rows). So every warp gets a PRIVATE [category, month] table (no other warp ever touches it), and a
-// step of 32 rows goes through claim rounds: every pending lane stores its lane number into claim[cell], the warp
-// synchronises, and the lane that reads its own number back has won the cell for this round — it adds its value with a plain
-// load / add / store; the losers (same cell, other lane) go round again. ~1.8 rounds per step on random cells, most of the
-// second round's lanes idle. 32-bit cells with the lo/hi split of aggregate_kernel: a warp sees 512 rows of a tile, so
-// nothing overflows. At the end of a piece the 8 warp tables are summed per cell by the CTA and leave as one 64-bit global
-// reduction per observed cell, exactly like aggregate_kernel's shared cells.
-__device__ __forceinline__ void agg_claim_add(bool valid, int cell, int32_t v, int32_t *w_lo, int32_t *w_hi, uint8_t *w_claim,
-                                              uint8_t *w_present, int lane) {
-    bool mine = valid;
-    unsigned pend = __ballot_sync(FCB_FULL, mine);
-    while (pend) {
-        if (mine) w_claim[cell] = (uint8_t)lane;
-        __syncwarp();
-        const bool win = mine && w_claim[cell] == (uint8_t)lane;
-        __syncwarp();                                          // every read of this round's claims before the next round's writes
-        if (win) {
-            if (v > -(1 << 18) && v < (1 << 18)) {
-                w_lo[cell] += v;
-            } else {
-                const int32_t lo16 = (int32_t)(int16_t)(v & 0xffff);
-                w_lo[cell] += lo16;
-                w_hi[cell] += (int32_t)(((int64_t)v - lo16) >> 16);
-            }
-            w_present[cell] = 1;
-            mine = false;
-        }
-        __syncwarp();                                          // the winner's store before a loser's load of the same cell
-        pend = __ballot_sync(FCB_FULL, mine);
-    }
-}
-
-__global__ void __launch_bounds__(AGG_THREADS, 4) aggregate_claim_kernel(const __grid_constant__ AggParams p) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    const int C = p.n_categories * p.n_months;
-    const int Cp = (C + 3) & ~3;                                       // per-warp table stride (cells), 16-byte friendly
-    constexpr int W = AGG_THREADS / 32;
-    int32_t *t_lo = reinterpret_cast<int32_t *>(smem_raw);             // [W][Cp]
-    int32_t *t_hi = t_lo + W * Cp;                                     // [W][Cp]
-    uint16_t *month_tab = reinterpret_cast<uint16_t *>(t_hi + W * Cp); // [n_days]
-    uint8_t *t_claim = reinterpret_cast<uint8_t *>(month_tab + ((p.n_days + 1) & ~1));   // [W][Cp]
-    uint8_t *t_present = t_claim + W * Cp;                             // [W][Cp]
-    __shared__ int64_t s_piece[2];
-
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    int32_t *w_lo = t_lo + warp * Cp, *w_hi = t_hi + warp * Cp;
-    uint8_t *w_claim = t_claim + warp * Cp, *w_present = t_present + warp * Cp;
-    for (int i = tid; i < p.n_days; i += AGG_THREADS) month_tab[i] = (uint16_t)(month_of_day(p.day0 + i) - p.month_lo);
-    for (int i = tid; i < W * Cp; i += AGG_THREADS) { t_lo[i] = 0; t_hi[i] = 0; t_present[i] = 0; t_claim[i] = 0xff; }
-    __syncthreads();
-
-    int64_t R0 = p.seg_offsets[p.seg_begin], R1 = p.seg_offsets[p.seg_end];
-    if (R0 < p.row_base) R0 = p.row_base;
-    if (R1 > p.row_base + p.n_rows) R1 = p.row_base + p.n_rows;
-    const int64_t n_tiles = R1 > R0 ? (R1 - R0 + AGG_TILE - 1) / AGG_TILE : 0;
-    unsigned dropped = 0;
-    const int4 *cents4 = reinterpret_cast<const int4 *>(p.cents);
-    const int4 *dates4 = reinterpret_cast<const int4 *>(p.dates);
-    const uchar4 *cats4 = reinterpret_cast<const uchar4 *>(p.cats);
-
-    for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x) {
-        const int64_t a = R0 + t * AGG_TILE;
-        const int64_t b = a + AGG_TILE < R1 ? a + AGG_TILE : R1;
-        if (tid == 0) {                                    // first user whose segment ends after a
-            int64_t lo = p.seg_begin, hi = p.seg_end - 1;
-            while (lo < hi) {
-                const int64_t mid = (lo + hi) >> 1;
-                if (p.seg_offsets[mid + 1] > a) hi = mid; else lo = mid + 1;
-            }
-            s_piece[0] = lo;
-        }
-        __syncthreads();
-        int64_t u = s_piece[0];
-        __syncthreads();
-        int64_t pa = a;
-        while (pa < b) {
-            int64_t uend = p.seg_offsets[u + 1];
-            while (uend <= pa) { ++u; uend = p.seg_offsets[u + 1]; }   // skip empty users
-            const int64_t pb = uend < b ? uend : b;
-            if (p.split == 1 && uend - p.seg_offsets[u] < AGS_TABLE_USER) { pa = pb; continue; }   // the other launch's user
-            int64_t *out_s = p.sums + (u - p.seg_begin) * (int64_t)C;
-            uint8_t *out_p = p.present + (u - p.seg_begin) * (int64_t)C;
-            const bool small = pb - pa < p.small_piece;
-            const int64_t la = pa - p.row_base, lb = pb - p.row_base;
-            const int64_t q0 = la >> 2, q1 = (lb + 3) >> 2;            // quads [q0, q1) cover [la, lb)
-            for (int64_t qb = q0; qb < q1; qb += AGG_THREADS) {       // warp-uniform trip count: the claim rounds are warp-wide
-                const int64_t q = qb + tid, r = q << 2;
-                int v[4] = {0, 0, 0, 0}, d[4] = {0, 0, 0, 0};
-                unsigned c[4] = {0, 0, 0, 0};
-                unsigned in = 0;
-                if (q < q1) {
-                    if (r >= la && r + 4 <= lb) {                       // interior quad: three vector loads
-                        const int4 vv = __ldg(cents4 + q), dd = __ldg(dates4 + q);
-                        const uchar4 cc = __ldg(cats4 + q);
-                        v[0] = vv.x; v[1] = vv.y; v[2] = vv.z; v[3] = vv.w;
-                        d[0] = dd.x; d[1] = dd.y; d[2] = dd.z; d[3] = dd.w;
-                        c[0] = cc.x; c[1] = cc.y; c[2] = cc.z; c[3] = cc.w;
-                        in = 0xfu;
-                    } else {                                            // ragged head / tail of the piece
-#pragma unroll
-                        for (int i = 0; i < 4; ++i)
-                            if (r + i >= la && r + i < lb) { v[i] = p.cents[r + i]; d[i] = p.dates[r + i]; c[i] = p.cats[r + i]; in |= 1u << i; }
-                    }
-                }
-#pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    bool valid = (in >> i) & 1u;
-                    int cell = 0;
-                    if (valid) {
-                        const int32_t di = floor_day(d[i]) - p.day0;
-                        const unsigned mo = (unsigned)di < (unsigned)p.n_days ? month_tab[di] : 0xffffu;
-                        if (c[i] >= (unsigned)p.n_categories || mo >= (unsigned)p.n_months) { ++dropped; valid = false; }
-                        else cell = c[i] * p.n_months + mo;
-                    }
-                    if (small) {                                        // tiny piece: straight to the global cells
-                        if (valid) {
-                            atomicAdd(reinterpret_cast<unsigned long long *>(out_s + cell), (unsigned long long)(long long)v[i]);
-                            out_p[cell] = 1;
-                        }
-                    } else {
-                        agg_claim_add(valid, cell, v[i], w_lo, w_hi, w_claim, w_present, lane);
-                    }
-                }
-            }
-            if (!small) {
-                __syncthreads();
-                for (int cidx = tid; cidx < C; cidx += AGG_THREADS) {   // the 8 warp tables of a cell -> one global reduction
-                    long long lo = 0, hi = 0;
-                    unsigned seen = 0;
-#pragma unroll
-                    for (int w = 0; w < W; ++w) {
-                        seen |= t_present[w * Cp + cidx];
-                        lo += t_lo[w * Cp + cidx]; hi += t_hi[w * Cp + cidx];
-                        t_lo[w * Cp + cidx] = 0; t_hi[w * Cp + cidx] = 0; t_present[w * Cp + cidx] = 0;
-                    }
-                    if (seen) {
-                        atomicAdd(reinterpret_cast<unsigned long long *>(out_s + cidx), (unsigned long long)(hi * 65536 + lo));
-                        out_p[cidx] = 1;
-                    }
-                }
-                __syncthreads();
-            }
-            pa = pb;
-        }
-    }
-    if (dropped) atomicAdd(p.dropped, (unsigned long long)dropped);
-}
-
-// ---- any row order, large users: no atomics on the hot path either ------------------------------------------------
-// The shared-memory atomic unit retires about one lane per clock and SM, which caps aggregate_kernel at ~3.5 ms per 1B rows
-// (0.38 of the HBM rate) however the cells are laid out. This kernel spends plain loads and stores instead:
-//   1. a pass takes up to 4096 consecutive rows of ONE user (512 threads x 8 rows, 128-bit column loads);
-//   2. the rows are BUCKETED BY CATEGORY through shared memory without atomics: per 32 rows the four bits of the category
-//      are turned into four ballots, every lane derives the mask of the lanes sharing its category (its rank inside the
-//      step) and lane c the mask of category c (the warp's running count); a 16 x 16 table of warp counts gives every
-//      (warp, category) its slice of the staging buffer, and each row is stored there as (month, cents);
-//   3. warp c then walks bucket c: lane l adds the cents of its row to bins[c][month][l] — a column of 64-bit bins that is
-//      private to the lane (one bank pair per lane: conflict-free, collision-free, plain load / add / store).
-// The bins stay in shared memory (categories x months x 32 lanes x 8 B = 96 KB for 16 x 24) while the passes of one user
-// follow each other; when the user changes, warp c sums its columns (skewed, conflict-free), sends one 64-bit global
-// reduction per observed cell and clears them. That flush reads and clears all 96 KB (~2000 clocks), which is why only users
-// of at least AGS_TABLE_USER rows come here — the others take the warp-table path of aggregate_sorted_kernel (split = 2).
-// Work = blocks of 16 passes' worth of rows, dealt round-robin to a persistent grid, so a CTA stays on one user for a while.
-// The columns of the next pass are requested right after the scatter and arrive during the reduce.
-#define AGB_THREADS 512
-#define AGB_WARPS (AGB_THREADS / 32)
-#define AGB_PASS_ROWS 4092                 // rows per pass: 8 per thread, minus one quad so that an unaligned start still fits 1024 quads
-#define AGB_BLOCK_ROWS (16 * 4096)
-#define AGB_MAX_PIECES 48                  // passes one block can hold (>= 16 + the user boundaries inside it; more: the block is split)
-
-struct AgbPiece { int64_t user, a, b; };   // global rows [a, b) of `user`
-
-__global__ void __launch_bounds__(AGB_THREADS, 1) aggregate_bucket_kernel(const __grid_constant__ AggParams p) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    const int C = p.n_categories * p.n_months;
-    long long *bins = reinterpret_cast<long long *>(smem_raw);                                       // [n_categories][n_months][32]
-    unsigned long long *stage = reinterpret_cast<unsigned long long *>(bins + (size_t)C * 32);       // [4096]
-    uint16_t *month_tab = reinterpret_cast<uint16_t *>(stage + 4096);                                // [n_days]
-    uint32_t *wcnt = reinterpret_cast<uint32_t *>(month_tab + ((p.n_days + 3) & ~3));                // [AGB_WARPS][16] rows of the pass per warp and category
-    uint32_t *woff = wcnt + AGB_WARPS * 16;                                                          // [AGB_WARPS][16] where that slice starts in `stage`
-    uint32_t *cat_lo = woff + AGB_WARPS * 16;                                                        // [17] bucket boundaries
-    __shared__ AgbPiece pieces[AGB_MAX_PIECES];
-    __shared__ int n_pieces;
-    __shared__ int64_t s_resume;               // >= 0: the block held more passes than the list takes; continue from this row
-    __shared__ int64_t s_urange[2], s_large[16];
-    __shared__ int s_nlarge;
-
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const unsigned lt_mask = (1u << lane) - 1u;
-    for (int i = tid; i < p.n_days; i += AGB_THREADS) month_tab[i] = (uint16_t)(month_of_day(p.day0 + i) - p.month_lo);
-    for (int i = tid; i < C * 32; i += AGB_THREADS) bins[i] = 0;
-    __syncthreads();
-
-    int64_t R0 = p.seg_offsets[p.seg_begin], R1 = p.seg_offsets[p.seg_end];
-    if (R0 < p.row_base) R0 = p.row_base;
-    if (R1 > p.row_base + p.n_rows) R1 = p.row_base + p.n_rows;
-    const int64_t n_blocks = R1 > R0 ? (R1 - R0 + AGB_BLOCK_ROWS - 1) / AGB_BLOCK_ROWS : 0;
-    const int4 *cents4 = reinterpret_cast<const int4 *>(p.cents);
-    const int4 *dates4 = reinterpret_cast<const int4 *>(p.dates);
-    const uchar4 *cats4 = reinterpret_cast<const uchar4 *>(p.cats);
-    unsigned dropped = 0;
-    int64_t cur_user = -1;                                     // the user this warp's bins belong to
-    uint32_t seen = 0;                                         // months this lane has added to since the last flush
-
-    // warp `warp` owns category `warp`: sum its columns, one 64-bit reduction per observed cell, clear
-    auto flush = [&]() {
-        if (cur_user >= 0 && warp < p.n_categories) {
-            const uint32_t any = __reduce_or_sync(FCB_FULL, seen);
-            if (any) {
-                long long *mine = bins + (size_t)warp * p.n_months * 32;
-                if (lane < p.n_months) {
-                    long long total = 0;
-#pragma unroll 8
-                    for (int i = 0; i < 32; ++i) {
-                        const int col = (i + lane) & 31;
-                        total += mine[lane * 32 + col];
-                        mine[lane * 32 + col] = 0;
-                    }
-                    if ((any >> lane) & 1u) {
-                        const int64_t cell = (cur_user - p.seg_begin) * (int64_t)C + warp * p.n_months + lane;
-                        atomicAdd(reinterpret_cast<unsigned long long *>(p.sums + cell), (unsigned long long)total);
-                        p.present[cell] = 1;
-                    }
-                }
-                __syncwarp();
-            }
-        }
-        seen = 0;
-    };
-
-    // the 8 rows of this thread in the pass [la, lb) (LOCAL rows): quads tid and tid + 512, counted from the aligned start
-    struct Rows { int4 v[2], d[2]; uchar4 c[2]; unsigned in; };
-    auto load_rows = [&](int64_t la, int64_t lb) {
-        Rows r;
-        r.in = 0;
-        const int64_t q0 = la >> 2;
-#pragma unroll
-        for (int j = 0; j < 2; ++j) {
-            const int64_t q = q0 + tid + j * AGB_THREADS, row = q << 2;
-            r.v[j] = make_int4(0, 0, 0, 0); r.d[j] = make_int4(0, 0, 0, 0); r.c[j] = make_uchar4(0, 0, 0, 0);
-            if (row >= la && row + 4 <= lb) {
-                r.v[j] = __ldg(cents4 + q); r.d[j] = __ldg(dates4 + q); r.c[j] = __ldg(cats4 + q);
-                r.in |= 0xfu << (4 * j);
-            } else if (row + 4 > la && row < lb) {             // ragged head / tail of the pass
-                int v[4] = {0, 0, 0, 0}, d[4] = {0, 0, 0, 0};
-                unsigned char c[4] = {0, 0, 0, 0};
-#pragma unroll
-                for (int i = 0; i < 4; ++i)
-                    if (row + i >= la && row + i < lb) { v[i] = p.cents[row + i]; d[i] = p.dates[row + i]; c[i] = p.cats[row + i]; r.in |= 1u << (4 * j + i); }
-                r.v[j] = make_int4(v[0], v[1], v[2], v[3]); r.d[j] = make_int4(d[0], d[1], d[2], d[3]);
-                r.c[j] = make_uchar4(c[0], c[1], c[2], c[3]);
-            }
-        }
-        return r;
-    };
-
-    if (tid == 0) s_resume = -1;
-    __syncthreads();
-    for (int64_t blk = blockIdx.x; blk < n_blocks;) {
-        const int64_t ba_full = R0 + blk * AGB_BLOCK_ROWS;
-        const int64_t bb = ba_full + AGB_BLOCK_ROWS < R1 ? ba_full + AGB_BLOCK_ROWS : R1;
-        // ---- the passes of this block: rows of users with at least AGS_TABLE_USER rows, cut at user boundaries and every
-        //      AGB_PASS_ROWS rows, in row order. The users touching the block are examined by all threads (a block in the
-        //      long tail of small users holds hundreds of them and none to do); one thread then lays out the few large ones.
-        const int64_t ba = s_resume >= 0 ? s_resume : ba_full;
-        if (tid == 0 || tid == 32) {
-            const int64_t key = tid == 0 ? ba : bb - 1;        // first user whose segment ends after `key`
-            int64_t lo = p.seg_begin, hi = p.seg_end - 1;
-            while (lo < hi) {
-                const int64_t mid = (lo + hi) >> 1;
-                if (p.seg_offsets[mid + 1] > key) hi = mid; else lo = mid + 1;
-            }
-            s_urange[tid == 0 ? 0 : 1] = lo;
-            if (tid == 0) s_nlarge = 0;
-        }
-        __syncthreads();
-        for (int64_t u = s_urange[0] + tid; u <= s_urange[1]; u += AGB_THREADS)
-            if (p.seg_offsets[u + 1] - p.seg_offsets[u] >= AGS_TABLE_USER) {
-                const int slot = atomicAdd(&s_nlarge, 1);
-                if (slot < 16) s_large[slot] = u;              // a 64k-row block cannot touch more than 10 users of >= 8192 rows
-            }
-        __syncthreads();
-        if (tid == 0) {
-            s_resume = -1;
-            int nl = s_nlarge < 16 ? s_nlarge : 16, n = 0;
-            for (int i = 1; i < nl; ++i) {                     // ascending user order = row order
-                const int64_t x = s_large[i];
-                int j = i - 1;
-                while (j >= 0 && s_large[j] > x) { s_large[j + 1] = s_large[j]; --j; }
-                s_large[j + 1] = x;
-            }
-            for (int i = 0; i < nl && s_resume < 0; ++i) {
-                const int64_t u = s_large[i];
-                const int64_t ua = p.seg_offsets[u] > ba ? p.seg_offsets[u] : ba;
-                const int64_t ub = p.seg_offsets[u + 1] < bb ? p.seg_offsets[u + 1] : bb;
-                for (int64_t a = ua; a < ub; a += AGB_PASS_ROWS) {
-                    if (n == AGB_MAX_PIECES) { s_resume = a; break; }
-                    pieces[n].user = u; pieces[n].a = a; pieces[n].b = a + AGB_PASS_ROWS < ub ? a + AGB_PASS_ROWS : ub;
-                    ++n;
-                }
-            }
-            n_pieces = n;
-        }
-        __syncthreads();
-        const int np = n_pieces;
-        const bool more = s_resume >= 0;                       // the same block again (uniform: read between two barriers)
-
-        Rows rows;
-        if (np > 0) rows = load_rows(pieces[0].a - p.row_base, pieces[0].b - p.row_base);
-        for (int pi = 0; pi < np; ++pi) {
-            const int64_t user = pieces[pi].user;
-            // ---- months, validity; category ballots -> rank inside the step and the warp's running counts
-            unsigned cat[8], mon[8];
-            int val[8];
-            {
-                const int vv[8] = {rows.v[0].x, rows.v[0].y, rows.v[0].z, rows.v[0].w, rows.v[1].x, rows.v[1].y, rows.v[1].z, rows.v[1].w};
-                const int dd[8] = {rows.d[0].x, rows.d[0].y, rows.d[0].z, rows.d[0].w, rows.d[1].x, rows.d[1].y, rows.d[1].z, rows.d[1].w};
-                const unsigned cc[8] = {rows.c[0].x, rows.c[0].y, rows.c[0].z, rows.c[0].w, rows.c[1].x, rows.c[1].y, rows.c[1].z, rows.c[1].w};
-#pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                    val[j] = vv[j];
-                    cat[j] = cc[j];
-                    mon[j] = 0xffffu;
-                    if ((rows.in >> j) & 1u) {
-                        const int32_t di = floor_day(dd[j]) - p.day0;
-                        const unsigned mo = (unsigned)di < (unsigned)p.n_days ? month_tab[di] : 0xffffu;
-                        if (cc[j] < (unsigned)p.n_categories && mo < (unsigned)p.n_months) mon[j] = mo; else ++dropped;
-                    }
-                }
-            }
-            unsigned my_cnt = 0;                               // lane c: rows of category c this warp has seen in the pass so far
-            unsigned pos[8];
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                const bool ok = mon[j] != 0xffffu;
-                const unsigned vm = __ballot_sync(FCB_FULL, ok);
-                const unsigned b0 = __ballot_sync(FCB_FULL, cat[j] & 1u), b1 = __ballot_sync(FCB_FULL, cat[j] & 2u),
-                               b2 = __ballot_sync(FCB_FULL, cat[j] & 4u), b3 = __ballot_sync(FCB_FULL, cat[j] & 8u);
-                const unsigned same = vm & ((cat[j] & 1u) ? b0 : ~b0) & ((cat[j] & 2u) ? b1 : ~b1) &
-                                      ((cat[j] & 4u) ? b2 : ~b2) & ((cat[j] & 8u) ? b3 : ~b3);       // valid lanes with my category
-                const unsigned of_lane = vm & ((lane & 1) ? b0 : ~b0) & ((lane & 2) ? b1 : ~b1) &
-                                         ((lane & 4) ? b2 : ~b2) & ((lane & 8) ? b3 : ~b3);          // valid lanes with category `lane`
-                const unsigned before = __shfl_sync(FCB_FULL, my_cnt, cat[j] & 15u);
-                pos[j] = before + __popc(same & lt_mask);
-                if (lane < 16) my_cnt += __popc(of_lane);
-            }
-            if (lane < 16) wcnt[warp * 16 + lane] = my_cnt;
-            __syncthreads();
-            // ---- slices of the staging buffer: bucket c = [cat_lo[c], cat_lo[c + 1]), warp w's part of it starts at woff[w][c]
-            if (tid < 16) {
-                unsigned tot = 0;
-                for (int w = 0; w < AGB_WARPS; ++w) tot += wcnt[w * 16 + tid];
-                unsigned incl = tot;                           // inclusive scan over the 16 categories (lanes 0..15 of warp 0)
-#pragma unroll
-                for (int off = 1; off < 16; off <<= 1) {
-                    const unsigned up = __shfl_up_sync(0xffffu, incl, off, 16);
-                    if (tid >= off) incl += up;
-                }
-                unsigned run = incl - tot;
-                cat_lo[tid] = run;
-                if (tid == 15) cat_lo[16] = incl;
-                for (int w = 0; w < AGB_WARPS; ++w) { woff[w * 16 + tid] = run; run += wcnt[w * 16 + tid]; }
-            }
-            __syncthreads();
-#pragma unroll
-            for (int j = 0; j < 8; ++j)
-                if (mon[j] != 0xffffu)
-                    stage[woff[warp * 16 + (cat[j] & 15u)] + pos[j]] = ((unsigned long long)mon[j] << 32) | (unsigned)val[j];
-            // the next pass's columns are requested now and arrive during the reduce below
-            if (pi + 1 < np) rows = load_rows(pieces[pi + 1].a - p.row_base, pieces[pi + 1].b - p.row_base);
-            __syncthreads();
-            // ---- warp c walks bucket c: lane-private 64-bit bins per month
-            if (user != cur_user) { flush(); cur_user = user; }
-            if (warp < p.n_categories) {
-                long long *mine = bins + (size_t)warp * p.n_months * 32 + lane;
-                const unsigned e0 = cat_lo[warp], e1 = cat_lo[warp + 1];
-                for (unsigned i = e0 + lane; i < e1; i += 32) {
-                    const unsigned long long e = stage[i];
-                    const unsigned mo = (unsigned)(e >> 32);
-                    mine[mo * 32] += (long long)(int)(unsigned)e;
-                    seen |= 1u << mo;
-                }
-            }
-            // (the next pass's scatter happens two barriers from here: every warp has left this reduce by then)
-        }
-        __syncthreads();                                       // nobody still reads the pass list / s_resume when thread 0 rewrites them
-        if (!more) blk += gridDim.x;
-    }
-    flush();
-    if (dropped) atomicAdd(p.dropped, (unsigned long long)dropped);
-}
-
 // non-decreasing dates within every user of [seg_begin, seg_end)? (load-time check; writes 0 on a violation)
 __global__ void __launch_bounds__(256) dates_sorted_kernel(const int64_t *__restrict__ seg_offsets, int64_t n_segs,
                                                            const int32_t *__restrict__ dates, int64_t row_base,
@@ -1009,24 +613,7 @@ static int32_t agg_launch(fcb_engine *e, int device, int num_sms, int dates_sort
         p.split = 2;
         aggregate_sorted_kernel<<<num_sms * AGS_CTAS, AGG_THREADS, smem_s, st>>>(p);
         p.split = 1;
-        // users of at least AGS_TABLE_USER rows: the atomic-free bucket kernel when its bins fit (<= 16 categories, <= 32
-        // months, 256 B per cell), else the shared-atomic kernel. FCB_AGG_LARGE=atomic forces the latter (A/B runs).
-        const size_t smem_b = (size_t)C * 32 * 8 + (size_t)4096 * 8 + (size_t)((p.n_days + 3) & ~3) * 2 +
-                              (size_t)(2 * AGB_WARPS * 16 + 17) * 4 + 16;
-        const int Cp = (C + 3) & ~3;
-        const size_t smem_c = (size_t)(AGG_THREADS / 32) * Cp * 10 + (size_t)((p.n_days + 1) & ~1) * 2 + 16;
-        const char *large = getenv("FCB_AGG_LARGE");                // "atomic" / "bucket" / "claim" (A/B runs)
-        const char mode = large ? large[0] : 'c';
-        if (mode == 'b' && n_categories <= 16 && n_months <= 32 && smem_b <= 200 * 1024) {
-            FCB_CUDA(e, cudaFuncSetAttribute(aggregate_bucket_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_b));
-            aggregate_bucket_kernel<<<num_sms, AGB_THREADS, smem_b, st>>>(p);
-        } else if (mode == 'c' && smem_c <= 56 * 1024) {
-            if (smem_c > 48 * 1024)
-                FCB_CUDA(e, cudaFuncSetAttribute(aggregate_claim_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_c));
-            aggregate_claim_kernel<<<num_sms * 4, AGG_THREADS, smem_c, st>>>(p);
-        } else {
-            aggregate_kernel<<<num_sms * 4, AGG_THREADS, smem, st>>>(p);
-        }
+        aggregate_kernel<<<num_sms * 4, AGG_THREADS, smem, st>>>(p);
     } else if (use_sorted) {
         aggregate_sorted_kernel<<<num_sms * AGS_CTAS, AGG_THREADS, smem_s, st>>>(p);
     } else {

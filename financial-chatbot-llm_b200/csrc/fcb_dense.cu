@@ -91,7 +91,7 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity, int *e
     uint32_t spins = 0;
     while (!mbar_try_wait(bar, parity)) {
         if (++spins > DN_SPIN_LIMIT) {
-            atomicExch(error_flag, code);
+            *reinterpret_cast<volatile int *>(error_flag) = code;   // mapped pinned memory: the host reads it after the trap
             __threadfence_system();
             asm volatile("trap;");
         }
@@ -934,14 +934,23 @@ struct FcbDense {
     unsigned *gtop = nullptr;               // [DN_N][gt_stride] per-CTA best scores of the cta_group::2 kernel
     int gt_stride = 0;
     int32_t *redo = nullptr;                // [DN_N] flags, then [DN_N] compact list, then the count
-    int *error_flag = nullptr;
+    int *error_flag = nullptr;              // device alias of h_error (mapped pinned memory: readable by the host after a trap)
+    int *h_error = nullptr;
     int grid = 0;
 };
+
+// The bounded mbarrier waits of the tensor-core kernels write a code here and trap when the pipeline protocol is violated
+// (a bug, never an input): 1/11 producer, 2/12 MMA issuer waiting for drained accumulators, 3/13 for a full stage, 4/14
+// epilogue. The word lives in mapped pinned memory, so the host can still read it after the trap killed the context.
+int fcb_dense_error_code(const fcb_engine *e) {
+    const FcbDense *d = e ? reinterpret_cast<const FcbDense *>(e->dense) : nullptr;
+    return d && d->h_error ? *reinterpret_cast<volatile int *>(d->h_error) : 0;
+}
 
 void fcb_dense_free(fcb_engine *e) {
     FcbDense *d = reinterpret_cast<FcbDense *>(e->dense);
     if (!d) return;
-    cudaFree(d->q_bf16); cudaFree(d->slack); cudaFree(d->thr_out); cudaFree(d->widened); cudaFree(d->cta_top); cudaFree(d->pend); cudaFree(d->redo); cudaFree(d->error_flag); cudaFree(d->gtop);
+    cudaFree(d->q_bf16); cudaFree(d->slack); cudaFree(d->thr_out); cudaFree(d->widened); cudaFree(d->cta_top); cudaFree(d->pend); cudaFree(d->redo); cudaFreeHost(d->h_error); cudaFree(d->gtop);
     delete d;
     e->dense = nullptr;
 }
@@ -967,12 +976,13 @@ int32_t fcb_dense_alloc(fcb_engine *e) {
         cudaMalloc(&d->pend, lists * DN_PEND_CAP * sizeof(FcbCand)) != cudaSuccess ||
         cudaMalloc(&d->redo, (size_t)(2 * DN_N + 1) * sizeof(int32_t)) != cudaSuccess ||
         cudaMalloc(&d->gtop, (size_t)DN_N * d->gt_stride * sizeof(unsigned)) != cudaSuccess ||
-        cudaMalloc(&d->error_flag, sizeof(int)) != cudaSuccess) {
+        cudaHostAlloc(&d->h_error, sizeof(int), cudaHostAllocMapped) != cudaSuccess ||
+        cudaHostGetDevicePointer(&d->error_flag, d->h_error, 0) != cudaSuccess) {
         cudaGetLastError();
         fcb_dense_free(e);
         return fcb_fail(e, FCB_ERR_NOMEM, "fcb_load_shard: cannot allocate the batched-path scratch");
     }
-    FCB_CUDA(e, cudaMemset(d->error_flag, 0, sizeof(int)));
+    *d->h_error = 0;
     int32_t rc = encode_map(e, &d->map_x, s.vectors, (uint64_t)s.n_rows, (uint64_t)s.dim, DN_BLOCK_M);
     for (int i = 0; i < DN_N / 32 && rc == FCB_OK; ++i)
         rc = encode_map(e, &d->map_q[i], d->q_bf16, DN_N, (uint64_t)s.dim, 32 * (i + 1));

@@ -21,7 +21,15 @@ extern "C" int32_t fcb_abi_version(void) { return FCB_ABI_VERSION; }
 extern "C" int32_t fcb_shard_dates_sorted(const fcb_engine *e) { return e && e->loaded ? e->dates_sorted : -1; }
 
 extern "C" const char *fcb_last_error(const fcb_engine *e) {
-    return e ? e->err.c_str() : g_open_error.c_str();
+    if (!e) return g_open_error.c_str();
+    const int code = fcb_dense_error_code(e);                  // a trap in the batched tensor-core path: say so (once)
+    if (code != 0 && e->err.find("pipeline protocol") == std::string::npos) {
+        fcb_engine *m = const_cast<fcb_engine *>(e);
+        char buf[160];
+        snprintf(buf, sizeof buf, " [batched tensor-core kernel trapped: pipeline protocol violation, wait code %d]", code);
+        m->err += buf;
+    }
+    return e->err.c_str();
 }
 
 static void free_host_staging(fcb_engine *e) {

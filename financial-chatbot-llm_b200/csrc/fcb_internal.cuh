@@ -109,6 +109,7 @@ int32_t fcb_tune_scan(fcb_engine *e);            // fcb_search.cu: measure the s
 bool fcb_dense_eligible(const fcb_engine *e);
 int32_t fcb_dense_alloc(fcb_engine *e);
 void fcb_dense_free(fcb_engine *e);
+int fcb_dense_error_code(const fcb_engine *e);   // != 0: a tensor-core kernel trapped on a pipeline-protocol violation
 int32_t fcb_search_dense(fcb_engine *e, const double *d_queries, const fcb_filter &f, int32_t batch, int32_t k,
                          uint64_t *d_out_ids, double *d_out_scores, int32_t *d_out_counts, cudaStream_t st,
                          const int32_t **redo_list_out, const int32_t **redo_count_out);

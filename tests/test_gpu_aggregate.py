@@ -244,18 +244,18 @@ def test_group_by_over_retrieved_points_equals_pandas_on_their_payloads(built, i
     eng.close()
 
 
-def test_atomic_free_any_order_kernels_equal_atomic_kernel_and_pandas_on_awkward_shapes(built, monkeypatch):
-    """Users of at least 8192 rows take an atomic-free kernel: by default warp-private tables with claim rounds
-    (aggregate_claim_kernel); FCB_AGG_LARGE=bucket selects the category-bucket kernel. Awkward shapes: user starts that are not multiples of 4 (ragged quads), sizes around the
-    8192-row threshold and around the 4092-row pass length, a user spanning several 64k-row blocks, rows outside the
-    category / month window (must be counted as dropped, identically), full-range int32 values. The dense outputs of all
-    three must be identical (FCB_AGG_LARGE=atomic is the shared-atomic kernel) and equal pandas."""
+def test_any_order_kernels_on_awkward_shapes_equal_pandas(built, monkeypatch):
+    """The two-launch split of any-order data (users under 8192 rows: warp tables; the others: CTA-wide shared cells) on
+    awkward shapes: user starts that are not multiples of 4 (ragged quads), sizes around the 8192-row threshold and the
+    4096-row tile, a user spanning many tiles, rows outside the category / month window (counted as dropped), full-range
+    int32 values; the single-launch kernel (FCB_AGG_SPLIT=0) must give the identical dense output; both equal pandas; and
+    the engine-less entry point works on a sub-range of users over columns that start in the middle (row_base > 0)."""
     import torch
     from financial_chatbot_llm_b200 import synth
     from financial_chatbot_llm_b200.engine import aggregate_columns
     from oracle import groupby
     rng = np.random.default_rng(11)
-    sizes = np.array([3, 8191, 8192, 8193, 1, 4092 * 2 + 1, 200_001, 17, 8192 + 4093, 70_000, 5, 12_345], dtype=np.int64)
+    sizes = np.array([3, 8191, 8192, 8193, 1, 4096 * 2 + 1, 200_001, 17, 8192 + 4097, 70_000, 5, 12_345], dtype=np.int64)
     off = np.zeros(len(sizes) + 1, dtype=np.int64)
     np.cumsum(sizes, out=off[1:])
     n = int(off[-1])
@@ -269,22 +269,21 @@ def test_atomic_free_any_order_kernels_equal_atomic_kernel_and_pandas_on_awkward
     dd, cc, vv, oo = (torch.from_numpy(a).to(dev) for a in (d, c, v, off))
     mlo = int(groupby.month_index(np.array([synth.DATE_BASE]))[0])
     res = {}
-    for mode in ("claim", "bucket", "atomic"):
-        monkeypatch.setenv("FCB_AGG_LARGE", mode)
+    for mode in ("split", "single"):
+        if mode == "single":
+            monkeypatch.setenv("FCB_AGG_SPLIT", "0")
         sums, present, dropped = aggregate_columns(0, dd, cc, vv, oo, 0, len(sizes), mlo, 24, 16)
         torch.cuda.synchronize()
         res[mode] = (sums.cpu().numpy(), present.cpu().numpy(), int(dropped.item()))
-    for mode in ("claim", "bucket"):
-        assert np.array_equal(res[mode][0], res["atomic"][0]) and np.array_equal(res[mode][1], res["atomic"][1]), mode
+    monkeypatch.delenv("FCB_AGG_SPLIT")
+    assert np.array_equal(res["split"][0], res["single"][0]) and np.array_equal(res["split"][1], res["single"][1])
     keep = (c < 16) & (d >= synth.DATE_BASE)
-    assert res["claim"][2] == res["bucket"][2] == res["atomic"][2] == int((~keep).sum())
+    assert res["split"][2] == res["single"][2] == int((~keep).sum())
     ser = groupby.groupby_user_category_month(synth.row_users(off, np.arange(n))[keep], c[keep], d[keep], v[keep])
     idx = ser.index.to_frame(index=False)
-    monkeypatch.delenv("FCB_AGG_LARGE")
-    sums, present, _ = res["claim"]
+    sums, present, _ = res["split"]
     assert int(present.sum()) == len(ser)
     assert sums[idx["user"].to_numpy(), idx["category"].to_numpy(), idx["month"].to_numpy() - mlo].tolist() == ser.tolist()
-    # a sub-range of users and a shard that starts in the middle of the columns (row_base > 0)
     lo_u, hi_u = 5, 10
     a, b = int(off[lo_u]), int(off[hi_u])
     s2, p2, d2 = aggregate_columns(0, dd[a:b].contiguous(), cc[a:b].contiguous(), vv[a:b].contiguous(), oo, lo_u, hi_u, mlo, 24, 16,
