@@ -92,6 +92,7 @@ struct ExactParams {
     int64_t n_rows, row_base;
     int dim, k, batch;
     const int32_t *flags;
+    const int32_t *list, *list_count;      // optional (routed search): only these queries of the batch ran, look at their flags only
     uint64_t *keys;
     FcbExactState *st;
     FcbExactBarrier *bar;
@@ -145,14 +146,16 @@ __global__ void __launch_bounds__(EX_THREADS) exact_fallback_kernel(const __grid
     const T *__restrict__ vec = reinterpret_cast<const T *>(p.vectors);
 
     // the common case: nothing to do. Every CTA reads the same flags, so the decision is grid-uniform.
+    const int n_queries = p.list ? __ldcg(p.list_count) : p.batch;
     if (tid == 0) s_any = 0;
     __syncthreads();
-    for (int b = tid; b < p.batch; b += EX_THREADS)
-        if (__ldcg(p.flags + b) != 0) s_any = 1;
+    for (int i = tid; i < n_queries; i += EX_THREADS)
+        if (__ldcg(p.flags + (p.list ? __ldcg(p.list + i) : i)) != 0) s_any = 1;
     __syncthreads();
     if (!s_any) return;
 
-    for (int b = 0; b < p.batch; ++b) {
+    for (int i = 0; i < n_queries; ++i) {
+        const int b = p.list ? __ldcg(p.list + i) : i;
         if (__ldcg(p.flags + b) == 0) continue;                            // grid-uniform
         const fcb_filter f = p.use_inline == 2 ? p.inl[0] : (p.use_inline ? p.inl[b] : p.filters[b]);
         const double *__restrict__ qd = p.queries + (size_t)b * p.dim;
@@ -379,7 +382,8 @@ int32_t *fcb_exact_flags(fcb_engine *e) {
 // 1 = `inl[b]` (batch <= FCB_INLINE_FILTERS), 2 = `inl[0]` shared by every query.
 int32_t fcb_exact_enqueue(fcb_engine *e, const double *d_queries, const fcb_filter *d_filters, const fcb_filter *inl,
                           int filters_mode, int32_t batch, int32_t k, const int32_t *d_flags, uint64_t *d_out_ids,
-                          double *d_out_scores, int32_t *d_out_counts, cudaStream_t st) {
+                          double *d_out_scores, int32_t *d_out_counts, cudaStream_t st, const int32_t *d_list,
+                          const int32_t *d_list_count) {
     FcbExact *x = reinterpret_cast<FcbExact *>(e->exact);
     if (!x) return fcb_fail(e, FCB_ERR_STATE, "fcb_search: exact-path scratch missing");
     const fcb_shard &s = e->shard;
@@ -389,7 +393,7 @@ int32_t fcb_exact_enqueue(fcb_engine *e, const double *d_queries, const fcb_filt
     if (filters_mode == 1) for (int b = 0; b < batch && b < FCB_INLINE_FILTERS; ++b) p.inl[b] = inl[b];
     if (filters_mode == 2) p.inl[0] = inl[0];
     p.n_rows = s.n_rows; p.row_base = s.row_base; p.dim = s.dim; p.k = k; p.batch = batch;
-    p.flags = d_flags; p.keys = x->keys; p.st = x->state; p.bar = x->barrier;
+    p.flags = d_flags; p.list = d_list; p.list_count = d_list_count; p.keys = x->keys; p.st = x->state; p.bar = x->barrier;
     p.sel_keys = x->sel_keys; p.sel_rows = x->sel_rows; p.sel_ties = x->sel_ties;
     p.out_ids = d_out_ids; p.out_scores = d_out_scores; p.out_counts = d_out_counts; p.reruns = x->reruns;
     const size_t smem = (size_t)s.dim * sizeof(double);

@@ -120,7 +120,8 @@ void fcb_exact_free(fcb_engine *e);
 int32_t *fcb_exact_flags(fcb_engine *e);   // device [max_batch]
 int32_t fcb_exact_enqueue(fcb_engine *e, const double *d_queries, const fcb_filter *d_filters, const fcb_filter *inl,
                           int filters_mode, int32_t batch, int32_t k, const int32_t *d_flags, uint64_t *d_out_ids,
-                          double *d_out_scores, int32_t *d_out_counts, cudaStream_t st);
+                          double *d_out_scores, int32_t *d_out_counts, cudaStream_t st, const int32_t *d_list = nullptr,
+                          const int32_t *d_list_count = nullptr);
 
 // owner-computes exchange over peer memory (fcb_exchange.cu)
 __host__ __device__ inline size_t fcb_exchange_parity_bytes(int slots, int k) { return (size_t)slots * k * 16 + (size_t)slots * 8; }

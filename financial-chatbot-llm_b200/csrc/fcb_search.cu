@@ -563,7 +563,6 @@ extern "C" int32_t fcb_search_routed(fcb_engine *e, const fcb_exchange *x, const
         StagedFilters sf;
         rc = stage_filters(e, filters, batch, true, st, sf);
         if (rc != FCB_OK) return rc;
-        FCB_CUDA(e, cudaMemsetAsync(d_flags, 0, (size_t)batch * sizeof(int32_t), st));   // only the listed queries write theirs
         ScanParams p{};
         p.vectors = s.vectors; p.inv_norm = e->inv_norm; p.ids = s.ids; p.id_rank = s.id_rank;
         p.dates = s.dates; p.cats = s.categories; p.queries = queries;
@@ -579,7 +578,8 @@ extern "C" int32_t fcb_search_routed(fcb_engine *e, const fcb_exchange *x, const
         e->list_rows = 0;
         if (rc != FCB_OK) return rc;
         if (sf.max_rows >= FCB_FUSED_CAND) {
-            rc = fcb_exact_enqueue(e, queries, sf.d_filters, sf.inl, 0, batch, k, d_flags, d_ids, d_scores, d_counts, st);
+            rc = fcb_exact_enqueue(e, queries, sf.d_filters, sf.inl, 0, batch, k, d_flags, d_ids, d_scores, d_counts, st, d_subset,
+                                   d_count);                          // looks at the flags of the listed queries only
             if (rc != FCB_OK) return rc;
         }
     }
