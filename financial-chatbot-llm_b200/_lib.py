@@ -83,6 +83,7 @@ SIGNATURES = {
     "fcb_peer_alloc": (C.c_int32, [C.c_int32, C.c_int64, C.POINTER(C.c_void_p), C.c_void_p]),
     "fcb_peer_open": (C.c_int32, [C.c_int32, C.c_void_p, C.POINTER(C.c_void_p)]),
     "fcb_peer_close": (C.c_int32, [C.c_int32, C.c_void_p, C.c_int32]),
+    "fcb_debug_exchange_phases": (C.c_int32, [C.c_int32]),
     "fcb_search_routed": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_uint32,
                                       C.c_void_p, C.c_void_p]),
     "fcb_aggregate": (C.c_int32, [C.c_void_p, C.c_int64, C.c_int64, C.c_int32, C.c_int32, C.c_int32,

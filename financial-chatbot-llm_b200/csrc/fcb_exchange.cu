@@ -31,6 +31,7 @@ struct ExchangeParams {
     const double *scores;
     const int32_t *counts;
     int32_t *status;                       // device: set to 1 if a peer never delivered
+    int phases;                            // bit 0: push, bit 1: wait (both in production; see fcb_debug_exchange_phases)
 };
 
 __global__ void __launch_bounds__(XCH_THREADS) exchange_kernel(const __grid_constant__ ExchangeParams p) {
@@ -39,7 +40,7 @@ __global__ void __launch_bounds__(XCH_THREADS) exchange_kernel(const __grid_cons
     if (slot >= p.slots) return;
     const size_t par = (size_t)(p.seq & 1u) * fcb_exchange_parity_bytes(p.slots, p.k);
     const size_t off_scores = (size_t)p.slots * p.k * 8, off_counts = 2 * off_scores, off_stamps = off_counts + (size_t)p.slots * 4;
-    if (p.owner[slot] == p.rank) {
+    if ((p.phases & 1) && p.owner[slot] == p.rank) {
         // ---- push: k ids + k scores (+ the count) of this slot to every rank, then the stamp
         const int n = 2 * p.k;
         for (int g = 0; g < p.world; ++g) {
@@ -60,7 +61,7 @@ __global__ void __launch_bounds__(XCH_THREADS) exchange_kernel(const __grid_cons
         }
     }
     // ---- wait: this slot of MY buffer must carry the stamp (its owner may be me)
-    if (lane == 0) {
+    if ((p.phases & 2) && lane == 0) {
         volatile unsigned *mine = reinterpret_cast<volatile unsigned *>(p.bufs[p.rank] + par + off_stamps) + slot;
         unsigned spins = 0;
         while (*mine != p.seq) {
@@ -71,6 +72,17 @@ __global__ void __launch_bounds__(XCH_THREADS) exchange_kernel(const __grid_cons
     }
 }
 
+static int g_exchange_phases = 3;
+
+// Test hook: which halves of the exchange kernel run (bit 0: push this rank's results to every rank, bit 1: wait for
+// everybody's). Production = 3. Kernels that wait on one another must not be run as separate launches on ONE GPU (nothing
+// guarantees that they are resident together), so the single-GPU test plays two ranks with push-only exchanges and then
+// inspects both buffers; the wait half runs wherever every rank has its own GPU.
+extern "C" int32_t fcb_debug_exchange_phases(int32_t mask) {
+    g_exchange_phases = mask & 3;
+    return FCB_OK;
+}
+
 int32_t fcb_exchange_launch(fcb_engine *e, const fcb_exchange *x, int32_t slots, int32_t k, uint32_t seq, const int32_t *d_owner,
                             const uint64_t *d_ids, const double *d_scores, const int32_t *d_counts, int32_t *d_status,
                             cudaStream_t st) {
@@ -78,6 +90,7 @@ int32_t fcb_exchange_launch(fcb_engine *e, const fcb_exchange *x, int32_t slots,
     for (int g = 0; g < x->world; ++g) p.bufs[g] = reinterpret_cast<unsigned char *>(x->bufs[g]);
     p.world = x->world; p.rank = x->rank; p.slots = slots; p.k = k; p.seq = seq;
     p.owner = d_owner; p.ids = d_ids; p.scores = d_scores; p.counts = d_counts; p.status = d_status;
+    p.phases = g_exchange_phases;
     const int warps = XCH_THREADS / 32;
     exchange_kernel<<<(slots + warps - 1) / warps, XCH_THREADS, 0, st>>>(p);
     FCB_CUDA(e, cudaGetLastError());

@@ -285,6 +285,11 @@ int32_t fcb_peer_close(int32_t device, void *ptr, int32_t owned /* 1: from fcb_p
 int32_t fcb_search_routed(fcb_engine *e, const fcb_exchange *x, const double *queries, const fcb_filter *filters,
                           int32_t batch, int32_t k, uint32_t seq, int32_t *status, void *stream);
 
+/* Test hook for the exchange of fcb_search_routed: bit 0 = push this rank's results, bit 1 = wait for every rank's (3 = both,
+ * the production setting). Kernels of different ranks that wait on one another must each have their own GPU; a single-GPU
+ * test plays several ranks with push-only exchanges (mask 1) and inspects the buffers. Not for production use. */
+int32_t fcb_debug_exchange_phases(int32_t mask);
+
 /* 1 if fcb_load_shard found metadata.date non-decreasing within every user segment (a time-ordered
  * transaction log), 0 if not, -1 without a shard. fcb_aggregate then uses its atomic-free kernel; the
  * result is the same either way. */

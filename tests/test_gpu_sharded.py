@@ -111,10 +111,12 @@ def test_two_shards_on_one_gpu_client_payloads(built):
 
 def test_routed_search_two_ranks_on_one_gpu(built):
     """fcb_search_routed (owner-computes + peer-store exchange) on a 1-GPU box: two engines hold the two point ranges of a
-    corpus cut on a user boundary, each plays one rank on its own stream, and the two exchange buffers are ordinary
-    allocations of this process (on a multi-GPU box they are CUDA IPC mappings of the peers' memory; the kernels are the
-    same). Each rank scans only the queries it owns; after both calls have run, BOTH buffers must hold the oracle's
-    answer for every query — twice in a row, so the second exchange lands on the other parity."""
+    corpus cut on a user boundary and play the two ranks ONE AFTER THE OTHER on one stream, with the exchange kernel's
+    wait half switched off (fcb_debug_exchange_phases(1)): kernels that wait on one another must each have their own
+    GPU. The two exchange buffers are ordinary allocations of this process (on a multi-GPU box they are CUDA IPC mappings
+    of the peers' memory; the push is the same code). Each rank scans only the queries it owns; after both calls BOTH
+    buffers must hold the oracle's answer and the stamp for every query — three times, so both parities are used. The
+    wait half runs in the world-1 call at the end (its own stamps) and, between real GPUs, in the CUDA IPC test below."""
     import ctypes as C
     import torch
     from financial_chatbot_llm_b200 import _lib, loader, sharded, synth
@@ -139,9 +141,10 @@ def test_routed_search_two_ranks_on_one_gpu(built):
         ptrs.append(int(p.value))
     bufs = (C.c_void_p * _lib.FCB_MAX_WORLD)(*([C.c_void_p(p) for p in ptrs] + [None] * (_lib.FCB_MAX_WORLD - world)))
     xs = [_lib.FcbExchange(world, g, bufs, cuts.ctypes.data) for g in range(world)]
-    streams = [torch.cuda.Stream(device=dev) for _ in range(world)]
+    stream = torch.cuda.current_stream(dev).cuda_stream
     status = torch.zeros(world, dtype=torch.int32, device=dev)
     rng = np.random.default_rng(4)
+    lib.fcb_debug_exchange_phases(1)                                        # push only: nothing waits for another launch
     for seq in (1, 2, 3):
         users = rng.choice(spec.n_users, size=slots, replace=False)
         users[5] = 0                                                        # an empty filter rides along (count 0)
@@ -152,15 +155,17 @@ def test_routed_search_two_ranks_on_one_gpu(built):
         torch.cuda.synchronize()
         for g in range(world):
             _lib.check(lib.fcb_search_routed(engines[g]._h, C.byref(xs[g]), dq.data_ptr(), farr.ctypes.data, slots, K, seq,
-                                             status[g:].data_ptr(), C.c_void_p(streams[g].cuda_stream)), engines[g]._h)
+                                             status[g:].data_ptr(), C.c_void_p(stream)), engines[g]._h)
         torch.cuda.synchronize()
-        assert status.cpu().tolist() == [0, 0], "an exchange timed out"
+        assert status.cpu().tolist() == [0, 0]
         for g in range(world):
             base = ptrs[g] + (seq & 1) * (nbytes // 2)
             n = slots * K
             ids = torch.as_tensor(sharded._DevicePointer(base, (slots, K), "<i8"), device=dev).cpu().numpy().view(np.uint64)
             sc = torch.as_tensor(sharded._DevicePointer(base + 8 * n, (slots, K), "<f8"), device=dev).cpu().numpy()
             cnt = torch.as_tensor(sharded._DevicePointer(base + 16 * n, (slots,), "<i4"), device=dev).cpu().numpy()
+            stamps = torch.as_tensor(sharded._DevicePointer(base + 16 * n + 4 * slots, (slots,), "<i4"), device=dev).cpu().numpy()
+            assert stamps.tolist() == [seq] * slots, "every slot of every buffer carries this exchange's stamp"
             for b, u in enumerate(users):
                 if b == 5:
                     assert cnt[b] == 0
@@ -171,12 +176,27 @@ def test_routed_search_two_ranks_on_one_gpu(built):
     # a range that spans both shards is refused (it needs a merge: fcb_search + all-gather + fcb_merge_topk)
     bad = sharded.filters_array(np.full(slots, cuts[1] - 10), np.full(slots, cuts[1] + 10))
     rc = lib.fcb_search_routed(engines[0]._h, C.byref(xs[0]), dq.data_ptr(), bad.ctypes.data, slots, K, 9, status.data_ptr(),
-                               C.c_void_p(streams[0].cuda_stream))
+                               C.c_void_p(stream))
     assert rc == _lib.FCB_ERR_UNSUPPORTED
+    lib.fcb_debug_exchange_phases(3)
     for e in engines:
         e.close()
     for p in ptrs:
         lib.fcb_peer_close(0, C.c_void_p(p), 1)
+    # world of one rank, push AND wait (the production kernel): the rank owns everything and waits for its own stamps
+    eng = Engine(device=0, max_batch=slots, max_k=16)
+    col = loader.collection_from_host(hc, eng, bf16=True, with_ids=False)
+    xch = sharded.PeerExchange(0, 1, 0, slots, K, [0, spec.n_rows])
+    routed = sharded.RoutedSearcher(col, xch)
+    for it in range(2):
+        users = rng.choice(spec.n_users, size=slots, replace=False)
+        qs = np.stack([synth.query_vector(spec, 900 + 10 * it + b) for b in range(slots)])
+        ids, sc, cnt = routed.search(qs, sharded.filters_array(hc.offsets[users], hc.offsets[users + 1]), K)
+        for b, u in enumerate(users):
+            oi, os_ = canon.search(hc.bf16_bits, qs[b], K, row_begin=int(hc.offsets[u]), row_end=int(hc.offsets[u + 1]))
+            assert ids[b, :cnt[b]].tolist() == oi.tolist() and sc[b, :cnt[b]].tolist() == os_.tolist()
+    xch.close()
+    eng.close()
 
 
 def routed_worker(rank, world, port, ret):
