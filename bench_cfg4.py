@@ -5,11 +5,13 @@ events (max over ranks) after warm-up, inputs resident in HBM:
   tenants_closed_loop  ONE batch of 64 in flight: every rank scans the batch against its shard, one NCCL all-gather of the
                        per-shard candidates, one k-way merge launch. Three serialized latency-bound steps: the time does not
                        depend on N (this is what round 1 measured).
-  tenants_routed       owner-computes: shard cuts lie on user boundaries, so a tenant lives on ONE GPU. N batches of 64 are in
-                       flight (one per front-end rank, N x 64 queries per step); every rank scans only the queries it owns
-                       (~64) and writes their final top-10 straight into every rank's exchange buffer over NVLink peer
-                       mappings (fcb_search_routed: plain stores + a stamp, then a bounded wait for everybody else's).
-                       No NCCL call, no merge launch. Per-rank work per step is constant, so queries/s grows with N.
+  tenants_routed       owner-computes: shard cuts lie on user boundaries, so a tenant lives on ONE GPU. A step carries N batches
+                       of 64 (one per front-end rank, N x 64 queries); every rank scans only the queries it owns (~64) and
+                       writes their final top-10 straight into every rank's exchange buffer over NVLink peer mappings
+                       (fcb_search_routed: plain stores + a stamp, then a bounded wait for everybody else's). No NCCL call,
+                       no merge launch. Per-rank work per step is constant, so queries/s grows with N. Measured with one
+                       engine per GPU (N batches in flight) and with two engines per GPU alternating steps on two streams
+                       (2N in flight: the exchange wait of one step overlaps the scan of the next).
   whale_striped        one query whose segment is the whole corpus: N/G rows per GPU, all-gather + merge: bandwidth scaling.
 """
 from __future__ import annotations
@@ -71,33 +73,92 @@ def run(dev, world: int, rank: int, steps: int, timed_steps, rows: int = ROWS, t
     torch.cuda.synchronize()
     ok_closed = all_ok(check(m.ids.cpu().numpy().view(np.uint64), m.scores.cpu().numpy(), m.counts.cpu().numpy(), tsets[0], 0, range(3)))
 
-    # ---- routed: N batches of 64 in flight, owner-computes + peer-store exchange
+    # ---- routed: N batches of 64 in flight per engine, owner-computes + peer-store exchange. TWO engines per GPU share the
+    #      shard's columns (each has its own scratch, exchange buffers and stream) and alternate steps, so the exchange wait of
+    #      one step overlaps the scan of the next: 2N batches in flight.
     cuts = [r[0] for r in ranges] + [ranges[-1][1]]
     routed_res = None
     try:
-        xch = sharded.PeerExchange(dev.index, world, rank, slots, K, cuts)
-        routed = sharded.RoutedSearcher(col, xch)
+        engines, exchanges, searchers, streams = [eng], [], [], []
+        eng2 = Engine(device=dev.index, max_batch=slots, max_k=16)
+        vec, _ids, _rank, dts, cats, _cents, offs_d = eng._keep
+        eng2.load_shard(vec, dates=dts, categories=cats, seg_offsets=offs_d, row_base=lo)
+        engines.append(eng2)
+        from financial_chatbot_llm_b200.client import Collection
+        for e in engines:
+            xch = sharded.PeerExchange(dev.index, world, rank, slots, K, cuts)
+            exchanges.append(xch)
+            searchers.append(sharded.RoutedSearcher(Collection("transactions", e, col.users, col.offsets, col.payload_fn,
+                                                               n_total_rows=rows), xch))
+            streams.append(torch.cuda.Stream(device=dev))
         rsets = [rng.choice(tenants, size=slots, replace=False) for _ in range(n_sets)]
         farr = [sharded.filters_array(offsets[ts], offsets[ts + 1]) for ts in rsets]
         rq = [torch.from_numpy(np.stack([synth.query_vector(spec, 50_000 + s * 1000 + b) for b in range(slots)])).to(dev) for s in range(2)]
-        ms_r, per_r, clocks = timed_steps(lambda i: routed.search_device(rq[i % 2], farr[i % n_sets], K), steps, 5, dev, world,
-                                          sample_gpu=dev.index if rank == 0 else None)
-        seq = routed.search_device(rq[0], farr[0], K)
         torch.cuda.synchronize()
-        ids, sc, cnt = xch.results(seq)
-        ids, sc, cnt = ids.cpu().numpy().view(np.uint64), sc.cpu().numpy(), cnt.cpu().numpy()
-        # every rank checks slots owned by DIFFERENT ranks in its own buffer (so the delivery itself is checked)
-        which = [rank, (rank * BATCH + 7) % slots, slots - 1 - rank, slots // 2]
-        ok_routed = int(xch.status.item()) == 0 and bool((cnt == K).all()) and check(ids, sc, cnt, rsets[0], 50_000, which)
-        ok_routed = all_ok(ok_routed)
+
+        def run_routed(n_eng, n_steps, warm):
+            """n_steps steps alternating over n_eng engines / streams; CUDA events on each stream; returns ms per step (max over
+            ranks), this rank's sorted per-step spans, clocks."""
+            for i in range(warm):
+                searchers[i % n_eng].search_device(rq[i % 2], farr[i % n_sets], K, stream=streams[i % n_eng].cuda_stream)
+            torch.cuda.synchronize()
+            dist.barrier()
+            from bench import ClockSampler
+            sampler = ClockSampler(dev.index).start() if rank == 0 else None
+            time.sleep(0.3 if rank == 0 else 0.0)
+            dist.barrier()
+            torch.cuda.synchronize()
+            t_a = time.perf_counter()
+            first = [torch.cuda.Event(enable_timing=True) for _ in range(n_eng)]
+            last = [torch.cuda.Event(enable_timing=True) for _ in range(n_eng)]
+            marks = []
+            for j in range(n_eng):
+                first[j].record(streams[j])
+            for i in range(n_steps):
+                j = i % n_eng
+                searchers[j].search_device(rq[i % 2], farr[i % n_sets], K, stream=streams[j].cuda_stream)
+                ev = torch.cuda.Event(enable_timing=True)
+                ev.record(streams[j])
+                marks.append(ev)
+            for j in range(n_eng):
+                last[j].record(streams[j])
+            torch.cuda.synchronize()
+            dist.barrier()
+            t_b = time.perf_counter()
+            span = max(first[0].elapsed_time(last[j]) for j in range(n_eng))          # streams start together (synchronised above)
+            tm = torch.tensor([span], dtype=torch.float64, device=dev)
+            dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+            per = sorted(marks[i].elapsed_time(marks[i + n_eng]) / n_eng for i in range(len(marks) - n_eng))
+            return float(tm.item()) / n_steps, per, (sampler.stop(t_a, t_b) if sampler else None)
+
+        def check_routed(j):
+            seq = searchers[j].search_device(rq[0], farr[0], K, stream=streams[j].cuda_stream)
+            torch.cuda.synchronize()
+            ids, sc, cnt = exchanges[j].results(seq)
+            ids, sc, cnt = ids.cpu().numpy().view(np.uint64), sc.cpu().numpy(), cnt.cpu().numpy()
+            # every rank checks slots owned by DIFFERENT ranks in its own buffer (so the delivery itself is checked)
+            which = [rank, (rank * BATCH + 7) % slots, slots - 1 - rank, slots // 2]
+            return int(exchanges[j].status.item()) == 0 and bool((cnt == K).all()) and check(ids, sc, cnt, rsets[0], 50_000, which)
+
+        n_r = max(steps, 40)
+        ms_1, per_1, _ = run_routed(1, n_r, 6)
+        ms_2, per_2, clocks = run_routed(2, n_r, 6)
+        ok_routed = all_ok(check_routed(0) and check_routed(1))
         owned = int(np.sum((offsets[rsets[0]] >= lo) & (offsets[rsets[0]] < hi)))
-        routed_res = {"ms_per_step": ms_r, "p50_ms": per_r[len(per_r) // 2], "queries_per_step": slots, "batches_in_flight": world,
-                      "queries_per_s": slots * 1e3 / ms_r, "queries_owned_by_rank0_in_a_step": owned, "launches_per_step_per_rank": eng.last_search_launches,
-                      "nccl_calls_per_step": 0, "parity": ok_routed, "clocks": clocks, "exact_reruns": eng.exact_reruns}
+        routed_res = {"ms_per_step": ms_2, "p50_ms": per_2[len(per_2) // 2], "queries_per_step": slots, "engines_per_gpu": 2,
+                      "batches_in_flight": 2 * world, "queries_per_s": slots * 1e3 / ms_2,
+                      "one_engine_per_gpu": {"ms_per_step": ms_1, "p50_ms": per_1[len(per_1) // 2], "batches_in_flight": world,
+                                             "queries_per_s": slots * 1e3 / ms_1},
+                      "queries_owned_by_rank0_in_a_step": owned, "launches_per_step_per_rank": eng.last_search_launches,
+                      "nccl_calls_per_step": 0, "parity": ok_routed, "clocks": clocks,
+                      "exact_reruns": eng.exact_reruns + eng2.exact_reruns}
         dist.barrier()
-        xch.close()
+        for xch in exchanges:
+            xch.close()
+        eng2.close()
     except Exception as e:                                            # e.g. CUDA IPC unavailable on this box: the closed loop still stands
-        routed_res = {"error": f"{type(e).__name__}: {e}"}
+        import traceback
+        routed_res = {"error": f"{type(e).__name__}: {e}", "trace": traceback.format_exc()[-600:]}
 
     # ---- whale: one query over the whole corpus, striped over all shards
     qw = torch.from_numpy(synth.query_vector(spec, 999)[None, :]).to(dev)
