@@ -24,6 +24,13 @@
 #define AGG_THREADS 256
 #define AGG_TILE 4096
 #define AGG_SMALL_PIECE 96
+#ifndef AGG_BLOCK_TILES
+#define AGG_BLOCK_TILES 16                 // consecutive tiles per binary search over the user offsets
+#endif
+#ifndef AGG_UNROLL
+#define AGG_UNROLL 2
+#endif
+constexpr int kAggUnroll = AGG_UNROLL;     // (#pragma unroll takes a constant expression, not a macro)
 #define AGG_MAX_MONTHS 240
 #define AGG_MAX_CELLS 4096
 
@@ -182,20 +189,28 @@ __global__ void __launch_bounds__(AGG_THREADS, 4) aggregate_kernel(const __grid_
     const int4 *dates4 = reinterpret_cast<const int4 *>(p.dates);
     const uchar4 *cats4 = reinterpret_cast<const uchar4 *>(p.cats);
 
-    for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x) {
-        const int64_t a = R0 + t * AGG_TILE;
-        const int64_t b = a + AGG_TILE < R1 ? a + AGG_TILE : R1;
-        if (tid == 0) {                                    // first user whose segment ends after a
+    // Tiles are dealt in BLOCKS of AGG_BLOCK_TILES consecutive tiles: the user of a block's first row costs one binary search
+    // over seg_offsets (17 dependent global loads, ~8 us during which the whole CTA waits at a barrier — the round-2 ncu
+    // capture showed the shared-atomic pipe 11 % busy and the warps stalled on exactly this: barrier + long scoreboard);
+    // inside the block the user index only moves forward.
+    const int64_t n_blocks = (n_tiles + AGG_BLOCK_TILES - 1) / AGG_BLOCK_TILES;
+    for (int64_t blk = blockIdx.x; blk < n_blocks; blk += gridDim.x) {
+        const int64_t t0 = blk * AGG_BLOCK_TILES, t1 = t0 + AGG_BLOCK_TILES < n_tiles ? t0 + AGG_BLOCK_TILES : n_tiles;
+        if (tid == 0) {                                    // first user whose segment ends after the block's first row
+            const int64_t a0 = R0 + t0 * AGG_TILE;
             int64_t lo = p.seg_begin, hi = p.seg_end - 1;
             while (lo < hi) {
                 const int64_t mid = (lo + hi) >> 1;
-                if (p.seg_offsets[mid + 1] > a) hi = mid; else lo = mid + 1;
+                if (p.seg_offsets[mid + 1] > a0) hi = mid; else lo = mid + 1;
             }
             s_piece[0] = lo;
         }
         __syncthreads();
         int64_t u = s_piece[0];
         __syncthreads();
+      for (int64_t t = t0; t < t1; ++t) {
+        const int64_t a = R0 + t * AGG_TILE;
+        const int64_t b = a + AGG_TILE < R1 ? a + AGG_TILE : R1;
         int64_t pa = a;
         while (pa < b) {
             int64_t uend = p.seg_offsets[u + 1];
@@ -208,7 +223,7 @@ __global__ void __launch_bounds__(AGG_THREADS, 4) aggregate_kernel(const __grid_
             // local row range of the piece; quads aligned on the LOCAL row index so the 128-bit loads are aligned
             const int64_t la = pa - p.row_base, lb = pb - p.row_base;
             const int64_t q0 = la >> 2, q1 = (lb + 3) >> 2;            // quads [q0, q1) cover [la, lb)
-#pragma unroll 2
+#pragma unroll kAggUnroll
             for (int64_t q = q0 + tid; q < q1; q += AGG_THREADS) {
                 const int64_t r = q << 2;
                 if (r >= la && r + 4 <= lb) {                           // interior quad: three vector loads
@@ -239,6 +254,7 @@ __global__ void __launch_bounds__(AGG_THREADS, 4) aggregate_kernel(const __grid_
             }
             pa = pb;
         }
+      }
     }
     if (dropped) atomicAdd(p.dropped, (unsigned long long)dropped);
 }
