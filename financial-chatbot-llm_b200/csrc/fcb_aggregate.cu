@@ -106,7 +106,11 @@ __device__ __forceinline__ void agg_row(const AggParams &p, int32_t v, unsigned 
         atomicAdd(&c_lo[cell], lo16);
         atomicAdd(&c_hi[cell], (int32_t)(((int64_t)v - lo16) >> 16));
     }
-    if (!c_present[cell]) c_present[cell] = 1;             // plain byte store: every writer stores the same value
+#ifdef AGG_PRESENT_CHECK
+    if (!c_present[cell]) c_present[cell] = 1;
+#else
+    c_present[cell] = 1;                                   // plain byte store: every writer stores the same value
+#endif
 }
 
 #ifndef AGS_ROUND
@@ -148,7 +152,11 @@ __device__ __forceinline__ void agg_warp_table(const AggParams &p, int64_t la, i
                 atomicAdd(&t_lo[cell], lo16);
                 atomicAdd(&t_hi[cell], (int32_t)(((int64_t)v - lo16) >> 16));
             }
+#ifdef AGG_PRESENT_CHECK
             if (!t_p[cell]) t_p[cell] = 1;
+#else
+            t_p[cell] = 1;
+#endif
         }
     }
     __syncwarp();
@@ -574,6 +582,22 @@ int32_t fcb_check_dates_sorted(fcb_engine *e) {
     return FCB_OK;
 }
 
+// One side stream + two events per device, created on first use (a stream is a handle, not memory): lets the two launches
+// of the any-order split overlap.
+struct AggSide { cudaStream_t stream; cudaEvent_t fork, join; int state; };   // state: 0 = not tried, 1 = ready, -1 = unavailable
+static AggSide g_agg_side[64];
+static AggSide *agg_side_stream(int device) {
+    if (device < 0 || device >= 64) return nullptr;
+    AggSide &a = g_agg_side[device];
+    if (a.state == 0) {
+        a.state = (cudaStreamCreateWithFlags(&a.stream, cudaStreamNonBlocking) == cudaSuccess &&
+                   cudaEventCreateWithFlags(&a.fork, cudaEventDisableTiming) == cudaSuccess &&
+                   cudaEventCreateWithFlags(&a.join, cudaEventDisableTiming) == cudaSuccess) ? 1 : -1;
+        if (a.state < 0) cudaGetLastError();
+    }
+    return a.state == 1 ? &a : nullptr;
+}
+
 // Validates the window, zeroes the outputs and launches the kernel(s) for one shard's columns. `e` may be NULL (the
 // engine-less entry point): errors then land in the per-thread message fcb_last_error(NULL) returns.
 static int32_t agg_launch(fcb_engine *e, int device, int num_sms, int dates_sorted, const int32_t *dates, const uint8_t *cats,
@@ -626,10 +650,22 @@ static int32_t agg_launch(fcb_engine *e, int device, int num_sms, int dates_sort
     if ((split || use_sorted) && smem_s > 48 * 1024)
         FCB_CUDA(e, cudaFuncSetAttribute(aggregate_sorted_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_s));
     if (split) {
+        // the two launches touch disjoint users: the small-user one runs on a side stream next to the large-user one
+        // (fork / join by events), so its tail does not add to the total. FCB_AGG_CONCURRENT=0: one after the other.
+        const char *conc = getenv("FCB_AGG_CONCURRENT");
+        AggSide *side = (conc && conc[0] == '0') ? nullptr : agg_side_stream(device);
         p.split = 2;
-        aggregate_sorted_kernel<<<num_sms * AGS_CTAS, AGG_THREADS, smem_s, st>>>(p);
+        if (side) {
+            FCB_CUDA(e, cudaEventRecord(side->fork, st));
+            FCB_CUDA(e, cudaStreamWaitEvent(side->stream, side->fork, 0));
+            aggregate_sorted_kernel<<<num_sms * AGS_CTAS, AGG_THREADS, smem_s, side->stream>>>(p);
+            FCB_CUDA(e, cudaEventRecord(side->join, side->stream));
+        } else {
+            aggregate_sorted_kernel<<<num_sms * AGS_CTAS, AGG_THREADS, smem_s, st>>>(p);
+        }
         p.split = 1;
         aggregate_kernel<<<num_sms * 4, AGG_THREADS, smem, st>>>(p);
+        if (side) FCB_CUDA(e, cudaStreamWaitEvent(st, side->join, 0));
     } else if (use_sorted) {
         aggregate_sorted_kernel<<<num_sms * AGS_CTAS, AGG_THREADS, smem_s, st>>>(p);
     } else {
