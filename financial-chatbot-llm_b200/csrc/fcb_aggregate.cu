@@ -19,6 +19,8 @@
 // with the same civil-from-days arithmetic as the oracle.
 #include <stdlib.h>
 
+#include <type_traits>
+
 #include "fcb_internal.cuh"
 
 #define AGG_THREADS 256
@@ -84,22 +86,17 @@ __device__ __forceinline__ int32_t floor_day(int32_t ts) {
     return d;
 }
 
-// one row into the CTA's shared cells (big pieces) or straight to the global cells (tiny pieces)
-__device__ __forceinline__ void agg_row(const AggParams &p, int32_t v, unsigned cat, int32_t date, bool use_global,
-                                        int32_t *c_lo, int32_t *c_hi, uint8_t *c_present, const uint16_t *month_tab,
-                                        int64_t *out_s, uint8_t *out_p, unsigned &dropped) {
-    const int32_t di = floor_day(date) - p.day0;
-    const unsigned mo = (unsigned)di < (unsigned)p.n_days ? month_tab[di] : 0xffffu;
-    if (cat >= (unsigned)p.n_categories || mo >= (unsigned)p.n_months) { ++dropped; return; }
-    const int cell = cat * p.n_months + mo;
-    if (use_global) {
-        atomicAdd(reinterpret_cast<unsigned long long *>(out_s + cell), (unsigned long long)(long long)v);
-        out_p[cell] = 1;
-        return;
-    }
-    // |v| < 2^18: AGG_TILE (4096) such values cannot overflow an int32 cell -> ONE native 32-bit shared atomic.
-    // Larger values are split v = hi * 65536 + lo16 so that no int32 input can overflow either cell.
-    if (v > -(1 << 18) && v < (1 << 18)) {
+// month slot of a date inside the window, or 0xffff: one 64-bit subtract + compare against the window, an unsigned
+// division by a constant and a table lookup (cheaper than flooring a signed day number first)
+__device__ __forceinline__ unsigned agg_month(const AggParams &p, int32_t date, const uint16_t *month_tab) {
+    const uint64_t off = (uint64_t)((int64_t)date - (int64_t)p.day0 * 86400);
+    return off < (uint64_t)p.n_days * 86400u ? month_tab[(uint32_t)off / 86400u] : 0xffffu;
+}
+
+// one row into shared cells: |v| < 2^18 -> ONE native 32-bit shared atomic (4096 such values cannot overflow an int32
+// cell); larger values are split v = hi * 65536 + lo16 so that no int32 input can overflow either cell
+__device__ __forceinline__ void agg_cell_add(int32_t *c_lo, int32_t *c_hi, uint8_t *c_present, int cell, int32_t v) {
+    if ((uint32_t)v + ((1u << 18) - 1u) < (1u << 19) - 1u) {            // -2^18 < v < 2^18
         atomicAdd(&c_lo[cell], v);
     } else {
         const int32_t lo16 = (int32_t)(int16_t)(v & 0xffff);
@@ -111,6 +108,22 @@ __device__ __forceinline__ void agg_row(const AggParams &p, int32_t v, unsigned 
 #else
     c_present[cell] = 1;                                   // plain byte store: every writer stores the same value
 #endif
+}
+
+// one row into the CTA's shared cells (big pieces: SMALL = false) or straight to the global cells (tiny pieces)
+template <bool SMALL>
+__device__ __forceinline__ void agg_row(const AggParams &p, int32_t v, unsigned cat, int32_t date,
+                                        int32_t *c_lo, int32_t *c_hi, uint8_t *c_present, const uint16_t *month_tab,
+                                        int64_t *out_s, uint8_t *out_p, unsigned &dropped) {
+    const unsigned mo = agg_month(p, date, month_tab);
+    if (cat >= (unsigned)p.n_categories || mo >= (unsigned)p.n_months) { ++dropped; return; }
+    const int cell = cat * p.n_months + mo;
+    if (SMALL) {
+        atomicAdd(reinterpret_cast<unsigned long long *>(out_s + cell), (unsigned long long)(long long)v);
+        out_p[cell] = 1;
+        return;
+    }
+    agg_cell_add(c_lo, c_hi, c_present, cell, v);
 }
 
 #ifndef AGS_ROUND
@@ -140,23 +153,9 @@ __device__ __forceinline__ void agg_warp_table(const AggParams &p, int64_t la, i
 #pragma unroll
         for (int j = 0; j < AGS_ROUND; ++j) {
             if (cc[j] == 0x100u) continue;                       // past the piece
-            const int32_t di = floor_day(dd[j]) - p.day0;
-            const unsigned mo = (unsigned)di < (unsigned)p.n_days ? month_tab[di] : 0xffffu;
+            const unsigned mo = agg_month(p, dd[j], month_tab);
             if (cc[j] >= (unsigned)p.n_categories || mo >= (unsigned)p.n_months) { ++dropped; continue; }
-            const int cell = cc[j] * p.n_months + mo;
-            const int32_t v = vv[j];
-            if (v > -(1 << 18) && v < (1 << 18)) {
-                atomicAdd(&t_lo[cell], v);
-            } else {
-                const int32_t lo16 = (int32_t)(int16_t)(v & 0xffff);
-                atomicAdd(&t_lo[cell], lo16);
-                atomicAdd(&t_hi[cell], (int32_t)(((int64_t)v - lo16) >> 16));
-            }
-#ifdef AGG_PRESENT_CHECK
-            if (!t_p[cell]) t_p[cell] = 1;
-#else
-            t_p[cell] = 1;
-#endif
+            agg_cell_add(t_lo, t_hi, t_p, cc[j] * p.n_months + mo, vv[j]);
         }
     }
     __syncwarp();
@@ -231,23 +230,28 @@ __global__ void __launch_bounds__(AGG_THREADS, 4) aggregate_kernel(const __grid_
             // local row range of the piece; quads aligned on the LOCAL row index so the 128-bit loads are aligned
             const int64_t la = pa - p.row_base, lb = pb - p.row_base;
             const int64_t q0 = la >> 2, q1 = (lb + 3) >> 2;            // quads [q0, q1) cover [la, lb)
+            // one quad loop per kind of piece, so that the row path carries no per-row "small piece?" test
+            auto quads = [&](auto small_tag) {
+                constexpr bool SMALL = decltype(small_tag)::value;
 #pragma unroll kAggUnroll
-            for (int64_t q = q0 + tid; q < q1; q += AGG_THREADS) {
-                const int64_t r = q << 2;
-                if (r >= la && r + 4 <= lb) {                           // interior quad: three vector loads
-                    const int4 v = __ldg(cents4 + q);
-                    const int4 d = __ldg(dates4 + q);
-                    const uchar4 c = __ldg(cats4 + q);
-                    agg_row(p, v.x, c.x, d.x, small, c_lo, c_hi, c_present, month_tab, out_s, out_p, dropped);
-                    agg_row(p, v.y, c.y, d.y, small, c_lo, c_hi, c_present, month_tab, out_s, out_p, dropped);
-                    agg_row(p, v.z, c.z, d.z, small, c_lo, c_hi, c_present, month_tab, out_s, out_p, dropped);
-                    agg_row(p, v.w, c.w, d.w, small, c_lo, c_hi, c_present, month_tab, out_s, out_p, dropped);
-                } else {                                                // ragged head / tail of the piece
-                    for (int64_t rr = r > la ? r : la; rr < r + 4 && rr < lb; ++rr)
-                        agg_row(p, p.cents[rr], p.cats[rr], p.dates[rr], small, c_lo, c_hi, c_present, month_tab, out_s,
-                                out_p, dropped);
+                for (int64_t q = q0 + tid; q < q1; q += AGG_THREADS) {
+                    const int64_t r = q << 2;
+                    if (r >= la && r + 4 <= lb) {                       // interior quad: three vector loads
+                        const int4 v = __ldg(cents4 + q);
+                        const int4 d = __ldg(dates4 + q);
+                        const uchar4 c = __ldg(cats4 + q);
+                        agg_row<SMALL>(p, v.x, c.x, d.x, c_lo, c_hi, c_present, month_tab, out_s, out_p, dropped);
+                        agg_row<SMALL>(p, v.y, c.y, d.y, c_lo, c_hi, c_present, month_tab, out_s, out_p, dropped);
+                        agg_row<SMALL>(p, v.z, c.z, d.z, c_lo, c_hi, c_present, month_tab, out_s, out_p, dropped);
+                        agg_row<SMALL>(p, v.w, c.w, d.w, c_lo, c_hi, c_present, month_tab, out_s, out_p, dropped);
+                    } else {                                            // ragged head / tail of the piece
+                        for (int64_t rr = r > la ? r : la; rr < r + 4 && rr < lb; ++rr)
+                            agg_row<SMALL>(p, p.cents[rr], p.cats[rr], p.dates[rr], c_lo, c_hi, c_present, month_tab, out_s, out_p,
+                                           dropped);
+                    }
                 }
-            }
+            };
+            if (small) quads(std::true_type{}); else quads(std::false_type{});
             if (!small) {
                 __syncthreads();
                 for (int c = tid; c < C; c += AGG_THREADS) {
