@@ -93,37 +93,49 @@ __device__ __forceinline__ unsigned agg_month(const AggParams &p, int32_t date, 
     return off < (uint64_t)p.n_days * 86400u ? month_tab[(uint32_t)off / 86400u] : 0xffffu;
 }
 
-// one row into shared cells: |v| < 2^18 -> ONE native 32-bit shared atomic (4096 such values cannot overflow an int32
-// cell); larger values are split v = hi * 65536 + lo16 so that no int32 input can overflow either cell
-__device__ __forceinline__ void agg_cell_add(int32_t *c_lo, int32_t *c_hi, uint8_t *c_present, int cell, int32_t v) {
-    if ((uint32_t)v + ((1u << 18) - 1u) < (1u << 19) - 1u) {            // -2^18 < v < 2^18
-        atomicAdd(&c_lo[cell], v);
-    } else {
-        const int32_t lo16 = (int32_t)(int16_t)(v & 0xffff);
-        atomicAdd(&c_lo[cell], lo16);
-        atomicAdd(&c_hi[cell], (int32_t)(((int64_t)v - lo16) >> 16));
-    }
-#ifdef AGG_PRESENT_CHECK
-    if (!c_present[cell]) c_present[cell] = 1;
-#else
-    c_present[cell] = 1;                                   // plain byte store: every writer stores the same value
-#endif
+// predicated shared-memory reduction / byte store on 32-bit shared-window addresses (no branch, no generic -> shared
+// conversion per row)
+__device__ __forceinline__ void agg_red_shared(uint32_t addr, int32_t v, bool pred) {
+    asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.b32 q, %2, 0;\n\t@q red.shared.add.s32 [%0], %1;\n\t}"
+                 ::"r"(addr), "r"(v), "r"((int)pred) : "memory");
+}
+__device__ __forceinline__ void agg_st_shared_u8(uint32_t addr, bool pred) {
+    asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.b32 q, %1, 0;\n\t@q st.shared.u8 [%0], 1;\n\t}" ::"r"(addr), "r"((int)pred) : "memory");
+}
+
+// shared-window addresses of one set of cells: lo [C] int32, hi [C] int32, present [C] uint8
+struct AggCells { uint32_t lo, hi, present; };
+__device__ __forceinline__ AggCells agg_cells(const int32_t *c_lo, const int32_t *c_hi, const uint8_t *c_present) {
+    return AggCells{(uint32_t)__cvta_generic_to_shared(c_lo), (uint32_t)__cvta_generic_to_shared(c_hi),
+                    (uint32_t)__cvta_generic_to_shared(c_present)};
+}
+
+// one row into shared cells: |v| < 2^18 -> ONE native 32-bit shared reduction (4096 such values cannot overflow an int32
+// cell); larger values are split v = hi * 65536 + lo16 so that no int32 input can overflow either cell (rare second reduction)
+__device__ __forceinline__ void agg_cell_add(const AggCells &cells, bool valid, int cell, int32_t v) {
+    const bool large = !((uint32_t)v + ((1u << 18) - 1u) < (1u << 19) - 1u);   // not in (-2^18, 2^18)
+    const int32_t lo16 = (int32_t)(int16_t)(v & 0xffff);
+    agg_red_shared(cells.lo + 4u * (uint32_t)cell, large ? lo16 : v, valid);
+    if (valid && large) agg_red_shared(cells.hi + 4u * (uint32_t)cell, (int32_t)(((int64_t)v - lo16) >> 16), true);   // rare
+    agg_st_shared_u8(cells.present + (uint32_t)cell, valid);          // plain byte store: every writer stores the same value
 }
 
 // one row into the CTA's shared cells (big pieces: SMALL = false) or straight to the global cells (tiny pieces)
 template <bool SMALL>
-__device__ __forceinline__ void agg_row(const AggParams &p, int32_t v, unsigned cat, int32_t date,
-                                        int32_t *c_lo, int32_t *c_hi, uint8_t *c_present, const uint16_t *month_tab,
-                                        int64_t *out_s, uint8_t *out_p, unsigned &dropped) {
+__device__ __forceinline__ void agg_row(const AggParams &p, int32_t v, unsigned cat, int32_t date, const AggCells &cells,
+                                        const uint16_t *month_tab, int64_t *out_s, uint8_t *out_p, unsigned &dropped) {
     const unsigned mo = agg_month(p, date, month_tab);
-    if (cat >= (unsigned)p.n_categories || mo >= (unsigned)p.n_months) { ++dropped; return; }
-    const int cell = cat * p.n_months + mo;
+    const bool valid = cat < (unsigned)p.n_categories && mo < (unsigned)p.n_months;
+    dropped += valid ? 0u : 1u;
+    const int cell = valid ? (int)(cat * p.n_months + mo) : 0;
     if (SMALL) {
-        atomicAdd(reinterpret_cast<unsigned long long *>(out_s + cell), (unsigned long long)(long long)v);
-        out_p[cell] = 1;
+        if (valid) {
+            atomicAdd(reinterpret_cast<unsigned long long *>(out_s + cell), (unsigned long long)(long long)v);
+            out_p[cell] = 1;
+        }
         return;
     }
-    agg_cell_add(c_lo, c_hi, c_present, cell, v);
+    agg_cell_add(cells, valid, cell, v);
 }
 
 #ifndef AGS_ROUND
@@ -135,7 +147,9 @@ __device__ __forceinline__ void agg_row(const AggParams &p, int32_t v, unsigned 
 
 // One small user's piece [la, lb) (local rows) on ONE warp: a private [category, month] table in shared memory (t_lo, t_hi,
 // t_p: all zero on entry and on exit) fed with 32-bit shared atomics — one per row for |v| < 2^18, a lo/hi split otherwise; a
-// piece has at most 4096 rows, so no cell can overflow. AGS_ROUND x 32 rows per round, all column loads of a lane in flight
+// piece has at most 4096 rows, so no cell can overflow. (This path keeps the plain form of the row update — signed day number,
+// generic-pointer atomics: the leaner form of aggregate_kernel's agg_row costs aggregate_sorted_kernel, which inlines this
+// function at its 64-register cap, spills and 8 % of its time.) AGS_ROUND x 32 rows per round, all column loads of a lane in flight
 // before the first is used (one row per lane at a time streams ~1 TB/s across the GPU, latency-bound). The present cells go
 // out once: plain stores when the piece is the whole user (`whole`), 64-bit reductions otherwise.
 __device__ __forceinline__ void agg_warp_table(const AggParams &p, int64_t la, int64_t lb, bool whole, int64_t user, int32_t *t_lo,
@@ -153,9 +167,23 @@ __device__ __forceinline__ void agg_warp_table(const AggParams &p, int64_t la, i
 #pragma unroll
         for (int j = 0; j < AGS_ROUND; ++j) {
             if (cc[j] == 0x100u) continue;                       // past the piece
-            const unsigned mo = agg_month(p, dd[j], month_tab);
+            const int32_t di = floor_day(dd[j]) - p.day0;
+            const unsigned mo = (unsigned)di < (unsigned)p.n_days ? month_tab[di] : 0xffffu;
             if (cc[j] >= (unsigned)p.n_categories || mo >= (unsigned)p.n_months) { ++dropped; continue; }
-            agg_cell_add(t_lo, t_hi, t_p, cc[j] * p.n_months + mo, vv[j]);
+            const int cell = cc[j] * p.n_months + mo;
+            const int32_t v = vv[j];
+            if (v > -(1 << 18) && v < (1 << 18)) {
+                atomicAdd(&t_lo[cell], v);
+            } else {
+                const int32_t lo16 = (int32_t)(int16_t)(v & 0xffff);
+                atomicAdd(&t_lo[cell], lo16);
+                atomicAdd(&t_hi[cell], (int32_t)(((int64_t)v - lo16) >> 16));
+            }
+#ifdef AGG_PRESENT_CHECK
+            if (!t_p[cell]) t_p[cell] = 1;
+#else
+            t_p[cell] = 1;
+#endif
         }
     }
     __syncwarp();
@@ -183,6 +211,7 @@ __global__ void __launch_bounds__(AGG_THREADS, 4) aggregate_kernel(const __grid_
     __shared__ int64_t s_piece[2];
 
     const int tid = threadIdx.x;
+    const AggCells cells = agg_cells(c_lo, c_hi, c_present);
     for (int i = tid; i < p.n_days; i += AGG_THREADS) month_tab[i] = (uint16_t)(month_of_day(p.day0 + i) - p.month_lo);
     for (int i = tid; i < C; i += AGG_THREADS) { c_lo[i] = 0; c_hi[i] = 0; c_present[i] = 0; }
     __syncthreads();
@@ -240,14 +269,13 @@ __global__ void __launch_bounds__(AGG_THREADS, 4) aggregate_kernel(const __grid_
                         const int4 v = __ldg(cents4 + q);
                         const int4 d = __ldg(dates4 + q);
                         const uchar4 c = __ldg(cats4 + q);
-                        agg_row<SMALL>(p, v.x, c.x, d.x, c_lo, c_hi, c_present, month_tab, out_s, out_p, dropped);
-                        agg_row<SMALL>(p, v.y, c.y, d.y, c_lo, c_hi, c_present, month_tab, out_s, out_p, dropped);
-                        agg_row<SMALL>(p, v.z, c.z, d.z, c_lo, c_hi, c_present, month_tab, out_s, out_p, dropped);
-                        agg_row<SMALL>(p, v.w, c.w, d.w, c_lo, c_hi, c_present, month_tab, out_s, out_p, dropped);
+                        agg_row<SMALL>(p, v.x, c.x, d.x, cells, month_tab, out_s, out_p, dropped);
+                        agg_row<SMALL>(p, v.y, c.y, d.y, cells, month_tab, out_s, out_p, dropped);
+                        agg_row<SMALL>(p, v.z, c.z, d.z, cells, month_tab, out_s, out_p, dropped);
+                        agg_row<SMALL>(p, v.w, c.w, d.w, cells, month_tab, out_s, out_p, dropped);
                     } else {                                            // ragged head / tail of the piece
                         for (int64_t rr = r > la ? r : la; rr < r + 4 && rr < lb; ++rr)
-                            agg_row<SMALL>(p, p.cents[rr], p.cats[rr], p.dates[rr], c_lo, c_hi, c_present, month_tab, out_s, out_p,
-                                           dropped);
+                            agg_row<SMALL>(p, p.cents[rr], p.cats[rr], p.dates[rr], cells, month_tab, out_s, out_p, dropped);
                     }
                 }
             };
