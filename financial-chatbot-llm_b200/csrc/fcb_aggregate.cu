@@ -204,16 +204,20 @@ __device__ __forceinline__ void agg_warp_table(const AggParams &p, int64_t la, i
 __global__ void __launch_bounds__(AGG_THREADS, 4) aggregate_kernel(const __grid_constant__ AggParams p) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int C = p.n_categories * p.n_months;
-    int32_t *c_lo = reinterpret_cast<int32_t *>(smem_raw);             // [C]
-    int32_t *c_hi = c_lo + C;                                          // [C]
-    uint16_t *month_tab = reinterpret_cast<uint16_t *>(c_hi + C);      // [n_days]
-    uint8_t *c_present = reinterpret_cast<uint8_t *>(month_tab + ((p.n_days + 1) & ~1));   // [C]
+    // TWO sets of cells, used by alternate pieces: a piece is accumulated into one set, ONE barrier, then every thread flushes
+    // its cells of that set and goes straight on to the next piece in the other set — by the time a set is accumulated into
+    // again, the barrier of the piece in between has seen every thread finish flushing it.
+    int32_t *c_lo = reinterpret_cast<int32_t *>(smem_raw);             // [2][C]
+    int32_t *c_hi = c_lo + 2 * C;                                      // [2][C]
+    uint16_t *month_tab = reinterpret_cast<uint16_t *>(c_hi + 2 * C);  // [n_days]
+    uint8_t *c_present = reinterpret_cast<uint8_t *>(month_tab + ((p.n_days + 1) & ~1));   // [2][C]
     __shared__ int64_t s_piece[2];
 
     const int tid = threadIdx.x;
-    const AggCells cells = agg_cells(c_lo, c_hi, c_present);
+    const AggCells cells2[2] = {agg_cells(c_lo, c_hi, c_present), agg_cells(c_lo + C, c_hi + C, c_present + C)};
+    int cur = 0;                                                       // the set the next large piece accumulates into
     for (int i = tid; i < p.n_days; i += AGG_THREADS) month_tab[i] = (uint16_t)(month_of_day(p.day0 + i) - p.month_lo);
-    for (int i = tid; i < C; i += AGG_THREADS) { c_lo[i] = 0; c_hi[i] = 0; c_present[i] = 0; }
+    for (int i = tid; i < 2 * C; i += AGG_THREADS) { c_lo[i] = 0; c_hi[i] = 0; c_present[i] = 0; }
     __syncthreads();
 
     int64_t R0 = p.seg_offsets[p.seg_begin], R1 = p.seg_offsets[p.seg_end];
@@ -260,6 +264,7 @@ __global__ void __launch_bounds__(AGG_THREADS, 4) aggregate_kernel(const __grid_
             const int64_t la = pa - p.row_base, lb = pb - p.row_base;
             const int64_t q0 = la >> 2, q1 = (lb + 3) >> 2;            // quads [q0, q1) cover [la, lb)
             // one quad loop per kind of piece, so that the row path carries no per-row "small piece?" test
+            const AggCells cells = cells2[cur];
             auto quads = [&](auto small_tag) {
                 constexpr bool SMALL = decltype(small_tag)::value;
 #pragma unroll kAggUnroll
@@ -282,15 +287,17 @@ __global__ void __launch_bounds__(AGG_THREADS, 4) aggregate_kernel(const __grid_
             if (small) quads(std::true_type{}); else quads(std::false_type{});
             if (!small) {
                 __syncthreads();
+                int32_t *f_lo = c_lo + cur * C, *f_hi = c_hi + cur * C;
+                uint8_t *f_p = c_present + cur * C;
                 for (int c = tid; c < C; c += AGG_THREADS) {
-                    if (c_present[c]) {
-                        const long long s = (long long)c_hi[c] * 65536 + c_lo[c];
+                    if (f_p[c]) {
+                        const long long s = (long long)f_hi[c] * 65536 + f_lo[c];
                         atomicAdd(reinterpret_cast<unsigned long long *>(out_s + c), (unsigned long long)s);
                         out_p[c] = 1;
-                        c_lo[c] = 0; c_hi[c] = 0; c_present[c] = 0;
+                        f_lo[c] = 0; f_hi[c] = 0; f_p[c] = 0;
                     }
                 }
-                __syncthreads();
+                cur ^= 1;                                              // no second barrier: see the note at the cell sets
             }
             pa = pb;
         }
@@ -664,7 +671,7 @@ static int32_t agg_launch(fcb_engine *e, int device, int num_sms, int dates_sort
     p.sums = sums; p.present = present; p.dropped = (unsigned long long *)dropped;
     p.small_piece = AGG_SMALL_PIECE;
     if (const char *knob = getenv("FCB_AGG_SMALL_PIECE")) p.small_piece = atoll(knob);   // tuning knob
-    const size_t smem = (size_t)C * 8 + (size_t)((p.n_days + 1) & ~1) * 2 + (size_t)C + 16;
+    const size_t smem = (size_t)C * 16 + (size_t)((p.n_days + 1) & ~1) * 2 + (size_t)C * 2 + 16;   // two sets of cells
     if (smem > 48 * 1024)
         FCB_CUDA(e, cudaFuncSetAttribute(aggregate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const char *force = getenv("FCB_AGG_KERNEL");                   // tuning: "atomic" / "sorted"
