@@ -32,6 +32,9 @@
 #ifndef AGG_UNROLL
 #define AGG_UNROLL 2
 #endif
+#ifndef AGG_CTAS
+#define AGG_CTAS 4                         // resident CTAs per SM of aggregate_kernel (register cap 65536 / (256 * AGG_CTAS))
+#endif
 constexpr int kAggUnroll = AGG_UNROLL;     // (#pragma unroll takes a constant expression, not a macro)
 #define AGG_MAX_MONTHS 240
 #define AGG_MAX_CELLS 4096
@@ -201,7 +204,7 @@ __device__ __forceinline__ void agg_warp_table(const AggParams &p, int64_t la, i
     __syncwarp();
 }
 
-__global__ void __launch_bounds__(AGG_THREADS, 4) aggregate_kernel(const __grid_constant__ AggParams p) {
+__global__ void __launch_bounds__(AGG_THREADS, AGG_CTAS) aggregate_kernel(const __grid_constant__ AggParams p) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int C = p.n_categories * p.n_months;
     // TWO sets of cells, used by alternate pieces: a piece is accumulated into one set, ONE barrier, then every thread flushes
@@ -703,12 +706,12 @@ static int32_t agg_launch(fcb_engine *e, int device, int num_sms, int dates_sort
             aggregate_sorted_kernel<<<num_sms * AGS_CTAS, AGG_THREADS, smem_s, st>>>(p);
         }
         p.split = 1;
-        aggregate_kernel<<<num_sms * 4, AGG_THREADS, smem, st>>>(p);
+        aggregate_kernel<<<num_sms * AGG_CTAS, AGG_THREADS, smem, st>>>(p);
         if (side) FCB_CUDA(e, cudaStreamWaitEvent(st, side->join, 0));
     } else if (use_sorted) {
         aggregate_sorted_kernel<<<num_sms * AGS_CTAS, AGG_THREADS, smem_s, st>>>(p);
     } else {
-        aggregate_kernel<<<num_sms * 4, AGG_THREADS, smem, st>>>(p);
+        aggregate_kernel<<<num_sms * AGG_CTAS, AGG_THREADS, smem, st>>>(p);
     }
     FCB_CUDA(e, cudaGetLastError());
     return FCB_OK;
