@@ -24,18 +24,22 @@
 #include "fcb_internal.cuh"
 
 #define AGG_THREADS 256
+#ifndef AGG_TILE
 #define AGG_TILE 4096
+#endif
 #define AGG_SMALL_PIECE 96
 #ifndef AGG_BLOCK_TILES
 #define AGG_BLOCK_TILES 16                 // consecutive tiles per binary search over the user offsets
 #endif
-#ifndef AGG_UNROLL
-#define AGG_UNROLL 2
+#ifndef AGG_BATCH
+#define AGG_BATCH 2                        // quads per thread whose column loads are in flight together
+#endif
+#ifndef AGG_ABLATE
+#define AGG_ABLATE 0                       // timing experiments only (wrong results): 1 no cell reduction, 2 no presence store, 4 no month lookup
 #endif
 #ifndef AGG_CTAS
 #define AGG_CTAS 4                         // resident CTAs per SM of aggregate_kernel (register cap 65536 / (256 * AGG_CTAS))
 #endif
-constexpr int kAggUnroll = AGG_UNROLL;     // (#pragma unroll takes a constant expression, not a macro)
 #define AGG_MAX_MONTHS 240
 #define AGG_MAX_CELLS 4096
 
@@ -48,10 +52,20 @@ struct AggParams {
     int64_t row_base, n_rows;
     int32_t month_lo, n_months, n_categories;
     int32_t day0, n_days;                  // table covers days [day0, day0 + n_days)
+    // the same window in 32-bit seconds for aggregate_kernel's row path (dates are int32): a date d is inside iff
+    // (uint32)d - (uint32)base32 < window32 — the window clipped to the int32 range, so the wrap-around cannot alias —
+    // and its day slot is ((uint32)d - base32 + shift32) / 86400 (shift32 != 0 only for a window that starts before 1901)
+    int32_t base32;
+    uint32_t window32, shift32;
     int64_t *sums;                         // [segs, n_categories, n_months]
     uint8_t *present;                      // same shape
     unsigned long long *dropped;           // rows outside the category / month window
     int64_t small_piece;                   // pieces shorter than this reduce straight to the global cells
+    const uint16_t *keys;                  // group keys of the rows (aggregate_key_kernel only), see "group keys" below
+    uint32_t key_mo_off;                   // month_lo - key base: month slot of a row = (key's month field) - key_mo_off
+    uint32_t key_stride;                   // words per category in a warp's pos / neg tables: n_months | 1 (odd, see agk_row)
+    uint32_t key_neg_off, key_hi_off;      // byte offsets of the neg table and of the hi words in a warp's table
+    uint32_t key_step_cat, key_step_mo;    // 32 = key_step_cat * n_months + key_step_mo (the flush loop's walk over cells)
     int split;                             // any-order data, two launches: 1 = this launch skips users < AGS_TABLE_USER rows (the
                                            // atomic kernel), 2 = it handles ONLY them (the warp-table path of the ordered kernel)
 };
@@ -89,11 +103,18 @@ __device__ __forceinline__ int32_t floor_day(int32_t ts) {
     return d;
 }
 
-// month slot of a date inside the window, or 0xffff: one 64-bit subtract + compare against the window, an unsigned
-// division by a constant and a table lookup (cheaper than flooring a signed day number first)
-__device__ __forceinline__ unsigned agg_month(const AggParams &p, int32_t date, const uint16_t *month_tab) {
-    const uint64_t off = (uint64_t)((int64_t)date - (int64_t)p.day0 * 86400);
-    return off < (uint64_t)p.n_days * 86400u ? month_tab[(uint32_t)off / 86400u] : 0xffffu;
+// month slot of a date inside the window, or 0xffff — branch-free: one 32-bit subtract + compare against the window (see
+// AggParams), an unsigned division by a constant, and a table lookup whose entry [n_days] is the 0xffff sentinel
+__device__ __forceinline__ unsigned agg_month(const AggParams &p, int32_t date, uint32_t mtab_addr) {
+    const uint32_t off = (uint32_t)date - (uint32_t)p.base32;
+    const uint32_t day = off < p.window32 ? (off + p.shift32) / 86400u : (uint32_t)p.n_days;
+#if AGG_ABLATE & 4
+    return day >> 5;
+#else
+    unsigned short mo;
+    asm("ld.shared.u16 %0, [%1];" : "=h"(mo) : "r"(mtab_addr + 2u * day));
+    return mo;
+#endif
 }
 
 // predicated shared-memory reduction / byte store on 32-bit shared-window addresses (no branch, no generic -> shared
@@ -118,15 +139,19 @@ __device__ __forceinline__ AggCells agg_cells(const int32_t *c_lo, const int32_t
 __device__ __forceinline__ void agg_cell_add(const AggCells &cells, bool valid, int cell, int32_t v) {
     const bool large = !((uint32_t)v + ((1u << 18) - 1u) < (1u << 19) - 1u);   // not in (-2^18, 2^18)
     const int32_t lo16 = (int32_t)(int16_t)(v & 0xffff);
+#if !(AGG_ABLATE & 1)
     agg_red_shared(cells.lo + 4u * (uint32_t)cell, large ? lo16 : v, valid);
+#endif
     if (valid && large) agg_red_shared(cells.hi + 4u * (uint32_t)cell, (int32_t)(((int64_t)v - lo16) >> 16), true);   // rare
+#if !(AGG_ABLATE & 2)
     agg_st_shared_u8(cells.present + (uint32_t)cell, valid);          // plain byte store: every writer stores the same value
+#endif
 }
 
 // one row into the CTA's shared cells (big pieces: SMALL = false) or straight to the global cells (tiny pieces)
 template <bool SMALL>
 __device__ __forceinline__ void agg_row(const AggParams &p, int32_t v, unsigned cat, int32_t date, const AggCells &cells,
-                                        const uint16_t *month_tab, int64_t *out_s, uint8_t *out_p, unsigned &dropped) {
+                                        uint32_t month_tab, int64_t *out_s, uint8_t *out_p, unsigned &dropped) {
     const unsigned mo = agg_month(p, date, month_tab);
     const bool valid = cat < (unsigned)p.n_categories && mo < (unsigned)p.n_months;
     dropped += valid ? 0u : 1u;
@@ -212,14 +237,16 @@ __global__ void __launch_bounds__(AGG_THREADS, AGG_CTAS) aggregate_kernel(const 
     // again, the barrier of the piece in between has seen every thread finish flushing it.
     int32_t *c_lo = reinterpret_cast<int32_t *>(smem_raw);             // [2][C]
     int32_t *c_hi = c_lo + 2 * C;                                      // [2][C]
-    uint16_t *month_tab = reinterpret_cast<uint16_t *>(c_hi + 2 * C);  // [n_days]
-    uint8_t *c_present = reinterpret_cast<uint8_t *>(month_tab + ((p.n_days + 1) & ~1));   // [2][C]
+    uint16_t *month_tab_g = reinterpret_cast<uint16_t *>(c_hi + 2 * C);   // [n_days + 1]: entry n_days = 0xffff (outside the window)
+    uint8_t *c_present = reinterpret_cast<uint8_t *>(month_tab_g + ((p.n_days + 2) & ~1));   // [2][C]
+    const uint32_t month_tab = (uint32_t)__cvta_generic_to_shared(month_tab_g);
     __shared__ int64_t s_piece[2];
 
     const int tid = threadIdx.x;
-    const AggCells cells2[2] = {agg_cells(c_lo, c_hi, c_present), agg_cells(c_lo + C, c_hi + C, c_present + C)};
+    const AggCells cells_0 = agg_cells(c_lo, c_hi, c_present);
     int cur = 0;                                                       // the set the next large piece accumulates into
-    for (int i = tid; i < p.n_days; i += AGG_THREADS) month_tab[i] = (uint16_t)(month_of_day(p.day0 + i) - p.month_lo);
+    for (int i = tid; i <= p.n_days; i += AGG_THREADS)
+        month_tab_g[i] = i < p.n_days ? (uint16_t)(month_of_day(p.day0 + i) - p.month_lo) : (uint16_t)0xffff;
     for (int i = tid; i < 2 * C; i += AGG_THREADS) { c_lo[i] = 0; c_hi[i] = 0; c_present[i] = 0; }
     __syncthreads();
 
@@ -265,25 +292,42 @@ __global__ void __launch_bounds__(AGG_THREADS, AGG_CTAS) aggregate_kernel(const 
             const bool small = pb - pa < p.small_piece;
             // local row range of the piece; quads aligned on the LOCAL row index so the 128-bit loads are aligned
             const int64_t la = pa - p.row_base, lb = pb - p.row_base;
-            const int64_t q0 = la >> 2, q1 = (lb + 3) >> 2;            // quads [q0, q1) cover [la, lb)
-            // one quad loop per kind of piece, so that the row path carries no per-row "small piece?" test
-            const AggCells cells = cells2[cur];
+            // one loop nest per kind of piece, so that the row path carries no per-row "small piece?" test. Rows of the piece
+            // that do not fill an aligned quad (at most 3 at either end) go first, one per thread; the interior quads follow in
+            // a clean loop on 32-bit indices from the piece's first interior quad, AGG_BATCH quads per thread with all their
+            // column loads issued before the first row is touched (the ncu capture showed the warps waiting on exactly those
+            // loads: long scoreboard 5.8 of ~13 stall cycles per issue).
+            const AggCells cells{cells_0.lo + (uint32_t)(cur * C) * 4u, cells_0.hi + (uint32_t)(cur * C) * 4u,
+                                 cells_0.present + (uint32_t)(cur * C)};   // (computed: an indexed array would live in local memory)
             auto quads = [&](auto small_tag) {
                 constexpr bool SMALL = decltype(small_tag)::value;
-#pragma unroll kAggUnroll
-                for (int64_t q = q0 + tid; q < q1; q += AGG_THREADS) {
-                    const int64_t r = q << 2;
-                    if (r >= la && r + 4 <= lb) {                       // interior quad: three vector loads
-                        const int4 v = __ldg(cents4 + q);
-                        const int4 d = __ldg(dates4 + q);
-                        const uchar4 c = __ldg(cats4 + q);
-                        agg_row<SMALL>(p, v.x, c.x, d.x, cells, month_tab, out_s, out_p, dropped);
-                        agg_row<SMALL>(p, v.y, c.y, d.y, cells, month_tab, out_s, out_p, dropped);
-                        agg_row<SMALL>(p, v.z, c.z, d.z, cells, month_tab, out_s, out_p, dropped);
-                        agg_row<SMALL>(p, v.w, c.w, d.w, cells, month_tab, out_s, out_p, dropped);
-                    } else {                                            // ragged head / tail of the piece
-                        for (int64_t rr = r > la ? r : la; rr < r + 4 && rr < lb; ++rr)
-                            agg_row<SMALL>(p, p.cents[rr], p.cats[rr], p.dates[rr], cells, month_tab, out_s, out_p, dropped);
+                const int64_t qi0 = (la + 3) >> 2, qi1 = lb >> 2;       // interior quads [qi0, qi1); none when qi1 <= qi0
+                const int64_t head_end = qi1 > qi0 ? (qi0 << 2) : lb;   // ragged rows [la, head_end) and [tail_begin, lb)
+                const int64_t tail_begin = qi1 > qi0 ? (qi1 << 2) : lb;
+                const int n_head = (int)(head_end - la), n_tail = (int)(lb - tail_begin);
+                if (tid < n_head + n_tail) {
+                    const int64_t rr = tid < n_head ? la + tid : tail_begin + (tid - n_head);
+                    agg_row<SMALL>(p, p.cents[rr], p.cats[rr], p.dates[rr], cells, month_tab, out_s, out_p, dropped);
+                }
+                const int nq = qi1 > qi0 ? (int)(qi1 - qi0) : 0;
+                const int4 *tv = cents4 + qi0, *td = dates4 + qi0;
+                const uchar4 *tc = cats4 + qi0;
+                for (int qb = tid; qb < nq; qb += AGG_BATCH * AGG_THREADS) {
+                    int4 v[AGG_BATCH], d[AGG_BATCH];
+                    uchar4 c[AGG_BATCH];
+#pragma unroll
+                    for (int j = 0; j < AGG_BATCH; ++j) {
+                        const int qi = qb + j * AGG_THREADS;
+                        if (qi < nq) { v[j] = __ldg(tv + qi); d[j] = __ldg(td + qi); c[j] = __ldg(tc + qi); }
+                    }
+#pragma unroll
+                    for (int j = 0; j < AGG_BATCH; ++j) {
+                        if (qb + j * AGG_THREADS < nq) {
+                            agg_row<SMALL>(p, v[j].x, c[j].x, d[j].x, cells, month_tab, out_s, out_p, dropped);
+                            agg_row<SMALL>(p, v[j].y, c[j].y, d[j].y, cells, month_tab, out_s, out_p, dropped);
+                            agg_row<SMALL>(p, v[j].z, c[j].z, d[j].z, cells, month_tab, out_s, out_p, dropped);
+                            agg_row<SMALL>(p, v[j].w, c[j].w, d[j].w, cells, month_tab, out_s, out_p, dropped);
+                        }
                     }
                 }
             };
@@ -307,6 +351,251 @@ __global__ void __launch_bounds__(AGG_THREADS, AGG_CTAS) aggregate_kernel(const 
       }
     }
     if (dropped) atomicAdd(p.dropped, (unsigned long long)dropped);
+}
+
+// ---- group keys: the month of every row resolved ONCE, at load ------------------------------------
+// plot_tool groups by (category, calendar month of the date). The month of a row never changes, so fcb_load_shard derives a
+// 16-bit GROUP KEY per row and keeps it next to the columns (2 bytes per row, library-owned):
+//     bit 15      the row's amount is "rare": zero, or |v| >= 2^18 (see below)
+//     bits 14..9  category (0..63)
+//     bits 8..0   month - key_base (0..510); 511 = none
+// 0x7fff stands for a category >= 64 or a month outside [key_base, key_base + 511). A query whose month window lies inside
+// the key range then reads cents + key (6 bytes per row instead of 9) and spends no arithmetic on calendars. Rows with key
+// 0x7fff are outside every such window, so they count as dropped exactly as the date path counts them. Windows that reach
+// outside the key range, and columns that come without keys (fcb_aggregate_columns), take the date kernels above.
+#define AGK_MONTH_BITS 9
+#define AGK_MONTHS ((1 << AGK_MONTH_BITS) - 1)          // representable months; the all-ones month field means "none"
+#define AGK_NONE 0x7fffu
+#ifndef AGK_TILE
+#define AGK_TILE 8192                      // rows per piece at most: (2^18 - 1) * 8192 < 2^31, a 32-bit cell cannot overflow
+#endif
+#ifndef AGK_BLOCK_TILES
+#define AGK_BLOCK_TILES 4                  // consecutive tiles one warp takes per binary search over the users
+#endif
+#ifndef AGK_QUADS
+#define AGK_QUADS 4                        // quads (of 4 rows) per lane whose loads are in flight together
+#endif
+#ifndef AGK_CTAS
+#define AGK_CTAS 4
+#endif
+
+// Every WARP owns a private table in shared memory and a stream of pieces (tile x user); nothing in the kernel is CTA-wide:
+// no barrier, no shared piece descriptor. Per cell: a (pos, neg) pair of 32-bit sums of the positive / negative values —
+// for values below 2^18 in magnitude neither can cancel to zero nor overflow within a piece, so "pos | neg != 0" IS the
+// presence of the cell and the common row costs ONE shared reduction and no presence store — plus a hi word and a presence
+// byte for the rare rows. The row update is branch-free and unconditional (a predicated reduction compiles to a branch
+// around it): a row outside the window adds 1 to its lane's own drop counter instead of v to a cell. Rare rows — zero
+// (presence only) and |v| >= 2^18 (split v = hi * 65536 + lo16) — carry a flag in their key and are handled a second time,
+// quad by quad: the large ones add lo16 - v to the word the common path added v to (modular arithmetic: the word ends up
+// holding lo16) and their hi part to the hi word.
+__device__ __forceinline__ bool agk_is_rare(int32_t v) { return !((uint32_t)v + ((1u << 18) - 1u) < (1u << 19) - 1u && v != 0); }
+
+// table of one warp: pos [n_categories][key_stride] int32 | neg, same shape, at key_neg_off | hi [C] int32 at key_hi_off |
+// present [C] bytes | drop counters [32] uint32. Bank layout: in a time-ordered log the 128 rows of a warp round share
+// their month, so their words differ by category and sign only. key_stride is ODD — 16 categories land in 16 different
+// banks (the natural stride, 24 words for two years, would give 4) — and the neg table starts 16 banks (mod 32) after the
+// pos table, so the negative values use the other 16.
+__device__ __forceinline__ void agk_row(const AggParams &p, int32_t v, uint32_t mo_field, uint32_t cat, uint32_t tab,
+                                        uint32_t drop_word) {
+    const uint32_t mo = mo_field - p.key_mo_off;
+    const bool valid = mo < (uint32_t)p.n_months && cat < (uint32_t)p.n_categories;
+    const uint32_t addr = tab + 4u * (cat * p.key_stride + mo) + ((uint32_t)v >> 31) * p.key_neg_off;
+#ifdef AGK_PREDICATED
+    agg_red_shared(addr, v, valid);
+    agg_red_shared(drop_word, 1, !valid);
+#else
+    asm volatile("red.shared.add.s32 [%0], %1;" ::"r"(valid ? addr : drop_word), "r"(valid ? v : 1) : "memory");
+#endif
+}
+// the four rows of a quad: v = amounts, k = two packed pairs of keys
+__device__ __forceinline__ void agk_quad(const AggParams &p, const int4 &v, const uint2 &k, uint32_t tab, uint32_t drop_word) {
+    agk_row(p, v.x, k.x & (uint32_t)AGK_MONTHS, (k.x >> AGK_MONTH_BITS) & 63u, tab, drop_word);
+    agk_row(p, v.y, (k.x >> 16) & (uint32_t)AGK_MONTHS, (k.x >> (16 + AGK_MONTH_BITS)) & 63u, tab, drop_word);
+    agk_row(p, v.z, k.y & (uint32_t)AGK_MONTHS, (k.y >> AGK_MONTH_BITS) & 63u, tab, drop_word);
+    agk_row(p, v.w, (k.y >> 16) & (uint32_t)AGK_MONTHS, (k.y >> (16 + AGK_MONTH_BITS)) & 63u, tab, drop_word);
+}
+
+__device__ __noinline__ void agk_rare_row(const AggParams &p, int32_t v, uint32_t key, uint32_t tab, uint32_t C) {
+    if (!(key & 0x8000u)) return;
+    const uint32_t mo = (key & (uint32_t)AGK_MONTHS) - p.key_mo_off, cat = (key >> AGK_MONTH_BITS) & 63u;
+    if (!(mo < (uint32_t)p.n_months && cat < (uint32_t)p.n_categories)) return;
+    const uint32_t cell = cat * (uint32_t)p.n_months + mo;
+    if (v != 0) {
+        const int32_t lo16 = (int32_t)(int16_t)(v & 0xffff);
+        agg_red_shared(tab + 4u * (cat * p.key_stride + mo) + ((uint32_t)v >> 31) * p.key_neg_off,
+                       (int32_t)((uint32_t)lo16 - (uint32_t)v), true);
+        agg_red_shared(tab + p.key_hi_off + 4u * cell, (int32_t)(((int64_t)v - lo16) >> 16), true);
+    }
+    agg_st_shared_u8(tab + p.key_hi_off + 4u * C + cell, true);
+}
+
+__global__ void __launch_bounds__(AGG_THREADS, AGK_CTAS) aggregate_key_kernel(const __grid_constant__ AggParams p) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const uint32_t C = (uint32_t)(p.n_categories * p.n_months);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t tab_bytes = ((p.key_hi_off + 5u * C + 15u) & ~15u) + 128u;   // see agk_row
+    unsigned char *tab_g = smem_raw + (size_t)warp * tab_bytes;
+    const uint32_t tab = (uint32_t)__cvta_generic_to_shared(tab_g);
+    const uint32_t drop_word = tab + tab_bytes - 128u + 4u * lane;      // this lane's count of rows outside the window
+    for (uint32_t i = lane; i < tab_bytes / 4; i += 32) reinterpret_cast<uint32_t *>(tab_g)[i] = 0;
+    __syncwarp();
+
+    int64_t R0 = p.seg_offsets[p.seg_begin], R1 = p.seg_offsets[p.seg_end];
+    if (R0 < p.row_base) R0 = p.row_base;
+    if (R1 > p.row_base + p.n_rows) R1 = p.row_base + p.n_rows;
+    const int64_t n_tiles = R1 > R0 ? (R1 - R0 + AGK_TILE - 1) / AGK_TILE : 0;
+    const int64_t n_blocks = (n_tiles + AGK_BLOCK_TILES - 1) / AGK_BLOCK_TILES;
+    const int warps = blockDim.x >> 5;                                  // (fewer than 8 when the tables are large)
+    const int64_t n_warps = (int64_t)gridDim.x * warps;
+    
+    for (int64_t blk = (int64_t)blockIdx.x * warps + warp; blk < n_blocks; blk += n_warps) {
+        const int64_t a0 = R0 + blk * AGK_BLOCK_TILES * AGK_TILE;
+        const int64_t b0 = a0 + (int64_t)AGK_BLOCK_TILES * AGK_TILE < R1 ? a0 + (int64_t)AGK_BLOCK_TILES * AGK_TILE : R1;
+        int64_t u;                                                  // first user whose segment ends after a0 (every lane the same)
+        {
+            int64_t lo = p.seg_begin, hi = p.seg_end - 1;
+            while (lo < hi) {
+                const int64_t mid = (lo + hi) >> 1;
+                if (p.seg_offsets[mid + 1] > a0) hi = mid; else lo = mid + 1;
+            }
+            u = lo;
+        }
+        int64_t pa = a0;
+        int64_t ubeg = p.seg_offsets[u], uend = p.seg_offsets[u + 1];
+        while (pa < b0) {
+            while (uend <= pa) { ++u; ubeg = uend; uend = p.seg_offsets[u + 1]; }      // skip empty users
+            const int64_t tile_end = R0 + ((pa - R0) / AGK_TILE + 1) * AGK_TILE;
+            int64_t pb = uend < b0 ? uend : b0;
+            if (tile_end < pb) pb = tile_end;
+            const int64_t la = pa - p.row_base, lb = pb - p.row_base;           // local rows of the piece
+            // rows that do not fill an aligned quad (at most 3 at either end; quads are aligned on the LOCAL row index, where
+            // the 128-bit loads are) go first, one per lane
+            const int64_t qa = (la + 3) >> 2, qb = lb >> 2;
+            const int64_t head_end = qa * 4 < lb ? qa * 4 : lb;
+            const int n_head = (int)(head_end - la), n_tail = qb >= qa ? (int)(lb - qb * 4) : 0;
+            if (lane < n_head + n_tail) {
+                const int64_t r = lane < n_head ? la + lane : qb * 4 + (lane - n_head);
+                const int32_t v = p.cents[r];
+                const uint32_t key = p.keys[r];
+                agk_row(p, v, key & (uint32_t)AGK_MONTHS, (key >> AGK_MONTH_BITS) & 63u, tab, drop_word);
+                agk_rare_row(p, v, key, tab, C);
+            }
+            if (qb > qa) {
+                const int4 *cv = reinterpret_cast<const int4 *>(p.cents) + qa;
+                const uint2 *kv = reinterpret_cast<const uint2 *>(p.keys) + qa;
+                const int nq = (int)(qb - qa);
+                for (int q = lane; q < nq; q += 32 * AGK_QUADS) {
+                    int4 v[AGK_QUADS];
+                    uint2 k[AGK_QUADS];
+#pragma unroll
+                    for (int j = 0; j < AGK_QUADS; ++j) {
+                        const bool in = q + 32 * j < nq;
+                        v[j] = in ? __ldg(cv + q + 32 * j) : make_int4(0, 0, 0, 0);
+                        k[j] = in ? __ldg(kv + q + 32 * j) : make_uint2(0x7fff7fffu, 0x7fff7fffu);
+                    }
+#pragma unroll
+                    for (int j = 0; j < AGK_QUADS; ++j) {
+                        if (q + 32 * j >= nq) break;
+                        agk_quad(p, v[j], k[j], tab, drop_word);
+                        if ((k[j].x | k[j].y) & 0x80008000u) {          // a rare row among the four
+                            agk_rare_row(p, v[j].x, k[j].x & 0xffffu, tab, C);
+                            agk_rare_row(p, v[j].y, k[j].x >> 16, tab, C);
+                            agk_rare_row(p, v[j].z, k[j].y & 0xffffu, tab, C);
+                            agk_rare_row(p, v[j].w, k[j].y >> 16, tab, C);
+                        }
+                    }
+                }
+            }
+            __syncwarp();
+            // the piece's cells go out once: plain stores when the piece is the whole user (nobody else touches its cells,
+            // which the launch zeroed), 64-bit reductions otherwise; the table is left all zero
+            {
+                const bool whole = pa == ubeg && pb == uend;
+                int64_t *out_s = p.sums + (u - p.seg_begin) * (int64_t)C;
+                uint8_t *out_p = p.present + (u - p.seg_begin) * (int64_t)C;
+                int32_t *t_pos = reinterpret_cast<int32_t *>(tab_g), *t_neg = reinterpret_cast<int32_t *>(tab_g + p.key_neg_off);
+                int32_t *t_hi = reinterpret_cast<int32_t *>(tab_g + p.key_hi_off);
+                uint8_t *t_p = reinterpret_cast<uint8_t *>(t_hi + C);
+                uint32_t cat = lane / (uint32_t)p.n_months, mo = lane - cat * (uint32_t)p.n_months;
+                for (uint32_t c = lane; c < C; c += 32) {
+                    const uint32_t w = cat * p.key_stride + mo;
+                    const int32_t ps = t_pos[w], ng = t_neg[w], hi = t_hi[c];
+                    const uint8_t pr = t_p[c];
+                    if ((ps | ng | hi) != 0 || pr) {
+                        const long long s = (long long)hi * 65536 + ps + ng;
+                        if (whole) out_s[c] = s;
+                        else atomicAdd(reinterpret_cast<unsigned long long *>(out_s + c), (unsigned long long)s);
+                        out_p[c] = 1;
+                        t_pos[w] = 0; t_neg[w] = 0; t_hi[c] = 0; t_p[c] = 0;
+                    }
+                    cat += p.key_step_cat; mo += p.key_step_mo;              // cell c + 32
+                    if (mo >= (uint32_t)p.n_months) { mo -= (uint32_t)p.n_months; ++cat; }
+                }
+            }
+            __syncwarp();
+            pa = pb;
+        }
+    }
+    __syncwarp();
+    unsigned dropped = reinterpret_cast<const uint32_t *>(tab_g + tab_bytes - 128u)[lane];
+#pragma unroll
+    for (int o = 16; o; o >>= 1) dropped += __shfl_xor_sync(0xffffffffu, dropped, o);
+    if (lane == 0 && dropped) atomicAdd(p.dropped, (unsigned long long)dropped);
+}
+
+// month range of a shard's dates: [0] = min, [1] = max month index (months since 1970-01)
+__global__ void __launch_bounds__(256) agk_month_range_kernel(const int32_t *__restrict__ dates, int64_t n_rows, int *range) {
+    int lo = INT32_MAX, hi = INT32_MIN;
+    for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < n_rows; r += (int64_t)gridDim.x * blockDim.x) {
+        const int m = month_of_day(floor_day(dates[r]));
+        lo = m < lo ? m : lo; hi = m > hi ? m : hi;
+    }
+#pragma unroll
+    for (int o = 16; o; o >>= 1) {
+        const int l2 = __shfl_xor_sync(0xffffffffu, lo, o), h2 = __shfl_xor_sync(0xffffffffu, hi, o);
+        lo = l2 < lo ? l2 : lo; hi = h2 > hi ? h2 : hi;
+    }
+    if ((threadIdx.x & 31) == 0 && lo <= hi) { atomicMin(range, lo); atomicMax(range + 1, hi); }
+}
+
+__global__ void __launch_bounds__(256) agk_build_keys_kernel(const int32_t *__restrict__ dates, const uint8_t *__restrict__ cats,
+                                                             const int32_t *__restrict__ cents, int64_t n_rows, int32_t key_base,
+                                                             uint16_t *__restrict__ keys) {
+    for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < n_rows; r += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t m = (int64_t)month_of_day(floor_day(dates[r])) - key_base;
+        const unsigned c = cats[r];
+        keys[r] = (m >= 0 && m < AGK_MONTHS && c < 64u)
+                      ? (uint16_t)((agk_is_rare(cents[r]) ? 0x8000u : 0u) | (c << AGK_MONTH_BITS) | (unsigned)m) : (uint16_t)AGK_NONE;
+    }
+}
+
+// Called by fcb_load_shard: derives the key column when the shard has dates, categories and amounts. The key range ends
+// at the newest month of the data (rows older than 511 months before it get the "none" key; a window that reaches back
+// there takes the date kernels). Not being able to allocate the column is not an error: the date kernels serve.
+int32_t fcb_build_group_keys(fcb_engine *e) {
+    const fcb_shard &s = e->shard;
+    cudaFree(e->group_keys); e->group_keys = nullptr; e->key_base = 0;
+    const char *knob = getenv("FCB_AGG_KEYS");
+    if ((knob && knob[0] == '0') || !s.dates || !s.categories || !s.cents || !s.seg_offsets || s.n_rows <= 0) return FCB_OK;
+    if ((reinterpret_cast<uintptr_t>(s.cents) & 15u) != 0) return FCB_OK;          // the key kernel loads amounts 16 bytes at a time
+    int *d_range = nullptr;
+    FCB_CUDA(e, cudaMalloc(&d_range, 2 * sizeof(int)));
+    const int init[2] = {INT32_MAX, INT32_MIN};
+    FCB_CUDA(e, cudaMemcpyAsync(d_range, init, sizeof init, cudaMemcpyHostToDevice, e->stream));
+    agk_month_range_kernel<<<e->num_sms * 8, 256, 0, e->stream>>>(s.dates, s.n_rows, d_range);
+    int h_range[2] = {0, 0};
+    FCB_CUDA(e, cudaMemcpyAsync(h_range, d_range, sizeof h_range, cudaMemcpyDeviceToHost, e->stream));
+    FCB_CUDA(e, cudaStreamSynchronize(e->stream));
+    cudaFree(d_range);
+    if (h_range[0] > h_range[1]) return FCB_OK;
+    uint16_t *keys = nullptr;
+    if (cudaMalloc(&keys, ((size_t)s.n_rows * 2 + 15) & ~(size_t)15) != cudaSuccess) { cudaGetLastError(); return FCB_OK; }
+    const int64_t span = (int64_t)h_range[1] - h_range[0] + 1;
+    e->key_base = span <= AGK_MONTHS ? h_range[0] : h_range[1] - (AGK_MONTHS - 1);
+    agk_build_keys_kernel<<<e->num_sms * 8, 256, 0, e->stream>>>(s.dates, s.categories, s.cents, s.n_rows, e->key_base, keys);
+    FCB_CUDA(e, cudaGetLastError());
+    e->group_keys = keys;
+    return FCB_OK;
 }
 
 // ---- date-ordered segments: no atomics on the hot path ---------------------------------------------
@@ -645,7 +934,8 @@ static AggSide *agg_side_stream(int device) {
 static int32_t agg_launch(fcb_engine *e, int device, int num_sms, int dates_sorted, const int32_t *dates, const uint8_t *cats,
                           const int32_t *cents, const int64_t *seg_offsets, int64_t n_rows, int64_t n_segs, int64_t row_base,
                           int64_t seg_begin, int64_t seg_end, int32_t month_lo, int32_t n_months, int32_t n_categories,
-                          int64_t *sums, uint8_t *present, uint64_t *dropped, cudaStream_t st) {
+                          int64_t *sums, uint8_t *present, uint64_t *dropped, cudaStream_t st, const uint16_t *keys = nullptr,
+                          int32_t key_base = 0) {
     if (!dates || !cats || !cents || !seg_offsets)
         return fcb_fail(e, FCB_ERR_STATE, "fcb_aggregate: needs the dates, categories, cents and seg_offsets columns");
     if (!sums || !present || !dropped) return fcb_fail(e, FCB_ERR_INVALID, "fcb_aggregate: NULL output");
@@ -671,13 +961,57 @@ static int32_t agg_launch(fcb_engine *e, int device, int num_sms, int dates_sort
     p.month_lo = month_lo; p.n_months = n_months; p.n_categories = n_categories;
     p.day0 = first_day_of_month(month_lo);
     p.n_days = first_day_of_month(month_lo + n_months) - p.day0;
+    {
+        const int64_t t0 = (int64_t)p.day0 * 86400, t1 = t0 + (int64_t)p.n_days * 86400;
+        const int64_t lo = t0 < INT32_MIN ? (int64_t)INT32_MIN : t0, hi = t1 > (int64_t)INT32_MAX + 1 ? (int64_t)INT32_MAX + 1 : t1;
+        p.base32 = (int32_t)(hi > lo ? lo : 0);
+        p.window32 = hi > lo ? (uint32_t)(hi - lo) : 0u;
+        p.shift32 = hi > lo ? (uint32_t)(lo - t0) : 0u;
+    }
     p.sums = sums; p.present = present; p.dropped = (unsigned long long *)dropped;
     p.small_piece = AGG_SMALL_PIECE;
     if (const char *knob = getenv("FCB_AGG_SMALL_PIECE")) p.small_piece = atoll(knob);   // tuning knob
-    const size_t smem = (size_t)C * 16 + (size_t)((p.n_days + 1) & ~1) * 2 + (size_t)C * 2 + 16;   // two sets of cells
+    const size_t smem = (size_t)C * 16 + (size_t)((p.n_days + 2) & ~1) * 2 + (size_t)C * 2 + 16;   // two sets of cells
     if (smem > 48 * 1024)
         FCB_CUDA(e, cudaFuncSetAttribute(aggregate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    const char *force = getenv("FCB_AGG_KERNEL");                   // tuning: "atomic" / "sorted"
+    const char *force = getenv("FCB_AGG_KERNEL");                   // tuning: "atomic" / "sorted" / "key"
+    // group keys (engine shards): any row order, one launch, as long as the window lies inside the key range and the
+    // per-warp tables fit (8 warps per CTA up to ~1900 cells, fewer above)
+    if (keys && !(force && force[0] != 'k') && month_lo >= key_base && (int64_t)month_lo + n_months <= (int64_t)key_base + AGK_MONTHS) {
+        const char *lay = getenv("FCB_AGK_LAYOUT");                 // tuning: "n" = natural stride, neg table right after pos
+        const bool natural = lay && lay[0] == 'n';
+        p.key_stride = natural ? (uint32_t)n_months : (uint32_t)(n_months | 1);
+        const uint32_t tab_words = (uint32_t)n_categories * p.key_stride;
+        const uint32_t neg_word = natural ? tab_words
+                                          : (tab_words <= 16 ? 16u : ((tab_words - 16u + 31u) / 32u) * 32u + 16u);   // >= tab_words, = 16 (mod 32)
+        p.key_neg_off = 4u * neg_word;
+        p.key_hi_off = 4u * (neg_word + tab_words);
+        p.key_step_cat = 32u / (uint32_t)n_months; p.key_step_mo = 32u % (uint32_t)n_months;
+        const size_t tab_bytes = (((size_t)p.key_hi_off + 5u * (size_t)C + 15u) & ~(size_t)15) + 128;
+        int warps = (int)((200u * 1024u) / tab_bytes);
+        if (warps > AGG_THREADS / 32) warps = AGG_THREADS / 32;
+        if (warps >= 1) {
+            const size_t smem_k = tab_bytes * warps;
+            if (smem_k > 48 * 1024)
+                FCB_CUDA(e, cudaFuncSetAttribute(aggregate_key_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_k));
+            // shared-memory carve-out: what AGK_CTAS CTAs need and no more — the rest of the 256 KB stays L1, which is where
+            // the loads in flight are tracked (with the maximum carve-out the kernel ran 18 % slower)
+            int carve = (int)(((smem_k + 1024) * AGK_CTAS * 100 + 233471) / 233472);
+            if (const char *knob = getenv("FCB_AGK_CARVEOUT")) carve = atoi(knob);      // tuning
+            if (carve > 100) carve = 100;
+            FCB_CUDA(e, cudaFuncSetAttribute(aggregate_key_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, carve));
+            p.keys = keys;
+            p.key_mo_off = (uint32_t)(month_lo - key_base);
+            int per_sm = 0;
+            FCB_CUDA(e, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, aggregate_key_kernel, warps * 32, smem_k));
+            if (per_sm > AGK_CTAS) per_sm = AGK_CTAS;
+            if (per_sm < 1) per_sm = 1;
+            aggregate_key_kernel<<<num_sms * per_sm, warps * 32, smem_k, st>>>(p);
+            FCB_CUDA(e, cudaGetLastError());
+            return FCB_OK;
+        }
+    }
+    if (force && force[0] == 'k') force = nullptr;                  // (no keys, or the window is outside their range)
     const bool sorted_ok = n_categories <= 32;
     const bool use_sorted = sorted_ok && (force ? force[0] == 's' : dates_sorted != 0);
     // any-order data whose table fits the warp's bin matrix: users below AGS_TABLE_USER rows go to the ordered kernel's
@@ -723,7 +1057,8 @@ extern "C" int32_t fcb_aggregate(fcb_engine *e, int64_t seg_begin, int64_t seg_e
     if (!e->loaded) return fcb_fail(e, FCB_ERR_STATE, "fcb_aggregate: no shard loaded");
     const fcb_shard &s = e->shard;
     return agg_launch(e, e->device, e->num_sms, e->dates_sorted, s.dates, s.categories, s.cents, s.seg_offsets, s.n_rows, s.n_segs,
-                      s.row_base, seg_begin, seg_end, month_lo, n_months, n_categories, sums, present, dropped, (cudaStream_t)stream);
+                      s.row_base, seg_begin, seg_end, month_lo, n_months, n_categories, sums, present, dropped, (cudaStream_t)stream,
+                      e->group_keys, e->key_base);
 }
 
 // The same group-by over caller-owned device columns, without an engine: no vectors, no inverse norms, nothing allocated.

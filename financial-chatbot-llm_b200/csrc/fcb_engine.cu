@@ -47,6 +47,7 @@ extern "C" int32_t fcb_close(fcb_engine *e) {
         free_host_staging(e);
         cudaFree(e->inv_norm);
         cudaFree(e->row_of_rank);
+        cudaFree(e->group_keys);
         fcb_exact_free(e);
         fcb_general_free(e);
         fcb_dense_free(e);
@@ -201,6 +202,7 @@ extern "C" int32_t fcb_load_shard(fcb_engine *e, const fcb_shard *s) {
     e->scan_r = e->scan_u = 0;
     cudaFree(e->inv_norm); e->inv_norm = nullptr;
     cudaFree(e->row_of_rank); e->row_of_rank = nullptr;
+    cudaFree(e->group_keys); e->group_keys = nullptr;
     fcb_exact_free(e);
     fcb_general_free(e);
     fcb_dense_free(e);
@@ -246,6 +248,10 @@ extern "C" int32_t fcb_load_shard(fcb_engine *e, const fcb_shard *s) {
     }
     {
         const int32_t rc = fcb_check_dates_sorted(e);
+        if (rc != FCB_OK) return rc;
+    }
+    {
+        const int32_t rc = fcb_build_group_keys(e);
         if (rc != FCB_OK) return rc;
     }
     if (fcb_dense_eligible(e)) {

@@ -74,6 +74,8 @@ struct fcb_engine {
     uint64_t *d_bsel_ids = nullptr;        // [max_batch][1024]
 
     int dates_sorted = 0;                  // load-time check: dates non-decreasing within every user
+    uint16_t *group_keys = nullptr;        // device [n_rows], library-owned: (category << 10) | (month - key_base) per row, built
+    int32_t key_base = 0;                  //   at load when the shard has dates, categories and amounts (fcb_aggregate.cu)
     int scan_r = 0, scan_u = 0;            // fused scan: the (rows per step, unroll) pair measured fastest on this shard (0 = not yet)
     uint32_t *row_of_rank = nullptr;       // inverse of shard.id_rank, built by fcb_aggregate_hits on first use
     void *dense = nullptr;                 // FcbDense* (fcb_dense.cu): batched tensor-core path scratch
@@ -103,6 +105,7 @@ int32_t fcb_search_general(fcb_engine *e, const double *d_query, const fcb_filte
                            uint64_t *d_out_ids, double *d_out_scores, int32_t *d_out_count, int32_t *d_flag, cudaStream_t st);
 
 int32_t fcb_check_dates_sorted(fcb_engine *e);   // fcb_aggregate.cu
+int32_t fcb_build_group_keys(fcb_engine *e);     // fcb_aggregate.cu
 int32_t fcb_tune_scan(fcb_engine *e);            // fcb_search.cu: measure the scan's (R, U) candidates on the loaded shard
 
 // batched tensor-core path (fcb_dense.cu)

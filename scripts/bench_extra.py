@@ -174,26 +174,44 @@ def agg_bench(args):
     sums = torch.empty((users, 16, 24), dtype=torch.int64, device=DEV)
     pres = torch.empty((users, 16, 24), dtype=torch.uint8, device=DEV)
     drop = torch.empty(1, dtype=torch.int64, device=DEV)
-    ms, p50 = timed(lambda i: eng.aggregate(0, users, mlo, 24, 16, sums, pres, drop), args.steps)
-    assert int(drop.item()) == 0
-    total = int(sums.sum().item())
     ref = int(v.to(torch.int64).sum().item())
-    emit(f"cfg5: {n} rows, 100k users x 16 categories x 24 months, dates in random order (shared-atomic kernel)", ms, p50,
-         n * 9 + users * 384 * 9, rows_per_s=n / (ms / 1e3), checksum_ok=(total == ref), groups=int(pres.sum().item()),
-         max_user_rows=int(np.diff(off).max()))
+    algo = n * 9 + users * 384 * 9          # 9 B per row (date 4, category 1, cents 4) + the dense output
+
+    def run(label, kernel, **kw):
+        if kernel:
+            os.environ["FCB_AGG_KERNEL"] = kernel
+        try:
+            ms, p50 = timed(lambda i: eng.aggregate(0, users, mlo, 24, 16, sums, pres, drop), args.steps)
+        finally:
+            os.environ.pop("FCB_AGG_KERNEL", None)
+        assert int(drop.item()) == 0
+        emit(f"cfg5: {n} rows, 100k users x 16 categories x 24 months, {label}", ms, p50, algo, rows_per_s=n / (ms / 1e3),
+             checksum_ok=(int(sums.sum().item()) == ref), groups=int(pres.sum().item()), **kw)
+
+    run("dates in random order (group-key kernel: reads cents + 16-bit keys, 6 B/row)", "", bytes_read=n * 6 + users * 384 * 9,
+        max_user_rows=int(np.diff(off).max()))
+    if os.environ.get("FCB_BENCH_AGK_LAYOUTS"):
+        os.environ["FCB_AGK_LAYOUT"] = "n"
+        run("dates in random order (group-key kernel, NATURAL table layout)", "")
+        os.environ.pop("FCB_AGK_LAYOUT")
+        os.environ["FCB_AGK_CARVEOUT"] = "100"
+        run("dates in random order (group-key kernel, maximum shared-memory carve-out)", "")
+        os.environ.pop("FCB_AGK_CARVEOUT")
+    run("dates in random order (date kernels: shared-atomic + warp tables, 9 B/row)", "atomic")
     eng.close()
-    # the same table as a time-ordered log (dates non-decreasing within each user): atomic-free kernel
+    # the same table as a time-ordered log (dates non-decreasing within each user)
     from financial_chatbot_llm_b200.engine import synth_dates_sorted
     offs_d = torch.from_numpy(off).to(DEV)
     synth_dates_sorted(d, offs_d, 0, spec.date_span_seconds)
     eng = Engine(device=0, max_batch=1, max_k=1)
     eng.load_shard(vec, dates=d, categories=c, cents=v, seg_offsets=offs_d)
     assert eng.dates_sorted
-    ms, p50 = timed(lambda i: eng.aggregate(0, users, mlo, 24, 16, sums, pres, drop), args.steps)
-    assert int(drop.item()) == 0
-    total = int(sums.sum().item())
-    emit(f"cfg5: {n} rows, 100k users x 16 categories x 24 months, time-ordered log (atomic-free kernel)", ms, p50,
-         n * 9 + users * 384 * 9, rows_per_s=n / (ms / 1e3), checksum_ok=(total == ref), groups=int(pres.sum().item()))
+    run("time-ordered log (group-key kernel, 6 B/row)", "", bytes_read=n * 6 + users * 384 * 9)
+    if os.environ.get("FCB_BENCH_AGK_LAYOUTS"):
+        os.environ["FCB_AGK_LAYOUT"] = "n"
+        run("time-ordered log (group-key kernel, NATURAL table layout)", "")
+        os.environ.pop("FCB_AGK_LAYOUT")
+    run("time-ordered log (date kernel: atomic-free runs, 9 B/row)", "sorted")
     eng.close()
 
 

@@ -144,9 +144,14 @@ def test_tool_shaped_json_groupby_equals_pandas_golden(built):
     assert err.startswith("Error creating plot:")
 
 
-def test_time_ordered_log_uses_the_atomic_free_kernel_and_matches_pandas(built):
-    """Dates non-decreasing within every user (the load-time check sees it) -> aggregate_sorted_kernel.
-    Same bit-exact answer as pandas; the device generator of ordered dates equals the host recipe."""
+@pytest.mark.parametrize("kernel", ["default", "sorted"])
+def test_time_ordered_log_uses_the_atomic_free_kernel_and_matches_pandas(built, monkeypatch, kernel):
+    """Dates non-decreasing within every user (the load-time check sees it). An engine shard is aggregated from its group
+    keys by default; the date columns alone (FCB_AGG_KERNEL=sorted here, fcb_aggregate_columns in production) take
+    aggregate_sorted_kernel, the atomic-free kernel for ordered logs. Same bit-exact answer as pandas either way; the
+    device generator of ordered dates equals the host recipe."""
+    if kernel == "sorted":
+        monkeypatch.setenv("FCB_AGG_KERNEL", "sorted")
     import torch
     from financial_chatbot_llm_b200 import aggregate, synth
     from financial_chatbot_llm_b200.engine import synth_dates_sorted
@@ -290,3 +295,74 @@ def test_any_order_kernels_on_awkward_shapes_equal_pandas(built, monkeypatch):
                                    row_base=a)
     torch.cuda.synchronize()
     assert np.array_equal(s2.cpu().numpy(), sums[lo_u:hi_u]) and np.array_equal(p2.cpu().numpy(), present[lo_u:hi_u])
+
+
+def dense_from_engine(eng, lo_u, hi_u, mlo, nm, ncat):
+    import torch
+    sums, present, dropped = eng.aggregate(lo_u, hi_u, mlo, nm, ncat)
+    torch.cuda.synchronize()
+    return sums.cpu().numpy(), present.cpu().numpy(), int(dropped.item())
+
+
+def test_group_key_kernel_equals_the_date_kernels_and_pandas(built, monkeypatch):
+    """Engine shards carry a 16-bit group key per row (category, month, "rare amount" flag) built at load; windows inside
+    the key range are aggregated from cents + keys by aggregate_key_kernel. Same awkward shapes as above plus what is
+    special to this kernel: zero amounts (a cell whose only rows are zero is present with sum 0), amounts that cancel,
+    |v| around the 2^18 split, full-range int32, categories >= n_categories and >= 64, dates before / after the window,
+    windows narrower than the data. The dense output must be IDENTICAL to the date kernels' (FCB_AGG_KERNEL=atomic) and
+    equal pandas."""
+    import torch
+    from financial_chatbot_llm_b200 import synth
+    from financial_chatbot_llm_b200.engine import Engine
+    from oracle import groupby
+    rng = np.random.default_rng(21)
+    sizes = np.array([3, 8191, 8192, 8193, 1, 0, 4096 * 2 + 1, 150_001, 17, 8192 + 4097, 0, 0, 40_000, 5, 12_345, 2], dtype=np.int64)
+    off = np.zeros(len(sizes) + 1, dtype=np.int64)
+    np.cumsum(sizes, out=off[1:])
+    n = int(off[-1])
+    v = rng.integers(-(2 ** 31), 2 ** 31, size=n, dtype=np.int64).astype(np.int32)
+    v[::3] = rng.integers(-5000, 5000, size=v[::3].size)
+    v[1::7] = 0
+    edge = np.array([2 ** 18 - 1, 2 ** 18, -(2 ** 18) + 1, -(2 ** 18), 2 ** 31 - 1, -(2 ** 31), 65535, 65536, -65536, 1, -1], dtype=np.int64)
+    v[rng.integers(0, n, size=4000)] = edge[rng.integers(0, len(edge), size=4000)].astype(np.int32)
+    d = (synth.DATE_BASE + rng.integers(0, 730 * 86400, size=n)).astype(np.int32)
+    c = rng.integers(0, 16, size=n).astype(np.uint8)
+    c[rng.integers(0, n, size=300)] = 200
+    c[rng.integers(0, n, size=300)] = 40
+    d[rng.integers(0, n, size=300)] = synth.DATE_BASE - 86400
+    # user 13 (5 rows): one cell made of zeros only, one of amounts that cancel
+    a13 = int(off[13])
+    v[a13:a13 + 5] = [0, 0, 77, -77, 5]
+    c[a13:a13 + 5] = [3, 3, 4, 4, 5]
+    d[a13:a13 + 5] = synth.DATE_BASE + 40 * 86400
+    dev = torch.device("cuda", 0)
+    mlo = int(groupby.month_index(np.array([synth.DATE_BASE]))[0])
+    eng = Engine(device=0, max_batch=1, max_k=1)
+    eng.load_shard(torch.zeros((n, 4), dtype=torch.float32, device=dev), dates=torch.from_numpy(d).to(dev),
+                   categories=torch.from_numpy(c).to(dev), cents=torch.from_numpy(v).to(dev), seg_offsets=torch.from_numpy(off).to(dev))
+    users = synth.row_users(off, np.arange(n))
+    month = groupby.month_index(d)
+    for (w_lo, w_n, ncat) in ((mlo, 24, 16), (mlo + 5, 7, 9), (mlo - 1, 26, 64), (mlo - 3, 30, 64), (mlo - 600, 4, 16)):
+        got = dense_from_engine(eng, 0, len(sizes), w_lo, w_n, ncat)
+        monkeypatch.setenv("FCB_AGG_KERNEL", "atomic")
+        ref = dense_from_engine(eng, 0, len(sizes), w_lo, w_n, ncat)
+        monkeypatch.delenv("FCB_AGG_KERNEL")
+        assert np.array_equal(got[0], ref[0]) and np.array_equal(got[1], ref[1]) and got[2] == ref[2], (w_lo, w_n, ncat)
+        keep = (c < ncat) & (month >= w_lo) & (month < w_lo + w_n)
+        assert got[2] == int((~keep).sum())
+        if keep.any():
+            ser = groupby.groupby_user_category_month(users[keep], c[keep], d[keep], v[keep])
+            idx = ser.index.to_frame(index=False)
+            assert int(got[1].sum()) == len(ser)
+            assert got[0][idx["user"].to_numpy(), idx["category"].to_numpy(), idx["month"].to_numpy() - w_lo].tolist() == ser.tolist()
+        else:
+            assert int(got[1].sum()) == 0
+    # the two special cells of user 13
+    s, p_, _ = dense_from_engine(eng, 13, 14, mlo, 24, 16)
+    m13 = int(groupby.month_index(np.array([synth.DATE_BASE + 40 * 86400]))[0]) - mlo
+    assert p_[0, 3, m13] == 1 and s[0, 3, m13] == 0 and p_[0, 4, m13] == 1 and s[0, 4, m13] == 0 and s[0, 5, m13] == 5
+    # a sub-range of users
+    s2, p2, _ = dense_from_engine(eng, 5, 11, mlo, 24, 16)
+    full = dense_from_engine(eng, 0, len(sizes), mlo, 24, 16)
+    assert np.array_equal(s2, full[0][5:11]) and np.array_equal(p2, full[1][5:11])
+    eng.close()
