@@ -24,22 +24,18 @@
 #include "fcb_internal.cuh"
 
 #define AGG_THREADS 256
-#ifndef AGG_TILE
 #define AGG_TILE 4096
-#endif
 #define AGG_SMALL_PIECE 96
 #ifndef AGG_BLOCK_TILES
 #define AGG_BLOCK_TILES 16                 // consecutive tiles per binary search over the user offsets
 #endif
-#ifndef AGG_BATCH
-#define AGG_BATCH 2                        // quads per thread whose column loads are in flight together
-#endif
-#ifndef AGG_ABLATE
-#define AGG_ABLATE 0                       // timing experiments only (wrong results): 1 no cell reduction, 2 no presence store, 4 no month lookup
+#ifndef AGG_UNROLL
+#define AGG_UNROLL 2
 #endif
 #ifndef AGG_CTAS
 #define AGG_CTAS 4                         // resident CTAs per SM of aggregate_kernel (register cap 65536 / (256 * AGG_CTAS))
 #endif
+constexpr int kAggUnroll = AGG_UNROLL;     // (#pragma unroll takes a constant expression, not a macro)
 #define AGG_MAX_MONTHS 240
 #define AGG_MAX_CELLS 4096
 
@@ -52,11 +48,6 @@ struct AggParams {
     int64_t row_base, n_rows;
     int32_t month_lo, n_months, n_categories;
     int32_t day0, n_days;                  // table covers days [day0, day0 + n_days)
-    // the same window in 32-bit seconds for aggregate_kernel's row path (dates are int32): a date d is inside iff
-    // (uint32)d - (uint32)base32 < window32 — the window clipped to the int32 range, so the wrap-around cannot alias —
-    // and its day slot is ((uint32)d - base32 + shift32) / 86400 (shift32 != 0 only for a window that starts before 1901)
-    int32_t base32;
-    uint32_t window32, shift32;
     int64_t *sums;                         // [segs, n_categories, n_months]
     uint8_t *present;                      // same shape
     unsigned long long *dropped;           // rows outside the category / month window
@@ -65,7 +56,8 @@ struct AggParams {
     uint32_t key_mo_off;                   // month_lo - key base: month slot of a row = (key's month field) - key_mo_off
     uint32_t key_stride;                   // words per category in a warp's pos / neg tables: n_months | 1 (odd, see agk_row)
     uint32_t key_neg_off, key_hi_off;      // byte offsets of the neg table and of the hi words in a warp's table
-    uint32_t key_step_cat, key_step_mo;    // 32 = key_step_cat * n_months + key_step_mo (the flush loop's walk over cells)
+    uint32_t key_step_mo, key_step_w4, key_wrap_w4;   // the flush loop's walk from cell c to c + 32: month slot += key_step_mo, table
+                                           //   byte offset += key_step_w4, and on a month wrap -= n_months, += key_wrap_w4
     int split;                             // any-order data, two launches: 1 = this launch skips users < AGS_TABLE_USER rows (the
                                            // atomic kernel), 2 = it handles ONLY them (the warp-table path of the ordered kernel)
 };
@@ -103,18 +95,11 @@ __device__ __forceinline__ int32_t floor_day(int32_t ts) {
     return d;
 }
 
-// month slot of a date inside the window, or 0xffff — branch-free: one 32-bit subtract + compare against the window (see
-// AggParams), an unsigned division by a constant, and a table lookup whose entry [n_days] is the 0xffff sentinel
-__device__ __forceinline__ unsigned agg_month(const AggParams &p, int32_t date, uint32_t mtab_addr) {
-    const uint32_t off = (uint32_t)date - (uint32_t)p.base32;
-    const uint32_t day = off < p.window32 ? (off + p.shift32) / 86400u : (uint32_t)p.n_days;
-#if AGG_ABLATE & 4
-    return day >> 5;
-#else
-    unsigned short mo;
-    asm("ld.shared.u16 %0, [%1];" : "=h"(mo) : "r"(mtab_addr + 2u * day));
-    return mo;
-#endif
+// month slot of a date inside the window, or 0xffff: one 64-bit subtract + compare against the window, an unsigned
+// division by a constant and a table lookup (cheaper than flooring a signed day number first)
+__device__ __forceinline__ unsigned agg_month(const AggParams &p, int32_t date, const uint16_t *month_tab) {
+    const uint64_t off = (uint64_t)((int64_t)date - (int64_t)p.day0 * 86400);
+    return off < (uint64_t)p.n_days * 86400u ? month_tab[(uint32_t)off / 86400u] : 0xffffu;
 }
 
 // predicated shared-memory reduction / byte store on 32-bit shared-window addresses (no branch, no generic -> shared
@@ -139,19 +124,15 @@ __device__ __forceinline__ AggCells agg_cells(const int32_t *c_lo, const int32_t
 __device__ __forceinline__ void agg_cell_add(const AggCells &cells, bool valid, int cell, int32_t v) {
     const bool large = !((uint32_t)v + ((1u << 18) - 1u) < (1u << 19) - 1u);   // not in (-2^18, 2^18)
     const int32_t lo16 = (int32_t)(int16_t)(v & 0xffff);
-#if !(AGG_ABLATE & 1)
     agg_red_shared(cells.lo + 4u * (uint32_t)cell, large ? lo16 : v, valid);
-#endif
     if (valid && large) agg_red_shared(cells.hi + 4u * (uint32_t)cell, (int32_t)(((int64_t)v - lo16) >> 16), true);   // rare
-#if !(AGG_ABLATE & 2)
     agg_st_shared_u8(cells.present + (uint32_t)cell, valid);          // plain byte store: every writer stores the same value
-#endif
 }
 
 // one row into the CTA's shared cells (big pieces: SMALL = false) or straight to the global cells (tiny pieces)
 template <bool SMALL>
 __device__ __forceinline__ void agg_row(const AggParams &p, int32_t v, unsigned cat, int32_t date, const AggCells &cells,
-                                        uint32_t month_tab, int64_t *out_s, uint8_t *out_p, unsigned &dropped) {
+                                        const uint16_t *month_tab, int64_t *out_s, uint8_t *out_p, unsigned &dropped) {
     const unsigned mo = agg_month(p, date, month_tab);
     const bool valid = cat < (unsigned)p.n_categories && mo < (unsigned)p.n_months;
     dropped += valid ? 0u : 1u;
@@ -237,16 +218,14 @@ __global__ void __launch_bounds__(AGG_THREADS, AGG_CTAS) aggregate_kernel(const 
     // again, the barrier of the piece in between has seen every thread finish flushing it.
     int32_t *c_lo = reinterpret_cast<int32_t *>(smem_raw);             // [2][C]
     int32_t *c_hi = c_lo + 2 * C;                                      // [2][C]
-    uint16_t *month_tab_g = reinterpret_cast<uint16_t *>(c_hi + 2 * C);   // [n_days + 1]: entry n_days = 0xffff (outside the window)
-    uint8_t *c_present = reinterpret_cast<uint8_t *>(month_tab_g + ((p.n_days + 2) & ~1));   // [2][C]
-    const uint32_t month_tab = (uint32_t)__cvta_generic_to_shared(month_tab_g);
+    uint16_t *month_tab = reinterpret_cast<uint16_t *>(c_hi + 2 * C);  // [n_days]
+    uint8_t *c_present = reinterpret_cast<uint8_t *>(month_tab + ((p.n_days + 1) & ~1));   // [2][C]
     __shared__ int64_t s_piece[2];
 
     const int tid = threadIdx.x;
     const AggCells cells_0 = agg_cells(c_lo, c_hi, c_present);
     int cur = 0;                                                       // the set the next large piece accumulates into
-    for (int i = tid; i <= p.n_days; i += AGG_THREADS)
-        month_tab_g[i] = i < p.n_days ? (uint16_t)(month_of_day(p.day0 + i) - p.month_lo) : (uint16_t)0xffff;
+    for (int i = tid; i < p.n_days; i += AGG_THREADS) month_tab[i] = (uint16_t)(month_of_day(p.day0 + i) - p.month_lo);
     for (int i = tid; i < 2 * C; i += AGG_THREADS) { c_lo[i] = 0; c_hi[i] = 0; c_present[i] = 0; }
     __syncthreads();
 
@@ -292,42 +271,26 @@ __global__ void __launch_bounds__(AGG_THREADS, AGG_CTAS) aggregate_kernel(const 
             const bool small = pb - pa < p.small_piece;
             // local row range of the piece; quads aligned on the LOCAL row index so the 128-bit loads are aligned
             const int64_t la = pa - p.row_base, lb = pb - p.row_base;
-            // one loop nest per kind of piece, so that the row path carries no per-row "small piece?" test. Rows of the piece
-            // that do not fill an aligned quad (at most 3 at either end) go first, one per thread; the interior quads follow in
-            // a clean loop on 32-bit indices from the piece's first interior quad, AGG_BATCH quads per thread with all their
-            // column loads issued before the first row is touched (the ncu capture showed the warps waiting on exactly those
-            // loads: long scoreboard 5.8 of ~13 stall cycles per issue).
+            const int64_t q0 = la >> 2, q1 = (lb + 3) >> 2;            // quads [q0, q1) cover [la, lb)
+            // one quad loop per kind of piece, so that the row path carries no per-row "small piece?" test
             const AggCells cells{cells_0.lo + (uint32_t)(cur * C) * 4u, cells_0.hi + (uint32_t)(cur * C) * 4u,
                                  cells_0.present + (uint32_t)(cur * C)};   // (computed: an indexed array would live in local memory)
             auto quads = [&](auto small_tag) {
                 constexpr bool SMALL = decltype(small_tag)::value;
-                const int64_t qi0 = (la + 3) >> 2, qi1 = lb >> 2;       // interior quads [qi0, qi1); none when qi1 <= qi0
-                const int64_t head_end = qi1 > qi0 ? (qi0 << 2) : lb;   // ragged rows [la, head_end) and [tail_begin, lb)
-                const int64_t tail_begin = qi1 > qi0 ? (qi1 << 2) : lb;
-                const int n_head = (int)(head_end - la), n_tail = (int)(lb - tail_begin);
-                if (tid < n_head + n_tail) {
-                    const int64_t rr = tid < n_head ? la + tid : tail_begin + (tid - n_head);
-                    agg_row<SMALL>(p, p.cents[rr], p.cats[rr], p.dates[rr], cells, month_tab, out_s, out_p, dropped);
-                }
-                const int nq = qi1 > qi0 ? (int)(qi1 - qi0) : 0;
-                const int4 *tv = cents4 + qi0, *td = dates4 + qi0;
-                const uchar4 *tc = cats4 + qi0;
-                for (int qb = tid; qb < nq; qb += AGG_BATCH * AGG_THREADS) {
-                    int4 v[AGG_BATCH], d[AGG_BATCH];
-                    uchar4 c[AGG_BATCH];
-#pragma unroll
-                    for (int j = 0; j < AGG_BATCH; ++j) {
-                        const int qi = qb + j * AGG_THREADS;
-                        if (qi < nq) { v[j] = __ldg(tv + qi); d[j] = __ldg(td + qi); c[j] = __ldg(tc + qi); }
-                    }
-#pragma unroll
-                    for (int j = 0; j < AGG_BATCH; ++j) {
-                        if (qb + j * AGG_THREADS < nq) {
-                            agg_row<SMALL>(p, v[j].x, c[j].x, d[j].x, cells, month_tab, out_s, out_p, dropped);
-                            agg_row<SMALL>(p, v[j].y, c[j].y, d[j].y, cells, month_tab, out_s, out_p, dropped);
-                            agg_row<SMALL>(p, v[j].z, c[j].z, d[j].z, cells, month_tab, out_s, out_p, dropped);
-                            agg_row<SMALL>(p, v[j].w, c[j].w, d[j].w, cells, month_tab, out_s, out_p, dropped);
-                        }
+#pragma unroll kAggUnroll
+                for (int64_t q = q0 + tid; q < q1; q += AGG_THREADS) {
+                    const int64_t r = q << 2;
+                    if (r >= la && r + 4 <= lb) {                       // interior quad: three vector loads
+                        const int4 v = __ldg(cents4 + q);
+                        const int4 d = __ldg(dates4 + q);
+                        const uchar4 c = __ldg(cats4 + q);
+                        agg_row<SMALL>(p, v.x, c.x, d.x, cells, month_tab, out_s, out_p, dropped);
+                        agg_row<SMALL>(p, v.y, c.y, d.y, cells, month_tab, out_s, out_p, dropped);
+                        agg_row<SMALL>(p, v.z, c.z, d.z, cells, month_tab, out_s, out_p, dropped);
+                        agg_row<SMALL>(p, v.w, c.w, d.w, cells, month_tab, out_s, out_p, dropped);
+                    } else {                                            // ragged head / tail of the piece
+                        for (int64_t rr = r > la ? r : la; rr < r + 4 && rr < lb; ++rr)
+                            agg_row<SMALL>(p, p.cents[rr], p.cats[rr], p.dates[rr], cells, month_tab, out_s, out_p, dropped);
                     }
                 }
             };
@@ -484,18 +447,26 @@ __global__ void __launch_bounds__(AGG_THREADS, AGK_CTAS) aggregate_key_kernel(co
                 const int4 *cv = reinterpret_cast<const int4 *>(p.cents) + qa;
                 const uint2 *kv = reinterpret_cast<const uint2 *>(p.keys) + qa;
                 const int nq = (int)(qb - qa);
+                // AGK_QUADS quads per lane and round, all their loads in flight before the first row is used (issuing the next
+                // round's loads ahead of the current round's rows, from a second register set, measured 8 % SLOWER)
                 for (int q = lane; q < nq; q += 32 * AGK_QUADS) {
                     int4 v[AGK_QUADS];
                     uint2 k[AGK_QUADS];
+                    const bool full = q + 32 * (AGK_QUADS - 1) < nq;        // every round but a lane's last: no per-quad tests
+                    if (full) {
 #pragma unroll
-                    for (int j = 0; j < AGK_QUADS; ++j) {
-                        const bool in = q + 32 * j < nq;
-                        v[j] = in ? __ldg(cv + q + 32 * j) : make_int4(0, 0, 0, 0);
-                        k[j] = in ? __ldg(kv + q + 32 * j) : make_uint2(0x7fff7fffu, 0x7fff7fffu);
+                        for (int j = 0; j < AGK_QUADS; ++j) { v[j] = __ldg(cv + q + 32 * j); k[j] = __ldg(kv + q + 32 * j); }
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < AGK_QUADS; ++j) {
+                            const bool in = q + 32 * j < nq;
+                            v[j] = in ? __ldg(cv + q + 32 * j) : make_int4(0, 0, 0, 0);
+                            k[j] = in ? __ldg(kv + q + 32 * j) : make_uint2(0u, 0u);
+                        }
                     }
 #pragma unroll
                     for (int j = 0; j < AGK_QUADS; ++j) {
-                        if (q + 32 * j >= nq) break;
+                        if (!full && q + 32 * j >= nq) break;
                         agk_quad(p, v[j], k[j], tab, drop_word);
                         if ((k[j].x | k[j].y) & 0x80008000u) {          // a rare row among the four
                             agk_rare_row(p, v[j].x, k[j].x & 0xffffu, tab, C);
@@ -511,25 +482,33 @@ __global__ void __launch_bounds__(AGG_THREADS, AGK_CTAS) aggregate_key_kernel(co
             // which the launch zeroed), 64-bit reductions otherwise; the table is left all zero
             {
                 const bool whole = pa == ubeg && pb == uend;
-                int64_t *out_s = p.sums + (u - p.seg_begin) * (int64_t)C;
-                uint8_t *out_p = p.present + (u - p.seg_begin) * (int64_t)C;
-                int32_t *t_pos = reinterpret_cast<int32_t *>(tab_g), *t_neg = reinterpret_cast<int32_t *>(tab_g + p.key_neg_off);
-                int32_t *t_hi = reinterpret_cast<int32_t *>(tab_g + p.key_hi_off);
-                uint8_t *t_p = reinterpret_cast<uint8_t *>(t_hi + C);
-                uint32_t cat = lane / (uint32_t)p.n_months, mo = lane - cat * (uint32_t)p.n_months;
+                // this lane's cells lane, lane + 32, ...: pointers and table slots advance by constant steps (no per-cell
+                // multiplications or divisions)
+                int64_t *os = p.sums + (u - p.seg_begin) * (int64_t)C + lane;
+                uint8_t *op = p.present + (u - p.seg_begin) * (int64_t)C + lane;
+                uint32_t mo = (uint32_t)lane % (uint32_t)p.n_months;
+                uint32_t w4 = tab + 4u * (((uint32_t)lane / (uint32_t)p.n_months) * p.key_stride + mo);   // pos word of the cell
+                uint32_t h4 = tab + p.key_hi_off + 4u * lane, pb1 = tab + p.key_hi_off + 4u * C + lane;
                 for (uint32_t c = lane; c < C; c += 32) {
-                    const uint32_t w = cat * p.key_stride + mo;
-                    const int32_t ps = t_pos[w], ng = t_neg[w], hi = t_hi[c];
-                    const uint8_t pr = t_p[c];
-                    if ((ps | ng | hi) != 0 || pr) {
+                    int32_t ps, ng, hi;
+                    uint32_t pr;
+                    asm volatile("ld.shared.s32 %0, [%1];" : "=r"(ps) : "r"(w4));
+                    asm volatile("ld.shared.s32 %0, [%1];" : "=r"(ng) : "r"(w4 + p.key_neg_off));
+                    asm volatile("ld.shared.s32 %0, [%1];" : "=r"(hi) : "r"(h4));
+                    asm volatile("ld.shared.u8 %0, [%1];" : "=r"(pr) : "r"(pb1));
+                    if ((ps | ng | hi | (int32_t)pr) != 0) {
                         const long long s = (long long)hi * 65536 + ps + ng;
-                        if (whole) out_s[c] = s;
-                        else atomicAdd(reinterpret_cast<unsigned long long *>(out_s + c), (unsigned long long)s);
-                        out_p[c] = 1;
-                        t_pos[w] = 0; t_neg[w] = 0; t_hi[c] = 0; t_p[c] = 0;
+                        if (whole) *os = s;
+                        else atomicAdd(reinterpret_cast<unsigned long long *>(os), (unsigned long long)s);
+                        *op = 1;
+                        asm volatile("st.shared.b32 [%0], %1;" ::"r"(w4), "r"(0) : "memory");
+                        asm volatile("st.shared.b32 [%0], %1;" ::"r"(w4 + p.key_neg_off), "r"(0) : "memory");
+                        asm volatile("st.shared.b32 [%0], %1;" ::"r"(h4), "r"(0) : "memory");
+                        asm volatile("st.shared.u8 [%0], %1;" ::"r"(pb1), "r"(0) : "memory");
                     }
-                    cat += p.key_step_cat; mo += p.key_step_mo;              // cell c + 32
-                    if (mo >= (uint32_t)p.n_months) { mo -= (uint32_t)p.n_months; ++cat; }
+                    os += 32; op += 32; h4 += 128u; pb1 += 32u;
+                    mo += p.key_step_mo; w4 += p.key_step_w4;                    // cell c + 32
+                    if (mo >= (uint32_t)p.n_months) { mo -= (uint32_t)p.n_months; w4 += p.key_wrap_w4; }
                 }
             }
             __syncwarp();
@@ -961,20 +940,13 @@ static int32_t agg_launch(fcb_engine *e, int device, int num_sms, int dates_sort
     p.month_lo = month_lo; p.n_months = n_months; p.n_categories = n_categories;
     p.day0 = first_day_of_month(month_lo);
     p.n_days = first_day_of_month(month_lo + n_months) - p.day0;
-    {
-        const int64_t t0 = (int64_t)p.day0 * 86400, t1 = t0 + (int64_t)p.n_days * 86400;
-        const int64_t lo = t0 < INT32_MIN ? (int64_t)INT32_MIN : t0, hi = t1 > (int64_t)INT32_MAX + 1 ? (int64_t)INT32_MAX + 1 : t1;
-        p.base32 = (int32_t)(hi > lo ? lo : 0);
-        p.window32 = hi > lo ? (uint32_t)(hi - lo) : 0u;
-        p.shift32 = hi > lo ? (uint32_t)(lo - t0) : 0u;
-    }
     p.sums = sums; p.present = present; p.dropped = (unsigned long long *)dropped;
     p.small_piece = AGG_SMALL_PIECE;
     if (const char *knob = getenv("FCB_AGG_SMALL_PIECE")) p.small_piece = atoll(knob);   // tuning knob
-    const size_t smem = (size_t)C * 16 + (size_t)((p.n_days + 2) & ~1) * 2 + (size_t)C * 2 + 16;   // two sets of cells
+    const size_t smem = (size_t)C * 16 + (size_t)((p.n_days + 1) & ~1) * 2 + (size_t)C * 2 + 16;   // two sets of cells
     if (smem > 48 * 1024)
         FCB_CUDA(e, cudaFuncSetAttribute(aggregate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    const char *force = getenv("FCB_AGG_KERNEL");                   // tuning: "atomic" / "sorted" / "key"
+    const char *force = getenv("FCB_AGG_KERNEL");                   // tuning: "atomic" / "sorted" / "key" / "date"
     // group keys (engine shards): any row order, one launch, as long as the window lies inside the key range and the
     // per-warp tables fit (8 warps per CTA up to ~1900 cells, fewer above)
     if (keys && !(force && force[0] != 'k') && month_lo >= key_base && (int64_t)month_lo + n_months <= (int64_t)key_base + AGK_MONTHS) {
@@ -986,7 +958,9 @@ static int32_t agg_launch(fcb_engine *e, int device, int num_sms, int dates_sort
                                           : (tab_words <= 16 ? 16u : ((tab_words - 16u + 31u) / 32u) * 32u + 16u);   // >= tab_words, = 16 (mod 32)
         p.key_neg_off = 4u * neg_word;
         p.key_hi_off = 4u * (neg_word + tab_words);
-        p.key_step_cat = 32u / (uint32_t)n_months; p.key_step_mo = 32u % (uint32_t)n_months;
+        p.key_step_mo = 32u % (uint32_t)n_months;
+        p.key_step_w4 = 4u * ((32u / (uint32_t)n_months) * p.key_stride + p.key_step_mo);
+        p.key_wrap_w4 = 4u * (p.key_stride - (uint32_t)n_months);
         const size_t tab_bytes = (((size_t)p.key_hi_off + 5u * (size_t)C + 15u) & ~(size_t)15) + 128;
         int warps = (int)((200u * 1024u) / tab_bytes);
         if (warps > AGG_THREADS / 32) warps = AGG_THREADS / 32;
@@ -1011,7 +985,7 @@ static int32_t agg_launch(fcb_engine *e, int device, int num_sms, int dates_sort
             return FCB_OK;
         }
     }
-    if (force && force[0] == 'k') force = nullptr;                  // (no keys, or the window is outside their range)
+    if (force && (force[0] == 'k' || force[0] == 'd')) force = nullptr;   // ("date": no keys, the usual choice among the date kernels)
     const bool sorted_ok = n_categories <= 32;
     const bool use_sorted = sorted_ok && (force ? force[0] == 's' : dates_sorted != 0);
     // any-order data whose table fits the warp's bin matrix: users below AGS_TABLE_USER rows go to the ordered kernel's

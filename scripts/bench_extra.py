@@ -197,7 +197,7 @@ def agg_bench(args):
         os.environ["FCB_AGK_CARVEOUT"] = "100"
         run("dates in random order (group-key kernel, maximum shared-memory carve-out)", "")
         os.environ.pop("FCB_AGK_CARVEOUT")
-    run("dates in random order (date kernels: shared-atomic + warp tables, 9 B/row)", "atomic")
+    run("dates in random order (date kernels: shared-atomic + warp tables, 9 B/row)", "date")
     eng.close()
     # the same table as a time-ordered log (dates non-decreasing within each user)
     from financial_chatbot_llm_b200.engine import synth_dates_sorted
