@@ -548,31 +548,42 @@ __global__ void __launch_bounds__(256) agk_build_keys_kernel(const int32_t *__re
     }
 }
 
-// Called by fcb_load_shard: derives the key column when the shard has dates, categories and amounts. The key range ends
-// at the newest month of the data (rows older than 511 months before it get the "none" key; a window that reaches back
-// there takes the date kernels). Not being able to allocate the column is not an error: the date kernels serve.
+// Derives the key column of [n_rows] rows into `keys` (device, 16-byte aligned, n_rows * 2 bytes rounded up to 16). The key
+// range ends at the newest month of the data: rows older than 510 months before it get the "none" key, and a window that
+// reaches back there takes the date kernels. Waits for `st` (the month range of the data comes back to the host).
+static int32_t agk_build(fcb_engine *e, int num_sms, const int32_t *dates, const uint8_t *cats, const int32_t *cents, int64_t n_rows,
+                         uint16_t *keys, int32_t *key_base, cudaStream_t st) {
+    int *d_range = nullptr;
+    FCB_CUDA(e, cudaMalloc(&d_range, 2 * sizeof(int)));
+    const int init[2] = {INT32_MAX, INT32_MIN};
+    int h_range[2] = {0, 0};
+    cudaError_t rc = cudaMemcpyAsync(d_range, init, sizeof init, cudaMemcpyHostToDevice, st);
+    if (rc == cudaSuccess) {
+        agk_month_range_kernel<<<num_sms * 8, 256, 0, st>>>(dates, n_rows, d_range);
+        rc = cudaMemcpyAsync(h_range, d_range, sizeof h_range, cudaMemcpyDeviceToHost, st);
+    }
+    if (rc == cudaSuccess) rc = cudaStreamSynchronize(st);
+    cudaFree(d_range);
+    FCB_CUDA(e, rc);
+    const int64_t span = (int64_t)h_range[1] - h_range[0] + 1;
+    *key_base = h_range[0] > h_range[1] ? 0 : (span <= AGK_MONTHS ? h_range[0] : h_range[1] - (AGK_MONTHS - 1));
+    agk_build_keys_kernel<<<num_sms * 8, 256, 0, st>>>(dates, cats, cents, n_rows, *key_base, keys);
+    FCB_CUDA(e, cudaGetLastError());
+    return FCB_OK;
+}
+
+// Called by fcb_load_shard when the shard has dates, categories and amounts. Not being able to allocate the column is not
+// an error: the date kernels serve.
 int32_t fcb_build_group_keys(fcb_engine *e) {
     const fcb_shard &s = e->shard;
     cudaFree(e->group_keys); e->group_keys = nullptr; e->key_base = 0;
     const char *knob = getenv("FCB_AGG_KEYS");
     if ((knob && knob[0] == '0') || !s.dates || !s.categories || !s.cents || !s.seg_offsets || s.n_rows <= 0) return FCB_OK;
     if ((reinterpret_cast<uintptr_t>(s.cents) & 15u) != 0) return FCB_OK;          // the key kernel loads amounts 16 bytes at a time
-    int *d_range = nullptr;
-    FCB_CUDA(e, cudaMalloc(&d_range, 2 * sizeof(int)));
-    const int init[2] = {INT32_MAX, INT32_MIN};
-    FCB_CUDA(e, cudaMemcpyAsync(d_range, init, sizeof init, cudaMemcpyHostToDevice, e->stream));
-    agk_month_range_kernel<<<e->num_sms * 8, 256, 0, e->stream>>>(s.dates, s.n_rows, d_range);
-    int h_range[2] = {0, 0};
-    FCB_CUDA(e, cudaMemcpyAsync(h_range, d_range, sizeof h_range, cudaMemcpyDeviceToHost, e->stream));
-    FCB_CUDA(e, cudaStreamSynchronize(e->stream));
-    cudaFree(d_range);
-    if (h_range[0] > h_range[1]) return FCB_OK;
     uint16_t *keys = nullptr;
     if (cudaMalloc(&keys, ((size_t)s.n_rows * 2 + 15) & ~(size_t)15) != cudaSuccess) { cudaGetLastError(); return FCB_OK; }
-    const int64_t span = (int64_t)h_range[1] - h_range[0] + 1;
-    e->key_base = span <= AGK_MONTHS ? h_range[0] : h_range[1] - (AGK_MONTHS - 1);
-    agk_build_keys_kernel<<<e->num_sms * 8, 256, 0, e->stream>>>(s.dates, s.categories, s.cents, s.n_rows, e->key_base, keys);
-    FCB_CUDA(e, cudaGetLastError());
+    const int32_t rc = agk_build(e, e->num_sms, s.dates, s.categories, s.cents, s.n_rows, keys, &e->key_base, e->stream);
+    if (rc != FCB_OK) { cudaFree(keys); return rc; }
     e->group_keys = keys;
     return FCB_OK;
 }
@@ -915,9 +926,15 @@ static int32_t agg_launch(fcb_engine *e, int device, int num_sms, int dates_sort
                           int64_t seg_begin, int64_t seg_end, int32_t month_lo, int32_t n_months, int32_t n_categories,
                           int64_t *sums, uint8_t *present, uint64_t *dropped, cudaStream_t st, const uint16_t *keys = nullptr,
                           int32_t key_base = 0) {
-    if (!dates || !cats || !cents || !seg_offsets)
+    if (!cents || !seg_offsets || (!keys && (!dates || !cats)))
         return fcb_fail(e, FCB_ERR_STATE, "fcb_aggregate: needs the dates, categories, cents and seg_offsets columns");
     if (!sums || !present || !dropped) return fcb_fail(e, FCB_ERR_INVALID, "fcb_aggregate: NULL output");
+    // the kernels read the columns 4 rows at a time (128-bit loads of cents / dates, 32-bit of categories, 64-bit of keys)
+    if ((reinterpret_cast<uintptr_t>(cents) & 15u) || (reinterpret_cast<uintptr_t>(dates) & 15u) ||
+        (reinterpret_cast<uintptr_t>(cats) & 3u) || (reinterpret_cast<uintptr_t>(keys) & 7u) ||
+        (reinterpret_cast<uintptr_t>(seg_offsets) & 7u))
+        return fcb_fail(e, FCB_ERR_INVALID, "fcb_aggregate: columns must be aligned (cents / dates 16 bytes, categories 4, keys 8, "
+                        "seg_offsets 8)");
     if (seg_begin < 0 || seg_end > n_segs || seg_begin > seg_end)
         return fcb_fail(e, FCB_ERR_INVALID, "fcb_aggregate: segment range [%lld, %lld) outside 0..%lld",
                         (long long)seg_begin, (long long)seg_end, (long long)n_segs);
@@ -985,6 +1002,9 @@ static int32_t agg_launch(fcb_engine *e, int device, int num_sms, int dates_sort
             return FCB_OK;
         }
     }
+    if (!dates || !cats)
+        return fcb_fail(e, FCB_ERR_UNSUPPORTED, "fcb_aggregate: months [%d, %d) reach outside the group keys' range [%d, %d) and there "
+                        "are no date / category columns to fall back on", month_lo, month_lo + n_months, key_base, key_base + AGK_MONTHS);
     if (force && (force[0] == 'k' || force[0] == 'd')) force = nullptr;   // ("date": no keys, the usual choice among the date kernels)
     const bool sorted_ok = n_categories <= 32;
     const bool use_sorted = sorted_ok && (force ? force[0] == 's' : dates_sorted != 0);
@@ -1056,6 +1076,49 @@ extern "C" int32_t fcb_aggregate_columns(int32_t device, const int32_t *dates, c
     return agg_launch(nullptr, device, device < 64 ? sms[device] : 148, dates_sorted, dates, categories, cents, seg_offsets, n_rows,
                       n_segs, row_base, seg_begin, seg_end, month_lo, n_months, n_categories, sums, present, dropped,
                       (cudaStream_t)stream);
+}
+
+static int agg_device_sms(int32_t device, const char *who) {
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev) {
+        fcb_fail(nullptr, FCB_ERR_CUDA, "%s: no CUDA device %d (this library has no CPU path)", who, device);
+        return -1;
+    }
+    int v = 0;
+    if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, device) != cudaSuccess || v <= 0) {
+        fcb_fail(nullptr, FCB_ERR_CUDA, "%s: cannot query device %d", who, device);
+        return -1;
+    }
+    return v;
+}
+
+// Group keys for caller-owned columns (what fcb_load_shard builds for an engine's shard): see "group keys" above.
+extern "C" int32_t fcb_group_keys_build(int32_t device, const int32_t *dates, const uint8_t *categories, const int32_t *cents,
+                                        int64_t n_rows, uint16_t *keys, int32_t *key_base, void *stream) {
+    if (!dates || !categories || !cents || !keys || !key_base || n_rows < 0)
+        return fcb_fail(nullptr, FCB_ERR_INVALID, "fcb_group_keys_build: bad argument");
+    if ((reinterpret_cast<uintptr_t>(keys) & 15u) != 0)
+        return fcb_fail(nullptr, FCB_ERR_INVALID, "fcb_group_keys_build: keys must be a 16-byte aligned device pointer");
+    const int sms = agg_device_sms(device, "fcb_group_keys_build");
+    if (sms < 0) return FCB_ERR_CUDA;
+    FcbDeviceGuard g(device);
+    if (!g.ok) return fcb_fail(nullptr, FCB_ERR_CUDA, "fcb_group_keys_build: cannot select device %d", device);
+    *key_base = 0;
+    if (n_rows == 0) return FCB_OK;
+    return agk_build(nullptr, sms, dates, categories, cents, n_rows, keys, key_base, (cudaStream_t)stream);
+}
+
+extern "C" int32_t fcb_aggregate_columns_keyed(int32_t device, const uint16_t *keys, int32_t key_base, const int32_t *dates,
+                                               const uint8_t *categories, const int32_t *cents, const int64_t *seg_offsets,
+                                               int64_t n_rows, int64_t n_segs, int64_t row_base, int32_t dates_sorted,
+                                               int64_t seg_begin, int64_t seg_end, int32_t month_lo, int32_t n_months,
+                                               int32_t n_categories, int64_t *sums, uint8_t *present, uint64_t *dropped, void *stream) {
+    if (n_rows < 0 || n_segs < 0 || row_base < 0)
+        return fcb_fail(nullptr, FCB_ERR_INVALID, "fcb_aggregate_columns_keyed: negative n_rows / n_segs / row_base");
+    const int sms = agg_device_sms(device, "fcb_aggregate_columns_keyed");
+    if (sms < 0) return FCB_ERR_CUDA;
+    return agg_launch(nullptr, device, sms, dates_sorted, dates, categories, cents, seg_offsets, n_rows, n_segs, row_base, seg_begin,
+                      seg_end, month_lo, n_months, n_categories, sums, present, dropped, (cudaStream_t)stream, keys, key_base);
 }
 
 // ---- group-by over the points a search just returned ------------------------------

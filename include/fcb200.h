@@ -212,7 +212,8 @@ int32_t fcb_aggregate(fcb_engine *e, int64_t seg_begin, int64_t seg_end, int32_t
 /* The same group-by over caller-owned device columns, without an engine (nothing is allocated, no vectors are needed):
  * what the tool-shaped path uses for the rows of ONE transactions_json (tools/plot_tool.py:29,45,52 — one key column that
  * becomes the CSR segments, one value column) and what a caller holding only the payload columns uses at scale.
- *   dates / categories / cents   device [n_rows] as in fcb_shard; seg_offsets device [n_segs + 1] global CSR offsets
+ *   dates / categories / cents   device [n_rows] as in fcb_shard; seg_offsets device [n_segs + 1] global CSR offsets;
+ *                                aligned: cents / dates 16 bytes, categories 4 (FCB_ERR_INVALID otherwise)
  *   row_base                     global row number of the columns' first row
  *   dates_sorted                 1 if the dates are non-decreasing within every user (selects the atomic-free kernel;
  *                                the result is the same either way), else 0
@@ -221,6 +222,27 @@ int32_t fcb_aggregate_columns(int32_t device, const int32_t *dates, const uint8_
                               const int64_t *seg_offsets, int64_t n_rows, int64_t n_segs, int64_t row_base,
                               int32_t dates_sorted, int64_t seg_begin, int64_t seg_end, int32_t month_lo, int32_t n_months,
                               int32_t n_categories, int64_t *sums, uint8_t *present, uint64_t *dropped, void *stream);
+
+/* Group keys: the (category, month) of every row resolved once, so that the group-by reads 6 bytes per row (amount + key)
+ * instead of 9 and spends no arithmetic on calendars. plot_tool.py:45 derives the month of every row on every call
+ * (`dt.to_period("M")`); a resident table does it once. fcb_load_shard builds the keys of an engine's shard by itself
+ * (fcb_aggregate then uses them); these two entry points do the same for caller-owned columns.
+ *   keys       device [n_rows] uint16, 16-byte aligned, caller-allocated (n_rows * 2 bytes rounded up to 16)
+ *   key_base   out: first month (months since 1970-01) the keys can express; they cover [key_base, key_base + 511),
+ *              ending at the newest month of the data
+ * fcb_group_keys_build waits for `stream` (the month range of the data comes back to the host). */
+int32_t fcb_group_keys_build(int32_t device, const int32_t *dates, const uint8_t *categories, const int32_t *cents,
+                             int64_t n_rows, uint16_t *keys, int32_t *key_base, void *stream);
+
+/* fcb_aggregate_columns with the rows' group keys. Windows inside [key_base, key_base + 511) are aggregated from cents +
+ * keys (any row order, one launch); other windows fall back on dates / categories, which may be NULL if the caller never
+ * asks for such a window (FCB_ERR_UNSUPPORTED otherwise). keys == NULL: exactly fcb_aggregate_columns. Same outputs,
+ * bit for bit, whichever way the rows are read. */
+int32_t fcb_aggregate_columns_keyed(int32_t device, const uint16_t *keys, int32_t key_base, const int32_t *dates,
+                                    const uint8_t *categories, const int32_t *cents, const int64_t *seg_offsets,
+                                    int64_t n_rows, int64_t n_segs, int64_t row_base, int32_t dates_sorted,
+                                    int64_t seg_begin, int64_t seg_end, int32_t month_lo, int32_t n_months,
+                                    int32_t n_categories, int64_t *sums, uint8_t *present, uint64_t *dropped, void *stream);
 
 /* Group-by over the points a search just returned: the reference's agent feeds the
  * output of retrieve_transactions (tools/qdrant_tool.py:147-170) back through JSON into

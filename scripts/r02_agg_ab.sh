@@ -6,10 +6,10 @@ timeout 600 python -m pytest tests/test_gpu_aggregate.py -m gpu -q -x > gpurun_o
 : > gpurun_out/r02_agg_ab.jsonl
 for rep in 1; do
   echo "{\"lib\": \"in-tree\"}" >> gpurun_out/r02_agg_ab.jsonl
-  FCB_BENCH_AGK_LAYOUTS=1 timeout 300 python scripts/bench_extra.py --only agg --steps 10 2>> gpurun_out/r02_agg_ab.err | cut -c1-400 >> gpurun_out/r02_agg_ab.jsonl
+  timeout 300 python scripts/bench_extra.py --only agg --steps 10 2>> gpurun_out/r02_agg_ab.err | cut -c1-400 >> gpurun_out/r02_agg_ab.jsonl
   for so in build_ab/*.so; do
     echo "{\"lib\": \"$so\"}" >> gpurun_out/r02_agg_ab.jsonl
-    FCB_LIB_PATH=$PWD/$so FCB_BENCH_AGK_LAYOUTS=1 timeout 300 python scripts/bench_extra.py --only agg --steps 10 2>> gpurun_out/r02_agg_ab.err | cut -c1-400 >> gpurun_out/r02_agg_ab.jsonl
+    FCB_LIB_PATH=$PWD/$so timeout 300 python scripts/bench_extra.py --only agg --steps 10 2>> gpurun_out/r02_agg_ab.err | cut -c1-400 >> gpurun_out/r02_agg_ab.jsonl
   done
 done
 cat gpurun_out/r02_agg_ab.jsonl

@@ -366,3 +366,47 @@ def test_group_key_kernel_equals_the_date_kernels_and_pandas(built, monkeypatch)
     full = dense_from_engine(eng, 0, len(sizes), mlo, 24, 16)
     assert np.array_equal(s2, full[0][5:11]) and np.array_equal(p2, full[1][5:11])
     eng.close()
+
+
+def test_group_keys_for_caller_owned_columns(built):
+    """fcb_group_keys_build + fcb_aggregate_columns_keyed: the engine-less form of the same thing. Identical dense output
+    with and without keys (row_base > 0, a sub-range of users, time-ordered dates too); with keys the date / category columns
+    may be omitted as long as the window stays inside the key range, and a window outside it is refused, not mis-answered."""
+    import torch
+    from financial_chatbot_llm_b200 import _lib, synth
+    from financial_chatbot_llm_b200.engine import aggregate_columns, build_group_keys
+    from oracle import groupby
+    rng = np.random.default_rng(31)
+    sizes = np.array([7, 20_000, 8192, 1, 0, 33_333, 4095, 4097, 9_000], dtype=np.int64)
+    off = np.zeros(len(sizes) + 1, dtype=np.int64)
+    np.cumsum(sizes, out=off[1:])
+    n = int(off[-1])
+    spec = synth.SynthSpec(n_rows=n, dim=4, n_users=len(sizes), seed=5)
+    v = rng.integers(-(2 ** 20), 2 ** 20, size=n, dtype=np.int64).astype(np.int32)
+    v[::9] = 0
+    c = rng.integers(0, 20, size=n).astype(np.uint8)
+    mlo = int(groupby.month_index(np.array([synth.DATE_BASE]))[0])
+    dev = torch.device("cuda", 0)
+    for ordered in (False, True):
+        d = synth.dates_sorted(spec, off, 0, n) if ordered else (synth.DATE_BASE + rng.integers(0, 730 * 86400, size=n)).astype(np.int32)
+        dd, cc, vv, oo = (torch.from_numpy(a).to(dev) for a in (d, c, v, off))
+        keys, base = build_group_keys(0, dd, cc, vv)
+        assert keys.numel() == n and base <= mlo
+        for (lo_u, hi_u, w_lo, w_n, ncat) in ((0, len(sizes), mlo, 24, 16), (1, 6, mlo + 2, 11, 20), (0, len(sizes), base, 30, 7)):
+            a, b = int(off[lo_u]), int(off[hi_u])
+            cols = [x[a:b].clone() for x in (dd, cc, vv)]             # (a slice of a 1-D tensor is a view: not aligned)
+            k = keys[a:b].clone()
+            ref = aggregate_columns(0, *cols, oo, lo_u, hi_u, w_lo, w_n, ncat, row_base=a, dates_sorted=ordered)
+            got = aggregate_columns(0, *cols, oo, lo_u, hi_u, w_lo, w_n, ncat, row_base=a, dates_sorted=ordered, keys=k, key_base=base)
+            bare = aggregate_columns(0, None, None, cols[2], oo, lo_u, hi_u, w_lo, w_n, ncat, row_base=a, keys=k, key_base=base)
+            torch.cuda.synchronize()
+            for x, y, z in zip(ref, got, bare):
+                assert torch.equal(x, y) and torch.equal(x, z), (ordered, lo_u, hi_u, w_lo, w_n, ncat)
+        with pytest.raises(_lib.FcbError):
+            aggregate_columns(0, None, None, vv, oo, 0, len(sizes), base - 2, 4, 16, keys=keys, key_base=base)
+        with pytest.raises(_lib.FcbError):                                   # misaligned columns are refused, not read
+            aggregate_columns(0, dd[7:], cc[7:], vv[7:], oo, 1, len(sizes), mlo, 24, 16, row_base=7)
+        s_out, _, dr = aggregate_columns(0, dd, cc, vv, oo, 0, len(sizes), base - 2, 4, 16, keys=keys, key_base=base)   # falls back on the dates
+        s_ref, _, dr_ref = aggregate_columns(0, dd, cc, vv, oo, 0, len(sizes), base - 2, 4, 16)
+        torch.cuda.synchronize()
+        assert torch.equal(s_out, s_ref) and int(dr.item()) == int(dr_ref.item())
