@@ -691,11 +691,17 @@ extern "C" int32_t fcb_search_host(fcb_engine *e, const double *queries, const f
     int32_t *d_flags = d_counts + batch, *h_flags = h_counts + batch;
     bool pending = false;
     StagedFilters sf;
+    // a few single queries through the fused scan (the latency-sensitive call: one worker, one question): the kernel's last
+    // CTA writes ids, scores, counts and certificate flags STRAIGHT into the pinned staging block (mapped into the device's
+    // address space like all pinned memory), so no device-to-host copy is enqueued behind the kernel
+    static const bool direct_ok = []() { const char *v = getenv("FCB_HOST_DIRECT"); return !(v && v[0] == '0'); }();
+    const bool direct = direct_ok && batch <= 4 && k <= FCB_FUSED_MAX_K && e->rows_out_of_domain == 0;
+    if (direct) { d_ids = h_ids; d_scores = h_scores; d_counts = h_counts; d_flags = h_flags; }
     rc = search_device(e, e->d_q, filters, batch, k, d_ids, d_scores, d_counts, st, d_flags, true, &pending, &sf);
     if (rc != FCB_OK) return rc;
     FCB_CUDA(e, cudaEventRecord(e->ev1, st));
     const size_t res_bytes = rn * 16 + (size_t)batch * sizeof(int32_t) * (pending ? 2 : 1);
-    FCB_CUDA(e, cudaMemcpyAsync(h_ids, d_ids, res_bytes, cudaMemcpyDeviceToHost, st));
+    if (!direct) FCB_CUDA(e, cudaMemcpyAsync(h_ids, d_ids, res_bytes, cudaMemcpyDeviceToHost, st));
     FCB_CUDA(e, cudaStreamSynchronize(st));
     if (pending) {
         // the fused scan could not certify some query (the flags came back with the results): answer those exactly
@@ -706,7 +712,7 @@ extern "C" int32_t fcb_search_host(fcb_engine *e, const double *queries, const f
                                    d_counts, st);
             if (rc != FCB_OK) return rc;
             FCB_CUDA(e, cudaEventRecord(e->ev1, st));
-            FCB_CUDA(e, cudaMemcpyAsync(h_ids, d_ids, rn * 16 + (size_t)batch * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+            if (!direct) FCB_CUDA(e, cudaMemcpyAsync(h_ids, d_ids, rn * 16 + (size_t)batch * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
             FCB_CUDA(e, cudaStreamSynchronize(st));
         }
     }
