@@ -342,7 +342,9 @@ def test_group_key_kernel_equals_the_date_kernels_and_pandas(built, monkeypatch)
                    categories=torch.from_numpy(c).to(dev), cents=torch.from_numpy(v).to(dev), seg_offsets=torch.from_numpy(off).to(dev))
     users = synth.row_users(off, np.arange(n))
     month = groupby.month_index(d)
-    for (w_lo, w_n, ncat) in ((mlo, 24, 16), (mlo + 5, 7, 9), (mlo - 1, 26, 64), (mlo - 3, 30, 64), (mlo - 600, 4, 16)):
+    # (64 x 64 = 4096 cells: the largest table, three warps per CTA; 1 month x 1 category: the smallest)
+    for (w_lo, w_n, ncat) in ((mlo, 24, 16), (mlo + 5, 7, 9), (mlo - 1, 26, 64), (mlo - 1, 64, 64), (mlo + 3, 1, 1), (mlo - 3, 30, 64),
+                              (mlo - 600, 4, 16)):
         got = dense_from_engine(eng, 0, len(sizes), w_lo, w_n, ncat)
         monkeypatch.setenv("FCB_AGG_KERNEL", "atomic")
         ref = dense_from_engine(eng, 0, len(sizes), w_lo, w_n, ncat)
