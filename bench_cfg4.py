@@ -16,6 +16,7 @@ events (max over ranks) after warm-up, inputs resident in HBM:
 """
 from __future__ import annotations
 
+import os
 import time
 
 import numpy as np
@@ -80,10 +81,12 @@ def run(dev, world: int, rank: int, steps: int, timed_steps, rows: int = ROWS, t
     routed_res = None
     try:
         engines, exchanges, searchers, streams = [eng], [], [], []
-        eng2 = Engine(device=dev.index, max_batch=slots, max_k=16)
+        n_engines = max(2, int(os.environ.get("FCB_CFG4_ENGINES", "2")))
         vec, _ids, _rank, dts, cats, _cents, offs_d = eng._keep
-        eng2.load_shard(vec, dates=dts, categories=cats, seg_offsets=offs_d, row_base=lo)
-        engines.append(eng2)
+        for _ in range(n_engines - 1):
+            e_more = Engine(device=dev.index, max_batch=slots, max_k=16)
+            e_more.load_shard(vec, dates=dts, categories=cats, seg_offsets=offs_d, row_base=lo)
+            engines.append(e_more)
         from financial_chatbot_llm_b200.client import Collection
         for e in engines:
             xch = sharded.PeerExchange(dev.index, world, rank, slots, K, cuts)
@@ -143,7 +146,11 @@ def run(dev, world: int, rank: int, steps: int, timed_steps, rows: int = ROWS, t
         n_r = max(steps, 40)
         ms_1, per_1, _ = run_routed(1, n_r, 6)
         ms_2, per_2, clocks = run_routed(2, n_r, 6)
-        ok_routed = all_ok(check_routed(0) and check_routed(1))
+        more = {}
+        for ne in range(3, n_engines + 1):                              # experiments: FCB_CFG4_ENGINES > 2
+            ms_n, per_n, _ = run_routed(ne, n_r, 6)
+            more[f"{ne}_engines_per_gpu"] = {"ms_per_step": ms_n, "p50_ms": per_n[len(per_n) // 2], "queries_per_s": slots * 1e3 / ms_n}
+        ok_routed = all_ok(all(check_routed(j) for j in range(n_engines)))
         owned = int(np.sum((offsets[rsets[0]] >= lo) & (offsets[rsets[0]] < hi)))
         routed_res = {"ms_per_step": ms_2, "p50_ms": per_2[len(per_2) // 2], "queries_per_step": slots, "engines_per_gpu": 2,
                       "batches_in_flight": 2 * world, "queries_per_s": slots * 1e3 / ms_2,
@@ -151,11 +158,12 @@ def run(dev, world: int, rank: int, steps: int, timed_steps, rows: int = ROWS, t
                                              "queries_per_s": slots * 1e3 / ms_1},
                       "queries_owned_by_rank0_in_a_step": owned, "launches_per_step_per_rank": eng.last_search_launches,
                       "nccl_calls_per_step": 0, "parity": ok_routed, "clocks": clocks,
-                      "exact_reruns": eng.exact_reruns + eng2.exact_reruns}
+                      "exact_reruns": sum(e.exact_reruns for e in engines), **more}
         dist.barrier()
         for xch in exchanges:
             xch.close()
-        eng2.close()
+        for e_more in engines[1:]:
+            e_more.close()
     except Exception as e:                                            # e.g. CUDA IPC unavailable on this box: the closed loop still stands
         import traceback
         routed_res = {"error": f"{type(e).__name__}: {e}", "trace": traceback.format_exc()[-600:]}
