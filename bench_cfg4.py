@@ -134,6 +134,44 @@ def run(dev, world: int, rank: int, steps: int, timed_steps, rows: int = ROWS, t
             per = sorted(marks[i].elapsed_time(marks[i + n_eng]) / n_eng for i in range(len(marks) - n_eng))
             return float(tm.item()) / n_steps, per, (sampler.stop(t_a, t_b) if sampler else None)
 
+        def run_routed_threads(n_eng, n_steps, warm):
+            """The same steps issued by one host thread PER ENGINE (ctypes releases the GIL inside the library call), so the
+            ~50 us of host work per call overlap; ms per step = the longest stream's span / n_steps, max over ranks."""
+            import threading
+            per_eng = n_steps // n_eng
+            for i in range(warm):
+                searchers[i % n_eng].search_device(rq[i % 2], farr[i % n_sets], K, stream=streams[i % n_eng].cuda_stream)
+            torch.cuda.synchronize()
+            dist.barrier()
+            first = [torch.cuda.Event(enable_timing=True) for _ in range(n_eng)]
+            last = [torch.cuda.Event(enable_timing=True) for _ in range(n_eng)]
+            errors = []
+            go = threading.Barrier(n_eng)
+
+            def worker(j):
+                try:
+                    torch.cuda.set_device(dev)
+                    go.wait()
+                    first[j].record(streams[j])
+                    for i in range(per_eng):
+                        searchers[j].search_device(rq[i % 2], farr[(i * n_eng + j) % n_sets], K, stream=streams[j].cuda_stream)
+                    last[j].record(streams[j])
+                except Exception as exc:                                  # surfaced below: a failed thread must not hang the ranks
+                    errors.append(repr(exc))
+            threads = [threading.Thread(target=worker, args=(j,)) for j in range(n_eng)]
+            for t in threads:
+                t.start()
+            for t in threads:
+                t.join()
+            torch.cuda.synchronize()
+            dist.barrier()
+            if errors:
+                raise RuntimeError("; ".join(errors))
+            span = max(first[i].elapsed_time(last[j]) for i in range(n_eng) for j in range(n_eng))
+            tm = torch.tensor([span], dtype=torch.float64, device=dev)
+            dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+            return float(tm.item()) / (per_eng * n_eng)
+
         def check_routed(j):
             seq = searchers[j].search_device(rq[0], farr[0], K, stream=streams[j].cuda_stream)
             torch.cuda.synchronize()
@@ -150,6 +188,10 @@ def run(dev, world: int, rank: int, steps: int, timed_steps, rows: int = ROWS, t
         for ne in range(3, n_engines + 1):                              # experiments: FCB_CFG4_ENGINES > 2
             ms_n, per_n, _ = run_routed(ne, n_r, 6)
             more[f"{ne}_engines_per_gpu"] = {"ms_per_step": ms_n, "p50_ms": per_n[len(per_n) // 2], "queries_per_s": slots * 1e3 / ms_n}
+        if os.environ.get("FCB_CFG4_THREADS"):                           # experiment: one issuing thread per engine
+            for ne in range(2, n_engines + 1):
+                ms_t = run_routed_threads(ne, n_r * 2, 6)
+                more[f"{ne}_engines_per_gpu_one_thread_each"] = {"ms_per_step": ms_t, "queries_per_s": slots * 1e3 / ms_t}
         ok_routed = all_ok(all(check_routed(j) for j in range(n_engines)))
         owned = int(np.sum((offsets[rsets[0]] >= lo) & (offsets[rsets[0]] < hi)))
         routed_res = {"ms_per_step": ms_2, "p50_ms": per_2[len(per_2) // 2], "queries_per_step": slots, "engines_per_gpu": 2,

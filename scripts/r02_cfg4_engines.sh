@@ -3,7 +3,7 @@
 cd "$(dirname "$0")/.."
 N=${1:-2}
 mkdir -p gpurun_out
-FCB_CFG4_ENGINES=4 timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29513 bench.py --gpus $N --steps 20 --warmup 5 \
+FCB_CFG4_THREADS=1 FCB_CFG4_ENGINES=4 timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29513 bench.py --gpus $N --steps 20 --warmup 5 \
   > gpurun_out/r02_cfg4_engines_n$N.json 2> gpurun_out/r02_cfg4_engines_n$N.err; echo "bench rc=$?"
 python - <<P
 import json
