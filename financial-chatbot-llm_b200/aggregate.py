@@ -81,7 +81,8 @@ def grouped_sum_json(transactions_json: str, group_by: str, y_axis: str, device:
     keys = transactions[group_by]
     keep = keys.notna().to_numpy()                                        # groupby drops null keys
     y_all = transactions[y_axis].to_numpy()
-    uniq, inv = np.unique(keys.to_numpy()[keep], return_inverse=True)     # ascending, like sort=True
+    inv, uniq = pd.factorize(keys.to_numpy()[keep], sort=True)            # ascending keys, like groupby's sort=True (hash-based:
+    uniq = np.asarray(uniq)                                               #   several times cheaper than np.unique on strings)
     v, scale = _to_integer_units(y_all[keep])
     order = np.argsort(inv, kind="stable")
     offsets = np.zeros(len(uniq) + 1, dtype=np.int64)
