@@ -330,6 +330,7 @@ def test_group_key_kernel_equals_the_date_kernels_and_pandas(built, monkeypatch)
     c[rng.integers(0, n, size=300)] = 200
     c[rng.integers(0, n, size=300)] = 40
     d[rng.integers(0, n, size=300)] = synth.DATE_BASE - 86400
+    d[rng.integers(0, n, size=50)] = synth.DATE_BASE - 600 * 30 * 86400    # ~49 years back: older than the 511 months keys can express
     # user 13 (5 rows): one cell made of zeros only, one of amounts that cancel
     a13 = int(off[13])
     v[a13:a13 + 5] = [0, 0, 77, -77, 5]
@@ -344,7 +345,7 @@ def test_group_key_kernel_equals_the_date_kernels_and_pandas(built, monkeypatch)
     month = groupby.month_index(d)
     # (64 x 64 = 4096 cells: the largest table, three warps per CTA; 1 month x 1 category: the smallest)
     for (w_lo, w_n, ncat) in ((mlo, 24, 16), (mlo + 5, 7, 9), (mlo - 1, 26, 64), (mlo - 1, 64, 64), (mlo + 3, 1, 1), (mlo - 3, 30, 64),
-                              (mlo - 600, 4, 16)):
+                              (mlo - 593, 4, 16)):
         got = dense_from_engine(eng, 0, len(sizes), w_lo, w_n, ncat)
         monkeypatch.setenv("FCB_AGG_KERNEL", "atomic")
         ref = dense_from_engine(eng, 0, len(sizes), w_lo, w_n, ncat)
