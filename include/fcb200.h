@@ -97,8 +97,11 @@ int32_t fcb_open(const fcb_config *cfg, fcb_engine **out);
 int32_t fcb_close(fcb_engine *e);
 const char *fcb_last_error(const fcb_engine *e);
 
-/* Attach a resident shard (see fcb_shard) and compute the library-owned float32 inverse row
- * norms (4 bytes/row). Replaces the server-side collection load; nothing in the reference
+/* Attach a resident shard (see fcb_shard) and compute the library-owned derived columns: float32
+ * inverse row norms (4 bytes/row) and, when the shard has dates, categories and cents, the 16-bit
+ * group keys of fcb_aggregate (2 bytes/row; see fcb_group_keys_build). Both are functions of the
+ * caller's columns AS THEY ARE NOW: the columns must not be modified while the shard is loaded
+ * (load again after a change). Replaces the server-side collection load; nothing in the reference
  * writes points. Synchronous. */
 int32_t fcb_load_shard(fcb_engine *e, const fcb_shard *shard);
 
