@@ -197,7 +197,8 @@ def agg_bench(args):
         os.environ["FCB_AGK_CARVEOUT"] = "100"
         run("dates in random order (group-key kernel, maximum shared-memory carve-out)", "")
         os.environ.pop("FCB_AGK_CARVEOUT")
-    run("dates in random order (date kernels: shared-atomic + warp tables, 9 B/row)", "date")
+    run("dates in random order (date columns, 9 B/row: warp-table kernel, date form)", "date")
+    run("dates in random order (date columns, 9 B/row: round 1's CTA-wide shared-atomic kernel + warp tables)", "cta")
     eng.close()
     # the same table as a time-ordered log (dates non-decreasing within each user)
     from financial_chatbot_llm_b200.engine import synth_dates_sorted
@@ -211,7 +212,8 @@ def agg_bench(args):
         os.environ["FCB_AGK_LAYOUT"] = "n"
         run("time-ordered log (group-key kernel, NATURAL table layout)", "")
         os.environ.pop("FCB_AGK_LAYOUT")
-    run("time-ordered log (date kernel: atomic-free runs, 9 B/row)", "sorted")
+    run("time-ordered log (date columns, 9 B/row: atomic-free runs)", "sorted")
+    run("time-ordered log (date columns, 9 B/row: warp-table kernel, date form)", "date")
     eng.close()
 
 

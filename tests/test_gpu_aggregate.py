@@ -253,7 +253,8 @@ def test_any_order_kernels_on_awkward_shapes_equal_pandas(built, monkeypatch):
     """The two-launch split of any-order data (users under 8192 rows: warp tables; the others: CTA-wide shared cells) on
     awkward shapes: user starts that are not multiples of 4 (ragged quads), sizes around the 8192-row threshold and the
     4096-row tile, a user spanning many tiles, rows outside the category / month window (counted as dropped), full-range
-    int32 values; the single-launch kernel (FCB_AGG_SPLIT=0) must give the identical dense output; both equal pandas; and
+    int32 values; the warp-table kernel (the default for date columns now) and the single-launch kernel (FCB_AGG_SPLIT=0) must give the identical
+    dense output; all equal pandas; and
     the engine-less entry point works on a sub-range of users over columns that start in the middle (row_base > 0)."""
     import torch
     from financial_chatbot_llm_b200 import synth
@@ -274,16 +275,21 @@ def test_any_order_kernels_on_awkward_shapes_equal_pandas(built, monkeypatch):
     dd, cc, vv, oo = (torch.from_numpy(a).to(dev) for a in (d, c, v, off))
     mlo = int(groupby.month_index(np.array([synth.DATE_BASE]))[0])
     res = {}
-    for mode in ("split", "single"):
+    # "warp": what date columns get by default (the date form of the warp-table kernel); "split" / "single": round 1's kernels
+    for mode in ("warp", "split", "single"):
+        if mode != "warp":
+            monkeypatch.setenv("FCB_AGG_KERNEL", "cta")
         if mode == "single":
             monkeypatch.setenv("FCB_AGG_SPLIT", "0")
         sums, present, dropped = aggregate_columns(0, dd, cc, vv, oo, 0, len(sizes), mlo, 24, 16)
         torch.cuda.synchronize()
         res[mode] = (sums.cpu().numpy(), present.cpu().numpy(), int(dropped.item()))
     monkeypatch.delenv("FCB_AGG_SPLIT")
+    monkeypatch.delenv("FCB_AGG_KERNEL")
     assert np.array_equal(res["split"][0], res["single"][0]) and np.array_equal(res["split"][1], res["single"][1])
+    assert np.array_equal(res["split"][0], res["warp"][0]) and np.array_equal(res["split"][1], res["warp"][1])
     keep = (c < 16) & (d >= synth.DATE_BASE)
-    assert res["split"][2] == res["single"][2] == int((~keep).sum())
+    assert res["split"][2] == res["single"][2] == res["warp"][2] == int((~keep).sum())
     ser = groupby.groupby_user_category_month(synth.row_users(off, np.arange(n))[keep], c[keep], d[keep], v[keep])
     idx = ser.index.to_frame(index=False)
     sums, present, _ = res["split"]
@@ -347,10 +353,11 @@ def test_group_key_kernel_equals_the_date_kernels_and_pandas(built, monkeypatch)
     for (w_lo, w_n, ncat) in ((mlo, 24, 16), (mlo + 5, 7, 9), (mlo - 1, 26, 64), (mlo - 1, 64, 64), (mlo + 3, 1, 1), (mlo - 3, 30, 64),
                               (mlo - 593, 4, 16)):
         got = dense_from_engine(eng, 0, len(sizes), w_lo, w_n, ncat)
-        monkeypatch.setenv("FCB_AGG_KERNEL", "atomic")
-        ref = dense_from_engine(eng, 0, len(sizes), w_lo, w_n, ncat)
-        monkeypatch.delenv("FCB_AGG_KERNEL")
-        assert np.array_equal(got[0], ref[0]) and np.array_equal(got[1], ref[1]) and got[2] == ref[2], (w_lo, w_n, ncat)
+        for other in ("atomic", "warp"):                                  # round 1's kernel, and the date form of the new one
+            monkeypatch.setenv("FCB_AGG_KERNEL", other)
+            ref = dense_from_engine(eng, 0, len(sizes), w_lo, w_n, ncat)
+            monkeypatch.delenv("FCB_AGG_KERNEL")
+            assert np.array_equal(got[0], ref[0]) and np.array_equal(got[1], ref[1]) and got[2] == ref[2], (other, w_lo, w_n, ncat)
         keep = (c < ncat) & (month >= w_lo) & (month < w_lo + w_n)
         assert got[2] == int((~keep).sum())
         if keep.any():
