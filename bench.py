@@ -364,11 +364,11 @@ def extra_cfg5(dev, steps):
     gbs = alg / (ms / 1e3) / 1e9
     return {"workload": "configs[4]: 1B rows, int32 cents summed by user x category x month (100k Zipf users x 16 x 24), rows in any order",
             "ms": ms, "p50_ms": per[len(per) // 2], "rows_per_s": n / (ms / 1e3), "steps": steps,
-            "kernel": "aggregate_key_kernel (cents + 16-bit group keys resolved once per resident table)",
+            "kernel": "aggregate_warp_kernel<keyed> (cents + 16-bit group keys resolved once per resident table)",
             "group_keys_build_ms_once": keys_ms,
             "roofline": {"bound": "hbm", "achieved": gbs, "peak": hbm_peak, "unit": "GB/s", "frac": gbs / hbm_peak,
                          "algorithmic_bytes_per_launch": alg, "peak_source": src + " hbm_gbs",
-                         "traffic": (ncu_traffic("aggregate_key_kernel") or {}).get("dram_bytes_per_launch"),
+                         "traffic": (ncu_traffic("aggregate_warp_kernel<keyed>") or {}).get("dram_bytes_per_launch"),
                          "bytes_read_per_launch": read, "read_GBs": read / (ms / 1e3) / 1e9,
                          "read_frac": read / (ms / 1e3) / 1e9 / hbm_peak,
                          "note": "achieved/frac use the 9 B/row of the reference's columns (SURVEY 8d) so that they compare with "

@@ -218,8 +218,9 @@ int32_t fcb_aggregate(fcb_engine *e, int64_t seg_begin, int64_t seg_end, int32_t
  *   dates / categories / cents   device [n_rows] as in fcb_shard; seg_offsets device [n_segs + 1] global CSR offsets;
  *                                aligned: cents / dates 16 bytes, categories 4 (FCB_ERR_INVALID otherwise)
  *   row_base                     global row number of the columns' first row
- *   dates_sorted                 1 if the dates are non-decreasing within every user (selects the atomic-free kernel;
- *                                the result is the same either way), else 0
+ *   dates_sorted                 1 if the dates are non-decreasing within every user, else 0. A hint only: the result is the
+ *                                same either way, and since round 2 the default kernel is the same too (the ordered-log
+ *                                kernel it used to select is kept behind FCB_AGG_KERNEL=sorted)
  * Other arguments and outputs as for fcb_aggregate. Errors: fcb_last_error(NULL). Asynchronous on `stream`. */
 int32_t fcb_aggregate_columns(int32_t device, const int32_t *dates, const uint8_t *categories, const int32_t *cents,
                               const int64_t *seg_offsets, int64_t n_rows, int64_t n_segs, int64_t row_base,
