@@ -374,6 +374,8 @@ def extra_cfg5(dev, steps):
                          "note": "achieved/frac use the 9 B/row of the reference's columns (SURVEY 8d) so that they compare with "
                                  "round 1; the kernel reads 6 B/row, read_frac is its real share of the copy peak"},
             "without_group_keys": {"ms": ms_dates, "frac": alg / (ms_dates / 1e3) / 1e9 / hbm_peak,
+                                   "achieved": alg / (ms_dates / 1e3) / 1e9, "unit": "GB/s",
+                                   "traffic": (ncu_traffic("aggregate_warp_kernel<date>") or {}).get("dram_bytes_per_launch"),
                                    "kernel": "aggregate_warp_kernel, date form: dates / categories / cents (9 B/row)"},
             "clocks": clocks, "parity": bool(ok),
             "parity_how": "keyed and date-column kernels give the identical dense output, no row dropped, total of all cells == total "
