@@ -333,17 +333,18 @@ def extra_cfg5(dev, steps):
     sums = torch.empty((users, 16, 24), dtype=torch.int64, device=dev)
     pres = torch.empty((users, 16, 24), dtype=torch.uint8, device=dev)
     drop = torch.empty(1, dtype=torch.int64, device=dev)
-    # the resident table carries its group keys (built once, like the row norms of the search shard): (category, month) of
-    # every row in 16 bits, so the group-by reads 6 B per row; the date columns alone are timed beside it
+    # The line's own number is the RAW-COLUMN run — dates, categories, cents as the reference holds them, 9 B/row.
+    # A resident table can in addition carry group keys ((category, month) of every row in 16 bits, resolved once like the row
+    # norms of the search shard): the group-by then reads 6 B per row; that run is reported beside it under "with_group_keys".
     torch.cuda.synchronize(dev)
     t_k = time.perf_counter()
     keys, key_base = build_group_keys(dev.index, d, c, v)
     torch.cuda.synchronize(dev)
     keys_ms = 1e3 * (time.perf_counter() - t_k)                  # one-time cost per resident table (two passes over the columns)
-    run_dates = lambda i: aggregate_columns(dev.index, d, c, v, offs_d, 0, users, mlo, 24, 16, sums, pres, drop)
-    ms_dates, _, _ = timed_steps(run_dates, max(3, steps // 2), 3, dev, 1)
-    sums_dates, pres_dates = sums.clone(), pres.clone()
-    run = lambda i: aggregate_columns(dev.index, d, c, v, offs_d, 0, users, mlo, 24, 16, sums, pres, drop, keys=keys, key_base=key_base)
+    run_keyed = lambda i: aggregate_columns(dev.index, d, c, v, offs_d, 0, users, mlo, 24, 16, sums, pres, drop, keys=keys, key_base=key_base)
+    ms_keyed, _, _ = timed_steps(run_keyed, max(3, steps // 2), 3, dev, 1)
+    sums_dates, pres_dates = sums.clone(), pres.clone()              # (the keyed result, compared with the raw-column one below)
+    run = lambda i: aggregate_columns(dev.index, d, c, v, offs_d, 0, users, mlo, 24, 16, sums, pres, drop)
     ms, per, clocks = timed_steps(run, steps, 3, dev, 1, sample_gpu=dev.index)
     same = bool(torch.equal(sums, sums_dates)) and bool(torch.equal(pres, pres_dates))
     del sums_dates, pres_dates
@@ -360,23 +361,19 @@ def extra_cfg5(dev, steps):
     torch.cuda.empty_cache()
     hbm_peak, _, src = measured_peaks()
     alg = n * 9 + users * 384 * 9            # date 4 + category 1 + cents 4 bytes per row, + the dense output
-    read = n * 6 + users * 384 * 9           # what the keyed kernel really moves: cents 4 + key 2 bytes per row
+    read_keyed = n * 6 + users * 384 * 9     # what the keyed form really moves: cents 4 + key 2 bytes per row
     gbs = alg / (ms / 1e3) / 1e9
     return {"workload": "configs[4]: 1B rows, int32 cents summed by user x category x month (100k Zipf users x 16 x 24), rows in any order",
             "ms": ms, "p50_ms": per[len(per) // 2], "rows_per_s": n / (ms / 1e3), "steps": steps,
-            "kernel": "aggregate_warp_kernel<keyed> (cents + 16-bit group keys resolved once per resident table)",
-            "group_keys_build_ms_once": keys_ms,
+            "kernel": "aggregate_warp_kernel, date form: dates / categories / cents as the reference holds them (9 B/row)",
             "roofline": {"bound": "hbm", "achieved": gbs, "peak": hbm_peak, "unit": "GB/s", "frac": gbs / hbm_peak,
                          "algorithmic_bytes_per_launch": alg, "peak_source": src + " hbm_gbs",
-                         "traffic": (ncu_traffic("aggregate_warp_kernel<keyed>") or {}).get("dram_bytes_per_launch"),
-                         "bytes_read_per_launch": read, "read_GBs": read / (ms / 1e3) / 1e9,
-                         "read_frac": read / (ms / 1e3) / 1e9 / hbm_peak,
-                         "note": "achieved/frac use the 9 B/row of the reference's columns (SURVEY 8d) so that they compare with "
-                                 "round 1; the kernel reads 6 B/row, read_frac is its real share of the copy peak"},
-            "without_group_keys": {"ms": ms_dates, "frac": alg / (ms_dates / 1e3) / 1e9 / hbm_peak,
-                                   "achieved": alg / (ms_dates / 1e3) / 1e9, "unit": "GB/s",
-                                   "traffic": (ncu_traffic("aggregate_warp_kernel<date>") or {}).get("dram_bytes_per_launch"),
-                                   "kernel": "aggregate_warp_kernel, date form: dates / categories / cents (9 B/row)"},
+                         "traffic": (ncu_traffic("aggregate_warp_kernel<date>") or {}).get("dram_bytes_per_launch")},
+            "with_group_keys": {"ms": ms_keyed, "kernel": "aggregate_warp_kernel, keyed form: cents + 16-bit group keys (6 B/row)",
+                                "group_keys_build_ms_once": keys_ms, "bytes_read_per_launch": read_keyed,
+                                "read_GBs": read_keyed / (ms_keyed / 1e3) / 1e9, "read_frac": read_keyed / (ms_keyed / 1e3) / 1e9 / hbm_peak,
+                                "frac_in_9B_per_row_terms": alg / (ms_keyed / 1e3) / 1e9 / hbm_peak,
+                                "traffic": (ncu_traffic("aggregate_warp_kernel<keyed>") or {}).get("dram_bytes_per_launch")},
             "clocks": clocks, "parity": bool(ok),
             "parity_how": "keyed and date-column kernels give the identical dense output, no row dropped, total of all cells == total "
                           "of the cents column, and every cell of three users (up to 200k rows) equal to pandas groupby().sum() on "
