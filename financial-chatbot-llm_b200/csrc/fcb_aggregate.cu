@@ -321,7 +321,7 @@ __global__ void __launch_bounds__(AGG_THREADS, AGG_CTAS) aggregate_kernel(const 
     if (dropped) atomicAdd(p.dropped, (unsigned long long)dropped);
 }
 
-// ---- group keys: the month of every row resolved ONCE, at load ------------------------------------
+// ---- the warp-table kernel (default for every table) and group keys: the month of every row resolved ONCE, at load -------
 // plot_tool groups by (category, calendar month of the date). The month of a row never changes, so fcb_load_shard derives a
 // 16-bit GROUP KEY per row and keeps it next to the columns (2 bytes per row, library-owned):
 //     bit 15      the row's amount is "rare": zero, or |v| >= 2^18 (see below)
@@ -330,7 +330,9 @@ __global__ void __launch_bounds__(AGG_THREADS, AGG_CTAS) aggregate_kernel(const 
 // 0x7fff stands for a category >= 64 or a month outside [key_base, key_base + 511). A query whose month window lies inside
 // the key range then reads cents + key (6 bytes per row instead of 9) and spends no arithmetic on calendars. Rows with key
 // 0x7fff are outside every such window, so they count as dropped exactly as the date path counts them. Windows that reach
-// outside the key range, and columns that come without keys (fcb_aggregate_columns), take the date kernels above.
+// outside the key range, and columns that come without keys (fcb_aggregate_columns), take the DATE form of the same kernel
+// (aggregate_warp_kernel<false>: month through a day -> month table, rare test from the value). The two kernels above are
+// round 1's; they stay behind FCB_AGG_KERNEL as independent implementations for the tests.
 #define AGK_MONTH_BITS 9
 #define AGK_MONTHS ((1 << AGK_MONTH_BITS) - 1)          // representable months; the all-ones month field means "none"
 #define AGK_NONE 0x7fffu
@@ -353,7 +355,7 @@ __global__ void __launch_bounds__(AGG_THREADS, AGG_CTAS) aggregate_kernel(const 
 // presence of the cell and the common row costs ONE shared reduction and no presence store — plus a hi word and a presence
 // byte for the rare rows. The row update is branch-free and unconditional (a predicated reduction compiles to a branch
 // around it): a row outside the window adds 1 to its lane's own drop counter instead of v to a cell. Rare rows — zero
-// (presence only) and |v| >= 2^18 (split v = hi * 65536 + lo16) — carry a flag in their key and are handled a second time,
+// (presence only) and |v| >= 2^18 (split v = hi * 65536 + lo16) — carry a flag in their key (date form: tested from the value) and are handled a second time,
 // quad by quad: the large ones add lo16 - v to the word the common path added v to (modular arithmetic: the word ends up
 // holding lo16) and their hi part to the hi word.
 __device__ __forceinline__ bool agk_is_rare(int32_t v) { return !((uint32_t)v + ((1u << 18) - 1u) < (1u << 19) - 1u && v != 0); }
@@ -367,12 +369,7 @@ __device__ __forceinline__ bool agk_is_rare(int32_t v) { return !((uint32_t)v + 
 __device__ __forceinline__ void agk_row(const AggParams &p, int32_t v, uint32_t mo, uint32_t cat, uint32_t tab, uint32_t drop_word) {
     const bool valid = mo < (uint32_t)p.n_months && cat < (uint32_t)p.n_categories;
     const uint32_t addr = tab + 4u * (cat * p.key_stride + mo) + ((uint32_t)v >> 31) * p.key_neg_off;
-#ifdef AGK_PREDICATED
-    agg_red_shared(addr, v, valid);
-    agg_red_shared(drop_word, 1, !valid);
-#else
     asm volatile("red.shared.add.s32 [%0], %1;" ::"r"(valid ? addr : drop_word), "r"(valid ? v : 1) : "memory");
-#endif
 }
 
 // second visit of a row that may be rare (see above): nothing to do for rows outside the window or with a common amount
@@ -471,7 +468,7 @@ __global__ void __launch_bounds__(AGG_THREADS, AGK_CTAS) aggregate_warp_kernel(c
     const int64_t n_blocks = (n_tiles + AGK_BLOCK_TILES - 1) / AGK_BLOCK_TILES;
     const int warps = blockDim.x >> 5;                                  // (fewer than 8 when the tables are large)
     const int64_t n_warps = (int64_t)gridDim.x * warps;
-    
+
     for (int64_t blk = (int64_t)blockIdx.x * warps + warp; blk < n_blocks; blk += n_warps) {
         const int64_t a0 = R0 + blk * AGK_BLOCK_TILES * AGK_TILE;
         const int64_t b0 = a0 + (int64_t)AGK_BLOCK_TILES * AGK_TILE < R1 ? a0 + (int64_t)AGK_BLOCK_TILES * AGK_TILE : R1;
