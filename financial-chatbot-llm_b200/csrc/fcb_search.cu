@@ -79,7 +79,6 @@ __device__ __noinline__ void scan_tail(const ScanParams &p, int b, unsigned char
                                        FcbCand (*m_s)[FCB_FUSED_CAND], double *f_score, uint64_t *f_id) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t *__restrict__ id_rank = p.id_rank;
-    const double *__restrict__ qd = p.queries + (size_t)b * p.dim;
     const T *__restrict__ vec = reinterpret_cast<const T *>(p.vectors);
     float my_s;
     uint32_t my_r;
@@ -108,9 +107,7 @@ __device__ __noinline__ void scan_tail(const ScanParams &p, int b, unsigned char
     // ---- canonical float64 re-score of the 32 survivors: the float64 query goes to shared memory,
     //      each warp scores its 4 candidates with interleaved chains (one memory latency, not four)
     double *qd_s = reinterpret_cast<double *>(smem_raw + (((size_t)p.dim * sizeof(float) + 15) & ~(size_t)15));
-    for (int i = tid; i < p.dim; i += FCB_SCAN_THREADS) qd_s[i] = qd[i];
-    __syncthreads();
-    const double qq = fcb_canon_qq_warp(qd_s, p.dim, lane);
+    const double qq = fcb_canon_qq_warp(qd_s, p.dim, lane);       // (staged by scan_one_query when the kernel started)
     {
         const T *rows4[4];
         uint32_t rr[4];
@@ -177,7 +174,10 @@ __device__ __forceinline__ void scan_one_query(const ScanParams &p, const int b,
     const uint32_t *__restrict__ id_rank = p.id_rank;
 
     if (blockIdx.x == 0) stamp(p, 0);
-    for (int i = tid; i < p.dim; i += FCB_SCAN_THREADS) q_s[i] = (float)qd[i];
+    // (the float64 copy is what the LAST CTA re-scores with; every CTA keeps one — the values are in registers here anyway —
+    // so that the tail does not start with a load of its own)
+    double *qd_s0 = reinterpret_cast<double *>(smem_raw + (((size_t)p.dim * sizeof(float) + 15) & ~(size_t)15));
+    for (int i = tid; i < p.dim; i += FCB_SCAN_THREADS) { const double x = qd[i]; q_s[i] = (float)x; qd_s0[i] = x; }
     __syncthreads();
     if (blockIdx.x == 0) stamp(p, 1);
 
