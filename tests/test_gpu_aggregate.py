@@ -420,3 +420,48 @@ def test_group_keys_for_caller_owned_columns(built):
         s_ref, _, dr_ref = aggregate_columns(0, dd, cc, vv, oo, 0, len(sizes), base - 2, 4, 16)
         torch.cuda.synchronize()
         assert torch.equal(s_out, s_ref) and int(dr.item()) == int(dr_ref.item())
+
+
+def test_windows_at_the_ends_of_the_int32_date_range(built, monkeypatch):
+    """Dates are int32 unix seconds (1901-12-13 .. 2038-01-19). A window may start before the first or end after the last
+    representable second; the date form of the warp-table kernel tests `(uint32)date - base < length` on the window CLIPPED to
+    the int32 range (a shifted day index when the window starts before 1901). Rows at both ends, windows hanging over both
+    ends: equal to round 1's kernel (64-bit date arithmetic) and to pandas."""
+    import torch
+    from financial_chatbot_llm_b200 import synth
+    from financial_chatbot_llm_b200.engine import aggregate_columns
+    from oracle import groupby
+    rng = np.random.default_rng(41)
+    n = 30_000
+    sizes = np.array([9_000, 1, 12_000, 8_999], dtype=np.int64)
+    off = np.zeros(len(sizes) + 1, dtype=np.int64)
+    np.cumsum(sizes, out=off[1:])
+    lo32, hi32 = -(2 ** 31), 2 ** 31 - 1
+    d = np.concatenate([lo32 + rng.integers(0, 70 * 86400, size=n // 2), hi32 - rng.integers(0, 70 * 86400, size=n - n // 2)]).astype(np.int64)
+    d[:3] = [lo32, lo32 + 1, lo32 + 86399]
+    d[-3:] = [hi32, hi32 - 1, hi32 - 86399]
+    rng.shuffle(d)
+    d = d.astype(np.int32)
+    v = rng.integers(-(2 ** 20), 2 ** 20, size=n, dtype=np.int64).astype(np.int32)
+    c = rng.integers(0, 5, size=n).astype(np.uint8)
+    dev = torch.device("cuda", 0)
+    dd, cc, vv, oo = (torch.from_numpy(a).to(dev) for a in (d, c, v, off))
+    users = synth.row_users(off, np.arange(n))
+    month = groupby.month_index(d)
+    m_first, m_last = int(month.min()), int(month.max())
+    for (w_lo, w_n) in ((m_first - 3, 8), (m_first, 2), (m_last - 2, 6), (m_first - 1, m_last - m_first + 3 if m_last - m_first + 3 <= 240 else 240)):
+        got = aggregate_columns(0, dd, cc, vv, oo, 0, len(sizes), w_lo, w_n, 5)
+        monkeypatch.setenv("FCB_AGG_KERNEL", "cta")
+        ref = aggregate_columns(0, dd, cc, vv, oo, 0, len(sizes), w_lo, w_n, 5)
+        monkeypatch.delenv("FCB_AGG_KERNEL")
+        torch.cuda.synchronize()
+        for x, y in zip(got, ref):
+            assert torch.equal(x, y), (w_lo, w_n)
+        keep = (month >= w_lo) & (month < w_lo + w_n)
+        assert int(got[2].item()) == int((~keep).sum())
+        if keep.any():
+            ser = groupby.groupby_user_category_month(users[keep], c[keep], d[keep], v[keep])
+            idx = ser.index.to_frame(index=False)
+            sums = got[0].cpu().numpy()
+            assert int(got[1].sum().item()) == len(ser)
+            assert sums[idx["user"].to_numpy(), idx["category"].to_numpy(), idx["month"].to_numpy() - w_lo].tolist() == ser.tolist()
