@@ -87,12 +87,21 @@ __device__ __noinline__ void scan_tail(const ScanParams &p, int b, unsigned char
     {
         float s1 = -INFINITY;
         uint32_t r1 = FCB_NO_ROW;
+        // two lists per step, and the NEXT step's two lists are requested before this step's are merged: a warp of the last
+        // CTA folds up to 37 lists (2 CTAs per SM), and one L2 round trip per step used to be most of the 16 us that took
         unsigned L = warp;
-        for (; L + FCB_SCAN_WARPS < gridDim.x; L += 2 * FCB_SCAN_WARPS) {       // two lists per step
-            const uint2 a = __ldcg(reinterpret_cast<const uint2 *>(lists + (size_t)L * FCB_FUSED_CAND + lane));
-            const uint2 c = __ldcg(reinterpret_cast<const uint2 *>(lists + (size_t)(L + FCB_SCAN_WARPS) * FCB_FUSED_CAND + lane));
+        auto list_of = [&](unsigned l) { return __ldcg(reinterpret_cast<const uint2 *>(lists + (size_t)l * FCB_FUSED_CAND + lane)); };
+        bool have = L + FCB_SCAN_WARPS < gridDim.x;
+        uint2 a = make_uint2(0u, 0u), c = make_uint2(0u, 0u);
+        if (have) { a = list_of(L); c = list_of(L + FCB_SCAN_WARPS); }
+        while (have) {
+            const unsigned Ln = L + 2 * FCB_SCAN_WARPS;
+            const bool have_n = Ln + FCB_SCAN_WARPS < gridDim.x;
+            uint2 an = make_uint2(0u, 0u), cn = make_uint2(0u, 0u);
+            if (have_n) { an = list_of(Ln); cn = list_of(Ln + FCB_SCAN_WARPS); }
             fcb_warp_merge_list2(my_s, my_r, FcbCand{__uint_as_float(a.x), a.y}, s1, r1, FcbCand{__uint_as_float(c.x), c.y},
                              id_rank, lane);
+            L = Ln; a = an; c = cn; have = have_n;
         }
         if (L < gridDim.x) {
             const uint2 a = __ldcg(reinterpret_cast<const uint2 *>(lists + (size_t)L * FCB_FUSED_CAND + lane));
